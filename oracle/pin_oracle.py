@@ -1,0 +1,485 @@
+"""Pins oracle/bmhrl_oracle.py against the UNMODIFIED reference and writes tests/golden/*.pt.
+
+Run in the build container only (needs /root/reference):   python -m oracle.pin_oracle [--write]
+
+For every section the real reference modules (imported through oracle/refboot.py) and the oracle
+restatement are run on the same seeded synthetic inputs / weights (bmhrl_b200/synth.py); the script
+asserts they agree to fp32 round-off (bit-exact for integer outputs) and, with --write, stores compact
+golden fixtures (outputs of the REFERENCE, not of the oracle) that the CPU and GPU test-suites re-check
+without the reference tree.
+"""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import refboot, bmhrl_oracle as O  # noqa: E402
+from bmhrl_b200 import synth  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+VOC = 10172
+SMOOTH = 0.7
+PAD = 1
+TOL = 2e-5
+
+
+def rel(a, b, floor=1e-30):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / (b.norm() + floor))
+
+
+def grel(a, b, name=""):
+    """Gradient comparison.  linear_K2d.bias gradients are mathematically zero (softmax is invariant to a
+    per-row shift of the scores), so both sides hold ~1e-10 round-off there: for those only the magnitude
+    is checked."""
+    if name.endswith("linear_K2d.bias"):
+        assert float(a.norm()) < 1e-7 and float(b.norm()) < 1e-7, name
+        return 0.0
+    return rel(a, b, floor=1e-12)
+
+
+def check(name, a, b, tol=TOL):
+    if not a.dtype.is_floating_point:
+        assert torch.equal(a.long(), b.long()), f"{name}: integer mismatch"
+        print(f"  {name:40s} exact")
+        return
+    r = rel(a, b)
+    print(f"  {name:40s} rel {r:.2e}")
+    assert r < tol, f"{name}: rel err {r}"
+
+
+def agent_shapes(ref, cfg):
+    import torch.nn as nn
+    M = ref.agent
+
+    class _C(nn.Module):
+        def __init__(s):
+            super().__init__()
+            d = cfg.d_model_caps
+            s.lstm = nn.LSTM(d, 2 * d, num_layers=4, batch_first=True)
+            s.gru = nn.GRU(2 * d, 2 * d, num_layers=2, batch_first=True)
+            s.lin = nn.Linear(2 * d, 1)
+            s.relu = M.AReLU()
+            s.relu2 = M.AReLU()
+    torch.save(_C().state_dict(), cfg.rl_critic_path)
+    ds = refboot.make_dataset(VOC, cfg.d_model_caps, torch.zeros(VOC, cfg.d_model_caps))
+    with refboot.sink():
+        m = M.BMHrlAgent(cfg, ds)
+    return {k: tuple(v.shape) for k, v in m.state_dict().items()}
+
+
+def grads_of(model):
+    return {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
+
+
+def oracle_params(sd):
+    return {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point else v.clone()) for k, v in sd.items()}
+
+
+def pin_agent(ref, cfg, sd, tag, B, Sv, Sa, L, seed, ragged, gold):
+    print(f"[agent {tag}] B={B} Sv={Sv} Sa={Sa} L={L} ragged={ragged}")
+    model, ds = refboot.build_reference_agent(ref, cfg, VOC, sd)
+    model.train()
+    model.teach_warmstart()
+    model.manager.exploration = False
+    b = synth.synthetic_batch(B=B, Sv=Sv, Sa=Sa, L=L, V=VOC, seed=seed, ragged=ragged)
+    cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+    fs = {"rgb": b["rgb"], "flow": b["flow"], "audio": b["audio"]}
+    masks = ref.masking.make_masks(fs, cin, "audio_video", PAD)
+    crit = ref.label_smoothing.LabelSmoothing(SMOOTH, PAD)
+    with refboot.sink():
+        out = model((b["rgb"] + b["flow"], b["audio"]), cin, masks)
+        n_tok = (cy != PAD).sum()
+        loss = torch.sum(crit(out[0], cy)) / n_tok
+        loss.backward()
+    rg = grads_of(model)
+
+    p = oracle_params(sd)
+    om = O.make_masks(b["rgb"], b["audio"], cin, PAD)
+    for k in masks:
+        assert torch.equal(masks[k], om[k]), k
+    oo = O.agent_forward(p, b["rgb"] + b["flow"], b["audio"], cin, om)
+    oloss = O.label_smoothing_kl(oo[0], cy, SMOOTH, PAD).sum() / n_tok
+    oloss.backward()
+    for a, c, n in zip(oo, out, ["pred", "worker_feat", "manager_feat", "goals", "segment_labels"]):
+        check(n, a.detach(), c.detach())
+    check("loss", oloss.detach(), loss.detach())
+    worst, wname = 0.0, ""
+    for n, g in rg.items():
+        og = p[n].grad
+        assert og is not None, n
+        r = grel(og, g, n)
+        if r > worst:
+            worst, wname = r, n
+    print(f"  grads: {len(rg)} tensors, worst rel {worst:.2e} ({wname}, |g|={rg[wname].norm().item():.2e})")
+    assert worst < 5e-4  # both sides are fp32 with different summation orders
+    no_grad_ref = sorted(n for n, q in model.named_parameters() if q.requires_grad and q.grad is None)
+    gold[f"agent_{tag}"] = {
+        "cfg": dict(B=B, Sv=Sv, Sa=Sa, L=L, seed=seed, ragged=ragged, wseed=1234),
+        "pred_slice": out[0].detach()[:, :, ::101].clone(), "worker_feat": out[1].detach().clone(),
+        "manager_feat": out[2].detach().clone(), "goals": out[3].detach().clone(),
+        "segment_labels": out[4].clone(), "loss": loss.detach().clone(),
+        "grad_norm": {n: g.norm().item() for n, g in rg.items()},
+        "grad_slice": {n: g.flatten()[:: max(1, g.numel() // 64)][:64].clone() for n, g in rg.items()},
+        "never_grad": no_grad_ref,
+    }
+
+
+def pin_losses(ref, gold):
+    print("[losses]")
+    g = torch.Generator().manual_seed(5)
+    B, L, V = 3, 7, 50
+    logits = torch.randn(B, L, V, generator=g)
+    trg = torch.randint(2, V, (B, L), generator=g)
+    trg[0, 5:] = PAD
+    trg[2, 3:] = PAD
+    samp = torch.randint(0, V, (B, L), generator=g)
+    samp[1, 2] = trg[1, 2]          # sampled == ground truth
+    samp[1, 3] = PAD                # sampled the pad token
+    off = torch.rand(B, L, generator=g)
+    off[0, 0] = 0.0
+    off[0, 1] = 1.0
+    res = {}
+    for name in ("ls", "bkl"):
+        lp_r = torch.log_softmax(logits.clone().requires_grad_(True), -1)
+        lp_r.retain_grad()
+        lp_o = torch.log_softmax(logits.clone().requires_grad_(True), -1)
+        lp_o.retain_grad()
+        off_r = off.clone().requires_grad_(True)
+        off_o = off.clone().requires_grad_(True)
+        with refboot.sink():
+            if name == "ls":
+                r = ref.label_smoothing.LabelSmoothing(SMOOTH, PAD)(lp_r, trg)
+                o = O.label_smoothing_kl(lp_o, trg, SMOOTH, PAD)
+            else:
+                r = ref.biased_kl.BiasedKL(SMOOTH, PAD)(lp_r, trg, samp, off_r)
+                o = O.biased_kl_divergence(lp_o, trg, samp, off_o, SMOOTH, PAD)
+        w = torch.randn(r.shape, generator=torch.Generator().manual_seed(9))
+        (r * w).sum().backward()
+        (o * w).sum().backward()
+        check(f"{name} value", o.detach(), r.detach())
+        check(f"{name} dpred", lp_o.grad, lp_r.grad)
+        res[name] = {"out": r.detach().clone(), "dpred": lp_r.grad.clone(), "w": w}
+        if name == "bkl":
+            check("bkl doffset", off_o.grad, off_r.grad)
+            res[name]["doffset"] = off_r.grad.clone()
+    # Reinforce
+    probs_r = torch.softmax(logits, -1).clone().requires_grad_(True)
+    probs_o = torch.softmax(logits, -1).clone().requires_grad_(True)
+    value = torch.rand(B, L, generator=g)
+    cv_r = torch.rand(B, L, generator=g).requires_grad_(True)
+    cv_o = cv_r.detach().clone().requires_grad_(True)
+    r = ref.biased_kl.Reinforce()(probs_r, samp, value, cv_r)
+    o = O.reinforce_loss(probs_o, samp, value, cv_o)
+    r.backward()
+    o.backward()
+    check("reinforce value", o.detach(), r.detach())
+    check("reinforce dprobs", probs_o.grad, probs_r.grad)
+    check("reinforce dcritic", cv_o.grad, cv_r.grad)
+    res["reinforce"] = {"out": r.detach().clone(), "dprobs": probs_r.grad.clone(), "dcritic": cv_r.grad.clone(),
+                        "value": value, "critic": cv_r.detach().clone()}
+    res["inputs"] = {"logits": logits, "trg": trg, "samp": samp, "off": off}
+    gold["losses"] = res
+
+
+def pin_expand_goals(ref, gold):
+    print("[expand_goals]")
+    g = torch.Generator().manual_seed(11)
+    mgr = ref.agent.Manager("cpu", 8, 4, 0.0)
+    cases = []
+    pats = [
+        [[0, 1, 0, 1, 0], [0, 0, 0, 0, 0], [1, 0, 0, 0, 0], [0, 0, 0, 0, 0]],
+        [[0, 0, 0, 0, 0], [0, 0, 1, 0, 0], [0, 0, 0, 0, 1], [0, 1, 0, 0, 0]],
+        [[0, 0, 0, 0, 0], [0, 0, 0, 0, 0], [0, 0, 0, 0, 0], [0, 0, 0, 0, 0]],
+        [[1, 1, 1, 1, 1], [0, 0, 0, 0, 1], [1, 0, 0, 0, 0], [0, 0, 0, 1, 0]],
+        [[0, 0, 1, 0, 0], [0, 0, 0, 0, 0], [0, 0, 0, 0, 0], [0, 0, 0, 0, 0]],
+    ]
+    for _ in range(6):
+        pats.append((torch.rand(4, 5, generator=g) < 0.3).int().tolist())
+    for pat in pats:
+        seg = torch.tensor(pat, dtype=torch.int32)
+        x = torch.randn(seg.shape[0], seg.shape[1], 4, generator=g)
+        xr = x.clone().requires_grad_(True)
+        xo = x.clone().requires_grad_(True)
+        r = mgr.expand_goals(xr * 1.0, seg)
+        o = O.expand_goals(xo * 1.0, seg)
+        w = torch.randn(r.shape, generator=g)
+        (r * w).sum().backward()
+        (o * w).sum().backward()
+        assert torch.equal(r.detach(), o.detach()), pat
+        assert torch.allclose(xr.grad, xo.grad), pat
+        cases.append({"seg": seg, "x": x, "out": r.detach().clone(), "w": w, "dx": xr.grad.clone()})
+    print(f"  {len(cases)} patterns exact (values and grads)")
+    gold["expand_goals"] = cases
+
+
+def pin_rl(ref, cfg, sd, gold):
+    shapes_v = None
+    for train_worker in (True, False):
+        for stabilize in (False, True):
+            tag = f"{'worker' if train_worker else 'manager'}_{'stab' if stabilize else 'raw'}"
+            print(f"[rl {tag}]")
+            B, Sv, Sa, L, seed = 4, 10, 16, 9, 21
+            model, ds = refboot.build_reference_agent(ref, cfg, VOC, sd)
+            model.train()
+            with refboot.sink():
+                vf = (ref.agent.BMWorkerValueFunction if train_worker else ref.agent.BMManagerValueFunction)(cfg)
+            if shapes_v is None:
+                shapes_v = {k: tuple(v.shape) for k, v in vf.state_dict().items()}
+            vsd = synth.fill_state_dict(shapes_v, seed=77 if train_worker else 78)
+            vf.load_state_dict(vsd)
+            vf.train()
+            if train_worker:
+                model.teach_worker()
+            else:
+                model.teach_manager()
+                model.manager.exploration = False  # F7: CPU-safe; noise is covered by a separate case
+            b = synth.synthetic_batch(B=B, Sv=Sv, Sa=Sa, L=L, V=VOC, seed=seed, ragged=True)
+            cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+            fs = {"rgb": b["rgb"], "flow": b["flow"], "audio": b["audio"]}
+            masks = ref.masking.make_masks(fs, cin, "audio_video", PAD)
+            crit = ref.biased_kl.BiasedKL(SMOOTH, PAD)
+            score_in = b["score"] * 3.0
+            ref.loops.get_score = lambda tw, scorer, sampled, cap, mask, segs: (score_in.clone(), None)
+            with refboot.sink():
+                pred, wf, mf, gf, seg = model((b["rgb"] + b["flow"], b["audio"]), cin, masks)
+                loss_mask = cy != PAD
+                n_tok = loss_mask.sum()
+                if train_worker:
+                    ev = vf((wf.detach(), gf.detach())).squeeze()
+                else:
+                    ev = vf(mf.detach()).squeeze()
+                torch.manual_seed(99)
+                losses, scores, samples, _ = ref.loops.biased_kl(
+                    train_worker=train_worker, prediction=pred, scorer=None, expected_scores=ev.detach(),
+                    trg=cy, trg_caption=None, mask=loss_mask, segments=seg, device="cpu", biased_kldiv=crit,
+                    stabilize=stabilize)
+                cap_loss = torch.sum(losses) / (n_tok * (4.0 / 20.0))
+                cap_loss.backward()
+                lm = loss_mask if train_worker else seg.detach().float()
+                vloss = (torch.nn.MSELoss(reduction="none")(ev, scores[0].float()) * lm.float()).mean()
+                vloss.backward()
+            rg = grads_of(model)
+            vg = grads_of(vf)
+
+            # ---- oracle
+            p = oracle_params(sd)
+            pv = oracle_params(vsd)
+            om = O.make_masks(b["rgb"], b["audio"], cin, PAD)
+            opred, owf, omf, ogf, oseg = O.agent_forward(p, b["rgb"] + b["flow"], b["audio"], cin, om)
+            oev = O.value_function(pv, (owf if train_worker else omf).detach()).squeeze(-1)
+            torch.manual_seed(99)
+            q = torch.empty(B * L, VOC).exponential_(1).view(B, L, VOC) if train_worker else None
+            div, oscore, otok, oexp = O.biased_kl_rl(opred, cy, score_in.clone(), oev.detach(), loss_mask, oseg,
+                                                    train_worker, stabilize, SMOOTH, PAD, q)
+            ocap = div.sum() / (n_tok * (4.0 / 20.0))
+            ocap.backward()
+            # the reference's host loop wrote the segment sums INTO the value-function output (aliasing)
+            oev_used = oev + (oexp - oev).detach()
+            olm = loss_mask if train_worker else oseg.float()
+            ovl = (((oev_used - oscore.float()) ** 2) * olm.float()).mean()
+            ovl.backward()
+            check("tokens", otok, samples[0])
+            check("score", oscore.detach(), scores[0].detach())
+            check("divergence", div.detach(), losses.detach())
+            check("cap_loss", ocap.detach(), cap_loss.detach())
+            check("value_loss", ovl.detach(), vloss.detach())
+            worst = max(grel(p[n].grad, g, n) for n, g in rg.items())
+            print(f"  agent grads: {len(rg)} tensors, worst rel {worst:.2e}")
+            assert worst < 1e-4
+            assert set(n for n in p if p[n].dtype.is_floating_point and p[n].grad is not None) >= set(rg)
+            worstv = max(grel(pv[n].grad, g) for n, g in vg.items())
+            print(f"  value-fn grads: {len(vg)} tensors, worst rel {worstv:.2e}")
+            assert worstv < 1e-4
+            gold[f"rl_{tag}"] = {
+                "cfg": dict(B=B, Sv=Sv, Sa=Sa, L=L, seed=seed, wseed=1234, vseed=77 if train_worker else 78,
+                            noise_seed=99, score_scale=3.0),
+                "tokens": samples[0].clone(), "score": scores[0].detach().clone(),
+                "div_rowsum": losses.detach().sum(-1).clone(), "cap_loss": cap_loss.detach().clone(),
+                "value_loss": vloss.detach().clone(), "segment_labels": seg.clone(),
+                "grad_norm": {n: g.norm().item() for n, g in rg.items()},
+                "vgrad_norm": {n: g.norm().item() for n, g in vg.items()},
+            }
+    gold["value_fn_shapes"] = shapes_v
+
+
+def pin_exploration(ref, gold):
+    """Manager exploration noise (model/bm_hrl_agent.py:444-452) with an explicit normal draw."""
+    print("[manager exploration]")
+    g = torch.Generator().manual_seed(3)
+    mgr = ref.agent.Manager("cpu", 12, 6, 0.0)
+    mgr.exploration = True
+    x = torch.randn(3, 5, 12, generator=g)
+    seg = torch.tensor([[0, 1, 0, 0, 1], [0, 0, 0, 0, 0], [1, 0, 0, 1, 0]], dtype=torch.int32)
+    # the reference calls mean.get_device() (-1 on CPU, F7); emulate the same draw explicitly
+    pre = torch.nn.functional.linear(x, mgr.linear.weight, mgr.linear.bias)
+    mean, std = O.exploration_noise_params(pre.detach())
+    torch.manual_seed(4)
+    noise = torch.empty(6).normal_(mean=float(mean), std=float(std)) - 0.5 * mean
+    sd = {"manager.linear.weight": mgr.linear.weight.detach(), "manager.linear.bias": mgr.linear.bias.detach()}
+    o = O.manager_head(sd, x, seg, noise)
+    r = mgr.expand_goals((pre + noise).clone(), seg)
+    check("goals with noise", o, r.detach())
+    gold["exploration"] = {"x": x, "seg": seg, "w": mgr.linear.weight.detach().clone(),
+                           "b": mgr.linear.bias.detach().clone(), "noise": noise, "out": r.detach().clone(),
+                           "mean": mean, "std": std}
+
+
+def pin_greedy(ref, cfg, sd, gold):
+    print("[greedy decode, config 1: sample/women_long_jump]")
+    sp = os.path.join(refboot.REF_ROOT, "sample")
+    rgb = torch.from_numpy(np.load(os.path.join(sp, "women_long_jump_rgb.npy")))[None]
+    flow = torch.from_numpy(np.load(os.path.join(sp, "women_long_jump_flow.npy")))[None]
+    aud = torch.from_numpy(np.load(os.path.join(sp, "women_long_jump_vggish.npy")))[None]
+    model, ds = refboot.build_reference_agent(ref, cfg, VOC, sd)
+    model.eval()
+    model.set_inference_mode(True)
+    A = ref.agent
+
+    def pwf(self, C, V_, A_, mask):  # F6: squeeze(-1) keeps (B,L) for B=1 / L=1; otherwise :637-651 verbatim flow
+        segments = torch.sigmoid(self.critic(C))
+        labels = (segments > self.critic_score_threshhold).squeeze(-1).int()
+        C = self.pos_enc_C(C)
+        Va, Av = self.bm_enc((V_, A_), mask)
+        wf = self.bm_worker_fus((C, (Av, Va)), mask)
+        mf = self.bm_manager_fus((C, (Av, Va)), mask)
+        goals = self.manager(mf, labels)
+        return self.worker(wf, goals, mask["C_mask"]), wf, mf, goals, labels
+    orig = A.BMHrlAgent.predict_with_features
+    A.BMHrlAgent.predict_with_features = pwf
+    try:
+        max_len = 12
+        trg = torch.full((1, 1), 2, dtype=torch.long)
+        done = torch.zeros(1, 1, dtype=torch.bool)
+        last = []
+        with torch.no_grad(), refboot.sink():
+            while trg.shape[-1] <= max_len and not bool(done.all()):
+                masks = ref.masking.make_masks({"rgb": rgb, "flow": flow, "audio": aud}, trg, "audio_video", PAD)
+                preds = model.inference((rgb + flow, aud), trg, masks)
+                last.append(preds[:, -1])
+                nxt = preds[:, -1].max(dim=-1)[1][:, None]
+                trg = torch.cat([trg, nxt], dim=-1)
+                done = done | (nxt == 3)
+    finally:
+        A.BMHrlAgent.predict_with_features = orig
+    otrg, olast = O.greedy_decode(sd, rgb, flow, aud, max_len, 2, 3, PAD)
+    check("tokens", otrg, trg)
+    check("last-position log-probs", olast, torch.stack(last, 1))
+    gold["greedy"] = {"rgb": rgb.half(), "flow": flow.half(), "audio": aud.half(), "max_len": max_len,
+                      "tokens": trg.clone(), "last_slice": torch.stack(last, 1)[:, :, ::101].clone()}
+    # fp16 storage of the sample features keeps the fixture small; decode is re-run from the fp16 values
+    rgb2, flow2, aud2 = rgb.half().float(), flow.half().float(), aud.half().float()
+    t2, l2 = O.greedy_decode(sd, rgb2, flow2, aud2, max_len, 2, 3, PAD)
+    gold["greedy"]["tokens_fp16in"] = t2
+    gold["greedy"]["last_slice_fp16in"] = l2[:, :, ::101].clone()
+    gold["greedy"]["audio_mask_true"] = int((aud2[0, :, 0] != 0).sum())
+
+
+def pin_detr(ref, gold):
+    print("[DETR-variant layers]")
+    g = torch.Generator().manual_seed(13)
+    d_model, H, dC, dG, S, L, B = 32, 4, 20, 8, 6, 5, 2
+    with refboot.sink():
+        enc = ref.encoder.TransformerEncoderLayer(d_model, H, dim_feedforward=48, dropout=0.0, embed_size=dC)
+        dec = ref.decoder.TransformerDecoderLayer(d_model, H, dC, dG, dim_feedforward=40, dropout=0.0)
+    pe = lambda x: O.add_positional(x)  # noqa: E731
+    src = torch.randn(B, S, d_model, generator=g)
+    smask = torch.ones(B, 1, S, dtype=torch.bool)
+    smask[1, 0, 4:] = False
+    with refboot.sink():
+        r = enc(src, smask, pe)
+    esd = {k: v.detach() for k, v in enc.state_dict().items()}
+    o = O.detr_encoder_layer(esd, "", src, smask, H)
+    check("encoder layer", o, r.detach())
+    tgt = torch.randn(B, L, dC, generator=g)
+    qmask = torch.ones(B, 1, L, dtype=torch.bool)
+    qmask[0, 0, 3:] = False
+    goal = torch.randn(B, L, dG, generator=g)
+    gmask = torch.ones(B, 1, L, dtype=torch.bool)
+    det = torch.randn(B, 7, 256, generator=g)
+    # causal=True in the reference needs sm_input.get_device() >= 0 (F7) -> patch torch.ones' device arg
+    import model.multihead_attention as mm
+    orig_ones = mm.torch.ones
+
+    def ones_cpu(*a, **k):
+        k.pop("device", None)
+        return orig_ones(*a, **k)
+    mm.torch.ones = ones_cpu
+    try:
+        with refboot.sink():
+            r = dec(tgt, r.detach(), smask, pe, pe, qmask, goal, gmask, pe, add_pos=False, detected_objects=det)
+    finally:
+        mm.torch.ones = orig_ones
+    dsd = {k: v.detach() for k, v in dec.state_dict().items()}
+    o2 = O.detr_decoder_layer(dsd, "", tgt, o, smask, qmask, H, goal=goal, goal_mask=gmask, detected=det,
+                              obj_mask=None)
+    check("decoder layer", o2, r.detach())
+    gold["detr"] = {"enc_sd": esd, "dec_sd": dsd, "src": src, "smask": smask, "tgt": tgt, "qmask": qmask,
+                    "goal": goal, "gmask": gmask, "det": det, "enc_out": o.clone(), "dec_out": r.detach().clone(),
+                    "dims": dict(d_model=d_model, H=H, dC=dC, dG=dG, ff_e=48, ff_d=40)}
+
+
+def pin_posenc(ref, gold):
+    print("[positional encoder table]")
+    for D in (300, 128):
+        with refboot.sink():
+            pe = ref.blocks.PositionalEncoder(D, 0.0, seq_len=64)
+        check(f"table D={D}", O.positional_table(64, D), pe.pos_enc_mat[0], tol=1e-15)
+    gold["posenc"] = {"t300": O.positional_table(40, 300)[::7, ::13].clone()}
+
+
+def pin_adam(gold):
+    print("[adam]")
+    g = torch.Generator().manual_seed(17)
+    p0 = torch.randn(37, generator=g)
+    ps = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([ps], lr=1e-4)
+    params, state = {"p": p0.clone()}, {}
+    grads = []
+    for _ in range(3):
+        gr = torch.randn(37, generator=g)
+        grads.append(gr)
+        ps.grad = gr.clone()
+        opt.step()
+        params, state = O.adam_step(params, {"p": gr}, state)
+    check("adam 3 steps", params["p"], ps.detach(), tol=1e-6)
+    gold["adam"] = {"p0": p0, "grads": torch.stack(grads), "p3": ps.detach().clone()}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--write", action="store_true")
+    ap.add_argument("--big", action="store_true", help="also pin the C16 shapes (slow)")
+    args = ap.parse_args()
+    torch.manual_seed(0)
+    torch.set_num_threads(8)
+    ref = refboot.import_reference()
+    cfg = refboot.make_cfg()
+    shapes = agent_shapes(ref, cfg)
+    sd = synth.fill_state_dict(shapes, seed=1234)
+    gold = {"agent_shapes": shapes}
+    pin_posenc(ref, gold)
+    pin_losses(ref, gold)
+    pin_expand_goals(ref, gold)
+    pin_exploration(ref, gold)
+    pin_adam(gold)
+    pin_detr(ref, gold)
+    pin_agent(ref, cfg, sd, "small", 4, 12, 20, 8, 7, True, gold)
+    pin_agent(ref, cfg, sd, "c16", 16, 30, 80, 20, 1234, False, gold)
+    pin_rl(ref, cfg, sd, gold)
+    pin_greedy(ref, cfg, sd, gold)
+    if args.write:
+        os.makedirs(GOLD, exist_ok=True)
+        torch.save(gold, os.path.join(GOLD, "reference_golden.pt"))
+        print("wrote", os.path.join(GOLD, "reference_golden.pt"),
+              os.path.getsize(os.path.join(GOLD, "reference_golden.pt")) // 1024, "KiB")
+    print("ORACLE PINNED: all sections agree with the reference")
+
+
+if __name__ == "__main__":
+    main()
