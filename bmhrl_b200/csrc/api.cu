@@ -1,0 +1,33 @@
+// Library-level state of libbmhrl_b200: last-error string, kernel-launch counter, version / device queries.
+#include "common.cuh"
+#include "../../include/bmhrl_b200.h"
+#include <atomic>
+#include <string.h>
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+extern "C" void bmhrl_set_error(const char* msg) {
+    strncpy(g_err, msg ? msg : "", sizeof(g_err) - 1);
+    g_err[sizeof(g_err) - 1] = 0;
+}
+extern "C" void bmhrl_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+extern "C" const char* bmhrl_last_error(void) { return g_err; }
+extern "C" long long bmhrl_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+extern "C" void bmhrl_reset_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
+extern "C" int bmhrl_abi_version(void) { return BMHRL_ABI_VERSION; }
+
+// Returns 0 when the current device is a Blackwell sm_100 part this library was built for.
+extern "C" int bmhrl_check_device(void) {
+    int dev = 0;
+    cudaDeviceProp prop;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+        bmhrl_set_error("no CUDA device");
+        return BMHRL_ERR_CUDA;
+    }
+    if (prop.major != 10) {
+        bmhrl_set_error("libbmhrl_b200 is built for sm_100a (B200) only");
+        return BMHRL_ERR_UNSUPPORTED;
+    }
+    return BMHRL_OK;
+}

@@ -1,0 +1,122 @@
+// Shared device helpers for libbmhrl_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#define BMHRL_OK 0
+#define BMHRL_ERR_ARG (-1)
+#define BMHRL_ERR_CUDA (-2)
+#define BMHRL_ERR_UNSUPPORTED (-3)
+
+extern "C" void bmhrl_set_error(const char* msg);
+extern "C" void bmhrl_count_launch(int n);
+
+#define BMHRL_CHECK_ARG(cond, msg)                 \
+    do {                                           \
+        if (!(cond)) {                             \
+            bmhrl_set_error(msg);                  \
+            return BMHRL_ERR_ARG;                  \
+        }                                          \
+    } while (0)
+
+// Call after every kernel launch: surfaces launch-configuration errors without synchronising.
+#define BMHRL_POST_LAUNCH(name)                                    \
+    do {                                                           \
+        cudaError_t _e = cudaGetLastError();                       \
+        if (_e != cudaSuccess) {                                   \
+            bmhrl_set_error(cudaGetErrorString(_e));               \
+            return BMHRL_ERR_CUDA;                                 \
+        }                                                          \
+        bmhrl_count_launch(1);                                     \
+    } while (0)
+
+namespace bmhrl {
+
+constexpr float kNegFill = -1e9f;  // reference replaces masked scores by -1e9 (model/multihead_attention.py:21-22)
+
+// ---------------------------------------------------------------- Philox4x32-10 (counter based RNG)
+struct Philox4 {
+    uint32_t x, y, z, w;
+};
+
+__device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                                 uint32_t k1) {
+    constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0; k1 += W1;
+    }
+    return Philox4{c0, c1, c2, c3};
+}
+
+// rng_state: device pointer to {seed, step}.  salt identifies the call site; idx the element.
+// Four consecutive elements share one Philox block.
+__device__ __forceinline__ uint32_t philox_u32(const unsigned long long* rng_state, uint32_t salt, uint64_t idx) {
+    unsigned long long seed = rng_state[0], step = rng_state[1];
+    uint64_t blk = idx >> 2;
+    Philox4 r = philox4x32_10((uint32_t)blk, (uint32_t)(blk >> 32), salt, (uint32_t)step, (uint32_t)seed,
+                              (uint32_t)(seed >> 32) ^ (uint32_t)(step >> 32));
+    uint32_t lane = (uint32_t)idx & 3u;
+    return lane == 0 ? r.x : lane == 1 ? r.y : lane == 2 ? r.z : r.w;
+}
+
+__device__ __forceinline__ Philox4 philox_block(const unsigned long long* rng_state, uint32_t salt, uint64_t blk) {
+    unsigned long long seed = rng_state[0], step = rng_state[1];
+    return philox4x32_10((uint32_t)blk, (uint32_t)(blk >> 32), salt, (uint32_t)step, (uint32_t)seed,
+                         (uint32_t)(seed >> 32) ^ (uint32_t)(step >> 32));
+}
+
+// uniform in [0,1): 24 random bits
+__device__ __forceinline__ float u32_to_unit(uint32_t u) { return (float)(u >> 8) * (1.0f / 16777216.0f); }
+
+// dropout keep decision shared by forward and backward of every op: keep iff u >= p
+__device__ __forceinline__ bool dropout_keep(const unsigned long long* rng_state, uint32_t salt, uint64_t idx,
+                                             float p) {
+    return u32_to_unit(philox_u32(rng_state, salt, idx)) >= p;
+}
+
+// ---------------------------------------------------------------- reductions
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024 (multiple of 32).  `red` is >= 32 floats of shared memory.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    float r = (lane < nw) ? red[lane] : 0.f;
+    r = warp_sum(r);
+    return r;
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    float r = (lane < nw) ? red[lane] : -INFINITY;
+    r = warp_max(r);
+    return r;
+}
+
+__device__ __forceinline__ float4 ld_f4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st_f4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+
+__host__ __device__ __forceinline__ bool aligned16(const void* p) { return (((uintptr_t)p) & 15u) == 0; }
+
+}  // namespace bmhrl

@@ -1,0 +1,39 @@
+// Parameter block of the fp32 SIMT GEMM (gemm_simt.cu); shared with the fp32 attention path.
+#pragma once
+#include "common.cuh"
+
+namespace bmhrl {
+
+struct GemmParams {
+    const float* A;
+    const float* B;
+    float* C;
+    int M, N, K;
+    long long sAm, sAk, sBk, sBn, ldc;
+    int Hdiv;
+    long long bAo, bAi, bBo, bBi, bCo, bCi;
+    float alpha, beta;
+    const float* bias;
+    int act;
+    const float* resid;
+    long long ldr, bRo, bRi;
+    float drop_p;
+    const unsigned long long* rng;
+    unsigned int salt;
+    int vecA, vecB, vecC;  // 128-bit access allowed (alignment checked on host)
+};
+
+static inline bool mult4(long long v) { return (v & 3) == 0; }
+
+// Fills the 128-bit-access flags from pointer alignment and strides.
+static inline void gemm_set_vec_flags(GemmParams& p) {
+    p.vecA = aligned16(p.A) && (p.sAm == 1 || p.sAk == 1) && mult4(p.sAm == 1 ? p.sAk : p.sAm) && mult4(p.bAo) &&
+             mult4(p.bAi);
+    p.vecB = aligned16(p.B) && (p.sBk == 1 || p.sBn == 1) && mult4(p.sBk == 1 ? p.sBn : p.sBk) && mult4(p.bBo) &&
+             mult4(p.bBi);
+    p.vecC = aligned16(p.C) && mult4(p.ldc) && mult4(p.bCo) && mult4(p.bCi);
+}
+
+int launch_gemm_simt(const GemmParams& p, int batch, cudaStream_t st);
+
+}  // namespace bmhrl

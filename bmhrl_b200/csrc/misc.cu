@@ -1,0 +1,424 @@
+// K6 (embedding * sqrt(d) + positional encoding), K7 (goal expansion / segment scans), bias+activation+dropout
+// gradient prep for the linear layers, fused multi-tensor Adam and the device-side step/RNG tick.
+// Reference: VocabularyEmbedder model/blocks.py:44-48, PositionalEncoder model/blocks.py:105-112,
+// Manager.expand_goals model/bm_hrl_agent.py:415-429, biased_kl() manager loop
+// epoch_loops/captioning_bmrl_loops.py:299-317, torch.optim.Adam scripts/train_rl_captioning_module.py:81-83.
+#include "common.cuh"
+#include "../../include/bmhrl_b200.h"
+
+namespace bmhrl {
+
+// ------------------------------------------------------------------ K6
+// emb[r, :] = W[tok[r], :] * scale ; pos[r, :] = dropout(emb[r, :] + pe[r % L, :])
+__global__ void embed_posenc_kernel(const long long* __restrict__ tok, const float* __restrict__ W,
+                                    const float* __restrict__ pe, float* __restrict__ emb, float* __restrict__ pos,
+                                    long long rows, int L, int D, float scale, float drop_p,
+                                    const unsigned long long* __restrict__ rng, unsigned int salt) {
+    const long long n = rows * D;
+    const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D;
+        int d = (int)(i % D);
+        float e = W[tok[r] * D + d] * scale;
+        if (emb) emb[i] = e;
+        if (pos) {
+            float v = e + pe[(long long)(r % L) * D + d];
+            if (drop_p > 0.f) v = dropout_keep(rng, salt, (unsigned long long)i, drop_p) ? v * ks : 0.f;
+            pos[i] = v;
+        }
+    }
+}
+
+// out = dropout(x (+ x2) + pe[s])     x: (B, S, D) contiguous
+__global__ void add_posenc_kernel(const float* __restrict__ x, const float* __restrict__ x2,
+                                  const float* __restrict__ pe, float* __restrict__ out, long long rows, int S, int D,
+                                  float drop_p, const unsigned long long* __restrict__ rng, unsigned int salt) {
+    const long long n4 = rows * D / 4;  // D % 4 == 0 is checked on the host
+    const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+    const int D4 = D / 4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D4;
+        int c = (int)(i % D4);
+        float4 v = ld_f4(x + 4 * i);
+        if (x2) { float4 w = ld_f4(x2 + 4 * i); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+        float4 p = ld_f4(pe + ((long long)(r % S) * D4 + c) * 4);
+        v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+        if (drop_p > 0.f) {
+            Philox4 rr = philox_block(rng, salt, (unsigned long long)i);
+            v.x = u32_to_unit(rr.x) >= drop_p ? v.x * ks : 0.f;
+            v.y = u32_to_unit(rr.y) >= drop_p ? v.y * ks : 0.f;
+            v.z = u32_to_unit(rr.z) >= drop_p ? v.z * ks : 0.f;
+            v.w = u32_to_unit(rr.w) >= drop_p ? v.w * ks : 0.f;
+        }
+        st_f4(out + 4 * i, v);
+    }
+}
+
+// dx = keep ? dy / (1-p) : 0 with the flat element index as RNG counter
+__global__ void dropout_apply_kernel(const float* __restrict__ dy, float* __restrict__ dx, long long n, float drop_p,
+                                     const unsigned long long* __restrict__ rng, unsigned int salt) {
+    const float ks = 1.f / (1.f - drop_p);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        dx[i] = dropout_keep(rng, salt, (unsigned long long)i, drop_p) ? dy[i] * ks : 0.f;
+}
+
+// out = x + dropout(r): generic ResidualConnection tail (model/blocks.py:142-144) for caller-supplied sublayers
+__global__ void dropout_add_kernel(const float* __restrict__ x, const float* __restrict__ r, float* __restrict__ out,
+                                   long long n, float drop_p, const unsigned long long* __restrict__ rng,
+                                   unsigned int salt) {
+    const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float v = r[i];
+        if (drop_p > 0.f) v = dropout_keep(rng, salt, (unsigned long long)i, drop_p) ? v * ks : 0.f;
+        out[i] = x[i] + v;
+    }
+}
+
+// dW[tok[r], :] += g[r, :] * scale   (only when the word embedding is unfrozen)
+__global__ void embed_bwd_kernel(const long long* __restrict__ tok, const float* __restrict__ g, float* __restrict__ dW,
+                                 long long rows, int D, float scale) {
+    const long long n = rows * D;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        atomicAdd(&dW[tok[i / D] * D + (i % D)], g[i] * scale);
+}
+
+// ------------------------------------------------------------------ K7 goal expansion
+// One CTA, one thread per batch row.  map[b,l] = source position whose goal position (b,l) takes, -1 = zero.
+__global__ void goal_map_kernel(const int* __restrict__ seg, int* __restrict__ map, int B, int L) {
+    extern __shared__ int row_has[];
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        int any = 0;
+        for (int l = 0; l < L; ++l) any |= (seg[b * L + l] != 0);
+        row_has[b] = any;
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        int later = 0;
+        for (int bb = b + 1; bb < B; ++bb) later |= row_has[bb];
+        int nxt = -1;
+        for (int l = L - 1; l >= 0; --l) {
+            if (seg[b * L + l] != 0) nxt = l;
+            int m;
+            if (nxt >= 0) m = nxt;                                   // goal of the next boundary
+            else if (row_has[b]) m = later ? -1 : l;                 // tail after the row's last boundary
+            else m = (b == 0 && later) ? -1 : l;                     // boundary-free row (row-0 quirk)
+            map[b * L + l] = m;
+        }
+    }
+}
+
+__global__ void goal_gather_kernel(const float* __restrict__ x, const int* __restrict__ map, float* __restrict__ out,
+                                   long long rows, int L, int D) {
+    const long long n = rows * D;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D;
+        int d = (int)(i % D);
+        int m = map[r];
+        out[i] = m < 0 ? 0.f : x[((r / L) * L + m) * D + d];
+    }
+}
+
+// dx[b, l', :] = sum_{l <= l' : map[b,l] == l'} dy[b, l, :]
+__global__ void goal_scatter_kernel(const float* __restrict__ dy, const int* __restrict__ map, float* __restrict__ dx,
+                                    long long rows, int L, int D) {
+    const long long n = rows * D;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D;
+        int d = (int)(i % D);
+        long long b = r / L;
+        int lp = (int)(r % L);
+        float acc = 0.f;
+        for (int l = 0; l <= lp; ++l)
+            if (map[b * L + l] == lp) acc += dy[(b * L + l) * D + d];
+        dx[i] = acc;
+    }
+}
+
+// ------------------------------------------------------------------ manager segment scan
+// seg_prob[b, s..e] = prod p[b, s..e] for each closed segment; 0 elsewhere.
+// exp_out: per-segment sums of `expected`; tails follow the same quirks as expand_goals (see goal_map_kernel).
+__global__ void segment_scan_fwd_kernel(const float* __restrict__ p, const float* __restrict__ expected,
+                                        const int* __restrict__ seg, float* __restrict__ seg_prob,
+                                        float* __restrict__ exp_out, int B, int L) {
+    extern __shared__ int row_has[];
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        int any = 0;
+        for (int l = 0; l < L; ++l) any |= (seg[b * L + l] != 0);
+        row_has[b] = any;
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        int later = 0;
+        for (int bb = b + 1; bb < B; ++bb) later |= row_has[bb];
+        int start = 0;
+        for (int l = 0; l < L; ++l) {
+            seg_prob[b * L + l] = 0.f;
+            exp_out[b * L + l] = expected[b * L + l];
+        }
+        if (row_has[b]) {
+            for (int l = 0; l < L; ++l) {
+                if (seg[b * L + l] != 0) {
+                    float pr = 1.f, su = 0.f;
+                    for (int k = start; k <= l; ++k) { pr *= p[b * L + k]; su += expected[b * L + k]; }
+                    for (int k = start; k <= l; ++k) { seg_prob[b * L + k] = pr; exp_out[b * L + k] = su; }
+                    start = l + 1;
+                }
+            }
+            if (later)
+                for (int k = start; k < L; ++k) exp_out[b * L + k] = 0.f;
+        } else if (b == 0 && later) {
+            for (int k = 0; k < L; ++k) exp_out[k] = 0.f;
+        }
+    }
+}
+
+// dp[b,k] = (sum_{l in seg(k)} g[b,l]) * prod_{j in seg(k), j != k} p[b,j]
+__global__ void segment_scan_bwd_kernel(const float* __restrict__ p, const int* __restrict__ seg,
+                                        const float* __restrict__ g, float* __restrict__ dp, int B, int L) {
+    for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < B; b += gridDim.x * blockDim.x) {
+        int start = 0;
+        for (int l = 0; l < L; ++l) dp[b * L + l] = 0.f;
+        for (int l = 0; l < L; ++l) {
+            if (seg[b * L + l] != 0) {
+                float G = 0.f;
+                for (int k = start; k <= l; ++k) G += g[b * L + k];
+                for (int k = start; k <= l; ++k) {
+                    float pr = 1.f;
+                    for (int j = start; j <= l; ++j)
+                        if (j != k) pr *= p[b * L + j];
+                    dp[b * L + k] = G * pr;
+                }
+                start = l + 1;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ linear backward prep
+// dZ[m,n] = dY[m,n] * (act==relu ? Y[m,n] > 0 : 1) * (dropout keep ? 1/(1-p) : 0);  db[n] = sum_m dZ[m,n].
+// For relu + dropout the forward output Y = drop(relu(z)) is > 0 exactly where both let the gradient through.
+// One block per 32 columns; 8 warps stride the rows; deterministic reduction.
+__global__ void __launch_bounds__(256) linear_bwd_prep_kernel(const float* __restrict__ dY, long long lddy,
+                                                              const float* __restrict__ Y, long long ldy,
+                                                              float* __restrict__ dZ, float* __restrict__ db, int M,
+                                                              int N, int act, float drop_p,
+                                                              const unsigned long long* __restrict__ rng,
+                                                              unsigned int salt) {
+    __shared__ float sb[8][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int n = blockIdx.x * 32 + lane;
+    const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+    float acc = 0.f;
+    if (n < N) {
+        for (int m = w; m < M; m += 8) {
+            float g = dY[(long long)m * lddy + n];
+            if (act == 1) {
+                g = (Y[(long long)m * ldy + n] > 0.f) ? g * ks : 0.f;
+            } else if (drop_p > 0.f) {
+                g = dropout_keep(rng, salt, (unsigned long long)m * N + n, drop_p) ? g * ks : 0.f;
+            }
+            if (dZ) dZ[(long long)m * N + n] = g;
+            acc += g;
+        }
+    }
+    sb[w][lane] = acc;
+    __syncthreads();
+    if (w == 0 && n < N && db) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sb[i][lane];
+        db[n] = t;
+    }
+}
+
+// ------------------------------------------------------------------ fused multi-tensor Adam
+struct AdamChunk {
+    int tensor;
+    int start;  // element offset inside the tensor, chunks are ADAM_CHUNK long
+};
+constexpr int ADAM_CHUNK = 8192;
+
+__global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restrict__ params,
+                                                         const float* const* __restrict__ grads,
+                                                         float* const* __restrict__ exp_avg,
+                                                         float* const* __restrict__ exp_avg_sq,
+                                                         const long long* __restrict__ numels,
+                                                         const int* __restrict__ chunk_tensor,
+                                                         const int* __restrict__ chunk_start,
+                                                         const float* __restrict__ step_ptr, float lr, float beta1,
+                                                         float beta2, float eps, float grad_scale) {
+    const int t = chunk_tensor[blockIdx.x];
+    const long long s0 = chunk_start[blockIdx.x];
+    const long long n = numels[t];
+    float* __restrict__ p = params[t];
+    const float* __restrict__ g = grads[t];
+    float* __restrict__ m = exp_avg[t];
+    float* __restrict__ v = exp_avg_sq[t];
+    const float step = step_ptr[t];
+    const float bc1 = 1.f - powf(beta1, step);
+    const float bc2 = 1.f - powf(beta2, step);
+    const float step_size = lr / bc1;
+    const float inv_sqrt_bc2 = rsqrtf(bc2);
+    long long end = s0 + ADAM_CHUNK;
+    if (end > n) end = n;
+    for (long long i = s0 + threadIdx.x; i < end; i += 256) {
+        const float gi = g[i] * grad_scale;
+        const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+        const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        p[i] -= step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+    }
+}
+
+// steps[active[i]] += 1 for the tensors updated this step (torch keeps one step count per parameter and skips
+// parameters without a gradient);  rng_state[1] += 1 : dropout / sampling stream
+__global__ void tick_kernel(float* steps, const int* active, int n_active, unsigned long long* rng_state) {
+    if (steps)
+        for (int i = threadIdx.x; i < n_active; i += blockDim.x) steps[active ? active[i] : i] += 1.f;
+    if (rng_state && threadIdx.x == 0) rng_state[1] += 1ull;
+}
+
+static inline int grid_for(long long n, int threads) {
+    long long b = (n + threads - 1) / threads;
+    if (b > 148 * 8) b = 148 * 8;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+}  // namespace bmhrl
+using namespace bmhrl;
+
+extern "C" int bmhrl_embed_posenc_f32(const long long* tokens, const float* W, const float* pe, float* emb, float* pos,
+                                      long long rows, int L, int D, float scale, float drop_p,
+                                      const unsigned long long* rng_state, unsigned int salt, void* stream) {
+    BMHRL_CHECK_ARG(tokens && W && (emb || pos) && (!pos || pe), "bmhrl_embed_posenc_f32: null pointer");
+    BMHRL_CHECK_ARG(rows >= 0 && L > 0 && D > 0, "bmhrl_embed_posenc_f32: bad sizes");
+    BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || rng_state), "bmhrl_embed_posenc_f32: dropout");
+    if (rows == 0) return BMHRL_OK;
+    embed_posenc_kernel<<<grid_for(rows * D, 256), 256, 0, (cudaStream_t)stream>>>(tokens, W, pe, emb, pos, rows, L, D,
+                                                                                   scale, drop_p, rng_state, salt);
+    BMHRL_POST_LAUNCH("embed_posenc");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_add_posenc_f32(const float* x, const float* x2, const float* pe, float* out, long long rows,
+                                    int S, int D, float drop_p, const unsigned long long* rng_state,
+                                    unsigned int salt, void* stream) {
+    BMHRL_CHECK_ARG(x && pe && out, "bmhrl_add_posenc_f32: null pointer");
+    BMHRL_CHECK_ARG(rows >= 0 && S > 0 && D > 0 && D % 4 == 0, "bmhrl_add_posenc_f32: D must be a multiple of 4");
+    BMHRL_CHECK_ARG(aligned16(x) && aligned16(pe) && aligned16(out) && (!x2 || aligned16(x2)),
+                    "bmhrl_add_posenc_f32: pointers must be 16-byte aligned");
+    BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || rng_state), "bmhrl_add_posenc_f32: dropout");
+    if (rows == 0) return BMHRL_OK;
+    add_posenc_kernel<<<grid_for(rows * D / 4, 256), 256, 0, (cudaStream_t)stream>>>(x, x2, pe, out, rows, S, D, drop_p,
+                                                                                     rng_state, salt);
+    BMHRL_POST_LAUNCH("add_posenc");
+    return BMHRL_OK;
+}
+
+// Index convention: add_posenc draws one Philox block per float4, i.e. element i uses counter i -- identical to
+// dropout_keep(idx = i); dropout_apply therefore reproduces its mask.
+extern "C" int bmhrl_dropout_apply_f32(const float* dy, float* dx, long long n, float drop_p,
+                                       const unsigned long long* rng_state, unsigned int salt, void* stream) {
+    BMHRL_CHECK_ARG(dy && dx && rng_state && drop_p > 0.f && drop_p < 1.f, "bmhrl_dropout_apply_f32: bad arguments");
+    if (n <= 0) return BMHRL_OK;
+    dropout_apply_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(dy, dx, n, drop_p, rng_state, salt);
+    BMHRL_POST_LAUNCH("dropout_apply");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_dropout_add_f32(const float* x, const float* r, float* out, long long n, float drop_p,
+                                     const unsigned long long* rng_state, unsigned int salt, void* stream) {
+    BMHRL_CHECK_ARG(x && r && out, "bmhrl_dropout_add_f32: null pointer");
+    BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || rng_state), "bmhrl_dropout_add_f32: dropout");
+    if (n <= 0) return BMHRL_OK;
+    dropout_add_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(x, r, out, n, drop_p, rng_state, salt);
+    BMHRL_POST_LAUNCH("dropout_add");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_embed_bwd_f32(const long long* tokens, const float* g, float* dW, long long rows, int D,
+                                   float scale, void* stream) {
+    BMHRL_CHECK_ARG(tokens && g && dW && rows >= 0 && D > 0, "bmhrl_embed_bwd_f32: bad arguments");
+    if (rows == 0) return BMHRL_OK;
+    embed_bwd_kernel<<<grid_for(rows * D, 256), 256, 0, (cudaStream_t)stream>>>(tokens, g, dW, rows, D, scale);
+    BMHRL_POST_LAUNCH("embed_bwd");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_goal_expand_fwd_f32(const float* x, const int* seg, int* map, float* out, int B, int L, int D,
+                                         void* stream) {
+    BMHRL_CHECK_ARG(x && seg && map && out && B > 0 && L > 0 && D > 0, "bmhrl_goal_expand_fwd_f32: bad arguments");
+    BMHRL_CHECK_ARG(B <= 8192, "bmhrl_goal_expand_fwd_f32: B too large for the single-CTA scan");
+    cudaStream_t st = (cudaStream_t)stream;
+    goal_map_kernel<<<1, 256, B * sizeof(int), st>>>(seg, map, B, L);
+    BMHRL_POST_LAUNCH("goal_map");
+    goal_gather_kernel<<<grid_for((long long)B * L * D, 256), 256, 0, st>>>(x, map, out, (long long)B * L, L, D);
+    BMHRL_POST_LAUNCH("goal_gather");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_goal_expand_bwd_f32(const float* dy, const int* map, float* dx, int B, int L, int D,
+                                         void* stream) {
+    BMHRL_CHECK_ARG(dy && map && dx && B > 0 && L > 0 && D > 0, "bmhrl_goal_expand_bwd_f32: bad arguments");
+    goal_scatter_kernel<<<grid_for((long long)B * L * D, 256), 256, 0, (cudaStream_t)stream>>>(dy, map, dx,
+                                                                                               (long long)B * L, L, D);
+    BMHRL_POST_LAUNCH("goal_scatter");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_segment_scan_fwd_f32(const float* probs, const float* expected, const int* seg, float* seg_prob,
+                                          float* expected_out, int B, int L, void* stream) {
+    BMHRL_CHECK_ARG(probs && expected && seg && seg_prob && expected_out && B > 0 && L > 0,
+                    "bmhrl_segment_scan_fwd_f32: bad arguments");
+    BMHRL_CHECK_ARG(B <= 8192, "bmhrl_segment_scan_fwd_f32: B too large for the single-CTA scan");
+    segment_scan_fwd_kernel<<<1, 256, B * sizeof(int), (cudaStream_t)stream>>>(probs, expected, seg, seg_prob,
+                                                                               expected_out, B, L);
+    BMHRL_POST_LAUNCH("segment_scan_fwd");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_segment_scan_bwd_f32(const float* probs, const int* seg, const float* g, float* dprobs, int B,
+                                          int L, void* stream) {
+    BMHRL_CHECK_ARG(probs && seg && g && dprobs && B > 0 && L > 0, "bmhrl_segment_scan_bwd_f32: bad arguments");
+    segment_scan_bwd_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(probs, seg, g, dprobs, B, L);
+    BMHRL_POST_LAUNCH("segment_scan_bwd");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const float* Y, long long ldy, float* dZ,
+                                         float* db, int M, int N, int act, float drop_p,
+                                         const unsigned long long* rng_state, unsigned int salt, void* stream) {
+    BMHRL_CHECK_ARG(dY && (dZ || db) && M >= 0 && N > 0, "bmhrl_linear_bwd_prep_f32: bad arguments");
+    BMHRL_CHECK_ARG(act == 0 || (act == 1 && Y), "bmhrl_linear_bwd_prep_f32: relu needs the forward output");
+    BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || act == 1 || rng_state),
+                    "bmhrl_linear_bwd_prep_f32: dropout needs rng_state");
+    linear_bwd_prep_kernel<<<(N + 31) / 32, 256, 0, (cudaStream_t)stream>>>(dY, lddy, Y, ldy, dZ, db, M, N, act, drop_p,
+                                                                            rng_state, salt);
+    BMHRL_POST_LAUNCH("linear_bwd_prep");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_adam_chunk_elems(void) { return ADAM_CHUNK; }
+
+extern "C" int bmhrl_adam_multi_f32(float* const* params, const float* const* grads, float* const* exp_avg,
+                                    float* const* exp_avg_sq, const long long* numels, const int* chunk_tensor,
+                                    const int* chunk_start, int n_chunks, const float* step_counts, float lr,
+                                    float beta1, float beta2, float eps, float grad_scale, void* stream) {
+    BMHRL_CHECK_ARG(params && grads && exp_avg && exp_avg_sq && numels && chunk_tensor && chunk_start && step_counts,
+                    "bmhrl_adam_multi_f32: null pointer");
+    if (n_chunks <= 0) return BMHRL_OK;
+    adam_multi_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
+                                                                  chunk_tensor, chunk_start, step_counts, lr, beta1,
+                                                                  beta2, eps, grad_scale);
+    BMHRL_POST_LAUNCH("adam_multi");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_tick(float* step_counts, const int* active_tensors, int n_active,
+                          unsigned long long* rng_state, void* stream) {
+    tick_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(step_counts, active_tensors, n_active, rng_state);
+    BMHRL_POST_LAUNCH("tick");
+    return BMHRL_OK;
+}

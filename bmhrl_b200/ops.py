@@ -1,0 +1,709 @@
+"""Autograd-aware Python wrappers over the C ABI (include/bmhrl_b200.h).
+
+Every function here launches hand-written sm_100a kernels from libbmhrl_b200.so on torch's current CUDA stream and
+allocates outputs / workspaces through torch's caching allocator, so whole training steps are CUDA-graph
+capturable.  Nothing in this file computes on the CPU and nothing falls back to ATen math: a non-CUDA tensor
+raises.
+"""
+import math
+
+import torch
+
+from ._lib import LIB
+
+_F32 = torch.float32
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# plumbing
+# ----------------------------------------------------------------------------------------------------------------
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def _chk(t, name, dtype=_F32):
+    if not t.is_cuda:
+        raise RuntimeError(f"bmhrl_b200: `{name}` must be a CUDA tensor (there is no CPU fallback)")
+    if t.dtype != dtype:
+        raise RuntimeError(f"bmhrl_b200: `{name}` must be {dtype}, got {t.dtype}")
+    return t
+
+
+def _c(t, name, dtype=_F32):
+    return _chk(t, name, dtype).contiguous()
+
+
+class _Rng:
+    """Per-device dropout/sampling state: a device tensor {seed, step} plus the frozen snapshot that the ops of the
+    current forward pass (and their backward) read.  `new_epoch()` advances the step ON THE DEVICE (graph-safe)."""
+
+    def __init__(self):
+        self.state = {}
+        self.active = {}
+        self.salt = 0
+
+    def _dev(self, device):
+        return torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+
+    def seed(self, seed, device="cuda"):
+        d = self._dev(device)
+        self.state[d] = torch.tensor([seed, 0], dtype=torch.int64, device=f"cuda:{d}")
+        self.active[d] = self.state[d].clone()
+
+    def get_state(self, device):
+        d = self._dev(device)
+        if d not in self.state:
+            self.seed(0x5EED, f"cuda:{d}")
+        return self.state[d]
+
+    def new_epoch(self, device):
+        st = self.get_state(device)
+        LIB.call("bmhrl_tick", None, None, 0, st.data_ptr(), _stream())
+        self.active[self._dev(device)] = st.clone()
+        return self.active[self._dev(device)]
+
+    def current(self, device):
+        self.get_state(device)
+        return self.active[self._dev(device)]
+
+    def next_salt(self):
+        self.salt += 1
+        return self.salt
+
+
+RNG = _Rng()
+
+
+def manual_seed(seed, device="cuda"):
+    RNG.seed(int(seed), device)
+
+
+def new_rng_epoch(device="cuda"):
+    return RNG.new_epoch(device)
+
+
+def next_salt():
+    return RNG.next_salt()
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# contractions
+# ----------------------------------------------------------------------------------------------------------------
+def gemm(A, sAm, sAk, B, sBk, sBn, C, ldc, M, N, K, batch=1, Hdiv=1, bA=(0, 0), bB=(0, 0), bC=(0, 0), alpha=1.0,
+         beta=0.0):
+    LIB.call("bmhrl_gemm_f32", _p(A), sAm, sAk, _p(B), sBk, sBn, _p(C), ldc, M, N, K, batch, Hdiv, bA[0], bA[1], bB[0],
+             bB[1], bC[0], bC[1], alpha, beta, _stream())
+
+
+class _Linear(torch.autograd.Function):
+    """y = resid + dropout(act(x W^T + b)); reference call sites listed in include/bmhrl_b200.h."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, resid, act, drop_p, salt, rng):
+        x = _c(x, "x")
+        weight = _c(weight, "weight")
+        N, K = weight.shape
+        if x.shape[-1] != K:
+            raise RuntimeError(f"linear: input feature size {x.shape[-1]} != weight in_features {K}")
+        M = x.numel() // K
+        y = torch.empty(x.shape[:-1] + (N,), device=x.device, dtype=_F32)
+        r = None
+        if resid is not None:
+            r = _c(resid, "resid")
+            if r.shape != y.shape:
+                raise RuntimeError("linear: residual shape mismatch")
+        b = None if bias is None else _c(bias, "bias")
+        LIB.call("bmhrl_linear_fwd_f32", _p(x), K, _p(weight), _p(b), _p(r), N, _p(y), N, M, N, K, act, drop_p,
+                 _p(rng) if drop_p > 0 else None, salt, _stream())
+        ctx.save_for_backward(x, weight, y if act == 1 else None, rng if drop_p > 0 else None)
+        ctx.cfg = (act, drop_p, salt, M, N, K, bias is not None, resid is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y, rng = ctx.saved_tensors
+        act, drop_p, salt, M, N, K, has_bias, has_resid = ctx.cfg
+        dy = _c(dy, "dy")
+        need_x, need_w, need_b, need_r = ctx.needs_input_grad[0], ctx.needs_input_grad[1], \
+            has_bias and ctx.needs_input_grad[2], has_resid and ctx.needs_input_grad[3]
+        st = _stream()
+        dz = dy
+        db = None
+        if act == 1 or drop_p > 0:
+            dz = torch.empty(M, N, device=dy.device, dtype=_F32)
+            db = torch.empty(N, device=dy.device, dtype=_F32) if need_b else None
+            LIB.call("bmhrl_linear_bwd_prep_f32", _p(dy), N, _p(y), N, _p(dz), _p(db), M, N, act, drop_p, _p(rng), salt,
+                     st)
+        elif need_b:
+            db = torch.empty(N, device=dy.device, dtype=_F32)
+            LIB.call("bmhrl_linear_bwd_prep_f32", _p(dy), N, None, N, None, _p(db), M, N, 0, 0.0, None, 0, st)
+        dx = dw = None
+        if need_x:  # dX = dZ W : (M,N)(N,K)
+            dx = torch.empty(x.shape, device=dy.device, dtype=_F32)
+            gemm(dz, N, 1, weight, K, 1, dx, K, M, K, N)
+        if need_w:  # dW = dZ^T X : (N,M)(M,K)
+            dw = torch.empty(N, K, device=dy.device, dtype=_F32)
+            gemm(dz, 1, N, x, K, 1, dw, K, N, K, M)
+        return dx, dw, db, (dy if need_r else None), None, None, None, None
+
+
+def linear(x, weight, bias=None, resid=None, act=0, drop_p=0.0, salt=0, rng=None):
+    if drop_p > 0 and rng is None:
+        rng = RNG.current(x.device)
+    return _Linear.apply(x, weight, bias, resid, act, float(drop_p), int(salt), rng)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# K2
+# ----------------------------------------------------------------------------------------------------------------
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        x = _c(x, "x")
+        gamma = _c(gamma, "gamma")
+        beta = _c(beta, "beta")
+        D = x.shape[-1]
+        rows = x.numel() // D
+        y = torch.empty_like(x)
+        mean = torch.empty(rows, device=x.device, dtype=_F32)
+        rstd = torch.empty(rows, device=x.device, dtype=_F32)
+        LIB.call("bmhrl_layernorm_fwd_f32", _p(x), None, _p(gamma), _p(beta), None, _p(y), _p(mean), _p(rstd), rows, D,
+                 eps, _stream())
+        ctx.save_for_backward(x, gamma, mean, rstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, mean, rstd = ctx.saved_tensors
+        dy = _c(dy, "dy")
+        D = x.shape[-1]
+        rows = x.numel() // D
+        need_x = ctx.needs_input_grad[0]
+        need_aff = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        dx = torch.empty_like(x) if need_x else None
+        dg = torch.empty(D, device=x.device, dtype=_F32) if need_aff else None
+        db = torch.empty(D, device=x.device, dtype=_F32) if need_aff else None
+        LIB.call("bmhrl_layernorm_bwd_f32", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), None, _p(dx), _p(dg), _p(db),
+                 rows, D, _stream())
+        return dx, dg, db, None
+
+
+def layer_norm(x, gamma, beta, eps=1e-5):
+    return _LayerNorm.apply(x, gamma, beta, float(eps))
+
+
+class _GatedMix(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, v, a, gate):
+        v = _c(v, "v")
+        a = _c(a, "a")
+        gate = _c(gate, "gate")
+        out = torch.empty_like(v)
+        LIB.call("bmhrl_gated_mix_fwd_f32", _p(v), _p(a), _p(gate), _p(out), v.numel(), _stream())
+        ctx.save_for_backward(v, a, gate)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        v, a, gate = ctx.saved_tensors
+        g = _c(g, "g")
+        dv = torch.empty_like(v)
+        da = torch.empty_like(a)
+        dgate = torch.empty(1, device=v.device, dtype=_F32)
+        ws = torch.empty(592, device=v.device, dtype=_F32)
+        LIB.call("bmhrl_gated_mix_bwd_f32", _p(g), _p(v), _p(a), _p(gate), _p(dv), _p(da), _p(dgate), _p(ws), 592,
+                 v.numel(), _stream())
+        return dv, da, dgate
+
+
+def gated_mix(v, a, gate):
+    return _GatedMix.apply(v, a, gate)
+
+
+class _DropoutAdd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, r, drop_p, salt, rng):
+        x = _c(x, "x")
+        r = _c(r, "r")
+        out = torch.empty_like(x)
+        LIB.call("bmhrl_dropout_add_f32", _p(x), _p(r), _p(out), x.numel(), drop_p, _p(rng) if drop_p > 0 else None,
+                 salt, _stream())
+        ctx.save_for_backward(rng if drop_p > 0 else None)
+        ctx.cfg = (drop_p, salt)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (rng,) = ctx.saved_tensors
+        drop_p, salt = ctx.cfg
+        g = _c(g, "g")
+        dr = g
+        if drop_p > 0 and ctx.needs_input_grad[1]:
+            dr = torch.empty_like(g)
+            LIB.call("bmhrl_dropout_apply_f32", _p(g), _p(dr), g.numel(), drop_p, _p(rng), salt, _stream())
+        return g, dr, None, None, None
+
+
+def dropout_add(x, r, drop_p=0.0, salt=0, rng=None):
+    if drop_p > 0 and rng is None:
+        rng = RNG.current(x.device)
+    return _DropoutAdd.apply(x, r, float(drop_p), int(salt), rng)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# K1 attention core (exact-fp32 path)
+# ----------------------------------------------------------------------------------------------------------------
+def _mask_args(mask, B, Sq, Sk):
+    """mask: None | bool (B,1,Sk) / (B,1,1,Sk) key padding | bool (B,Sq,Sk) / (B,1,Sq,Sk) full."""
+    if mask is None:
+        return None, 0
+    if mask.dtype != torch.bool and mask.dtype != torch.uint8:
+        mask = mask != 0
+    m = mask
+    while m.dim() > 3:
+        m = m.squeeze(1)
+    if m.dim() != 3 or m.shape[0] != B or m.shape[-1] != Sk:
+        raise RuntimeError(f"attention mask shape {tuple(mask.shape)} incompatible with B={B}, Sq={Sq}, Sk={Sk}")
+    if m.shape[1] == 1 and Sq != 1:
+        return m.reshape(B, Sk).contiguous().view(torch.uint8), 1
+    if m.shape[1] != Sq:
+        raise RuntimeError(f"attention mask shape {tuple(mask.shape)} incompatible with Sq={Sq}")
+    return m.contiguous().view(torch.uint8), 2
+
+
+class _MhaCore(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, mask_u8, mask_kind, causal, H, drop_p, salt, rng):
+        q = _c(q, "q")
+        k = _c(k, "k")
+        v = _c(v, "v")
+        B, Sq, D = q.shape
+        Sk = k.shape[1]
+        dk = D // H
+        o = torch.empty(B, Sq, D, device=q.device, dtype=_F32)
+        nP = LIB.raw("bmhrl_mha_core_probs_floats")(B, H, Sq, Sk)
+        P = torch.empty(nP, device=q.device, dtype=_F32)
+        LIB.call("bmhrl_mha_core_fwd_f32", _p(q), D, Sq * D, _p(k), D, Sk * D, _p(v), D, Sk * D, _p(mask_u8), mask_kind,
+                 causal, _p(o), D, Sq * D, _p(P), B, H, Sq, Sk, dk, drop_p, _p(rng) if drop_p > 0 else None, salt,
+                 _stream())
+        ctx.save_for_backward(q, k, v, P, mask_u8, rng if drop_p > 0 else None)
+        ctx.cfg = (mask_kind, causal, H, drop_p, salt)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, P, mask_u8, rng = ctx.saved_tensors
+        mask_kind, causal, H, drop_p, salt = ctx.cfg
+        do = _c(do, "do")
+        B, Sq, D = q.shape
+        Sk = k.shape[1]
+        dk = D // H
+        dq = torch.empty_like(q)
+        dkk = torch.empty_like(k)
+        dv = torch.empty_like(v)
+        ws_dp = torch.empty_like(P)
+        ws_do = torch.empty_like(do) if drop_p > 0 else None
+        LIB.call("bmhrl_mha_core_bwd_f32", _p(do), D, Sq * D, _p(q), D, Sq * D, _p(k), D, Sk * D, _p(v), D, Sk * D, _p(P),
+                 _p(mask_u8), mask_kind, causal, _p(dq), D, Sq * D, _p(dkk), D, Sk * D, _p(dv), D, Sk * D, _p(ws_dp),
+                 _p(ws_do), B, H, Sq, Sk, dk, drop_p, _p(rng), salt, _stream())
+        return dq, dkk, dv, None, None, None, None, None, None, None
+
+
+def mha_core(q, k, v, mask, H, causal=False, drop_p=0.0, salt=0, rng=None):
+    """q (B,Sq,D), k/v (B,Sk,D) projected tensors; returns the head-merged (B,Sq,D) attention output."""
+    B, Sq, D = q.shape
+    Sk = k.shape[1]
+    if D % H != 0:
+        raise RuntimeError("mha_core: d_model must be divisible by H")
+    m, kind = _mask_args(mask, B, Sq, Sk)
+    if kind == 0:
+        causal = False  # the reference only builds the tril when a mask is given (multihead_attention.py:16-21)
+    if causal and Sq != Sk:
+        raise RuntimeError("mha_core: causal attention needs Sq == Sk")
+    if drop_p > 0 and rng is None:
+        rng = RNG.current(q.device)
+    return _MhaCore.apply(q, k, v, m, kind, int(bool(causal)), H, float(drop_p), int(salt), rng)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# K4 / K5
+# ----------------------------------------------------------------------------------------------------------------
+class _LogSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = _c(x, "x")
+        V = x.shape[-1]
+        y = torch.empty_like(x)
+        LIB.call("bmhrl_log_softmax_fwd_f32", _p(x), _p(y), x.numel() // V, V, _stream())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        dy = _c(dy, "dy")
+        V = y.shape[-1]
+        dx = torch.empty_like(y)
+        LIB.call("bmhrl_log_softmax_bwd_f32", _p(dy), _p(y), _p(dx), y.numel() // V, V, _stream())
+        return dx
+
+
+def log_softmax(x):
+    return _LogSoftmax.apply(x)
+
+
+class _KlLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, trg, samp, offset, mode, smoothing, pad_idx, rowsum):
+        pred = _c(pred, "pred")
+        V = pred.shape[-1]
+        rows = pred.numel() // V
+        trg = _c(trg, "target", torch.int64).reshape(-1)
+        if mode == 1:
+            samp = _c(samp, "biased_trg", torch.int64).reshape(-1)
+            offset = _c(offset, "biased_offset").reshape(-1)
+        out = None if rowsum else torch.empty(rows, V, device=pred.device, dtype=_F32)
+        rs = torch.empty(rows, device=pred.device, dtype=_F32) if rowsum else None
+        LIB.call("bmhrl_kl_loss_fwd_f32", mode, _p(pred), _p(trg), _p(samp), _p(offset), _p(out), _p(rs), rows, V,
+                 smoothing, pad_idx, _stream())
+        ctx.save_for_backward(pred, trg, samp, offset)
+        ctx.cfg = (mode, smoothing, pad_idx, rowsum, rows, V)
+        return rs if rowsum else out
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, trg, samp, offset = ctx.saved_tensors
+        mode, smoothing, pad_idx, rowsum, rows, V = ctx.cfg
+        g = _c(g, "grad")
+        dpred = torch.empty_like(pred) if ctx.needs_input_grad[0] else None
+        doff = None
+        if mode == 1 and ctx.needs_input_grad[3]:
+            doff = torch.empty(rows, device=pred.device, dtype=_F32)
+        LIB.call("bmhrl_kl_loss_bwd_f32", mode, _p(pred), _p(trg), _p(samp), _p(offset), None if rowsum else _p(g),
+                 _p(g) if rowsum else None, _p(dpred), _p(doff), rows, V, smoothing, pad_idx, _stream())
+        return dpred, None, None, doff, None, None, None, None
+
+
+def label_smoothing_kl(pred, target, smoothing, pad_idx, rowsum=False):
+    """loss/label_smoothing.py:12-32 -> (B*L, V) element-wise divergence, or (B*L,) row sums with rowsum=True."""
+    return _KlLoss.apply(pred, target, None, None, 0, float(smoothing), int(pad_idx), bool(rowsum))
+
+
+def biased_kl(pred, trg, biased_trg, biased_offset, smoothing, pad_idx, rowsum=False):
+    """loss/biased_kl.py:22-53; differentiable in pred AND biased_offset."""
+    return _KlLoss.apply(pred, trg, biased_trg, biased_offset.reshape(-1), 1, float(smoothing), int(pad_idx),
+                         bool(rowsum))
+
+
+class _SampleRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, mode, noise, salt, rng):
+        pred = _c(pred, "pred")
+        V = pred.shape[-1]
+        rows = pred.numel() // V
+        tok = torch.empty(pred.shape[:-1], device=pred.device, dtype=torch.int64)
+        prob = torch.empty(pred.shape[:-1], device=pred.device, dtype=_F32)
+        if mode == 1:
+            noise = _c(noise, "exp_noise")
+            if noise.numel() != pred.numel():
+                raise RuntimeError("sample: exp_noise must have pred's number of elements")
+        LIB.call("bmhrl_sample_rows_f32", mode, _p(pred), _p(noise) if mode == 1 else None, _p(tok), _p(prob), rows, V,
+                 _p(rng) if mode == 2 else None, salt, _stream())
+        ctx.save_for_backward(tok, prob)
+        ctx.shape = pred.shape
+        ctx.mark_non_differentiable(tok)
+        return tok, prob
+
+    @staticmethod
+    def backward(ctx, _gtok, gprob):
+        tok, prob = ctx.saved_tensors
+        gprob = _c(gprob, "gprob")
+        V = ctx.shape[-1]
+        dpred = torch.zeros(ctx.shape, device=prob.device, dtype=_F32)
+        LIB.call("bmhrl_scatter_prob_grad_f32", _p(dpred), _p(tok), _p(prob), _p(gprob), prob.numel(), V, _stream())
+        return dpred, None, None, None, None
+
+
+def sample_tokens(pred, mode="argmax", exp_noise=None, salt=0, rng=None):
+    """epoch_loops/captioning_bmrl_loops.py:273-285.  mode: 'argmax' (manager), 'noise' (explicit Exp(1) tensor,
+    bit-reproducible) or 'philox' (in-kernel noise).  Returns (tokens int64, exp(pred)[tokens] with grad)."""
+    m = {"argmax": 0, "noise": 1, "philox": 2}[mode]
+    if m == 2 and rng is None:
+        rng = RNG.current(pred.device)
+    return _SampleRows.apply(pred, m, exp_noise, int(salt), rng)
+
+
+class _ReinforceGather(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, probs, action, eps):
+        probs = _c(probs, "probs")
+        V = probs.shape[-1]
+        action = _c(action, "action", torch.int64).reshape(-1)
+        rows = probs.numel() // V
+        out = torch.empty(probs.shape[:-1], device=probs.device, dtype=_F32)
+        LIB.call("bmhrl_reinforce_gather_fwd_f32", _p(probs), _p(action), _p(out), rows, V, eps, _stream())
+        ctx.save_for_backward(probs, action)
+        ctx.eps = eps
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        probs, action = ctx.saved_tensors
+        g = _c(g, "g")
+        V = probs.shape[-1]
+        dp = torch.zeros_like(probs)
+        LIB.call("bmhrl_reinforce_gather_bwd_f32", _p(probs), _p(action), _p(g), _p(dp), probs.numel() // V, V, ctx.eps,
+                 _stream())
+        return dp, None, None
+
+
+def reinforce_log_prob(probs, action, eps=1e-5):
+    return _ReinforceGather.apply(probs, action, float(eps))
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# K6 / K7
+# ----------------------------------------------------------------------------------------------------------------
+_PE_CACHE = {}
+
+
+def positional_table(seq_len, d_model, device):
+    """fp64 table of model/blocks.py:95-103 cast to fp32 (exactly what `.type_as(x)` yields), cached per device."""
+    key = (seq_len, d_model, str(device))
+    if key not in _PE_CACHE:
+        pos = torch.arange(seq_len, dtype=torch.float64)[:, None]
+        j = torch.arange(d_model, dtype=torch.float64)[None, :]
+        ang = pos / torch.pow(torch.tensor(10000.0, dtype=torch.float64), j / d_model)
+        even = (torch.arange(d_model) % 2 == 0)[None, :]
+        _PE_CACHE[key] = torch.where(even, torch.sin(ang), torch.cos(ang)).to(_F32).to(device).contiguous()
+    return _PE_CACHE[key]
+
+
+class _EmbedPos(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens, W, pe, scale, drop_p, salt, rng):
+        tokens = _c(tokens, "tokens", torch.int64)
+        W = _c(W, "embedding weight")
+        B, L = tokens.shape
+        D = W.shape[1]
+        emb = torch.empty(B, L, D, device=W.device, dtype=_F32)
+        pos = torch.empty(B, L, D, device=W.device, dtype=_F32)
+        LIB.call("bmhrl_embed_posenc_f32", _p(tokens), _p(W), _p(pe), _p(emb), _p(pos), B * L, L, D, scale, drop_p,
+                 _p(rng) if drop_p > 0 else None, salt, _stream())
+        ctx.save_for_backward(tokens, rng if drop_p > 0 else None)
+        ctx.cfg = (scale, drop_p, salt, W.shape)
+        return emb, pos
+
+    @staticmethod
+    def backward(ctx, gemb, gpos):
+        tokens, rng = ctx.saved_tensors
+        scale, drop_p, salt, wshape = ctx.cfg
+        if not ctx.needs_input_grad[1]:
+            return None, None, None, None, None, None, None
+        dW = torch.zeros(wshape, device=tokens.device, dtype=_F32)
+        st = _stream()
+        rows, D = tokens.numel(), wshape[1]
+        if gemb is not None:
+            LIB.call("bmhrl_embed_bwd_f32", _p(tokens), _p(_c(gemb, "gemb")), _p(dW), rows, D, scale, st)
+        if gpos is not None:
+            g = _c(gpos, "gpos")
+            if drop_p > 0:
+                g2 = torch.empty_like(g)
+                LIB.call("bmhrl_dropout_apply_f32", _p(g), _p(g2), g.numel(), drop_p, _p(rng), salt, st)
+                g = g2
+            LIB.call("bmhrl_embed_bwd_f32", _p(tokens), _p(g), _p(dW), rows, D, scale, st)
+        return None, dW, None, None, None, None, None
+
+
+def embed_posenc(tokens, W, drop_p=0.0, salt=0, rng=None, max_len=3660):
+    """(W[tok]*sqrt(D), dropout(W[tok]*sqrt(D) + PE)) -- model/blocks.py:44-48 and :105-112 in one pass."""
+    pe = positional_table(max_len, W.shape[1], W.device)
+    if tokens.shape[1] > max_len:
+        raise RuntimeError("embed_posenc: sequence longer than the positional table")
+    if drop_p > 0 and rng is None:
+        rng = RNG.current(W.device)
+    return _EmbedPos.apply(tokens, W, pe, math.sqrt(W.shape[1]), float(drop_p), int(salt), rng)
+
+
+class _AddPosenc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, x2, pe, drop_p, salt, rng):
+        x = _c(x, "x")
+        B, S, D = x.shape
+        out = torch.empty_like(x)
+        if x2 is not None:
+            x2 = _c(x2, "x2")
+        LIB.call("bmhrl_add_posenc_f32", _p(x), _p(x2), _p(pe), _p(out), B * S, S, D, drop_p,
+                 _p(rng) if drop_p > 0 else None, salt, _stream())
+        ctx.save_for_backward(rng if drop_p > 0 else None)
+        ctx.cfg = (drop_p, salt, x2 is not None)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (rng,) = ctx.saved_tensors
+        drop_p, salt, has2 = ctx.cfg
+        g = _c(g, "g")
+        if drop_p > 0:
+            g2 = torch.empty_like(g)
+            LIB.call("bmhrl_dropout_apply_f32", _p(g), _p(g2), g.numel(), drop_p, _p(rng), salt, _stream())
+            g = g2
+        return g, (g if has2 else None), None, None, None, None
+
+
+def add_posenc(x, x2=None, drop_p=0.0, salt=0, rng=None, max_len=3660):
+    """dropout(x (+ x2) + PE[:S]) -- PositionalEncoder.forward model/blocks.py:105-112 (x2 fuses rgb + flow)."""
+    if x.dim() != 3:
+        return x  # the reference leaves non-3D inputs untouched (blocks.py:106)
+    if x.shape[-1] % 4 != 0:
+        raise RuntimeError("add_posenc: feature size must be a multiple of 4")
+    if x.shape[1] > max_len:
+        raise RuntimeError("add_posenc: sequence longer than the positional table")
+    pe = positional_table(max_len, x.shape[-1], x.device)
+    if drop_p > 0 and rng is None:
+        rng = RNG.current(x.device)
+    return _AddPosenc.apply(x, x2, pe, float(drop_p), int(salt), rng)
+
+
+class _GoalExpand(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, seg):
+        x = _c(x, "x")
+        seg = _c(seg, "segment labels", torch.int32)
+        B, L, D = x.shape
+        if seg.shape != (B, L):
+            raise RuntimeError(f"expand_goals: segment labels must be (B,L)=({B},{L}), got {tuple(seg.shape)}")
+        out = torch.empty_like(x)
+        gmap = torch.empty(B, L, device=x.device, dtype=torch.int32)
+        LIB.call("bmhrl_goal_expand_fwd_f32", _p(x), _p(seg), _p(gmap), _p(out), B, L, D, _stream())
+        ctx.save_for_backward(gmap)
+        ctx.shape = (B, L, D)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (gmap,) = ctx.saved_tensors
+        B, L, D = ctx.shape
+        g = _c(g, "g")
+        dx = torch.empty_like(g)
+        LIB.call("bmhrl_goal_expand_bwd_f32", _p(g), _p(gmap), _p(dx), B, L, D, _stream())
+        return dx, None
+
+
+def expand_goals(x, seg):
+    """Manager.expand_goals model/bm_hrl_agent.py:415-429 as one device-side scan (no host loop, no sync)."""
+    return _GoalExpand.apply(x, seg)
+
+
+class _SegmentScan(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, probs, expected, seg):
+        probs = _c(probs, "probs")
+        expected = _c(expected, "expected")
+        seg = _c(seg, "segments", torch.int32)
+        B, L = probs.shape
+        sp = torch.empty_like(probs)
+        eo = torch.empty_like(expected)
+        LIB.call("bmhrl_segment_scan_fwd_f32", _p(probs), _p(expected), _p(seg), _p(sp), _p(eo), B, L, _stream())
+        ctx.save_for_backward(probs, seg)
+        ctx.mark_non_differentiable(eo)
+        return sp, eo
+
+    @staticmethod
+    def backward(ctx, gsp, _geo):
+        probs, seg = ctx.saved_tensors
+        B, L = probs.shape
+        gsp = _c(gsp, "g")
+        dp = torch.empty_like(probs)
+        LIB.call("bmhrl_segment_scan_bwd_f32", _p(probs), _p(seg), _p(gsp), _p(dp), B, L, _stream())
+        return dp, None, None
+
+
+def segment_scan(probs, expected, seg):
+    """Manager branch of biased_kl() (epoch_loops/captioning_bmrl_loops.py:299-317): per-segment product of the
+    sampled-token probabilities and per-segment sum of the value baseline."""
+    return _SegmentScan.apply(probs, expected, seg)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# optimiser
+# ----------------------------------------------------------------------------------------------------------------
+class FusedAdam:
+    """torch.optim.Adam(lr, betas=(0.9,0.999), eps=1e-8, weight_decay=0) (scripts/train_rl_captioning_module.py:81-83)
+    as ONE kernel launch over all currently trainable parameters.  State (moments, one step count per tensor like
+    torch) lives on the device and the counters are advanced by a kernel, so `step()` is graph-capturable.  Gradients
+    accumulate straight into one persistent flat buffer (`p.grad` are views of it): pointer tables stay valid across
+    steps and the flat buffer is what the data-parallel all-reduce buckets slice.
+
+    Phase switching (BMHrlAgent.teach_worker / teach_manager flip requires_grad): call `refresh_active()` afterwards;
+    frozen tensors are then skipped exactly like torch skips parameters whose grad is None."""
+
+    def __init__(self, params, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
+        self.params = list(params)
+        if not self.params:
+            raise RuntimeError("FusedAdam: no parameters")
+        dev = self.params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("FusedAdam: parameters must live on a CUDA device (there is no CPU fallback)")
+        self.lr, self.betas, self.eps, self.grad_scale = lr, betas, eps, grad_scale
+        total = sum(p.numel() for p in self.params)
+        self.flat_grad = torch.zeros(total, device=dev, dtype=_F32)
+        self.exp_avg = torch.zeros(total, device=dev, dtype=_F32)
+        self.exp_avg_sq = torch.zeros(total, device=dev, dtype=_F32)
+        self.step_counts = torch.zeros(len(self.params), device=dev, dtype=_F32)
+        self.chunk = LIB.raw("bmhrl_adam_chunk_elems")()
+        pp, gp, mp, vp, ne = [], [], [], [], []
+        off = 0
+        self.grad_views, self.offsets = [], []
+        for p in self.params:
+            n = p.numel()
+            gv = self.flat_grad[off:off + n].view_as(p)
+            self.grad_views.append(gv)
+            self.offsets.append(off)
+            pp.append(p.data_ptr())
+            gp.append(gv.data_ptr())
+            mp.append(self.exp_avg[off:off + n].data_ptr())
+            vp.append(self.exp_avg_sq[off:off + n].data_ptr())
+            ne.append(n)
+            off += n
+        i64 = dict(device=dev, dtype=torch.int64)
+        self._pp, self._gp = torch.tensor(pp, **i64), torch.tensor(gp, **i64)
+        self._mp, self._vp = torch.tensor(mp, **i64), torch.tensor(vp, **i64)
+        self._ne = torch.tensor(ne, **i64)
+        self.refresh_active()
+
+    def refresh_active(self):
+        dev = self.flat_grad.device
+        act, ct, cs = [], [], []
+        for i, p in enumerate(self.params):
+            if not p.requires_grad:
+                p.grad = None
+                continue
+            p.grad = self.grad_views[i]  # autograd accumulates in place into the flat buffer
+            act.append(i)
+            for s in range(0, p.numel(), self.chunk):
+                ct.append(i)
+                cs.append(s)
+        self.active = act
+        self._act = torch.tensor(act, device=dev, dtype=torch.int32)
+        self._ct = torch.tensor(ct, device=dev, dtype=torch.int32)
+        self._cs = torch.tensor(cs, device=dev, dtype=torch.int32)
+        self.n_chunks = len(ct)
+
+    def zero_grad(self, set_to_none=False):
+        self.flat_grad.zero_()
+        for i in self.active:
+            self.params[i].grad = self.grad_views[i]
+
+    def step(self):
+        st = _stream()
+        if self.n_chunks == 0:
+            return
+        LIB.call("bmhrl_tick", _p(self.step_counts), _p(self._act), len(self.active), None, st)
+        LIB.call("bmhrl_adam_multi_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne),
+                 _p(self._ct), _p(self._cs), self.n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
+                 self.eps, self.grad_scale, st)

@@ -1,0 +1,153 @@
+/* bmhrl_b200.h -- C ABI of libbmhrl_b200.so (sm_100a).
+ *
+ * The reference (Berghojo/bmhrl) is pure Python/PyTorch and has no FFI of its own: its "plugin boundary" for
+ * the hot path is the nn.Module surface (model/multihead_attention.py, model/blocks.py, model/bm_hrl_agent.py,
+ * loss/label_smoothing.py, loss/biased_kl.py).  The Python modules in bmhrl_b200/ keep that surface and call the
+ * entry points below through ctypes; each entry point cites the reference code it replaces (paths relative to the
+ * reference root).  INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated; tensors are fp32, row-major, contiguous unless a leading
+ *     dimension / stride argument says otherwise; token / index tensors are int64 (torch.long), segment labels and
+ *     maps int32, masks uint8 (torch.bool storage);
+ *   - `stream` is a cudaStream_t; all work is enqueued on it, nothing synchronises, nothing allocates: workspaces are
+ *     passed in by the caller (so every call is CUDA-graph capturable);
+ *   - return value 0 = ok, negative = error (BMHRL_ERR_*), message via bmhrl_last_error(); never throws / exits;
+ *   - dropout / sampling randomness is counter based (Philox4x32-10): rng_state points to two device uint64
+ *     {seed, step}; `salt` names the call site; forward and backward of an op regenerate the same mask;
+ *   - there is no CPU implementation behind any of these symbols.
+ */
+#ifndef BMHRL_B200_H
+#define BMHRL_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BMHRL_ABI_VERSION 1
+
+/* ---- library state ---------------------------------------------------------------------------------------- */
+int bmhrl_abi_version(void);
+int bmhrl_check_device(void);             /* 0 iff the current device is sm_100 */
+const char* bmhrl_last_error(void);       /* thread-local message of the last failing call */
+long long bmhrl_launch_count(void);       /* kernels launched by this library since the last reset */
+void bmhrl_reset_launch_count(void);
+
+/* ---- contractions (fp32 SIMT path, gemm_simt.cu) ------------------------------------------------------------ */
+/* C[z](m,n) = beta*C + alpha * sum_k A[z](m,k) B[z](k,n);  A(m,k) at A + m*sAm + k*sAk, B(k,n) at B + k*sBk + n*sBn.
+ * z in [0,batch): outer = z / Hdiv, inner = z % Hdiv, offsets outer*b?o + inner*b?i.
+ * Replaces the aten mm/bmm calls behind nn.Linear backward (dX = dY W, dW = dY^T X). */
+int bmhrl_gemm_f32(const float* A, long long sAm, long long sAk, const float* B, long long sBk, long long sBn,
+                   float* C, long long ldc, int M, int N, int K, int batch, int Hdiv, long long bAo, long long bAi,
+                   long long bBo, long long bBi, long long bCo, long long bCi, float alpha, float beta, void* stream);
+
+/* Y = resid + dropout(act(X W^T + bias)); W is (N,K) like nn.Linear.weight.  act: 0 none, 1 ReLU.
+ * Replaces linear_Q2d/K2d/V2d/d2Q (model/multihead_attention.py:70-72,89), fc1/fc2 (model/blocks.py:175-187,
+ * with the ResidualConnection add of model/blocks.py:144 fused), Manager.linear (model/bm_hrl_agent.py:439-440),
+ * WorkerCore.projection (model/bm_hrl_agent.py:464). */
+int bmhrl_linear_fwd_f32(const float* X, long long ldx, const float* W, const float* bias, const float* resid,
+                         long long ldr, float* Y, long long ldy, int M, int N, int K, int act, float drop_p,
+                         const unsigned long long* rng_state, unsigned int salt, void* stream);
+
+/* dZ = dY * relu'(Y) * dropout-mask/(1-p) (dZ may be NULL when act == 0 and drop_p == 0); db[n] = sum_m dZ[m,n]. */
+int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const float* Y, long long ldy, float* dZ, float* db,
+                              int M, int N, int act, float drop_p, const unsigned long long* rng_state,
+                              unsigned int salt, void* stream);
+
+/* ---- K2: residual + LayerNorm, gated mix (norm.cu) ---------------------------------------------------------- */
+/* z = x (+ resid); y = LayerNorm(z) (eps, affine).  z_out may be NULL.  ResidualConnection model/blocks.py:135-144,
+ * normCA/normCV model/bm_hrl_agent.py:107-108, post-LN model/encoder.py:64-68, model/decoder.py:77-99. */
+int bmhrl_layernorm_fwd_f32(const float* x, const float* resid, const float* gamma, const float* beta, float* z_out,
+                            float* y, float* mean, float* rstd, int rows, int D, float eps, void* stream);
+/* dx = LN'(dy) (+ dres); dgamma, dbeta (both or neither; dx may be NULL). */
+int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                            const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int D, void* stream);
+/* out = s*v + (1-s)*a, s = sigmoid(clamp(*gate_param,-2,2)); model/bm_hrl_agent.py:111-114. */
+int bmhrl_gated_mix_fwd_f32(const float* v, const float* a, const float* gate_param, float* out, long long n,
+                            void* stream);
+int bmhrl_gated_mix_bwd_f32(const float* g, const float* v, const float* a, const float* gate_param, float* dv,
+                            float* da, float* dgate, float* partial_ws, int ws_floats, long long n, void* stream);
+
+/* ---- K1: attention core, exact-fp32 path (attn_simt.cu) ----------------------------------------------------- */
+/* attention() model/multihead_attention.py:7-31.  Q/K/V/O are (B, S, H*dk) views: row pitch ld?, batch pitch bs?,
+ * head h at column h*dk.  mask_kind 0 none, 1 key padding uint8 (B,Sk), 2 full uint8 (B,Sq,Sk); causal adds k<=q
+ * (only together with a mask, like the reference).  P: workspace AND saved tensor, bmhrl_mha_core_probs_floats()
+ * floats.  Dropout is applied to the per-head output P V. */
+long long bmhrl_mha_core_probs_floats(int B, int H, int Sq, int Sk);
+int bmhrl_mha_core_fwd_f32(const float* Q, long long ldq, long long bsq, const float* K, long long ldk, long long bsk,
+                           const float* V, long long ldv, long long bsv, const unsigned char* mask, int mask_kind,
+                           int causal, float* O, long long ldo, long long bso, float* P, int B, int H, int Sq, int Sk,
+                           int dk, float drop_p, const unsigned long long* rng_state, unsigned int salt, void* stream);
+/* ws_dP: probs_floats() floats; ws_dO: B*Sq*H*dk floats, only needed when drop_p > 0. */
+int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long bso, const float* Q, long long ldq, long long bsq,
+                           const float* K, long long ldk, long long bsk, const float* V, long long ldv, long long bsv,
+                           const float* P, const unsigned char* mask, int mask_kind, int causal, float* dQ,
+                           long long lddq, long long bsdq, float* dK, long long lddk, long long bsdk, float* dV,
+                           long long lddv, long long bsdv, float* ws_dP, float* ws_dO, int B, int H, int Sq, int Sk,
+                           int dk, float drop_p, const unsigned long long* rng_state, unsigned int salt, void* stream);
+
+/* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
+int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */
+int bmhrl_log_softmax_bwd_f32(const float* dy, const float* y, float* dx, long long rows, int V, void* stream);
+/* mode 0: LabelSmoothing loss/label_smoothing.py:12-32; mode 1: BiasedKL loss/biased_kl.py:22-53.
+ * out (rows,V) element-wise divergence and/or rowsum (rows) -- either may be NULL. */
+int bmhrl_kl_loss_fwd_f32(int mode, const float* pred, const long long* trg, const long long* biased_trg,
+                          const float* biased_offset, float* out, float* rowsum, long long rows, int V, float smoothing,
+                          int pad_idx, void* stream);
+/* upstream gradient either element-wise (dout) or per row (drow); doffset only for mode 1 (may be NULL). */
+int bmhrl_kl_loss_bwd_f32(int mode, const float* pred, const long long* trg, const long long* biased_trg,
+                          const float* biased_offset, const float* dout, const float* drow, float* dpred,
+                          float* doffset, long long rows, int V, float smoothing, int pad_idx, void* stream);
+/* biased_kl() epoch_loops/captioning_bmrl_loops.py:273-285.  mode 0 argmax, 1 Categorical sample with explicit
+ * Exp(1) noise (rows,V), 2 Categorical sample with in-kernel Philox noise.  probs[row] = exp(pred[row, token]). */
+int bmhrl_sample_rows_f32(int mode, const float* pred, const float* exp_noise, long long* tokens, float* probs,
+                          long long rows, int V, const unsigned long long* rng_state, unsigned int salt, void* stream);
+int bmhrl_scatter_prob_grad_f32(float* dpred, const long long* tokens, const float* probs, const float* g,
+                                long long rows, int V, void* stream);
+/* Reinforce loss/biased_kl.py:69-75: out[row] = log(clamp(probs[row, action[row]], eps, 1-eps)). */
+int bmhrl_reinforce_gather_fwd_f32(const float* probs, const long long* action, float* out, long long rows, int V,
+                                   float eps, void* stream);
+int bmhrl_reinforce_gather_bwd_f32(const float* probs, const long long* action, const float* g, float* dprobs,
+                                   long long rows, int V, float eps, void* stream);
+
+/* ---- K6 / K7 and step plumbing (misc.cu) --------------------------------------------------------------------- */
+/* emb = W[tok]*scale (model/blocks.py:44-48); pos = dropout(emb + pe[l]) (model/blocks.py:105-112). */
+int bmhrl_embed_posenc_f32(const long long* tokens, const float* W, const float* pe, float* emb, float* pos,
+                           long long rows, int L, int D, float scale, float drop_p,
+                           const unsigned long long* rng_state, unsigned int salt, void* stream);
+int bmhrl_embed_bwd_f32(const long long* tokens, const float* g, float* dW, long long rows, int D, float scale,
+                        void* stream);
+/* out = dropout(x (+ x2) + pe[s]); x2 fuses V = rgb + flow (epoch_loops/captioning_bmrl_loops.py:498). */
+int bmhrl_add_posenc_f32(const float* x, const float* x2, const float* pe, float* out, long long rows, int S, int D,
+                         float drop_p, const unsigned long long* rng_state, unsigned int salt, void* stream);
+/* out = x + dropout(r): tail of ResidualConnection model/blocks.py:142-144 for arbitrary sublayers. */
+int bmhrl_dropout_add_f32(const float* x, const float* r, float* out, long long n, float drop_p,
+                          const unsigned long long* rng_state, unsigned int salt, void* stream);
+int bmhrl_dropout_apply_f32(const float* dy, float* dx, long long n, float drop_p, const unsigned long long* rng_state,
+                            unsigned int salt, void* stream);
+/* Manager.expand_goals model/bm_hrl_agent.py:415-429 without the host loop; map (B,L) int32 is saved for bwd. */
+int bmhrl_goal_expand_fwd_f32(const float* x, const int* seg, int* map, float* out, int B, int L, int D, void* stream);
+int bmhrl_goal_expand_bwd_f32(const float* dy, const int* map, float* dx, int B, int L, int D, void* stream);
+/* manager branch of biased_kl() epoch_loops/captioning_bmrl_loops.py:299-317. */
+int bmhrl_segment_scan_fwd_f32(const float* probs, const float* expected, const int* seg, float* seg_prob,
+                               float* expected_out, int B, int L, void* stream);
+int bmhrl_segment_scan_bwd_f32(const float* probs, const int* seg, const float* g, float* dprobs, int B, int L,
+                               void* stream);
+/* torch.optim.Adam (scripts/train_rl_captioning_module.py:81-83), one launch for all tensors.  The pointer tables,
+ * numels and chunk tables live in device memory; chunk c covers elements [chunk_start[c], +bmhrl_adam_chunk_elems())
+ * of tensor chunk_tensor[c].  step_counts: one device float per tensor holding its (already incremented) step
+ * number -- torch keeps a step per parameter and skips parameters that have no gradient in a phase. */
+int bmhrl_adam_chunk_elems(void);
+int bmhrl_adam_multi_f32(float* const* params, const float* const* grads, float* const* exp_avg,
+                         float* const* exp_avg_sq, const long long* numels, const int* chunk_tensor,
+                         const int* chunk_start, int n_chunks, const float* step_counts, float lr, float beta1,
+                         float beta2, float eps, float grad_scale, void* stream);
+/* step_counts[active_tensors[i]] += 1 for i < n_active (active_tensors NULL = identity) and rng_state[1] += 1, on
+ * the device; step_counts / rng_state may be NULL. */
+int bmhrl_tick(float* step_counts, const int* active_tensors, int n_active, unsigned long long* rng_state,
+               void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BMHRL_B200_H */
