@@ -54,6 +54,45 @@ __global__ void add_posenc_kernel(const float* __restrict__ x, const float* __re
     }
 }
 
+// scalar variant for feature sizes that are not a multiple of 4 (same RNG indexing: element i -> counter i)
+__global__ void add_posenc_scalar_kernel(const float* __restrict__ x, const float* __restrict__ x2,
+                                         const float* __restrict__ pe, float* __restrict__ out, long long rows, int S,
+                                         int D, float drop_p, const unsigned long long* __restrict__ rng,
+                                         unsigned int salt) {
+    const long long n = rows * D;
+    const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D;
+        int d = (int)(i % D);
+        float v = x[i] + (x2 ? x2[i] : 0.f) + pe[(long long)(r % S) * D + d];
+        if (drop_p > 0.f) v = dropout_keep(rng, salt, (unsigned long long)i, drop_p) ? v * ks : 0.f;
+        out[i] = v;
+    }
+}
+
+// out[r, :Da] = a[r, :], out[r, Da:] = b[r, :]   (torch.cat([x, goal_completion], -1), model/bm_hrl_agent.py:483)
+__global__ void concat2_kernel(const float* __restrict__ a, int Da, const float* __restrict__ b, int Db,
+                               float* __restrict__ out, long long rows) {
+    const int D = Da + Db;
+    const long long n = rows * D;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D;
+        int d = (int)(i % D);
+        out[i] = d < Da ? a[r * Da + d] : b[r * Db + (d - Da)];
+    }
+}
+__global__ void split2_kernel(const float* __restrict__ g, float* __restrict__ da, int Da, float* __restrict__ db,
+                              int Db, long long rows) {
+    const int D = Da + Db;
+    const long long n = rows * D;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        long long r = i / D;
+        int d = (int)(i % D);
+        if (d < Da) { if (da) da[r * Da + d] = g[i]; }
+        else if (db) db[r * Db + (d - Da)] = g[i];
+    }
+}
+
 // dx = keep ? dy / (1-p) : 0 with the flat element index as RNG counter
 __global__ void dropout_apply_kernel(const float* __restrict__ dy, float* __restrict__ dx, long long n, float drop_p,
                                      const unsigned long long* __restrict__ rng, unsigned int salt) {
@@ -107,14 +146,54 @@ __global__ void goal_map_kernel(const int* __restrict__ seg, int* __restrict__ m
     }
 }
 
-__global__ void goal_gather_kernel(const float* __restrict__ x, const int* __restrict__ map, float* __restrict__ out,
-                                   long long rows, int L, int D) {
+__global__ void goal_gather_kernel(const float* __restrict__ x, const float* __restrict__ noise,
+                                   const int* __restrict__ map, float* __restrict__ out, long long rows, int L, int D) {
     const long long n = rows * D;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         long long r = i / D;
         int d = (int)(i % D);
         int m = map[r];
-        out[i] = m < 0 ? 0.f : x[((r / L) * L + m) * D + d];
+        out[i] = m < 0 ? 0.f : x[((r / L) * L + m) * D + d] + (noise ? noise[d] : 0.f);
+    }
+}
+
+// Manager exploration noise (model/bm_hrl_agent.py:444-452): mean / std over ALL (non-NaN) elements of the goal
+// tensor, noise[j] = N(mean/10, std/5) - 0.5 * mean/10, one d_goal vector shared by every position.  eps: optional
+// explicit N(0,1) draws (tests); otherwise Box-Muller over Philox.  Single CTA (the tensor is B*L*64 floats).
+__global__ void __launch_bounds__(1024) exploration_noise_kernel(const float* __restrict__ x, long long n, int d_goal,
+                                                                 const float* __restrict__ eps, float* __restrict__ noise,
+                                                                 float* __restrict__ stats,
+                                                                 const unsigned long long* __restrict__ rng,
+                                                                 unsigned int salt) {
+    __shared__ float red[32];
+    float s = 0.f, c = 0.f;
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+        float v = x[i];
+        if (v == v) { s += v; c += 1.f; }
+    }
+    s = block_sum(s, red);
+    c = block_sum(c, red);
+    const float mean = s / c;
+    float q = 0.f;
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+        float v = x[i];
+        if (v == v) { float d = fabsf(v - mean); q += d * d; }
+    }
+    q = block_sum(q, red);
+    const float stdv = sqrtf(q / c);
+    const float mu = mean / 10.f, sd = stdv / 5.f;
+    if (threadIdx.x == 0 && stats) { stats[0] = mean; stats[1] = stdv; }
+    for (int j = threadIdx.x; j < d_goal; j += blockDim.x) {
+        float z;
+        if (eps) {
+            z = eps[j];
+        } else {
+            Philox4 r = philox_block(rng, salt, (unsigned long long)j);
+            float u1 = ((float)(r.x >> 8) + 1.f) * (1.0f / 16777216.0f);  // (0,1]
+            float u2 = u32_to_unit(r.y);
+            z = sqrtf(-2.f * logf(u1)) * cosf(6.283185307179586f * u2);
+        }
+        noise[j] = mu + sd * z - 0.5f * mu;
     }
 }
 
@@ -306,11 +385,15 @@ extern "C" int bmhrl_add_posenc_f32(const float* x, const float* x2, const float
                                     int S, int D, float drop_p, const unsigned long long* rng_state,
                                     unsigned int salt, void* stream) {
     BMHRL_CHECK_ARG(x && pe && out, "bmhrl_add_posenc_f32: null pointer");
-    BMHRL_CHECK_ARG(rows >= 0 && S > 0 && D > 0 && D % 4 == 0, "bmhrl_add_posenc_f32: D must be a multiple of 4");
-    BMHRL_CHECK_ARG(aligned16(x) && aligned16(pe) && aligned16(out) && (!x2 || aligned16(x2)),
-                    "bmhrl_add_posenc_f32: pointers must be 16-byte aligned");
+    BMHRL_CHECK_ARG(rows >= 0 && S > 0 && D > 0, "bmhrl_add_posenc_f32: bad sizes");
     BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || rng_state), "bmhrl_add_posenc_f32: dropout");
     if (rows == 0) return BMHRL_OK;
+    if (D % 4 != 0 || !(aligned16(x) && aligned16(pe) && aligned16(out) && (!x2 || aligned16(x2)))) {
+        add_posenc_scalar_kernel<<<grid_for(rows * D, 256), 256, 0, (cudaStream_t)stream>>>(x, x2, pe, out, rows, S, D,
+                                                                                            drop_p, rng_state, salt);
+        BMHRL_POST_LAUNCH("add_posenc_scalar");
+        return BMHRL_OK;
+    }
     add_posenc_kernel<<<grid_for(rows * D / 4, 256), 256, 0, (cudaStream_t)stream>>>(x, x2, pe, out, rows, S, D, drop_p,
                                                                                      rng_state, salt);
     BMHRL_POST_LAUNCH("add_posenc");
@@ -338,6 +421,23 @@ extern "C" int bmhrl_dropout_add_f32(const float* x, const float* r, float* out,
     return BMHRL_OK;
 }
 
+extern "C" int bmhrl_concat2_f32(const float* a, int Da, const float* b, int Db, float* out, long long rows,
+                                 void* stream) {
+    BMHRL_CHECK_ARG(a && b && out && Da > 0 && Db > 0 && rows >= 0, "bmhrl_concat2_f32: bad arguments");
+    if (rows == 0) return BMHRL_OK;
+    concat2_kernel<<<grid_for(rows * (Da + Db), 256), 256, 0, (cudaStream_t)stream>>>(a, Da, b, Db, out, rows);
+    BMHRL_POST_LAUNCH("concat2");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_split2_f32(const float* g, float* da, int Da, float* db, int Db, long long rows, void* stream) {
+    BMHRL_CHECK_ARG(g && (da || db) && Da > 0 && Db > 0 && rows >= 0, "bmhrl_split2_f32: bad arguments");
+    if (rows == 0) return BMHRL_OK;
+    split2_kernel<<<grid_for(rows * (Da + Db), 256), 256, 0, (cudaStream_t)stream>>>(g, da, Da, db, Db, rows);
+    BMHRL_POST_LAUNCH("split2");
+    return BMHRL_OK;
+}
+
 extern "C" int bmhrl_embed_bwd_f32(const long long* tokens, const float* g, float* dW, long long rows, int D,
                                    float scale, void* stream) {
     BMHRL_CHECK_ARG(tokens && g && dW && rows >= 0 && D > 0, "bmhrl_embed_bwd_f32: bad arguments");
@@ -347,14 +447,26 @@ extern "C" int bmhrl_embed_bwd_f32(const long long* tokens, const float* g, floa
     return BMHRL_OK;
 }
 
-extern "C" int bmhrl_goal_expand_fwd_f32(const float* x, const int* seg, int* map, float* out, int B, int L, int D,
-                                         void* stream) {
+extern "C" int bmhrl_exploration_noise_f32(const float* x, long long n, int d_goal, const float* eps_normal,
+                                           float* noise, float* stats, const unsigned long long* rng_state,
+                                           unsigned int salt, void* stream) {
+    BMHRL_CHECK_ARG(x && noise && n > 0 && d_goal > 0, "bmhrl_exploration_noise_f32: bad arguments");
+    BMHRL_CHECK_ARG(eps_normal || rng_state, "bmhrl_exploration_noise_f32: needs explicit draws or rng_state");
+    exploration_noise_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, d_goal, eps_normal, noise, stats, rng_state,
+                                                                   salt);
+    BMHRL_POST_LAUNCH("exploration_noise");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_goal_expand_fwd_f32(const float* x, const float* noise, const int* seg, int* map, float* out,
+                                         int B, int L, int D, void* stream) {
     BMHRL_CHECK_ARG(x && seg && map && out && B > 0 && L > 0 && D > 0, "bmhrl_goal_expand_fwd_f32: bad arguments");
     BMHRL_CHECK_ARG(B <= 8192, "bmhrl_goal_expand_fwd_f32: B too large for the single-CTA scan");
     cudaStream_t st = (cudaStream_t)stream;
     goal_map_kernel<<<1, 256, B * sizeof(int), st>>>(seg, map, B, L);
     BMHRL_POST_LAUNCH("goal_map");
-    goal_gather_kernel<<<grid_for((long long)B * L * D, 256), 256, 0, st>>>(x, map, out, (long long)B * L, L, D);
+    goal_gather_kernel<<<grid_for((long long)B * L * D, 256), 256, 0, st>>>(x, noise, map, out, (long long)B * L, L,
+                                                                           D);
     BMHRL_POST_LAUNCH("goal_gather");
     return BMHRL_OK;
 }

@@ -1,0 +1,175 @@
+// Frozen SegmentCritic recurrences (model/bm_hrl_agent.py:186-215): nn.LSTM(300->600, 4 layers) -> AReLU ->
+// nn.GRU(600->600, 2 layers) -> AReLU -> Linear(600->1), then sigmoid > threshold -> int32 segment labels
+// (model/bm_hrl_agent.py:638-640).  Forward only (the critic runs under no_grad) and exact fp32: the labels are
+// integers that must match the reference bit for bit, so nothing here uses reduced precision or fast-math.
+//
+// The input contribution gx = x W_ih^T + b_ih of ALL time steps is one GEMM (bmhrl_linear_fwd_f32); the recurrent
+// part is one fused kernel per time step: h_{t-1} W_hh^T, the gate non-linearities and the state update.  One
+// warp owns one hidden unit (its 4 / 3 gate rows of W_hh, read once, coalesced) for up to 16 batch rows whose
+// h_{t-1} sits in shared memory.
+#include "common.cuh"
+#include "../../include/bmhrl_b200.h"
+
+namespace bmhrl {
+
+constexpr int RNN_BT = 16;     // batch rows per block
+constexpr int RNN_WARPS = 8;   // hidden units per block
+
+__device__ __forceinline__ float sigmoid_exact(float x) { return 1.f / (1.f + expf(-x)); }
+
+// NG = 4: LSTM (gate order i,f,g,o; b_hh added to the pre-activations); NG = 3: GRU (r,z,n; b_hh inside r*(...)).
+template <int NG>
+__global__ void __launch_bounds__(RNN_WARPS * 32) rnn_step_kernel(const float* __restrict__ gx,    // (B,L,NG*H)
+                                                                 const float* __restrict__ W_hh,  // (NG*H,H)
+                                                                 const float* __restrict__ b_hh,  // (NG*H)
+                                                                 float* __restrict__ out,         // (B,L,H)
+                                                                 float* __restrict__ c,           // (B,H) LSTM only
+                                                                 int B, int L, int H, int t) {
+    extern __shared__ float hs[];  // RNN_BT x H
+    const int b0 = blockIdx.y * RNN_BT;
+    const int nb = min(RNN_BT, B - b0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int j = blockIdx.x * RNN_WARPS + warp;
+    if (t > 0) {
+        for (int i = threadIdx.x; i < RNN_BT * H; i += blockDim.x) {
+            int bb = i / H, k = i - bb * H;
+            hs[i] = bb < nb ? out[((long long)(b0 + bb) * L + (t - 1)) * H + k] : 0.f;
+        }
+    }
+    __syncthreads();
+    if (j >= H) return;
+    float acc[NG][RNN_BT];
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+        for (int bb = 0; bb < RNN_BT; ++bb) acc[g][bb] = 0.f;
+    if (t > 0) {
+        for (int k = lane; k < H; k += 32) {
+            float w[NG];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) w[g] = W_hh[((long long)g * H + j) * H + k];
+#pragma unroll
+            for (int bb = 0; bb < RNN_BT; ++bb) {
+                float hv = hs[bb * H + k];
+#pragma unroll
+                for (int g = 0; g < NG; ++g) acc[g][bb] = fmaf(w[g], hv, acc[g][bb]);
+            }
+        }
+    }
+    float mine[NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) mine[g] = 0.f;
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+        for (int bb = 0; bb < RNN_BT; ++bb) {
+            float s = warp_sum(acc[g][bb]);
+            if (lane == bb) mine[g] = s;
+        }
+    if (lane >= nb) return;
+    const int b = b0 + lane;
+    const float* gxr = gx + ((long long)b * L + t) * (NG * H);
+    float hprev = t > 0 ? hs[lane * H + j] : 0.f;
+    float hnew;
+    if (NG == 4) {
+        float pi = gxr[j] + b_hh[j] + mine[0];
+        float pf = gxr[H + j] + b_hh[H + j] + mine[1];
+        float pg = gxr[2 * H + j] + b_hh[2 * H + j] + mine[2];
+        float po = gxr[3 * H + j] + b_hh[3 * H + j] + mine[NG - 1];
+        float cprev = t > 0 ? c[(long long)b * H + j] : 0.f;
+        float cn = sigmoid_exact(pf) * cprev + sigmoid_exact(pi) * tanhf(pg);
+        c[(long long)b * H + j] = cn;
+        hnew = sigmoid_exact(po) * tanhf(cn);
+    } else {
+        float r = sigmoid_exact(gxr[j] + mine[0] + b_hh[j]);
+        float z = sigmoid_exact(gxr[H + j] + mine[1] + b_hh[H + j]);
+        float n = tanhf(gxr[2 * H + j] + r * (mine[2] + b_hh[2 * H + j]));
+        hnew = (1.f - z) * n + z * hprev;
+    }
+    out[((long long)b * L + t) * H + j] = hnew;
+}
+
+// AReLU (model/bm_hrl_agent.py:13-23): relu(x) * (1 + sigmoid(beta)) - relu(-x) * clamp(alpha, 0.01, 0.99)
+__global__ void arelu_kernel(const float* __restrict__ x, const float* __restrict__ alpha_p,
+                             const float* __restrict__ beta_p, float* __restrict__ y, long long n) {
+    const float alpha = fminf(fmaxf(alpha_p[0], 0.01f), 0.99f);
+    const float beta = 1.f + sigmoid_exact(beta_p[0]);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float v = x[i];
+        y[i] = fmaxf(v, 0.f) * beta - fmaxf(-v, 0.f) * alpha;
+    }
+}
+
+// score = x . w + b (one warp per row); label = sigmoid(score) > thr.
+__global__ void __launch_bounds__(128) segment_label_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                            const float* __restrict__ b, float thr,
+                                                            float* __restrict__ scores, int* __restrict__ labels,
+                                                            long long rows, int D) {
+    const long long row = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const float* xr = x + row * D;
+    float s = 0.f;
+    for (int k = lane; k < D; k += 32) s = fmaf(xr[k], w[k], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+        s += b[0];
+        if (scores) scores[row] = s;
+        labels[row] = sigmoid_exact(s) > thr ? 1 : 0;
+    }
+}
+
+}  // namespace bmhrl
+
+using namespace bmhrl;
+
+extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out,
+                                   float* c_ws, int B, int L, int H, void* stream) {
+    BMHRL_CHECK_ARG(cell == 0 || cell == 1, "bmhrl_rnn_layer_f32: cell must be 0 (LSTM) or 1 (GRU)");
+    BMHRL_CHECK_ARG(gx && W_hh && b_hh && out, "bmhrl_rnn_layer_f32: null pointer");
+    BMHRL_CHECK_ARG(cell == 1 || c_ws, "bmhrl_rnn_layer_f32: LSTM needs the (B,H) cell-state workspace");
+    BMHRL_CHECK_ARG(B >= 0 && L >= 0 && H > 0, "bmhrl_rnn_layer_f32: bad sizes");
+    if (B == 0 || L == 0) return BMHRL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t smem = (size_t)RNN_BT * H * sizeof(float);
+    BMHRL_CHECK_ARG(smem <= 200 * 1024, "bmhrl_rnn_layer_f32: hidden size too large");
+    static bool attr_set[2] = {false, false};
+    if (smem > 48 * 1024 && !attr_set[cell]) {
+        cudaError_t e = cell == 0 ? cudaFuncSetAttribute(rnn_step_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                         200 * 1024)
+                                  : cudaFuncSetAttribute(rnn_step_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                         200 * 1024);
+        if (e != cudaSuccess) {
+            bmhrl_set_error(cudaGetErrorString(e));
+            return BMHRL_ERR_CUDA;
+        }
+        attr_set[cell] = true;
+    }
+    dim3 grid((H + RNN_WARPS - 1) / RNN_WARPS, (B + RNN_BT - 1) / RNN_BT);
+    for (int t = 0; t < L; ++t) {
+        if (cell == 0) rnn_step_kernel<4><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, c_ws, B, L, H, t);
+        else rnn_step_kernel<3><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, nullptr, B, L, H, t);
+        BMHRL_POST_LAUNCH("rnn_step");
+    }
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_arelu_f32(const float* x, const float* alpha, const float* beta, float* y, long long n,
+                               void* stream) {
+    BMHRL_CHECK_ARG(x && alpha && beta && y && n >= 0, "bmhrl_arelu_f32: bad argument");
+    if (n == 0) return BMHRL_OK;
+    int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
+    arelu_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, alpha, beta, y, n);
+    BMHRL_POST_LAUNCH("arelu");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_segment_labels_f32(const float* x, const float* w, const float* b, float threshold, float* scores,
+                                        int* labels, long long rows, int D, void* stream) {
+    BMHRL_CHECK_ARG(x && w && b && labels && rows >= 0 && D > 0, "bmhrl_segment_labels_f32: bad argument");
+    if (rows == 0) return BMHRL_OK;
+    segment_label_kernel<<<(unsigned)((rows + 3) / 4), 128, 0, (cudaStream_t)stream>>>(x, w, b, threshold, scores,
+                                                                                       labels, rows, D);
+    BMHRL_POST_LAUNCH("segment_labels");
+    return BMHRL_OK;
+}

@@ -471,15 +471,20 @@ def reinforce_log_prob(probs, action, eps=1e-5):
 _PE_CACHE = {}
 
 
+def positional_table_f64(seq_len, d_model):
+    """model/blocks.py:95-103: fp64 table; column j uses exponent j/d_model itself (even j sin, odd j cos)."""
+    pos = torch.arange(seq_len, dtype=torch.float64)[:, None]
+    j = torch.arange(d_model, dtype=torch.float64)[None, :]
+    ang = pos / torch.pow(torch.tensor(10000.0, dtype=torch.float64), j / d_model)
+    even = (torch.arange(d_model) % 2 == 0)[None, :]
+    return torch.where(even, torch.sin(ang), torch.cos(ang))
+
+
 def positional_table(seq_len, d_model, device):
     """fp64 table of model/blocks.py:95-103 cast to fp32 (exactly what `.type_as(x)` yields), cached per device."""
     key = (seq_len, d_model, str(device))
     if key not in _PE_CACHE:
-        pos = torch.arange(seq_len, dtype=torch.float64)[:, None]
-        j = torch.arange(d_model, dtype=torch.float64)[None, :]
-        ang = pos / torch.pow(torch.tensor(10000.0, dtype=torch.float64), j / d_model)
-        even = (torch.arange(d_model) % 2 == 0)[None, :]
-        _PE_CACHE[key] = torch.where(even, torch.sin(ang), torch.cos(ang)).to(_F32).to(device).contiguous()
+        _PE_CACHE[key] = positional_table_f64(seq_len, d_model).to(_F32).to(device).contiguous()
     return _PE_CACHE[key]
 
 
@@ -529,6 +534,71 @@ def embed_posenc(tokens, W, drop_p=0.0, salt=0, rng=None, max_len=3660):
     return _EmbedPos.apply(tokens, W, pe, math.sqrt(W.shape[1]), float(drop_p), int(salt), rng)
 
 
+class _Embed(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens, W, scale):
+        tokens = _c(tokens, "tokens", torch.int64)
+        W = _c(W, "embedding weight")
+        D = W.shape[1]
+        emb = torch.empty(tokens.shape + (D,), device=W.device, dtype=_F32)
+        LIB.call("bmhrl_embed_posenc_f32", _p(tokens), _p(W), None, _p(emb), None, tokens.numel(), 1, D, scale, 0.0,
+                 None, 0, _stream())
+        ctx.save_for_backward(tokens)
+        ctx.cfg = (scale, W.shape)
+        return emb
+
+    @staticmethod
+    def backward(ctx, g):
+        (tokens,) = ctx.saved_tensors
+        scale, wshape = ctx.cfg
+        if not ctx.needs_input_grad[1]:
+            return None, None, None
+        dW = torch.zeros(wshape, device=tokens.device, dtype=_F32)
+        LIB.call("bmhrl_embed_bwd_f32", _p(tokens), _p(_c(g, "g")), _p(dW), tokens.numel(), wshape[1], scale, _stream())
+        return None, dW, None
+
+
+def embed(tokens, W, scale):
+    """VocabularyEmbedder model/blocks.py:44-48: W[tokens] * scale."""
+    return _Embed.apply(tokens, W, float(scale))
+
+
+class _Concat2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        a = _c(a, "a")
+        b = _c(b, "b")
+        Da, Db = a.shape[-1], b.shape[-1]
+        if a.shape[:-1] != b.shape[:-1]:
+            raise RuntimeError("concat_last: leading dimensions differ")
+        out = torch.empty(a.shape[:-1] + (Da + Db,), device=a.device, dtype=_F32)
+        LIB.call("bmhrl_concat2_f32", _p(a), Da, _p(b), Db, _p(out), a.numel() // Da, _stream())
+        ctx.dims = (Da, Db, a.shape, b.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        Da, Db, sa, sb = ctx.dims
+        g = _c(g, "g")
+        da = torch.empty(sa, device=g.device, dtype=_F32) if ctx.needs_input_grad[0] else None
+        db = torch.empty(sb, device=g.device, dtype=_F32) if ctx.needs_input_grad[1] else None
+        if da is not None or db is not None:
+            LIB.call("bmhrl_split2_f32", _p(g), _p(da), Da, _p(db), Db, g.numel() // (Da + Db), _stream())
+        return da, db
+
+
+def concat_last(a, b):
+    """torch.cat([a, b], dim=-1) (model/bm_hrl_agent.py:483)."""
+    return _Concat2.apply(a, b)
+
+
+def reinforce_loss(logp, value, critic_value):
+    """loss/biased_kl.py:76-80 on the (B,S) gathered log-probabilities: -mean(adv.detach * log pi) + mean(adv^2).
+    (B*S scalars: plain tensor arithmetic, the (B,S,V) gather is the kernel.)"""
+    adv = value - critic_value
+    return -torch.mean(adv.clone().detach().squeeze() * logp) + torch.mean(torch.pow(adv, 2))
+
+
 class _AddPosenc(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, x2, pe, drop_p, salt, rng):
@@ -559,8 +629,6 @@ def add_posenc(x, x2=None, drop_p=0.0, salt=0, rng=None, max_len=3660):
     """dropout(x (+ x2) + PE[:S]) -- PositionalEncoder.forward model/blocks.py:105-112 (x2 fuses rgb + flow)."""
     if x.dim() != 3:
         return x  # the reference leaves non-3D inputs untouched (blocks.py:106)
-    if x.shape[-1] % 4 != 0:
-        raise RuntimeError("add_posenc: feature size must be a multiple of 4")
     if x.shape[1] > max_len:
         raise RuntimeError("add_posenc: sequence longer than the positional table")
     pe = positional_table(max_len, x.shape[-1], x.device)
@@ -571,7 +639,7 @@ def add_posenc(x, x2=None, drop_p=0.0, salt=0, rng=None, max_len=3660):
 
 class _GoalExpand(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, seg):
+    def forward(ctx, x, seg, noise):
         x = _c(x, "x")
         seg = _c(seg, "segment labels", torch.int32)
         B, L, D = x.shape
@@ -579,7 +647,11 @@ class _GoalExpand(torch.autograd.Function):
             raise RuntimeError(f"expand_goals: segment labels must be (B,L)=({B},{L}), got {tuple(seg.shape)}")
         out = torch.empty_like(x)
         gmap = torch.empty(B, L, device=x.device, dtype=torch.int32)
-        LIB.call("bmhrl_goal_expand_fwd_f32", _p(x), _p(seg), _p(gmap), _p(out), B, L, D, _stream())
+        if noise is not None:
+            noise = _c(noise, "noise")
+            if noise.numel() != D:
+                raise RuntimeError("expand_goals: noise must have d_goal elements")
+        LIB.call("bmhrl_goal_expand_fwd_f32", _p(x), _p(noise), _p(seg), _p(gmap), _p(out), B, L, D, _stream())
         ctx.save_for_backward(gmap)
         ctx.shape = (B, L, D)
         return out
@@ -591,12 +663,63 @@ class _GoalExpand(torch.autograd.Function):
         g = _c(g, "g")
         dx = torch.empty_like(g)
         LIB.call("bmhrl_goal_expand_bwd_f32", _p(g), _p(gmap), _p(dx), B, L, D, _stream())
-        return dx, None
+        return dx, None, None
 
 
-def expand_goals(x, seg):
-    """Manager.expand_goals model/bm_hrl_agent.py:415-429 as one device-side scan (no host loop, no sync)."""
-    return _GoalExpand.apply(x, seg)
+def expand_goals(x, seg, noise=None):
+    """Manager.expand_goals model/bm_hrl_agent.py:415-429 as one device-side scan (no host loop, no sync), applied
+    to x + noise (the detached exploration vector of model/bm_hrl_agent.py:444-452) when noise is given."""
+    return _GoalExpand.apply(x, seg, noise)
+
+
+def exploration_noise(x, d_goal, eps_normal=None, salt=0, rng=None, return_stats=False):
+    """model/bm_hrl_agent.py:444-451: the shared d_goal noise vector N(mean/10, std/5) - 0.5*mean/10 (no grad)."""
+    x = _c(x.detach(), "x")
+    noise = torch.empty(d_goal, device=x.device, dtype=_F32)
+    stats = torch.empty(2, device=x.device, dtype=_F32) if return_stats else None
+    if eps_normal is None and rng is None:
+        rng = RNG.current(x.device)
+    if eps_normal is not None:
+        eps_normal = _c(eps_normal, "eps_normal")
+    LIB.call("bmhrl_exploration_noise_f32", _p(x), x.numel(), d_goal, _p(eps_normal), _p(noise), _p(stats),
+             _p(rng), int(salt), _stream())
+    return (noise, stats) if return_stats else noise
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# frozen SegmentCritic (forward only)
+# ----------------------------------------------------------------------------------------------------------------
+def rnn_layer(cell, x, w_ih, w_hh, b_ih, b_hh):
+    """One batch_first nn.LSTM ('lstm') / nn.GRU ('gru') layer with zero initial state, no autograd."""
+    x = _c(x, "x")
+    B, L, _ = x.shape
+    H = w_hh.shape[1]
+    with torch.no_grad():
+        gx = linear(x, w_ih, b_ih)
+        out = torch.empty(B, L, H, device=x.device, dtype=_F32)
+        c = torch.empty(B, H, device=x.device, dtype=_F32) if cell == "lstm" else None
+        LIB.call("bmhrl_rnn_layer_f32", 0 if cell == "lstm" else 1, _p(gx), _p(_c(w_hh, "w_hh")), _p(_c(b_hh, "b_hh")),
+                 _p(out), _p(c), B, L, H, _stream())
+    return out
+
+
+def arelu(x, alpha, beta):
+    x = _c(x, "x")
+    y = torch.empty_like(x)
+    LIB.call("bmhrl_arelu_f32", _p(x), _p(_c(alpha, "alpha")), _p(_c(beta, "beta")), _p(y), x.numel(), _stream())
+    return y
+
+
+def segment_labels(x, w, b, threshold):
+    """Linear(D->1) + sigmoid > threshold (model/bm_hrl_agent.py:213,638-640) -> (scores (B,L,1), labels int32 (B,L))."""
+    x = _c(x, "x")
+    D = x.shape[-1]
+    rows = x.numel() // D
+    scores = torch.empty(x.shape[:-1] + (1,), device=x.device, dtype=_F32)
+    labels = torch.empty(x.shape[:-1], device=x.device, dtype=torch.int32)
+    LIB.call("bmhrl_segment_labels_f32", _p(x), _p(_c(w, "w")), _p(_c(b, "b")), float(threshold), _p(scores),
+             _p(labels), rows, D, _stream())
+    return scores, labels
 
 
 class _SegmentScan(torch.autograd.Function):

@@ -1,0 +1,201 @@
+"""Training steps of the BMHRL hot path on one B200 (per data-parallel rank).
+
+Restates the bodies of the reference's epoch loops as fixed-shape device programs:
+  * warm-start step  epoch_loops/captioning_bmrl_loops.py:1148-1160  (fwd + LabelSmoothing + bwd + Adam)
+  * RL step          epoch_loops/captioning_bmrl_loops.py:837-877    (fwd + value fn + biased_kl() + BiasedKL +
+                     bwd + Adam + value-function MSE bwd + Adam), worker and manager phases (F4-free).
+The reward scorer (host Python n-gram code in the reference, metrics/cider.py) is OUTSIDE this path: a step takes
+the (B, L) score tensor as an input (synthetic rewards in the timed runs).
+
+Every step can be captured into ONE CUDA graph (`StepRunner.capture`): the library's entry points never
+synchronise or allocate, dropout/sampling counters and Adam step counts advance on the device.  No CPU fallback.
+"""
+import torch
+
+from . import ops
+from .loss.biased_kl import BiasedKL
+from .loss.label_smoothing import LabelSmoothing
+from .model.masking import make_masks
+
+# parameters the reference constructs but never calls: they never receive a gradient
+_NEVER_USED = (".feed_forward.fc", "manager_core.", "manager.core.")
+
+
+def used_parameters(model):
+    """model.parameters() minus the never-called ones, in registration order (named_parameters de-duplicates the
+    module that is registered twice, manager_core == manager.core)."""
+    return [p for n, p in model.named_parameters()
+            if not (("_fus." in n and ".feed_forward.fc" in n) or n.startswith("manager_core.")
+                    or n.startswith("manager.core."))]
+
+
+class BMHRLTrainer:
+    """Holds the agent, the two value functions, their fused Adam optimisers (torch.optim.Adam defaults,
+    scripts/train_rl_captioning_module.py:81-83) and the criteria (:66-67, :132)."""
+
+    def __init__(self, cap_model, wv_model, mv_model, pad_idx=1, smoothing=0.7, lr=1e-4, modality="audio_video",
+                 grad_sync=None):
+        self.cap_model, self.wv_model, self.mv_model = cap_model, wv_model, mv_model
+        self.pad_idx, self.modality = pad_idx, modality
+        self.ls = LabelSmoothing(smoothing, pad_idx)
+        self.bkl = BiasedKL(smoothing, pad_idx)
+        self.cap_opt = ops.FusedAdam(used_parameters(cap_model), lr=lr)
+        self.wv_opt = ops.FusedAdam(wv_model.parameters(), lr=lr)
+        self.mv_opt = ops.FusedAdam(mv_model.parameters(), lr=lr)
+        self.grad_sync = grad_sync  # data-parallel hook: callable(optimizer) all-reducing optimizer.flat_grad
+        self.loss_factor = 4.0 / 20.0  # captioning_bmrl_loops.py:831-833
+
+    # ---- phase switching (captioning_bmrl_loops.py:809-820, :1144) ------------------------------------------------
+    def teach_warmstart(self):
+        self.cap_model.train()
+        self.cap_model.teach_warmstart()
+        self.cap_opt.refresh_active()
+
+    def teach_worker(self):
+        self.cap_model.train()
+        self.wv_model.train()
+        self.cap_model.teach_worker()
+        self.cap_opt.refresh_active()
+
+    def teach_manager(self):
+        self.cap_model.train()
+        self.mv_model.train()
+        self.cap_model.teach_manager()
+        self.cap_opt.refresh_active()
+
+    # ---- pieces ------------------------------------------------------------------------------------------------------
+    def _inputs(self, batch):
+        """feature_getter (captioning_bmrl_loops.py:488-500) without the host-side token corruption."""
+        cap = batch["caption"]
+        cap_in, y = cap[:, :-1], cap[:, 1:]
+        masks = make_masks({"rgb": batch["rgb"], "flow": batch["flow"], "audio": batch["audio"]}, cap_in,
+                           self.modality, self.pad_idx)
+        return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y.contiguous(), masks
+
+    def _sync(self, opt):
+        if self.grad_sync is not None:
+            self.grad_sync(opt)
+
+    def _global_tokens(self, n_tokens):
+        """The reference computes the loss once over the gathered global batch (DataParallel), so the normaliser is
+        the GLOBAL token count; ranks contribute sum/global_n and gradients are summed."""
+        if self.grad_sync is not None and hasattr(self.grad_sync, "all_reduce_scalar"):
+            return self.grad_sync.all_reduce_scalar(n_tokens)
+        return n_tokens
+
+    # ---- warm-start step -------------------------------------------------------------------------------------------
+    def warmstart_step(self, batch):
+        """captioning_bmrl_loops.py:1148-1160.  Returns the scalar loss tensor (device)."""
+        ops.new_rng_epoch(batch["rgb"].device)
+        self.cap_opt.zero_grad()
+        x, cap_in, y, masks = self._inputs(batch)
+        pred = self.cap_model(x, cap_in, masks)[0]
+        n_tokens = self._global_tokens((y != self.pad_idx).sum())
+        loss = self.ls.row_sums(pred, y).sum() / n_tokens
+        loss.backward()
+        self._sync(self.cap_opt)
+        self.cap_opt.step()
+        return loss.detach()
+
+    # ---- RL step -----------------------------------------------------------------------------------------------------
+    def rl_losses(self, batch, train_worker, stabilize=False, exp_noise=None):
+        """Forward part of train_bimodal_bl (:843-862, :873-875): returns (cap_loss, value_loss, tokens, score)."""
+        x, cap_in, y, masks = self._inputs(batch)
+        pred, worker_feat, manager_feat, goal_feat, seg = self.cap_model(x, cap_in, masks)
+        loss_mask = y != self.pad_idx
+        n_tokens = self._global_tokens(loss_mask.sum())
+        if train_worker:
+            ev = self.wv_model((worker_feat.detach(), goal_feat.detach())).squeeze(-1)
+        else:
+            ev = self.mv_model(manager_feat.detach()).squeeze(-1)
+        # biased_kl() :271-334
+        score = batch["score"].to(pred.dtype)
+        lm = loss_mask.to(pred.dtype)
+        expected = ev.detach()
+        if train_worker:
+            mode = "noise" if exp_noise is not None else "philox"
+            tok, sp = ops.sample_tokens(pred, mode, exp_noise, salt=self._sample_salt())
+            norm = lm.sum(-1, keepdim=True)
+        else:
+            tok, sp = ops.sample_tokens(pred, "argmax")
+            segf = seg.to(pred.dtype)
+            norm = segf.sum(-1, keepdim=True)
+            score = score * segf
+            sp, expected = ops.segment_scan(sp, expected, seg)
+        if stabilize:
+            score = (score - expected) * lm
+        amplitude = torch.clamp(score * sp * norm, 0, 1)
+        div = self.bkl.row_sums(pred, y, tok, amplitude)
+        cap_loss = div.sum() / (n_tokens * self.loss_factor)
+        # value function :873-875; the reference's host loop wrote the segment sums INTO the value output (aliasing)
+        ev_used = ev if train_worker else ev + (expected - ev).detach()
+        vmask = lm if train_worker else seg.to(pred.dtype)
+        value_loss = (((ev_used - score.detach()) ** 2) * vmask).mean()
+        return cap_loss, value_loss, tok, score.detach(), div.detach()
+
+    def _sample_salt(self):
+        if not hasattr(self, "_ssalt"):
+            self._ssalt = ops.next_salt()
+        return self._ssalt
+
+    def rl_step(self, batch, train_worker, stabilize=False, exp_noise=None):
+        """captioning_bmrl_loops.py:837-877.  Returns (cap_loss, value_loss) device scalars."""
+        ops.new_rng_epoch(batch["rgb"].device)
+        vopt = self.wv_opt if train_worker else self.mv_opt
+        self.cap_opt.zero_grad()
+        vopt.zero_grad()
+        cap_loss, value_loss, _, _, _ = self.rl_losses(batch, train_worker, stabilize, exp_noise)
+        cap_loss.backward()
+        self._sync(self.cap_opt)
+        self.cap_opt.step()
+        value_loss.backward()
+        self._sync(vopt)
+        vopt.step()
+        return cap_loss.detach(), value_loss.detach()
+
+
+class StepRunner:
+    """One training step as a CUDA graph over static input buffers.
+
+    `step(host_batch)` copies the pinned host batch into the static device buffers (H2D), replays the graph and
+    returns the device loss tensors; `replay()` re-runs the step on whatever the buffers hold."""
+
+    def __init__(self, trainer, kind, example_batch, stabilize=False, use_graph=True, warmup=3):
+        self.trainer, self.kind, self.stabilize = trainer, kind, stabilize
+        dev = next(trainer.cap_model.parameters()).device
+        self.static = {k: torch.empty_like(v, device=dev).copy_(v) for k, v in example_batch.items()
+                       if k in ("rgb", "flow", "audio", "caption", "score")}
+        self.graph = None
+        self.out = None
+        if use_graph:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(warmup):  # lazily-created salts / workspaces / cuBLAS-free paths settle here
+                    self._eager()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.out = self._eager()
+
+    def _eager(self):
+        t = self.trainer
+        if self.kind == "warmstart":
+            return (t.warmstart_step(self.static),)
+        return t.rl_step(self.static, self.kind == "worker", self.stabilize)
+
+    def load(self, host_batch, non_blocking=True):
+        for k, buf in self.static.items():
+            buf.copy_(host_batch[k], non_blocking=non_blocking)
+
+    def replay(self):
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.out = self._eager()
+        return self.out
+
+    def step(self, host_batch):
+        self.load(host_batch)
+        return self.replay()

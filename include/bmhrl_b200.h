@@ -110,6 +110,18 @@ int bmhrl_reinforce_gather_fwd_f32(const float* probs, const long long* action, 
 int bmhrl_reinforce_gather_bwd_f32(const float* probs, const long long* action, const float* g, float* dprobs,
                                    long long rows, int V, float eps, void* stream);
 
+/* ---- frozen SegmentCritic recurrences, forward only (rnn.cu) ------------------------------------------------- */
+/* One nn.LSTM (cell 0, gates i,f,g,o) or nn.GRU (cell 1, gates r,z,n) layer, batch_first, zero initial state
+ * (model/bm_hrl_agent.py:192-193,206,209).  gx (B,L,NG*H) = x W_ih^T + b_ih for all steps (bmhrl_linear_fwd_f32);
+ * out (B,L,H); c_ws (B,H) cell-state workspace (LSTM only).  Launches L kernels. */
+int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* c_ws, int B,
+                        int L, int H, void* stream);
+/* AReLU model/bm_hrl_agent.py:13-23 (alpha, beta: device scalars). */
+int bmhrl_arelu_f32(const float* x, const float* alpha, const float* beta, float* y, long long n, void* stream);
+/* scores[row] = x[row,:] . w + b; labels[row] = sigmoid(score) > threshold (model/bm_hrl_agent.py:213,638-640). */
+int bmhrl_segment_labels_f32(const float* x, const float* w, const float* b, float threshold, float* scores,
+                             int* labels, long long rows, int D, void* stream);
+
 /* ---- K6 / K7 and step plumbing (misc.cu) --------------------------------------------------------------------- */
 /* emb = W[tok]*scale (model/blocks.py:44-48); pos = dropout(emb + pe[l]) (model/blocks.py:105-112). */
 int bmhrl_embed_posenc_f32(const long long* tokens, const float* W, const float* pe, float* emb, float* pos,
@@ -120,13 +132,23 @@ int bmhrl_embed_bwd_f32(const long long* tokens, const float* g, float* dW, long
 /* out = dropout(x (+ x2) + pe[s]); x2 fuses V = rgb + flow (epoch_loops/captioning_bmrl_loops.py:498). */
 int bmhrl_add_posenc_f32(const float* x, const float* x2, const float* pe, float* out, long long rows, int S, int D,
                          float drop_p, const unsigned long long* rng_state, unsigned int salt, void* stream);
+/* out = cat([a, b], -1) (model/bm_hrl_agent.py:483) and its gradient split (da / db may be NULL). */
+int bmhrl_concat2_f32(const float* a, int Da, const float* b, int Db, float* out, long long rows, void* stream);
+int bmhrl_split2_f32(const float* g, float* da, int Da, float* db, int Db, long long rows, void* stream);
 /* out = x + dropout(r): tail of ResidualConnection model/blocks.py:142-144 for arbitrary sublayers. */
 int bmhrl_dropout_add_f32(const float* x, const float* r, float* out, long long n, float drop_p,
                           const unsigned long long* rng_state, unsigned int salt, void* stream);
 int bmhrl_dropout_apply_f32(const float* dy, float* dx, long long n, float drop_p, const unsigned long long* rng_state,
                             unsigned int salt, void* stream);
-/* Manager.expand_goals model/bm_hrl_agent.py:415-429 without the host loop; map (B,L) int32 is saved for bwd. */
-int bmhrl_goal_expand_fwd_f32(const float* x, const int* seg, int* map, float* out, int B, int L, int D, void* stream);
+/* Manager exploration noise model/bm_hrl_agent.py:444-452: noise[j] = N(mean/10, std/5) - 0.5*mean/10 with mean/std
+ * over all non-NaN elements of x (n floats); eps_normal: optional explicit N(0,1) draws (d_goal), else Philox;
+ * stats (optional): {mean, std}. */
+int bmhrl_exploration_noise_f32(const float* x, long long n, int d_goal, const float* eps_normal, float* noise,
+                                float* stats, const unsigned long long* rng_state, unsigned int salt, void* stream);
+/* Manager.expand_goals model/bm_hrl_agent.py:415-429 without the host loop, applied to x + noise (noise (D) may be
+ * NULL); map (B,L) int32 is saved for bwd. */
+int bmhrl_goal_expand_fwd_f32(const float* x, const float* noise, const int* seg, int* map, float* out, int B, int L,
+                              int D, void* stream);
 int bmhrl_goal_expand_bwd_f32(const float* dy, const int* map, float* dx, int B, int L, int D, void* stream);
 /* manager branch of biased_kl() epoch_loops/captioning_bmrl_loops.py:299-317. */
 int bmhrl_segment_scan_fwd_f32(const float* probs, const float* expected, const int* seg, float* seg_prob,
