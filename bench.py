@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- BMHRL train-step throughput (clips/s, B=16 per GPU) on N B200s, or the CPU reference arm.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload warmstart|worker|manager] [--impl reference]
+
+N > 1 is launched by torch.distributed.run (one rank per GPU, NCCL).  Prints ONE JSON line (rank 0).
+  value     device-timed whole-job clips/s, inputs resident in HBM, one CUDA-graph replay per step
+  e2e       same step through the public API (StepRunner.step) from pinned HOST buffers: H2D copies of the batch and
+            the D2H read of the loss inside the timed region
+  roofline  the dominant kernel class (projection / FFN / vocab / gradient GEMMs): the step's GEMM launches are
+            re-issued with their exact shapes and timed with CUDA events; achieved = algorithmic FLOPs / time
+  cpu_baseline  the oracle port of the reference step timed on this box's host cores (bounded sample)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+VOC, PAD, SMOOTH = 10172, 1, 0.7
+SHAPE = dict(B=16, Sv=30, Sa=80, L=20)  # SURVEY.md section 8 "C16"
+METRIC = "bmhrl_train_step_clips_per_sec"
+
+
+def cfg_ns(device):
+    from types import SimpleNamespace as NS
+    return NS(d_vid=1024, d_aud=128, d_model_video=1024, d_model_audio=128, d_model=1024, d_model_caps=300,
+              rl_projection_d=512, rl_att_heads=4, rl_att_layers=2, rl_goal_d=64, rl_ff_v=1024, rl_ff_a=512,
+              rl_ff_c=2048, dout_p=0.1, rl_critic_score_threshhold=0.25, unfreeze_word_emb=False, device=device,
+              device_ids=[torch.cuda.current_device()] if device == "cuda" else [0], rl_critic_path=None)
+
+
+def agent_shapes():
+    g = torch.load(os.path.join(ROOT, "tests", "golden", "reference_golden.pt"), weights_only=False)
+    return g["agent_shapes"], g["value_fn_shapes"]
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference arm
+def cpu_step_fn(workload, threads):
+    """The oracle port of the reference step (fwd + loss + bwd + Adam) on the host cores.  Checker code, timed only
+    as the reported CPU baseline."""
+    from oracle import bmhrl_oracle as O
+    from bmhrl_b200 import synth
+    torch.set_num_threads(threads)
+    shapes, vshapes = agent_shapes()
+    sd = synth.fill_state_dict(shapes, seed=1234)
+    b = synth.synthetic_batch(V=VOC, seed=1234, **SHAPE)
+    cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+    masks = O.make_masks(b["rgb"], b["audio"], cin, PAD)
+    frozen_w = ("bm_manager_fus.", "manager.")
+    frozen_m = ("bm_enc.", "bm_worker_fus.", "worker.")
+    state = {"params": {k: v.clone() for k, v in sd.items()}, "adam": {}}
+    vsd = synth.fill_state_dict(vshapes, seed=77)
+    vstate = {"params": {k: v.clone() for k, v in vsd.items()}, "adam": {}}
+
+    def trainable(k):
+        if k.startswith("critic.") or k.startswith("emb_C."):
+            return False
+        if workload == "worker":
+            return not k.startswith(frozen_w)
+        if workload == "manager":
+            return not k.startswith(frozen_m)
+        return True
+
+    def step():
+        p = {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point and trainable(k) else v)
+             for k, v in state["params"].items()}
+        pred, wf, mf, gf, seg = O.agent_forward(p, b["rgb"] + b["flow"], b["audio"], cin, masks)
+        if workload == "warmstart":
+            loss = O.label_smoothing_kl(pred, cy, SMOOTH, PAD).sum() / (cy != PAD).sum()
+            loss.backward()
+        else:
+            tw = workload == "worker"
+            pv = {k: v.clone().requires_grad_(True) for k, v in vstate["params"].items()}
+            ev = O.value_function(pv, (wf if tw else mf).detach()).squeeze(-1)
+            q = torch.empty(pred.shape).exponential_(1) if tw else None
+            lm = cy != PAD
+            div, score, tok, oexp = O.biased_kl_rl(pred, cy, b["score"].clone(), ev.detach(), lm, seg, tw, False,
+                                                   SMOOTH, PAD, q)
+            loss = div.sum() / (lm.sum() * 0.2)
+            loss.backward()
+            ev_used = ev + (oexp - ev).detach()
+            vl = (((ev_used - score.float()) ** 2) * (lm if tw else seg).float()).mean()
+            vl.backward()
+            vg = {k: v.grad for k, v in pv.items() if v.grad is not None}
+            vstate["params"], vstate["adam"] = O.adam_step({k: v.detach() for k, v in pv.items()}, vg, vstate["adam"])
+        grads = {k: v.grad for k, v in p.items() if torch.is_tensor(v) and v.requires_grad and v.grad is not None}
+        state["params"], state["adam"] = O.adam_step({k: v.detach() for k, v in p.items()}, grads, state["adam"])
+        return float(loss.detach())
+    return step
+
+
+def time_cpu(workload, steps, warmup, threads):
+    step = cpu_step_fn(workload, threads)
+    for _ in range(warmup):
+        step()
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        step()
+        ts.append(time.perf_counter() - t0)
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    med = time_cpu(args.workload, max(1, args.steps), max(1, args.warmup), threads)
+    val = SHAPE["B"] / med
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "clips/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": med * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.workload),
+            "cpu_baseline": {"value": val, "unit": "clips/s", "cores": threads, "kind": "port",
+                             "sample": f"{args.steps} full B=16 steps (median) of the oracle port of the reference "
+                                       f"step: fwd + loss + bwd + Adam, fp32, torch CPU, {threads} threads"},
+            "e2e": {"value": val, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(workload):
+    names = {"warmstart": "warm-start KL (label-smoothing) caption train step",
+             "worker": "BMHRL RL step, worker phase (REINFORCE-biased KL + value fn)",
+             "manager": "BMHRL RL step, manager phase (REINFORCE-biased KL + value fn)"}
+    return {"workload": f"{names[workload]}, B=16/GPU, Sv=30, Sa=80, L=20, V=10172, d_model=1024, H=4, N=2, "
+                        f"synthetic I3D(1024 rgb+flow)+VGGish(128), random-init BMHRL, dropout 0.1, Adam lr 1e-4",
+            "phase": workload, "batch_per_gpu": SHAPE["B"],
+            "l2": "no explicit flush: parameters + Adam state + gradients touched every step (~1 GB) exceed the 126 MB L2"}
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+class Clocks:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-i", str(index), "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [l.strip().split(", ") for l in open(self.f.name) if l.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], None, set()
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.strip().lower() == "active":
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def gemm_roofline(recorded, iters=20):
+    """Re-issues every GEMM launch of one training step (exact shapes/strides, scratch operands) and times the
+    sequence with CUDA events on the launching stream.  Returns (flops per launch, seconds per launch, n)."""
+    from bmhrl_b200 import ops
+    if not recorded:
+        return 0.0, 0.0, 0
+    dev = torch.device("cuda")
+    calls = []
+    flops = 0.0
+    span = lambda n, s: 1 + (n - 1) * s
+    for rec in recorded:
+        kind, M, N, K = rec[:4]
+        if min(M, N, K) <= 0:
+            continue
+        flops += 2.0 * M * N * K
+        if kind == "linear":
+            a, w, c = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev), torch.empty(M, N, device=dev)
+            calls.append((a, K, 1, w, 1, K, c, N, M, N, K))
+        else:
+            sAm, sAk, sBk, sBn, ldc = rec[4:]
+            a = torch.randn(span(M, sAm) + span(K, sAk), device=dev)
+            w = torch.randn(span(K, sBk) + span(N, sBn), device=dev)
+            c = torch.empty(M * ldc, device=dev)
+            calls.append((a, sAm, sAk, w, sBk, sBn, c, ldc, M, N, K))
+    torch.cuda.synchronize()
+
+    def run():
+        for a, sAm, sAk, w, sBk, sBn, c, ldc, M, N, K in calls:
+            ops.gemm(a, sAm, sAk, w, sBk, sBn, c, ldc, M, N, K)
+    with torch.no_grad():
+        for _ in range(3):
+            run()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) / 1e3 / iters
+    n = len(calls)
+    return flops / n, sec / n, n
+
+
+def run_gpu(args):
+    import torch.distributed as dist
+    from bmhrl_b200 import ops, synth, _lib
+    from bmhrl_b200.ddp import GradSync
+    from bmhrl_b200.model.bm_hrl_agent import BMHrlAgent, BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, StepRunner
+    from types import SimpleNamespace as NS
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.LIB.load()
+    assert _lib.LIB.raw("bmhrl_check_device")() == 0, _lib.LIB.raw("bmhrl_last_error")().decode()
+
+    shapes, vshapes = agent_shapes()
+    sd = synth.fill_state_dict(shapes, seed=1234)  # same weights on every rank (replicated, never broadcast)
+    cfg = cfg_ns("cuda")
+    ds = NS(trg_voc_size=VOC, train_vocab=NS(vectors=sd["emb_C.embedder.weight"].clone()), pad_idx=PAD, start_idx=2,
+            end_idx=3)
+    model = BMHrlAgent(cfg, ds)
+    model.load_state_dict(sd)
+    model = model.to(dev)
+    wv, mv = BMWorkerValueFunction(cfg), BMManagerValueFunction(cfg)
+    wv.load_state_dict(synth.fill_state_dict(vshapes, seed=77))
+    mv.load_state_dict(synth.fill_state_dict(vshapes, seed=78))
+    sync = GradSync() if world > 1 else None
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync)
+    {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[args.workload]()
+    ops.manual_seed(1234 + rank, dev)
+
+    # pinned host batches (a different one per rank and per step slot), H2D'd inside the e2e region
+    n_host = 4
+    host = []
+    for i in range(n_host):
+        b = synth.synthetic_batch(V=VOC, seed=1234 + rank + 1000 * i, **SHAPE)
+        host.append({k: b[k].pin_memory() for k in ("rgb", "flow", "audio", "caption", "score")})
+    h2d = sum(t.numel() * t.element_size() for t in host[0].values())
+
+    # shapes of the GEMM launches of one eager step (for the roofline section)
+    eager = StepRunner(tr, args.workload, host[0], use_graph=False)
+    eager.replay()
+    ops.RECORD = []
+    eager.replay()
+    per_step_gemms, ops.RECORD = ops.RECORD, None
+    del eager
+    runner = StepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value)
+    for _ in range(args.warmup):
+        runner.replay()
+    barrier()
+    _lib.reset_launch_count()
+    clocks = Clocks(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        runner.replay()
+    e1.record()
+    barrier()
+    sec = e0.elapsed_time(e1) / 1e3
+    # ---- end-to-end timing through the public step API with host buffers
+    for i in range(args.warmup):
+        float(runner.step(host[i % n_host])[0])
+    barrier()
+    t0 = time.perf_counter()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    last = 0.0
+    for i in range(args.steps):
+        last = float(runner.step(host[i % n_host])[0])  # D2H read of the step's loss (synchronises)
+    e3.record()
+    barrier()
+    sec_e2e = max(e2.elapsed_time(e3) / 1e3, 0.0)
+    wall_e2e = time.perf_counter() - t0
+    clk = clocks.stop() if clocks else None
+    launches_eager = _lib.launch_count()  # launches issued by python after capture (0 with graphs) ...
+    t = torch.tensor([sec, sec_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    sec, sec_e2e = float(t[0]), float(t[1])
+
+    if rank == 0:
+        pk, pk_src = peaks()
+        graph_launches = getattr(runner, "captured_launches", None)
+        fl, sl, ng = gemm_roofline(per_step_gemms)
+        ach = fl / sl / 1e12 if sl > 0 else 0.0
+        peak = pk["bf16_tflops_sustained"]
+        cpu_threads = os.cpu_count() or 1
+        cpu_med = time_cpu(args.workload, 5, 1, cpu_threads) if not args.no_cpu else None
+        clips = SHAPE["B"] * world * args.steps
+        line = {
+            "metric": METRIC, "value": clips / sec, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.workload),
+            "e2e": {"value": clips / sec_e2e, "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "ms_per_step": sec_e2e / args.steps * 1e3, "wall_ms_per_step": wall_e2e / args.steps * 1e3},
+            "gpu_launches": graph_launches * (2 * args.steps + args.warmup) if graph_launches else launches_eager,
+            "launches_per_step": graph_launches,
+            "clocks": clk,
+            "roofline": {"bound": "tensor", "kernel": "projection/FFN/vocab GEMMs (gemm_simt_kernel, fp32 SIMT)",
+                         "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
+                         "traffic": None, "peak_source": f"{pk_src} bf16_tflops_sustained",
+                         "launches_per_step": ng, "avg_launch_us": sl * 1e6, "flops_per_launch": fl},
+            "step_hbm_roofline": {"algorithmic_bytes": step_bytes(args.workload), "peak_gbs": pk["hbm_gbs"],
+                                  "frac": step_bytes(args.workload) / (sec / args.steps) / 1e9 / pk["hbm_gbs"]},
+            "loss": last,
+        }
+        if cpu_med is not None:
+            line["cpu_baseline"] = {"value": SHAPE["B"] / cpu_med, "unit": "clips/s", "cores": cpu_threads,
+                                    "kind": "port",
+                                    "sample": "5 full B=16 steps (median, 1 warm-up) of the oracle port of the "
+                                              "reference step on the host cores: fwd + loss + bwd + Adam, fp32"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def step_bytes(workload):
+    """SURVEY.md section 8(d) algorithmic bytes per step (weights fwd + 36 B per updated param + logits)."""
+    p_fwd = 62.33e6
+    p_upd = {"warmstart": 47.18e6, "worker": 37.50e6, "manager": 9.68e6}[workload]
+    return 4 * p_fwd + 36 * p_upd + 2 * 4 * SHAPE["B"] * SHAPE["L"] * VOC
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="warmstart", choices=["warmstart", "worker", "manager"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -93,8 +93,13 @@ def next_salt():
 # ----------------------------------------------------------------------------------------------------------------
 # contractions
 # ----------------------------------------------------------------------------------------------------------------
+RECORD = None  # bench.py: when a list, every GEMM launch appends its shape/stride tuple (roofline re-issue)
+
+
 def gemm(A, sAm, sAk, B, sBk, sBn, C, ldc, M, N, K, batch=1, Hdiv=1, bA=(0, 0), bB=(0, 0), bC=(0, 0), alpha=1.0,
          beta=0.0):
+    if RECORD is not None:
+        RECORD.append(("gemm", M, N, K, sAm, sAk, sBk, sBn, ldc))
     LIB.call("bmhrl_gemm_f32", _p(A), sAm, sAk, _p(B), sBk, sBn, _p(C), ldc, M, N, K, batch, Hdiv, bA[0], bA[1], bB[0],
              bB[1], bC[0], bC[1], alpha, beta, _stream())
 
@@ -117,6 +122,8 @@ class _Linear(torch.autograd.Function):
             if r.shape != y.shape:
                 raise RuntimeError("linear: residual shape mismatch")
         b = None if bias is None else _c(bias, "bias")
+        if RECORD is not None:
+            RECORD.append(("linear", M, N, K))
         LIB.call("bmhrl_linear_fwd_f32", _p(x), K, _p(weight), _p(b), _p(r), N, _p(y), N, M, N, K, act, drop_p,
                  _p(rng) if drop_p > 0 else None, salt, _stream())
         ctx.save_for_backward(x, weight, y if act == 1 else None, rng if drop_p > 0 else None)

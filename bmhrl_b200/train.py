@@ -72,9 +72,9 @@ class BMHRLTrainer:
                            self.modality, self.pad_idx)
         return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y.contiguous(), masks
 
-    def _sync(self, opt):
+    def _sync(self, opt, mean=False):
         if self.grad_sync is not None:
-            self.grad_sync(opt)
+            self.grad_sync(opt, mean=mean)
 
     def _global_tokens(self, n_tokens):
         """The reference computes the loss once over the gathered global batch (DataParallel), so the normaliser is
@@ -149,7 +149,7 @@ class BMHRLTrainer:
         self._sync(self.cap_opt)
         self.cap_opt.step()
         value_loss.backward()
-        self._sync(vopt)
+        self._sync(vopt, mean=True)  # the value loss is a .mean() over the global (B,L) batch (:874-875)
         vopt.step()
         return cap_loss.detach(), value_loss.detach()
 
@@ -175,9 +175,12 @@ class StepRunner:
                     self._eager()
             torch.cuda.current_stream(dev).wait_stream(side)
             torch.cuda.synchronize(dev)
+            from ._lib import launch_count, reset_launch_count
             self.graph = torch.cuda.CUDAGraph()
+            n0 = launch_count()
             with torch.cuda.graph(self.graph):
                 self.out = self._eager()
+            self.captured_launches = launch_count() - n0  # kernels of libbmhrl_b200 inside one graph replay
 
     def _eager(self):
         t = self.trainer

@@ -1,0 +1,183 @@
+"""GPU: the whole hot path (BMHrlAgent forward/backward, warm-start and RL training steps, greedy decode) against
+golden vectors produced by the UNMODIFIED reference, plus CUDA-graph and size-independent property checks."""
+import pytest
+import torch
+
+from oracle import bmhrl_oracle as O
+from bmhrl_b200 import synth
+from conftest import PAD, SMOOTH, VOC, build_agent, make_cfg, rel
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3
+
+
+def _dev(b):
+    return {k: v.cuda() for k, v in b.items()}
+
+
+def _check_grads(model, g, tol, names=None):
+    params = dict(model.named_parameters())
+    for n, gs in g["grad_slice"].items() if "grad_slice" in g else []:
+        gr = params[n].grad
+        assert gr is not None, n
+        if n.endswith("linear_K2d.bias"):
+            continue
+        gn = g["grad_norm"][n]
+        assert abs(float(gr.norm()) - gn) <= tol * gn + 1e-9, (n, float(gr.norm()), gn)
+        sl = gr.flatten()[:: max(1, gr.numel() // 64)][:64].cpu()
+        assert float((sl - gs).norm()) <= tol * gn + 1e-9, n
+
+
+@pytest.mark.parametrize("tag", ["small", "c16"])
+def test_agent_forward_backward_golden(gpu_lib, golden, agent_sd, tag):
+    from bmhrl_b200.model.masking import make_masks
+    from bmhrl_b200.loss.label_smoothing import LabelSmoothing
+    g = golden[f"agent_{tag}"]
+    c = g["cfg"]
+    model, _ = build_agent(agent_sd)
+    model.train()
+    model.teach_warmstart()
+    model.manager.exploration = False
+    b = _dev(synth.synthetic_batch(B=c["B"], Sv=c["Sv"], Sa=c["Sa"], L=c["L"], V=VOC, seed=c["seed"], ragged=c["ragged"]))
+    cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+    masks = make_masks(b, cin, "audio_video", PAD)
+    out = model((b["rgb"] + b["flow"], b["audio"]), cin, masks)
+    loss = torch.sum(LabelSmoothing(SMOOTH, PAD)(out[0], cy)) / (cy != PAD).sum()
+    loss.backward()
+    assert out[0].shape == (c["B"], c["L"], VOC)
+    assert torch.equal(out[4].cpu(), g["segment_labels"])
+    assert rel(out[0][:, :, ::101], g["pred_slice"]) < TOL
+    assert rel(out[1], g["worker_feat"]) < TOL and rel(out[2], g["manager_feat"]) < TOL
+    assert rel(out[3], g["goals"]) < TOL
+    assert rel(loss, g["loss"]) < TOL
+    _check_grads(model, g, TOL)
+    params = dict(model.named_parameters())
+    for n in g["never_grad"]:
+        assert params[n].grad is None, n
+    # fused (rgb, flow) input form gives the same result
+    out2 = model(((b["rgb"], b["flow"]), b["audio"]), cin, masks)
+    assert rel(out2[0], out[0]) < 1e-6
+
+
+@pytest.mark.parametrize("tag", ["worker_raw", "worker_stab", "manager_raw", "manager_stab"])
+def test_rl_step_golden(gpu_lib, golden, agent_sd, tag):
+    """train_bimodal_bl body (captioning_bmrl_loops.py:837-877) vs the reference: sampled tokens bit-exact,
+    divergence / losses / gradients within 1e-3."""
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer
+    g = golden[f"rl_{tag}"]
+    c = g["cfg"]
+    train_worker, stabilize = tag.startswith("worker"), tag.endswith("stab")
+    model, cfg = build_agent(agent_sd)
+    wv, mv = BMWorkerValueFunction(cfg), BMManagerValueFunction(cfg)
+    vsd = synth.fill_state_dict(golden["value_fn_shapes"], seed=c["vseed"])
+    (wv if train_worker else mv).load_state_dict(vsd)
+    tr = BMHRLTrainer(model, wv.cuda(), mv.cuda(), pad_idx=PAD, smoothing=SMOOTH)
+    if train_worker:
+        tr.teach_worker()
+    else:
+        tr.teach_manager()
+        model.manager.exploration = False
+    b = synth.synthetic_batch(B=c["B"], Sv=c["Sv"], Sa=c["Sa"], L=c["L"], V=VOC, seed=c["seed"], ragged=True)
+    b["score"] = b["score"] * c["score_scale"]
+    torch.manual_seed(c["noise_seed"])
+    q = torch.empty(c["B"] * c["L"], VOC).exponential_(1).view(c["B"], c["L"], VOC).cuda() if train_worker else None
+    tr.cap_opt.zero_grad()
+    (tr.wv_opt if train_worker else tr.mv_opt).zero_grad()
+    cap_loss, value_loss, tok, score, div = tr.rl_losses(_dev(b), train_worker, stabilize, q)
+    cap_loss.backward()
+    value_loss.backward()
+    assert torch.equal(tok.cpu(), g["tokens"])
+    assert rel(score, g["score"]) < TOL and rel(div, g["div_rowsum"]) < TOL
+    assert rel(cap_loss, g["cap_loss"]) < TOL and rel(value_loss, g["value_loss"]) < TOL
+    params = dict(model.named_parameters())
+    for n, gn in g["grad_norm"].items():
+        if n.endswith("linear_K2d.bias"):
+            continue
+        assert abs(float(params[n].grad.norm()) - gn) <= TOL * gn + 1e-9, n
+    vparams = dict((wv if train_worker else mv).named_parameters())
+    for n, gn in g["vgrad_norm"].items():
+        assert abs(float(vparams[n].grad.norm()) - gn) <= TOL * gn + 1e-9, n
+    # frozen side receives nothing
+    frozen = [n for n, p in params.items() if not p.requires_grad]
+    assert frozen and all(params[n].grad is None for n in frozen)
+
+
+def test_greedy_decode_golden(gpu_lib, golden, agent_sd):
+    """Config 1: single-clip greedy captioning of sample/women_long_jump (fp16-stored features), B=1, L=1 start."""
+    from bmhrl_b200.decode import greedy_decoder
+    g = golden["greedy"]
+    model, _ = build_agent(agent_sd)
+    model.eval()
+    model.set_inference_mode(True)
+    fs = {"rgb": g["rgb"].float().cuda(), "flow": g["flow"].float().cuda(), "audio": g["audio"].float().cuda()}
+    trg, last = greedy_decoder(model, fs, g["max_len"], 2, 3, PAD, "audio_video", return_last=True)
+    assert torch.equal(trg.cpu(), g["tokens_fp16in"])
+    assert rel(last[:, :, ::101], g["last_slice_fp16in"]) < TOL
+
+
+def test_warmstart_step_matches_oracle_adam(gpu_lib, golden, agent_sd):
+    """Two full warm-start steps (fwd + LabelSmoothing + bwd + fused Adam) vs oracle autograd + oracle Adam."""
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer
+    model, cfg = build_agent(agent_sd)
+    tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD)
+    tr.teach_warmstart()
+    model.manager.exploration = False
+    b = synth.synthetic_batch(B=3, Sv=8, Sa=10, L=6, V=VOC, seed=31, ragged=True)
+    cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+    params = {k: v.clone() for k, v in agent_sd.items()}
+    state, losses = {}, []
+    for _ in range(2):
+        p = {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point else v) for k, v in params.items()}
+        pred = O.agent_forward(p, b["rgb"] + b["flow"], b["audio"], cin, O.make_masks(b["rgb"], b["audio"], cin, PAD))[0]
+        loss = O.label_smoothing_kl(pred, cy, SMOOTH, PAD).sum() / (cy != PAD).sum()
+        loss.backward()
+        grads = {k: v.grad for k, v in p.items() if torch.is_tensor(v) and v.grad is not None and not k.startswith("manager.core.")}
+        params, state = O.adam_step({k: v.detach() for k, v in p.items()}, grads, state)
+        losses.append(float(loss))
+    dl = [float(tr.warmstart_step(_dev(b))) for _ in range(2)]
+    assert abs(dl[0] - losses[0]) < 1e-3 * abs(losses[0]) and abs(dl[1] - losses[1]) < 1e-3 * abs(losses[1])
+    worst = 0.0
+    for n, q in model.named_parameters():
+        worst = max(worst, rel(q, params[n]))
+    assert worst < 1e-3, worst
+
+
+def test_cuda_graph_step_equals_eager(gpu_lib, agent_sd):
+    from bmhrl_b200 import ops
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, StepRunner
+    b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=2, ragged=True)
+    res = []
+    for use_graph in (False, True):
+        model, cfg = build_agent(agent_sd)
+        tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD)
+        tr.teach_warmstart()
+        model.manager.exploration = False
+        run = StepRunner(tr, "warmstart", b, use_graph=use_graph, warmup=0 if not use_graph else 2)
+        n0 = 2 if use_graph else 0
+        losses = [float(run.step(b)[0]) for _ in range(5 - n0)]
+        res.append((losses, model.worker.core.projection.weight.detach().clone()))
+    assert abs(res[0][0][-1] - res[1][0][-1]) < 1e-4 * abs(res[0][0][-1])
+    assert rel(res[1][1], res[0][1]) < 1e-5
+    assert res[0][0][-1] < res[0][0][0]  # the loss goes down
+
+
+def test_padding_invariance_full_size(gpu_lib, agent_sd):
+    """Size-independent property at C16 sizes: extending every clip with masked (zero) frames and the captions
+    with pad tokens must not change the un-padded outputs (masked keys get exp(-1e9 - max) == 0 weight)."""
+    from bmhrl_b200.model.masking import make_masks
+    model, _ = build_agent(agent_sd)
+    model.eval()
+    model.set_inference_mode(True)
+    b = _dev(synth.synthetic_batch(B=16, Sv=30, Sa=80, L=20, V=VOC, seed=77, ragged=True))
+    cin = b["caption"][:, :-1]
+    with torch.no_grad():
+        out = model((b["rgb"] + b["flow"], b["audio"]), cin, make_masks(b, cin, "audio_video", PAD))
+        zp = lambda t, n: torch.cat([t, t.new_zeros(t.shape[0], n, t.shape[2])], 1)
+        b2 = {"rgb": zp(b["rgb"], 13), "flow": zp(b["flow"], 13), "audio": zp(b["audio"], 21)}
+        out2 = model((b2["rgb"] + b2["flow"], b2["audio"]), cin, make_masks(b2, cin, "audio_video", PAD))
+    assert rel(out2[0], out[0]) < 1e-5 and torch.equal(out2[4], out[4])
+    lse = torch.logsumexp(out[0], -1)
+    assert float(lse.abs().max()) < 1e-4  # rows are log-probabilities
