@@ -4,22 +4,23 @@ look at component 0 only (of rgb, before flow is added), so a real frame whose f
 import torch
 
 
-def subsequent_mask(size):
-    """model/masking.py:3-11 -> (1, size, size) uint8 lower-triangular."""
-    return torch.tril(torch.ones(1, size, size), 0).byte()
+def subsequent_mask(size, device=None):
+    """model/masking.py:3-11 -> (1, size, size) uint8 lower-triangular (built on `device`: no H2D copy, so the
+    mask construction is CUDA-graph capturable)."""
+    return torch.tril(torch.ones(1, size, size, device=device), 0).byte()
 
 
 def c_mask(trg, pad_idx):
     """model/masking.py:13-15."""
     m = (trg != pad_idx).unsqueeze(-2)
-    return m & subsequent_mask(trg.size(-1)).type_as(m).to(m.device)
+    return m & subsequent_mask(trg.size(-1), trg.device).type_as(m)
 
 
 def mask(src, trg, pad_idx, data_pad=0):
     """model/masking.py:18-25: src (B,S') -> (B,1,S'); trg -> (B,L,L) pad AND causal."""
     src_mask = (src != data_pad).unsqueeze(1)
     if trg is not None:
-        trg_mask = (trg != pad_idx).unsqueeze(-2) & subsequent_mask(trg.size(-1)).type_as(src_mask.data).to(trg.device)
+        trg_mask = (trg != pad_idx).unsqueeze(-2) & subsequent_mask(trg.size(-1), trg.device).type_as(src_mask.data)
         return src_mask, trg_mask
     return src_mask
 

@@ -135,7 +135,7 @@ def test_warmstart_step_matches_oracle_adam(gpu_lib, golden, agent_sd):
         loss.backward()
         grads = {k: v.grad for k, v in p.items() if torch.is_tensor(v) and v.grad is not None and not k.startswith("manager.core.")}
         params, state = O.adam_step({k: v.detach() for k, v in p.items()}, grads, state)
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
     dl = [float(tr.warmstart_step(_dev(b))) for _ in range(2)]
     assert abs(dl[0] - losses[0]) < 1e-3 * abs(losses[0]) and abs(dl[1] - losses[1]) < 1e-3 * abs(losses[1])
     worst = 0.0
