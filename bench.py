@@ -268,6 +268,7 @@ def run_gpu(args):
     tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync)
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[args.workload]()
     ops.manual_seed(1234 + rank, dev)
+    ops.set_math_mode(args.math)
 
     # pinned host batches (a different one per rank and per step slot), H2D'd inside the e2e region
     n_host = 4
@@ -338,13 +339,17 @@ def run_gpu(args):
         line = {
             "metric": METRIC, "value": clips / sec, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.workload),
+            "vs_baseline": None, "dtype": "tf32" if args.math == "tf32" else "f32", "data": "synthetic",
+            "config": workload_config(args.workload),
             "e2e": {"value": clips / sec_e2e, "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3, "wall_ms_per_step": wall_e2e / args.steps * 1e3},
             "gpu_launches": graph_launches * (2 * args.steps + args.warmup) if graph_launches else launches_eager,
             "launches_per_step": graph_launches,
             "clocks": clk,
-            "roofline": {"bound": "tensor", "kernel": "projection/FFN/vocab GEMMs (gemm_simt_kernel, fp32 SIMT)",
+            "roofline": {"bound": "tensor",
+                         "kernel": ("projection/FFN/vocab/gradient GEMMs (gemm_tf32_tc_kernel: TMA + tcgen05.mma "
+                                    "kind::tf32, TMEM accumulators)") if args.math == "tf32" else
+                                   "projection/FFN/vocab/gradient GEMMs (gemm_simt_kernel, fp32 SIMT)",
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
                          "traffic": None, "peak_source": f"{pk_src} bf16_tflops_sustained",
                          "launches_per_step": ng, "avg_launch_us": sl * 1e6, "flops_per_launch": fl},
@@ -376,6 +381,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="warmstart", choices=["warmstart", "worker", "manager"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--math", default="tf32", choices=["tf32", "fp32"],
+                    help="tf32: tcgen05 tensor-core GEMMs (default); fp32: exact SIMT contractions")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

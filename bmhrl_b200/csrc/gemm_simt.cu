@@ -195,6 +195,13 @@ extern "C" int bmhrl_gemm_f32(const float* A, long long sAm, long long sAk, cons
     p.sAm = sAm; p.sAk = sAk; p.sBk = sBk; p.sBn = sBn; p.ldc = ldc;
     p.Hdiv = Hdiv; p.bAo = bAo; p.bAi = bAi; p.bBo = bBo; p.bBi = bBi; p.bCo = bCo; p.bCi = bCi;
     p.alpha = alpha; p.beta = beta;
+    if (math_mode() == 1 && batch == 1 && (sAk == 1 || sAm == 1) && (sBk == 1 || sBn == 1) && (beta == 0.f || beta == 1.f)) {
+        TcGemmArgs t{};
+        t.A = A; t.a_mn = (sAk == 1) ? 0 : 1; t.lda = t.a_mn ? sAk : sAm;
+        t.B = B; t.b_mn = (sBk == 1) ? 0 : 1; t.ldb = t.b_mn ? sBk : sBn;
+        t.C = C; t.ldc = ldc; t.M = M; t.N = N; t.K = K; t.alpha = alpha; t.beta = beta;
+        if (tc_gemm_supported(t)) return launch_gemm_tc(t, (cudaStream_t)stream);
+    }
     gemm_set_vec_flags(p);
     return launch_gemm_simt(p, batch, (cudaStream_t)stream);
 }
@@ -214,6 +221,13 @@ extern "C" int bmhrl_linear_fwd_f32(const float* X, long long ldx, const float* 
     p.Hdiv = 1;
     p.alpha = 1.f; p.beta = 0.f; p.bias = bias; p.act = act; p.resid = resid; p.ldr = ldr;
     p.drop_p = drop_p; p.rng = rng_state; p.salt = salt;
+    if (math_mode() == 1) {
+        TcGemmArgs t{};
+        t.A = X; t.lda = ldx; t.a_mn = 0; t.B = W; t.ldb = K; t.b_mn = 0; t.C = Y; t.ldc = ldy;
+        t.M = M; t.N = N; t.K = K; t.alpha = 1.f; t.beta = 0.f; t.bias = bias; t.act = act; t.resid = resid; t.ldr = ldr;
+        t.drop_p = drop_p; t.rng = rng_state; t.salt = salt;
+        if (tc_gemm_supported(t)) return launch_gemm_tc(t, (cudaStream_t)stream);
+    }
     gemm_set_vec_flags(p);
     return launch_gemm_simt(p, 1, (cudaStream_t)stream);
 }

@@ -36,4 +36,18 @@ static inline void gemm_set_vec_flags(GemmParams& p) {
 
 int launch_gemm_simt(const GemmParams& p, int batch, cudaStream_t st);
 
+// ---- tensor-core path (gemm_tc.cu)
+struct TcGemmArgs {
+    const float* A; long long lda; int a_mn;  // a_mn = 0: A(m,k) at A[m*lda + k]; 1: A(m,k) at A[k*lda + m]
+    const float* B; long long ldb; int b_mn;  // b_mn = 0: B(k,n) at B[n*ldb + k]; 1: B(k,n) at B[k*ldb + n]
+    float* C; long long ldc;
+    int M, N, K;
+    float alpha, beta;
+    const float* bias; int act; const float* resid; long long ldr;
+    float drop_p; const unsigned long long* rng; unsigned int salt;
+};
+int math_mode();                                  // 0 exact fp32 (SIMT), 1 tf32 (tcgen05)
+bool tc_gemm_supported(const TcGemmArgs& a);      // alignment / pitch constraints of TMA
+int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st);
+
 }  // namespace bmhrl

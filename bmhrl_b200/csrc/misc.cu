@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(256) linear_bwd_prep_kernel(const float* __res
                                                               float* __restrict__ dZ, float* __restrict__ db, int M,
                                                               int N, int act, float drop_p,
                                                               const unsigned long long* __restrict__ rng,
-                                                              unsigned int salt) {
+                                                              unsigned int salt, int accumulate) {
     __shared__ float sb[8][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int n = blockIdx.x * 32 + lane;
@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(256) linear_bwd_prep_kernel(const float* __res
         float t = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += sb[i][lane];
-        db[n] = t;
+        db[n] = accumulate ? db[n] + t : t;
     }
 }
 
@@ -501,13 +501,14 @@ extern "C" int bmhrl_segment_scan_bwd_f32(const float* probs, const int* seg, co
 
 extern "C" int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const float* Y, long long ldy, float* dZ,
                                          float* db, int M, int N, int act, float drop_p,
-                                         const unsigned long long* rng_state, unsigned int salt, void* stream) {
+                                         const unsigned long long* rng_state, unsigned int salt, int accumulate_db,
+                                         void* stream) {
     BMHRL_CHECK_ARG(dY && (dZ || db) && M >= 0 && N > 0, "bmhrl_linear_bwd_prep_f32: bad arguments");
     BMHRL_CHECK_ARG(act == 0 || (act == 1 && Y), "bmhrl_linear_bwd_prep_f32: relu needs the forward output");
     BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || act == 1 || rng_state),
                     "bmhrl_linear_bwd_prep_f32: dropout needs rng_state");
     linear_bwd_prep_kernel<<<(N + 31) / 32, 256, 0, (cudaStream_t)stream>>>(dY, lddy, Y, ldy, dZ, db, M, N, act, drop_p,
-                                                                            rng_state, salt);
+                                                                            rng_state, salt, accumulate_db);
     BMHRL_POST_LAUNCH("linear_bwd_prep");
     return BMHRL_OK;
 }

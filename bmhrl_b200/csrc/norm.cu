@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(LN_WARPS * 32) layernorm_bwd_dx_kernel(
 // the rows (128-byte coalesced row segments), deterministic shared-memory tree at the end.
 __global__ void __launch_bounds__(256) layernorm_bwd_affine_kernel(
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
-    const float* __restrict__ rstd_in, float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int D) {
+    const float* __restrict__ rstd_in, float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int D,
+    int accumulate) {
     __shared__ float sg[8][33], sb[8][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
@@ -142,8 +143,8 @@ __global__ void __launch_bounds__(256) layernorm_bwd_affine_kernel(
         float tg = 0.f, tb = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) { tg += sg[i][lane]; tb += sb[i][lane]; }
-        dgamma[c] = tg;
-        dbeta[c] = tb;
+        dgamma[c] = accumulate ? dgamma[c] + tg : tg;
+        dbeta[c] = accumulate ? dbeta[c] + tb : tb;
     }
 }
 
@@ -195,7 +196,7 @@ __global__ void __launch_bounds__(256) gated_mix_bwd_kernel(const float* __restr
 
 // dc = (sum partial) * s(1-s) * [ -2 <= c <= 2 ]
 __global__ void gated_mix_bwd_final_kernel(const float* __restrict__ partial, int nparts,
-                                           const float* __restrict__ cptr, float* __restrict__ dc) {
+                                           const float* __restrict__ cptr, float* __restrict__ dc, int accumulate) {
     __shared__ float red[32];
     float acc = 0.f;
     for (int i = threadIdx.x; i < nparts; i += blockDim.x) acc += partial[i];
@@ -203,7 +204,8 @@ __global__ void gated_mix_bwd_final_kernel(const float* __restrict__ partial, in
     if (threadIdx.x == 0) {
         float c = cptr[0];
         float s = gate_of(c);
-        dc[0] = (c >= -2.f && c <= 2.f) ? acc * s * (1.f - s) : 0.f;
+        const float d = (c >= -2.f && c <= 2.f) ? acc * s * (1.f - s) : 0.f;
+        dc[0] = accumulate ? dc[0] + d : d;
     }
 }
 
@@ -227,7 +229,7 @@ extern "C" int bmhrl_layernorm_fwd_f32(const float* x, const float* resid, const
 
 extern "C" int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const float* gamma, const float* mean,
                                        const float* rstd, const float* dres, float* dx, float* dgamma, float* dbeta,
-                                       int rows, int D, void* stream) {
+                                       int rows, int D, int accumulate_affine, void* stream) {
     BMHRL_CHECK_ARG(dy && x && gamma && mean && rstd, "bmhrl_layernorm_bwd_f32: null pointer");
     BMHRL_CHECK_ARG(rows >= 0 && D > 0, "bmhrl_layernorm_bwd_f32: bad sizes");
     cudaStream_t st = (cudaStream_t)stream;
@@ -239,7 +241,8 @@ extern "C" int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const fl
         BMHRL_POST_LAUNCH("layernorm_bwd_dx");
     }
     if (dgamma && dbeta) {
-        layernorm_bwd_affine_kernel<<<(D + 31) / 32, 256, 0, st>>>(dy, x, mean, rstd, dgamma, dbeta, rows, D);
+        layernorm_bwd_affine_kernel<<<(D + 31) / 32, 256, 0, st>>>(dy, x, mean, rstd, dgamma, dbeta, rows, D,
+                                                                        accumulate_affine);
         BMHRL_POST_LAUNCH("layernorm_bwd_affine");
     }
     return BMHRL_OK;
@@ -260,7 +263,7 @@ extern "C" int bmhrl_gated_mix_fwd_f32(const float* v, const float* a, const flo
 
 extern "C" int bmhrl_gated_mix_bwd_f32(const float* g, const float* v, const float* a, const float* gate_param,
                                        float* dv, float* da, float* dgate, float* partial_ws, int ws_floats,
-                                       long long n, void* stream) {
+                                       long long n, int accumulate_gate, void* stream) {
     BMHRL_CHECK_ARG(g && v && a && gate_param && dv && da && dgate && partial_ws,
                     "bmhrl_gated_mix_bwd_f32: null pointer");
     BMHRL_CHECK_ARG(ws_floats >= 1, "bmhrl_gated_mix_bwd_f32: workspace too small");
@@ -271,7 +274,7 @@ extern "C" int bmhrl_gated_mix_bwd_f32(const float* g, const float* v, const flo
     cudaStream_t st = (cudaStream_t)stream;
     gated_mix_bwd_kernel<<<blocks, 256, 0, st>>>(g, v, a, gate_param, dv, da, partial_ws, n);
     BMHRL_POST_LAUNCH("gated_mix_bwd");
-    gated_mix_bwd_final_kernel<<<1, 256, 0, st>>>(partial_ws, blocks, gate_param, dgate);
+    gated_mix_bwd_final_kernel<<<1, 256, 0, st>>>(partial_ws, blocks, gate_param, dgate, accumulate_gate);
     BMHRL_POST_LAUNCH("gated_mix_bwd_final");
     return BMHRL_OK;
 }

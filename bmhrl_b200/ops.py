@@ -93,6 +93,16 @@ def next_salt():
 # ----------------------------------------------------------------------------------------------------------------
 # contractions
 # ----------------------------------------------------------------------------------------------------------------
+def set_math_mode(mode):
+    """'fp32': exact SIMT contractions (default); 'tf32': tcgen05 tensor-core GEMMs (fp32 storage, tf32 multiplies,
+    fp32 accumulation in TMEM)."""
+    LIB.call("bmhrl_set_math_mode", {"fp32": 0, "tf32": 1}[mode])
+
+
+def get_math_mode():
+    return ("fp32", "tf32")[LIB.raw("bmhrl_get_math_mode")()]
+
+
 RECORD = None  # bench.py: when a list, every GEMM launch appends its shape/stride tuple (roofline re-issue)
 
 
@@ -104,11 +114,20 @@ def gemm(A, sAm, sAk, B, sBk, sBn, C, ldc, M, N, K, batch=1, Hdiv=1, bA=(0, 0), 
              bB[1], bC[0], bC[1], alpha, beta, _stream())
 
 
+def _gbuf(p):
+    """The slice of a FusedAdam flat gradient buffer that belongs to parameter `p` (None outside a trainer, or when
+    the parameter is frozen): backward kernels then accumulate into it directly and autograd gets no gradient tensor
+    to add (no per-parameter AccumulateGrad kernels)."""
+    if p is None or not p.requires_grad:
+        return None
+    return getattr(p, "_bmhrl_grad", None)
+
+
 class _Linear(torch.autograd.Function):
     """y = resid + dropout(act(x W^T + b)); reference call sites listed in include/bmhrl_b200.h."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, resid, act, drop_p, salt, rng):
+    def forward(ctx, x, weight, bias, resid, act, drop_p, salt, rng, wgrad, bgrad):
         x = _c(x, "x")
         weight = _c(weight, "weight")
         N, K = weight.shape
@@ -126,13 +145,13 @@ class _Linear(torch.autograd.Function):
             RECORD.append(("linear", M, N, K))
         LIB.call("bmhrl_linear_fwd_f32", _p(x), K, _p(weight), _p(b), _p(r), N, _p(y), N, M, N, K, act, drop_p,
                  _p(rng) if drop_p > 0 else None, salt, _stream())
-        ctx.save_for_backward(x, weight, y if act == 1 else None, rng if drop_p > 0 else None)
+        ctx.save_for_backward(x, weight, y if act == 1 else None, rng if drop_p > 0 else None, wgrad, bgrad)
         ctx.cfg = (act, drop_p, salt, M, N, K, bias is not None, resid is not None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, weight, y, rng = ctx.saved_tensors
+        x, weight, y, rng, wgrad, bgrad = ctx.saved_tensors
         act, drop_p, salt, M, N, K, has_bias, has_resid = ctx.cfg
         dy = _c(dy, "dy")
         need_x, need_w, need_b, need_r = ctx.needs_input_grad[0], ctx.needs_input_grad[1], \
@@ -140,28 +159,34 @@ class _Linear(torch.autograd.Function):
         st = _stream()
         dz = dy
         db = None
+        acc_b = 1 if (need_b and bgrad is not None) else 0  # straight into the flat gradient buffer
         if act == 1 or drop_p > 0:
             dz = torch.empty(M, N, device=dy.device, dtype=_F32)
-            db = torch.empty(N, device=dy.device, dtype=_F32) if need_b else None
+            db = (bgrad if acc_b else torch.empty(N, device=dy.device, dtype=_F32)) if need_b else None
             LIB.call("bmhrl_linear_bwd_prep_f32", _p(dy), N, _p(y), N, _p(dz), _p(db), M, N, act, drop_p, _p(rng), salt,
-                     st)
+                     acc_b, st)
         elif need_b:
-            db = torch.empty(N, device=dy.device, dtype=_F32)
-            LIB.call("bmhrl_linear_bwd_prep_f32", _p(dy), N, None, N, None, _p(db), M, N, 0, 0.0, None, 0, st)
+            db = bgrad if acc_b else torch.empty(N, device=dy.device, dtype=_F32)
+            LIB.call("bmhrl_linear_bwd_prep_f32", _p(dy), N, None, N, None, _p(db), M, N, 0, 0.0, None, 0, acc_b, st)
+        if acc_b:
+            db = None
         dx = dw = None
         if need_x:  # dX = dZ W : (M,N)(N,K)
             dx = torch.empty(x.shape, device=dy.device, dtype=_F32)
             gemm(dz, N, 1, weight, K, 1, dx, K, M, K, N)
         if need_w:  # dW = dZ^T X : (N,M)(M,K)
-            dw = torch.empty(N, K, device=dy.device, dtype=_F32)
-            gemm(dz, 1, N, x, K, 1, dw, K, N, K, M)
-        return dx, dw, db, (dy if need_r else None), None, None, None, None
+            if wgrad is not None:  # accumulate into the parameter's slice of the flat gradient buffer (beta = 1)
+                gemm(dz, 1, N, x, K, 1, wgrad, K, N, K, M, beta=1.0)
+            else:
+                dw = torch.empty(N, K, device=dy.device, dtype=_F32)
+                gemm(dz, 1, N, x, K, 1, dw, K, N, K, M)
+        return dx, dw, db, (dy if need_r else None), None, None, None, None, None, None
 
 
 def linear(x, weight, bias=None, resid=None, act=0, drop_p=0.0, salt=0, rng=None):
     if drop_p > 0 and rng is None:
         rng = RNG.current(x.device)
-    return _Linear.apply(x, weight, bias, resid, act, float(drop_p), int(salt), rng)
+    return _Linear.apply(x, weight, bias, resid, act, float(drop_p), int(salt), rng, _gbuf(weight), _gbuf(bias))
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -169,7 +194,7 @@ def linear(x, weight, bias=None, resid=None, act=0, drop_p=0.0, salt=0, rng=None
 # ----------------------------------------------------------------------------------------------------------------
 class _LayerNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps):
+    def forward(ctx, x, gamma, beta, eps, ggrad, bgrad):
         x = _c(x, "x")
         gamma = _c(gamma, "gamma")
         beta = _c(beta, "beta")
@@ -180,55 +205,59 @@ class _LayerNorm(torch.autograd.Function):
         rstd = torch.empty(rows, device=x.device, dtype=_F32)
         LIB.call("bmhrl_layernorm_fwd_f32", _p(x), None, _p(gamma), _p(beta), None, _p(y), _p(mean), _p(rstd), rows, D,
                  eps, _stream())
-        ctx.save_for_backward(x, gamma, mean, rstd)
+        ctx.save_for_backward(x, gamma, mean, rstd, ggrad, bgrad)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, gamma, mean, rstd = ctx.saved_tensors
+        x, gamma, mean, rstd, ggrad, bgrad = ctx.saved_tensors
         dy = _c(dy, "dy")
         D = x.shape[-1]
         rows = x.numel() // D
         need_x = ctx.needs_input_grad[0]
         need_aff = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
         dx = torch.empty_like(x) if need_x else None
-        dg = torch.empty(D, device=x.device, dtype=_F32) if need_aff else None
-        db = torch.empty(D, device=x.device, dtype=_F32) if need_aff else None
+        acc = 1 if (need_aff and ggrad is not None and bgrad is not None) else 0
+        dg = (ggrad if acc else torch.empty(D, device=x.device, dtype=_F32)) if need_aff else None
+        db = (bgrad if acc else torch.empty(D, device=x.device, dtype=_F32)) if need_aff else None
         LIB.call("bmhrl_layernorm_bwd_f32", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), None, _p(dx), _p(dg), _p(db),
-                 rows, D, _stream())
-        return dx, dg, db, None
+                 rows, D, acc, _stream())
+        if acc:
+            dg = db = None
+        return dx, dg, db, None, None, None
 
 
 def layer_norm(x, gamma, beta, eps=1e-5):
-    return _LayerNorm.apply(x, gamma, beta, float(eps))
+    return _LayerNorm.apply(x, gamma, beta, float(eps), _gbuf(gamma), _gbuf(beta))
 
 
 class _GatedMix(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, v, a, gate):
+    def forward(ctx, v, a, gate, ggrad):
         v = _c(v, "v")
         a = _c(a, "a")
         gate = _c(gate, "gate")
         out = torch.empty_like(v)
         LIB.call("bmhrl_gated_mix_fwd_f32", _p(v), _p(a), _p(gate), _p(out), v.numel(), _stream())
-        ctx.save_for_backward(v, a, gate)
+        ctx.save_for_backward(v, a, gate, ggrad)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        v, a, gate = ctx.saved_tensors
+        v, a, gate, ggrad = ctx.saved_tensors
         g = _c(g, "g")
         dv = torch.empty_like(v)
         da = torch.empty_like(a)
-        dgate = torch.empty(1, device=v.device, dtype=_F32)
+        acc = 1 if ggrad is not None else 0
+        dgate = ggrad if acc else torch.empty(1, device=v.device, dtype=_F32)
         ws = torch.empty(592, device=v.device, dtype=_F32)
         LIB.call("bmhrl_gated_mix_bwd_f32", _p(g), _p(v), _p(a), _p(gate), _p(dv), _p(da), _p(dgate), _p(ws), 592,
-                 v.numel(), _stream())
-        return dv, da, dgate
+                 v.numel(), acc, _stream())
+        return dv, da, (None if acc else dgate), None
 
 
 def gated_mix(v, a, gate):
-    return _GatedMix.apply(v, a, gate)
+    return _GatedMix.apply(v, a, gate, _gbuf(gate))
 
 
 class _DropoutAdd(torch.autograd.Function):
@@ -812,8 +841,10 @@ class FusedAdam:
         for i, p in enumerate(self.params):
             if not p.requires_grad:
                 p.grad = None
+                p._bmhrl_grad = None
                 continue
-            p.grad = self.grad_views[i]  # autograd accumulates in place into the flat buffer
+            p.grad = self.grad_views[i]  # autograd accumulates in place into the flat buffer ...
+            p._bmhrl_grad = self.grad_views[i]  # ... and the library's backward kernels write into it directly
             act.append(i)
             for s in range(0, p.numel(), self.chunk):
                 ct.append(i)

@@ -33,6 +33,16 @@ const char* bmhrl_last_error(void);       /* thread-local message of the last fa
 long long bmhrl_launch_count(void);       /* kernels launched by this library since the last reset */
 void bmhrl_reset_launch_count(void);
 
+/* ---- math mode ------------------------------------------------------------------------------------------------ */
+/* 0 (default): every contraction in exact fp32 on the SIMT pipes (parity bound 1e-3, in practice ~1e-6).
+ * 1: projection / FFN / vocabulary / gradient GEMMs on the 5th-gen tensor cores (tcgen05.mma kind::tf32, TMA-staged
+ *    fp32 operands, fp32 accumulation in TMEM; parity bound 2e-2 like the north_star's reduced-precision bound). */
+int bmhrl_set_math_mode(int mode);
+int bmhrl_get_math_mode(void);
+/* tuning / test hook of the tensor-core GEMM: force the tile width (0 = heuristic, 32, 64, 128) and the split-K factor
+ * (0 = heuristic). */
+int bmhrl_tc_tuning(int force_bn, int force_split);
+
 /* ---- contractions (fp32 SIMT path, gemm_simt.cu) ------------------------------------------------------------ */
 /* C[z](m,n) = beta*C + alpha * sum_k A[z](m,k) B[z](k,n);  A(m,k) at A + m*sAm + k*sAk, B(k,n) at B + k*sBk + n*sBn.
  * z in [0,batch): outer = z / Hdiv, inner = z % Hdiv, offsets outer*b?o + inner*b?i.
@@ -49,24 +59,27 @@ int bmhrl_linear_fwd_f32(const float* X, long long ldx, const float* W, const fl
                          long long ldr, float* Y, long long ldy, int M, int N, int K, int act, float drop_p,
                          const unsigned long long* rng_state, unsigned int salt, void* stream);
 
-/* dZ = dY * relu'(Y) * dropout-mask/(1-p) (dZ may be NULL when act == 0 and drop_p == 0); db[n] = sum_m dZ[m,n]. */
+/* dZ = dY * relu'(Y) * dropout-mask/(1-p) (dZ may be NULL when act == 0 and drop_p == 0); db[n] (+)= sum_m dZ[m,n]
+ * (accumulate_db != 0: added to db, which then is the parameter's slice of the flat gradient buffer). */
 int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const float* Y, long long ldy, float* dZ, float* db,
                               int M, int N, int act, float drop_p, const unsigned long long* rng_state,
-                              unsigned int salt, void* stream);
+                              unsigned int salt, int accumulate_db, void* stream);
 
 /* ---- K2: residual + LayerNorm, gated mix (norm.cu) ---------------------------------------------------------- */
 /* z = x (+ resid); y = LayerNorm(z) (eps, affine).  z_out may be NULL.  ResidualConnection model/blocks.py:135-144,
  * normCA/normCV model/bm_hrl_agent.py:107-108, post-LN model/encoder.py:64-68, model/decoder.py:77-99. */
 int bmhrl_layernorm_fwd_f32(const float* x, const float* resid, const float* gamma, const float* beta, float* z_out,
                             float* y, float* mean, float* rstd, int rows, int D, float eps, void* stream);
-/* dx = LN'(dy) (+ dres); dgamma, dbeta (both or neither; dx may be NULL). */
+/* dx = LN'(dy) (+ dres); dgamma, dbeta (both or neither; dx may be NULL; accumulate_affine != 0: added in place). */
 int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
-                            const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int D, void* stream);
+                            const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int D,
+                            int accumulate_affine, void* stream);
 /* out = s*v + (1-s)*a, s = sigmoid(clamp(*gate_param,-2,2)); model/bm_hrl_agent.py:111-114. */
 int bmhrl_gated_mix_fwd_f32(const float* v, const float* a, const float* gate_param, float* out, long long n,
                             void* stream);
 int bmhrl_gated_mix_bwd_f32(const float* g, const float* v, const float* a, const float* gate_param, float* dv,
-                            float* da, float* dgate, float* partial_ws, int ws_floats, long long n, void* stream);
+                            float* da, float* dgate, float* partial_ws, int ws_floats, long long n, int accumulate_gate,
+                            void* stream);
 
 /* ---- K1: attention core, exact-fp32 path (attn_simt.cu) ----------------------------------------------------- */
 /* attention() model/multihead_attention.py:7-31.  Q/K/V/O are (B, S, H*dk) views: row pitch ld?, batch pitch bs?,
