@@ -274,39 +274,68 @@ __global__ void segment_scan_bwd_kernel(const float* __restrict__ p, const int* 
 }
 
 // ------------------------------------------------------------------ linear backward prep
-// dZ[m,n] = dY[m,n] * (act==relu ? Y[m,n] > 0 : 1) * (dropout keep ? 1/(1-p) : 0);  db[n] = sum_m dZ[m,n].
+// dZ[m,n] = dY[m,n] * (act==relu ? Y[m,n] > 0 : 1) * (dropout keep ? 1/(1-p) : 0);  db[n] += sum_m dZ[m,n].
 // For relu + dropout the forward output Y = drop(relu(z)) is > 0 exactly where both let the gradient through.
-// One block per 32 columns; 8 warps stride the rows; deterministic reduction.
+// Grid (column blocks, row splits): a block owns CPT*32 columns x rows_per_block rows, its 8 warps stride the rows
+// with CPT*4-byte accesses per lane (128-bit when CPT == 4); partial column sums are combined in shared memory and
+// added to db with one RED per column per block (db is zeroed by the host wrapper when it does not accumulate).
+template <int CPT>
 __global__ void __launch_bounds__(256) linear_bwd_prep_kernel(const float* __restrict__ dY, long long lddy,
                                                               const float* __restrict__ Y, long long ldy,
                                                               float* __restrict__ dZ, float* __restrict__ db, int M,
                                                               int N, int act, float drop_p,
                                                               const unsigned long long* __restrict__ rng,
-                                                              unsigned int salt, int accumulate) {
-    __shared__ float sb[8][33];
+                                                              unsigned int salt, int rows_per_block) {
+    __shared__ float sb[8][32 * CPT + 1];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int n = blockIdx.x * 32 + lane;
+    const int n0 = (blockIdx.x * 32 + lane) * CPT;
+    const int m_begin = blockIdx.y * rows_per_block;
+    const int m_end = min(M, m_begin + rows_per_block);
     const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
-    float acc = 0.f;
-    if (n < N) {
-        for (int m = w; m < M; m += 8) {
-            float g = dY[(long long)m * lddy + n];
-            if (act == 1) {
-                g = (Y[(long long)m * ldy + n] > 0.f) ? g * ks : 0.f;
-            } else if (drop_p > 0.f) {
-                g = dropout_keep(rng, salt, (unsigned long long)m * N + n, drop_p) ? g * ks : 0.f;
+    float acc[CPT];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) acc[j] = 0.f;
+    if (n0 < N) {
+        for (int m = m_begin + w; m < m_end; m += 8) {
+            float g[CPT], y[CPT];
+            if (CPT == 4) {
+                float4 t = ld_f4(dY + (long long)m * lddy + n0);
+                g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
+                if (act == 1) {
+                    float4 u = ld_f4(Y + (long long)m * ldy + n0);
+                    y[0] = u.x; y[1] = u.y; y[2] = u.z; y[3] = u.w;
+                }
+            } else {
+                g[0] = dY[(long long)m * lddy + n0];
+                if (act == 1) y[0] = Y[(long long)m * ldy + n0];
             }
-            if (dZ) dZ[(long long)m * N + n] = g;
-            acc += g;
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) {
+                if (act == 1) {
+                    g[j] = (y[j] > 0.f) ? g[j] * ks : 0.f;
+                } else if (drop_p > 0.f) {
+                    g[j] = dropout_keep(rng, salt, (unsigned long long)m * N + n0 + j, drop_p) ? g[j] * ks : 0.f;
+                }
+                acc[j] += g[j];
+            }
+            if (dZ) {
+                if (CPT == 4) st_f4(dZ + (long long)m * N + n0, make_float4(g[0], g[1], g[2], g[3]));
+                else dZ[(long long)m * N + n0] = g[0];
+            }
         }
     }
-    sb[w][lane] = acc;
-    __syncthreads();
-    if (w == 0 && n < N && db) {
-        float t = 0.f;
+    if (!db) return;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) t += sb[i][lane];
-        db[n] = accumulate ? db[n] + t : t;
+    for (int j = 0; j < CPT; ++j) sb[w][lane * CPT + j] = acc[j];
+    __syncthreads();
+    for (int c = threadIdx.x; c < 32 * CPT; c += 256) {
+        const int n = blockIdx.x * 32 * CPT + c;
+        if (n < N) {
+            float t = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) t += sb[i][c];
+            atomicAdd(db + n, t);
+        }
     }
 }
 
@@ -507,8 +536,28 @@ extern "C" int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const 
     BMHRL_CHECK_ARG(act == 0 || (act == 1 && Y), "bmhrl_linear_bwd_prep_f32: relu needs the forward output");
     BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || act == 1 || rng_state),
                     "bmhrl_linear_bwd_prep_f32: dropout needs rng_state");
-    linear_bwd_prep_kernel<<<(N + 31) / 32, 256, 0, (cudaStream_t)stream>>>(dY, lddy, Y, ldy, dZ, db, M, N, act, drop_p,
-                                                                            rng_state, salt, accumulate_db);
+    if (M == 0) return BMHRL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (db && !accumulate_db && cudaMemsetAsync(db, 0, sizeof(float) * (size_t)N, st) != cudaSuccess) {
+        bmhrl_set_error("bmhrl_linear_bwd_prep_f32: memset failed");
+        return BMHRL_ERR_CUDA;
+    }
+    const bool vec = (N % 4 == 0) && (lddy % 4 == 0) && aligned16(dY) && (!dZ || aligned16(dZ)) &&
+                     (act != 1 || ((ldy % 4 == 0) && aligned16(Y)));
+    const int cols_per_block = vec ? 128 : 32;
+    const int col_blocks = (N + cols_per_block - 1) / cols_per_block;
+    int splits = (2 * 148 + col_blocks - 1) / col_blocks;           // ~2 blocks per SM
+    const int max_splits = (M + 7) / 8;
+    if (splits > max_splits) splits = max_splits;
+    const int rows_per_block = ((M + splits - 1) / splits + 7) / 8 * 8;
+    splits = (M + rows_per_block - 1) / rows_per_block;
+    dim3 grid(col_blocks, splits);
+    if (vec)
+        linear_bwd_prep_kernel<4><<<grid, 256, 0, st>>>(dY, lddy, Y, ldy, dZ, db, M, N, act, drop_p, rng_state, salt,
+                                                        rows_per_block);
+    else
+        linear_bwd_prep_kernel<1><<<grid, 256, 0, st>>>(dY, lddy, Y, ldy, dZ, db, M, N, act, drop_p, rng_state, salt,
+                                                        rows_per_block);
     BMHRL_POST_LAUNCH("linear_bwd_prep");
     return BMHRL_OK;
 }

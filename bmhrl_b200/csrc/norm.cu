@@ -148,6 +148,95 @@ __global__ void __launch_bounds__(256) layernorm_bwd_affine_kernel(
     }
 }
 
+// Fused backward: dx (as layernorm_bwd_dx_kernel) AND the affine gradients in one pass over dy / x.  A block owns
+// `rows_per_block` consecutive rows, its warps stride them; every lane keeps the dgamma / dbeta partial sums of its
+// NV float4 column groups in registers, the 4 warps are combined in shared memory and each block issues one RED per
+// column into dgamma / dbeta (the parameter's slice of the flat gradient buffer, or a zeroed temporary).
+template <int NV>
+__global__ void __launch_bounds__(LN_WARPS * 32) layernorm_bwd_fused_kernel(
+    const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
+    const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ dres,
+    float* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int D,
+    int rows_per_block) {
+    extern __shared__ float sred[];  // [LN_WARPS][2][D]
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int D4 = D >> 2;
+    const int r_begin = blockIdx.x * rows_per_block;
+    const int r_end = min(rows, r_begin + rows_per_block);
+    float4 ag[NV], ab[NV], gw[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        ag[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        ab[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int i = lane + 32 * j;
+        gw[j] = i < D4 ? ld_f4(gamma + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int row = r_begin + w; row < r_end; row += LN_WARPS) {
+        const float* dyr = dy + (long long)row * D;
+        const float* xr = x + (long long)row * D;
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float4 g[NV], v[NV];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int i = lane + 32 * j;
+            if (i < D4) {
+                g[j] = ld_f4(dyr + 4 * i);
+                v[j] = ld_f4(xr + 4 * i);
+                v[j].x = (v[j].x - mean) * rstd; v[j].y = (v[j].y - mean) * rstd;
+                v[j].z = (v[j].z - mean) * rstd; v[j].w = (v[j].w - mean) * rstd;
+                ab[j].x += g[j].x; ab[j].y += g[j].y; ab[j].z += g[j].z; ab[j].w += g[j].w;
+                ag[j].x += g[j].x * v[j].x; ag[j].y += g[j].y * v[j].y;
+                ag[j].z += g[j].z * v[j].z; ag[j].w += g[j].w * v[j].w;
+                g[j].x *= gw[j].x; g[j].y *= gw[j].y; g[j].z *= gw[j].z; g[j].w *= gw[j].w;
+                s1 += (g[j].x + g[j].y) + (g[j].z + g[j].w);
+                s2 += (g[j].x * v[j].x + g[j].y * v[j].y) + (g[j].z * v[j].z + g[j].w * v[j].w);
+            }
+        }
+        if (dx) {
+            s1 = warp_sum(s1) / (float)D;
+            s2 = warp_sum(s2) / (float)D;  // mean(g * xhat)
+            float* dxr = dx + (long long)row * D;
+            const float* dr = dres ? dres + (long long)row * D : nullptr;
+#pragma unroll
+            for (int j = 0; j < NV; ++j) {
+                const int i = lane + 32 * j;
+                if (i < D4) {
+                    float4 o;
+                    o.x = rstd * (g[j].x - s1 - v[j].x * s2);
+                    o.y = rstd * (g[j].y - s1 - v[j].y * s2);
+                    o.z = rstd * (g[j].z - s1 - v[j].z * s2);
+                    o.w = rstd * (g[j].w - s1 - v[j].w * s2);
+                    if (dr) { float4 r = ld_f4(dr + 4 * i); o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
+                    st_f4(dxr + 4 * i, o);
+                }
+            }
+        }
+    }
+    if (!dgamma) return;
+    float* mg = sred + (size_t)w * 2 * D;
+    float* mb = mg + D;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        const int i = lane + 32 * j;
+        if (i < D4) {
+            st_f4(mg + 4 * i, ag[j]);
+            st_f4(mb + 4 * i, ab[j]);
+        }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < D; c += LN_WARPS * 32) {
+        float tg = 0.f, tb = 0.f;
+#pragma unroll
+        for (int i = 0; i < LN_WARPS; ++i) {
+            tg += sred[(size_t)i * 2 * D + c];
+            tb += sred[(size_t)i * 2 * D + D + c];
+        }
+        atomicAdd(dgamma + c, tg);
+        atomicAdd(dbeta + c, tb);
+    }
+}
+
 // ---------------------------------------------------------------- gated mix
 __device__ __forceinline__ float gate_of(float c) {
     float cc = fminf(fmaxf(c, -2.f), 2.f);
@@ -233,6 +322,36 @@ extern "C" int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const fl
     BMHRL_CHECK_ARG(dy && x && gamma && mean && rstd, "bmhrl_layernorm_bwd_f32: null pointer");
     BMHRL_CHECK_ARG(rows >= 0 && D > 0, "bmhrl_layernorm_bwd_f32: bad sizes");
     cudaStream_t st = (cudaStream_t)stream;
+    const bool want_affine = dgamma && dbeta;
+    if (rows > 0 && D % 4 == 0 && D <= 1024 && aligned16(x) && aligned16(dy) && aligned16(gamma) &&
+        (!dx || aligned16(dx)) && (!dres || aligned16(dres))) {
+        if (want_affine && !accumulate_affine) {
+            if (cudaMemsetAsync(dgamma, 0, sizeof(float) * D, st) != cudaSuccess ||
+                cudaMemsetAsync(dbeta, 0, sizeof(float) * D, st) != cudaSuccess) {
+                bmhrl_set_error("bmhrl_layernorm_bwd_f32: memset failed");
+                return BMHRL_ERR_CUDA;
+            }
+        }
+        int rpb = (rows + 2 * 148 - 1) / (2 * 148);       // ~2 blocks per SM ...
+        if (rpb < 2 * LN_WARPS) rpb = 2 * LN_WARPS;       // ... but at least 2 rows per warp to amortise the REDs
+        rpb = (rpb + LN_WARPS - 1) / LN_WARPS * LN_WARPS;
+        const int blocks = (rows + rpb - 1) / rpb;
+        const size_t smem = want_affine ? sizeof(float) * LN_WARPS * 2 * D : 0;
+        float* dg = want_affine ? dgamma : nullptr;
+        float* dbp = want_affine ? dbeta : nullptr;
+        const int nv = (D / 4 + 31) / 32;
+#define BMHRL_LN_BWD(NV)                                                                                          \
+    layernorm_bwd_fused_kernel<NV><<<blocks, LN_WARPS * 32, smem, st>>>(dy, x, gamma, mean, rstd, dres, dx, dg, dbp, \
+                                                                        rows, D, rpb)
+        if (nv <= 1) BMHRL_LN_BWD(1);
+        else if (nv <= 2) BMHRL_LN_BWD(2);
+        else if (nv <= 3) BMHRL_LN_BWD(3);
+        else if (nv <= 4) BMHRL_LN_BWD(4);
+        else BMHRL_LN_BWD(8);
+#undef BMHRL_LN_BWD
+        BMHRL_POST_LAUNCH("layernorm_bwd_fused");
+        return BMHRL_OK;
+    }
     if (dx && rows > 0) {
         int vec = (D % 4 == 0) && aligned16(x) && aligned16(dy) && aligned16(gamma) && aligned16(dx) &&
                   (!dres || aligned16(dres));

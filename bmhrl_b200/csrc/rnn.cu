@@ -17,6 +17,8 @@ constexpr int RNN_WARPS = 8;   // hidden units per block
 
 __device__ __forceinline__ float sigmoid_exact(float x) { return 1.f / (1.f + expf(-x)); }
 
+__device__ __forceinline__ void load_h_tile(float* hs, const float* out, int b0, int nb, int L, int H, int t);
+
 // NG = 4: LSTM (gate order i,f,g,o; b_hh added to the pre-activations); NG = 3: GRU (r,z,n; b_hh inside r*(...)).
 template <int NG>
 __global__ void __launch_bounds__(RNN_WARPS * 32) rnn_step_kernel(const float* __restrict__ gx,    // (B,L,NG*H)
@@ -30,12 +32,7 @@ __global__ void __launch_bounds__(RNN_WARPS * 32) rnn_step_kernel(const float* _
     const int nb = min(RNN_BT, B - b0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int j = blockIdx.x * RNN_WARPS + warp;
-    if (t > 0) {
-        for (int i = threadIdx.x; i < RNN_BT * H; i += blockDim.x) {
-            int bb = i / H, k = i - bb * H;
-            hs[i] = bb < nb ? out[((long long)(b0 + bb) * L + (t - 1)) * H + k] : 0.f;
-        }
-    }
+    if (t > 0) load_h_tile(hs, out, b0, nb, L, H, t - 1);
     __syncthreads();
     if (j >= H) return;
     float acc[NG][RNN_BT];
@@ -89,6 +86,174 @@ __global__ void __launch_bounds__(RNN_WARPS * 32) rnn_step_kernel(const float* _
     out[((long long)b * L + t) * H + j] = hnew;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Persistent variant: ONE cooperative launch per layer.  CTA c owns `upb` hidden units (one warp each); their NG
+// rows of W_hh are loaded into shared memory once and stay there for all L time steps (5.76 MB of LSTM weights
+// spread over ~120 SMs = 48 KB each), so a time step costs one grid-wide barrier + the broadcast of h_{t-1} (B x H
+// floats through L2) instead of a kernel launch that re-streams W_hh.  Batch rows are processed in groups of 16 that
+// share the resident weights.  Arithmetic order per (unit, batch row) is identical to rnn_step_kernel, so both
+// variants give bit-identical states.
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// All CTAs of a cooperative launch are co-resident; `counter` only grows (zeroed by the host before the launch).
+__device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        unsigned spins = 0;
+        while (ld_acquire_u32(counter) < target) {
+            if (++spins > (1u << 28)) __trap();  // a scheduling bug must fault, never hang the GPU
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// hs[bb][k] = out[b0 + bb][t][k] for bb < nb (0 beyond): L2 loads (.cg: the rows were written by other SMs in this
+// same launch), 4 independent 128-bit requests in flight per thread.
+__device__ __forceinline__ void load_h_tile(float* hs, const float* out, int b0, int nb, int L, int H, int t) {
+    if ((H & 3) == 0 && aligned16(out)) {
+        const int H4 = H >> 2, total = RNN_BT * H4;
+        for (int i0 = threadIdx.x; i0 < total; i0 += 4 * blockDim.x) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * blockDim.x;
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i < total) {
+                    const int bb = i / H4, k4 = i - bb * H4;
+                    if (bb < nb)
+                        v[u] = __ldcg(reinterpret_cast<const float4*>(out + ((long long)(b0 + bb) * L + t) * H) + k4);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * blockDim.x;
+                if (i < total) reinterpret_cast<float4*>(hs)[i] = v[u];
+            }
+        }
+    } else {
+        for (int i = threadIdx.x; i < RNN_BT * H; i += blockDim.x) {
+            int bb = i / H, k = i - bb * H;
+            hs[i] = bb < nb ? __ldcg(out + ((long long)(b0 + bb) * L + t) * H + k) : 0.f;
+        }
+    }
+}
+
+template <int NG>
+__global__ void __launch_bounds__(512) rnn_layer_persistent_kernel(const float* __restrict__ gx,    // (B,L,NG*H)
+                                                                   const float* __restrict__ W_hh,  // (NG*H,H)
+                                                                   const float* __restrict__ b_hh,  // (NG*H)
+                                                                   float* out,                      // (B,L,H)
+                                                                   float* c,                        // (B,H) LSTM
+                                                                   unsigned* bar, int B, int L, int H, int upb) {
+    extern __shared__ float smem[];
+    float* Ws = smem;                                 // [upb][NG][H]
+    float* hs = smem + (size_t)upb * NG * H;          // [RNN_BT][H]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int j = blockIdx.x * upb + warp;
+    const bool unit_ok = warp < upb && j < H;
+    if (unit_ok) {
+        if ((H & 3) == 0 && aligned16(W_hh)) {  // 128-bit loads, NG*4 independent requests in flight per lane
+            const int H4 = H >> 2;
+            for (int k4 = lane; k4 < H4; k4 += 128) {
+                float4 v[NG][4];
+#pragma unroll
+                for (int g = 0; g < NG; ++g)
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (k4 + 32 * u < H4)
+                            v[g][u] = __ldg(reinterpret_cast<const float4*>(W_hh + ((long long)g * H + j) * H) + k4 + 32 * u);
+#pragma unroll
+                for (int g = 0; g < NG; ++g)
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (k4 + 32 * u < H4)
+                            reinterpret_cast<float4*>(Ws + ((size_t)warp * NG + g) * H)[k4 + 32 * u] = v[g][u];
+            }
+        } else {
+#pragma unroll
+            for (int g = 0; g < NG; ++g)
+                for (int k = lane; k < H; k += 32)
+                    Ws[((size_t)warp * NG + g) * H + k] = W_hh[((long long)g * H + j) * H + k];
+        }
+    }
+    float bh[NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) bh[g] = unit_ok ? b_hh[g * H + j] : 0.f;
+    const float* Wr = Ws + (size_t)warp * NG * H;
+    __syncthreads();
+    for (int t = 0; t < L; ++t) {
+        for (int b0 = 0; b0 < B; b0 += RNN_BT) {
+            const int nb = min(RNN_BT, B - b0);
+            // input contributions of this step do not depend on h: request them before waiting on the h broadcast
+            float gxv[NG];
+#pragma unroll
+            for (int g = 0; g < NG; ++g)
+                gxv[g] = (unit_ok && lane < nb) ? __ldg(gx + ((long long)(b0 + lane) * L + t) * (NG * H) + g * H + j) : 0.f;
+            if (t > 0) load_h_tile(hs, out, b0, nb, L, H, t - 1);
+            __syncthreads();
+            if (unit_ok) {
+                float acc[NG][RNN_BT];
+#pragma unroll
+                for (int g = 0; g < NG; ++g)
+#pragma unroll
+                    for (int bb = 0; bb < RNN_BT; ++bb) acc[g][bb] = 0.f;
+                if (t > 0) {
+                    for (int k = lane; k < H; k += 32) {
+                        float w[NG];
+#pragma unroll
+                        for (int g = 0; g < NG; ++g) w[g] = Wr[g * H + k];
+#pragma unroll
+                        for (int bb = 0; bb < RNN_BT; ++bb) {
+                            float hv = hs[bb * H + k];
+#pragma unroll
+                            for (int g = 0; g < NG; ++g) acc[g][bb] = fmaf(w[g], hv, acc[g][bb]);
+                        }
+                    }
+                }
+                float mine[NG];
+#pragma unroll
+                for (int g = 0; g < NG; ++g) mine[g] = 0.f;
+#pragma unroll
+                for (int g = 0; g < NG; ++g)
+#pragma unroll
+                    for (int bb = 0; bb < RNN_BT; ++bb) {
+                        float s = warp_sum(acc[g][bb]);
+                        if (lane == bb) mine[g] = s;
+                    }
+                if (lane < nb) {
+                    const int b = b0 + lane;
+                    float hprev = t > 0 ? hs[lane * H + j] : 0.f;
+                    float hnew;
+                    if (NG == 4) {
+                        float pi = gxv[0] + bh[0] + mine[0];
+                        float pf = gxv[1] + bh[1] + mine[1];
+                        float pg = gxv[2] + bh[2] + mine[2];
+                        float po = gxv[NG - 1] + bh[NG - 1] + mine[NG - 1];
+                        float cprev = t > 0 ? c[(long long)b * H + j] : 0.f;
+                        float cn = sigmoid_exact(pf) * cprev + sigmoid_exact(pi) * tanhf(pg);
+                        c[(long long)b * H + j] = cn;
+                        hnew = sigmoid_exact(po) * tanhf(cn);
+                    } else {
+                        float r = sigmoid_exact(gxv[0] + mine[0] + bh[0]);
+                        float z = sigmoid_exact(gxv[1] + mine[1] + bh[1]);
+                        float n = tanhf(gxv[2] + r * (mine[2] + bh[2]));
+                        hnew = (1.f - z) * n + z * hprev;
+                    }
+                    out[((long long)b * L + t) * H + j] = hnew;
+                }
+            }
+            __syncthreads();  // hs is overwritten by the next batch group / time step
+        }
+        if (t + 1 < L) grid_barrier(bar, (unsigned)(t + 1) * gridDim.x);
+    }
+}
+
 // AReLU (model/bm_hrl_agent.py:13-23): relu(x) * (1 + sigmoid(beta)) - relu(-x) * clamp(alpha, 0.01, 0.99)
 __global__ void arelu_kernel(const float* __restrict__ x, const float* __restrict__ alpha_p,
                              const float* __restrict__ beta_p, float* __restrict__ y, long long n) {
@@ -123,11 +288,78 @@ __global__ void __launch_bounds__(128) segment_label_kernel(const float* __restr
 
 using namespace bmhrl;
 
+static int g_rnn_persistent = 1;
+
+// Returns BMHRL_OK / error, or 1 when the shape cannot run as one co-resident grid.
+template <int NG>
+static int launch_rnn_persistent_t(const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B,
+                                   int L, int H, cudaStream_t st) {
+    static int n_sm = 0;
+    static bool attr = false;
+    if (!n_sm) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    }
+    if (!attr) {
+        if (cudaFuncSetAttribute(rnn_layer_persistent_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 220 * 1024) != cudaSuccess) {
+            bmhrl_set_error("rnn persistent: cannot raise the shared-memory limit");
+            return BMHRL_ERR_CUDA;
+        }
+        attr = true;
+    }
+    // smallest units-per-block whose grid is co-resident (1 CTA per SM is assumed; smaller smem only helps)
+    int upb = (H + n_sm - 1) / n_sm;
+    for (; upb <= 16; ++upb) {
+        const size_t smem = sizeof(float) * ((size_t)upb * NG * H + (size_t)RNN_BT * H);
+        if (smem > 220 * 1024) return 1;
+        int per_sm = 0;
+        const int threads = upb * 32 < 256 ? 256 : upb * 32;  // warps beyond `upb` only help broadcasting h
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rnn_layer_persistent_kernel<NG>, threads, smem) !=
+            cudaSuccess) {
+            bmhrl_set_error("rnn persistent: occupancy query failed");
+            return BMHRL_ERR_CUDA;
+        }
+        const int grid = (H + upb - 1) / upb;
+        if (per_sm * n_sm < grid) continue;
+        float* c = ws;
+        unsigned* bar = reinterpret_cast<unsigned*>(ws + (size_t)B * H);
+        if (cudaMemsetAsync(bar, 0, sizeof(unsigned), st) != cudaSuccess) {
+            bmhrl_set_error("rnn persistent: memset failed");
+            return BMHRL_ERR_CUDA;
+        }
+        void* args[] = {(void*)&gx, (void*)&W_hh, (void*)&b_hh, (void*)&out, (void*)&c, (void*)&bar,
+                        (void*)&B,  (void*)&L,    (void*)&H,    (void*)&upb};
+        cudaError_t e = cudaLaunchCooperativeKernel((const void*)rnn_layer_persistent_kernel<NG>, dim3(grid),
+                                                    dim3(threads), args, smem, st);
+        if (e != cudaSuccess) {
+            bmhrl_set_error(cudaGetErrorString(e));
+            return BMHRL_ERR_CUDA;
+        }
+        bmhrl_count_launch(1);
+        return BMHRL_OK;
+    }
+    return 1;
+}
+
+static int launch_rnn_persistent(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws,
+                                 int B, int L, int H, cudaStream_t st) {
+    return cell == 0 ? launch_rnn_persistent_t<4>(gx, W_hh, b_hh, out, ws, B, L, H, st)
+                     : launch_rnn_persistent_t<3>(gx, W_hh, b_hh, out, ws, B, L, H, st);
+}
+
+extern "C" long long bmhrl_rnn_ws_floats(int B, int H) { return (long long)B * H + 32; }
+extern "C" int bmhrl_rnn_set_persistent(int on) {
+    g_rnn_persistent = on ? 1 : 0;
+    return BMHRL_OK;
+}
+
 extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out,
-                                   float* c_ws, int B, int L, int H, void* stream) {
+                                   float* ws, int B, int L, int H, void* stream) {
     BMHRL_CHECK_ARG(cell == 0 || cell == 1, "bmhrl_rnn_layer_f32: cell must be 0 (LSTM) or 1 (GRU)");
     BMHRL_CHECK_ARG(gx && W_hh && b_hh && out, "bmhrl_rnn_layer_f32: null pointer");
-    BMHRL_CHECK_ARG(cell == 1 || c_ws, "bmhrl_rnn_layer_f32: LSTM needs the (B,H) cell-state workspace");
+    BMHRL_CHECK_ARG(cell == 1 || ws, "bmhrl_rnn_layer_f32: LSTM needs the workspace (bmhrl_rnn_ws_floats)");
     BMHRL_CHECK_ARG(B >= 0 && L >= 0 && H > 0, "bmhrl_rnn_layer_f32: bad sizes");
     if (B == 0 || L == 0) return BMHRL_OK;
     cudaStream_t st = (cudaStream_t)stream;
@@ -145,9 +377,13 @@ extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh,
         }
         attr_set[cell] = true;
     }
+    if (g_rnn_persistent && ws) {
+        int rc = launch_rnn_persistent(cell, gx, W_hh, b_hh, out, ws, B, L, H, st);
+        if (rc != 1) return rc;  // 1 = shape does not fit the persistent kernel: use the per-step kernels
+    }
     dim3 grid((H + RNN_WARPS - 1) / RNN_WARPS, (B + RNN_BT - 1) / RNN_BT);
     for (int t = 0; t < L; ++t) {
-        if (cell == 0) rnn_step_kernel<4><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, c_ws, B, L, H, t);
+        if (cell == 0) rnn_step_kernel<4><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, ws, B, L, H, t);
         else rnn_step_kernel<3><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, nullptr, B, L, H, t);
         BMHRL_POST_LAUNCH("rnn_step");
     }

@@ -471,13 +471,36 @@ class BMHrlAgent(nn.Module):
         V, A = self._encode_features(x)
         return self.predict_with_features(C, V, A, mask)
 
+    concurrent_branches = True  # critic / worker fusion stack on side streams (same results, fewer idle SMs)
+
     def predict_with_features(self, C, V, A, mask):
-        """:637-651."""
-        _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
-        C = self.pos_enc_C(C)
-        Va, Av = self.bm_enc((V, A), mask)
-        worker_feat = self.bm_worker_fus((C, (Av, Va)), mask)
-        manager_feat = self.bm_manager_fus((C, (Av, Va)), mask)
+        """:637-651.  The frozen critic (depends only on the caption embedding) and the worker fusion stack
+        (independent of the manager one, model/bm_hrl_agent.py:646-647) are forked onto side streams."""
+        if not self.concurrent_branches:
+            _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
+            C = self.pos_enc_C(C)
+            Va, Av = self.bm_enc((V, A), mask)
+            worker_feat = self.bm_worker_fus((C, (Av, Va)), mask)
+            manager_feat = self.bm_manager_fus((C, (Av, Va)), mask)
+        else:
+            cur = torch.cuda.current_stream(C.device)
+            s_critic, s_worker = ops.side_stream(C.device, 0), ops.side_stream(C.device, 1)
+            s_critic.wait_stream(cur)
+            with torch.cuda.stream(s_critic):
+                _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
+            C = self.pos_enc_C(C)
+            Va, Av = self.bm_enc((V, A), mask)
+            s_worker.wait_stream(cur)
+            with torch.cuda.stream(s_worker):
+                worker_feat = self.bm_worker_fus((C, (Av, Va)), mask)
+            manager_feat = self.bm_manager_fus((C, (Av, Va)), mask)
+            cur.wait_stream(s_critic)
+            cur.wait_stream(s_worker)
+            if not torch.cuda.is_current_stream_capturing():  # eager mode: tell the allocator about the cross-stream uses
+                for t in (C, Av, Va):
+                    t.record_stream(s_worker)
+                segment_labels.record_stream(cur)
+                worker_feat.record_stream(cur)
         goals = self.manager(manager_feat, segment_labels)
         pred = self.worker(worker_feat, goals, mask["C_mask"])
         return pred, worker_feat, manager_feat, goals, segment_labels

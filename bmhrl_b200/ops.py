@@ -78,6 +78,31 @@ class _Rng:
 RNG = _Rng()
 
 
+# ----------------------------------------------------------------------------------------------------------------
+# side streams: independent branches of the agent (frozen critic, worker fusion stack) run concurrently with the main
+# stream; fork/join is plain event ordering, so it is captured into the step's CUDA graph as parallel branches.
+# ----------------------------------------------------------------------------------------------------------------
+_SIDE = {}
+
+
+def side_stream(device, slot):
+    dev = torch.device(device)
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), slot)
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=key[0])
+    return _SIDE[key]
+
+
+def join_side_streams(device=None):
+    """Makes the current stream wait for everything enqueued on the side streams.  Backward kernels that accumulate
+    straight into a FusedAdam flat buffer run on the stream of their forward op and hand autograd no gradient tensor,
+    so the trainer joins explicitly before the optimiser step."""
+    cur = torch.cuda.current_stream(device)
+    for (d, _), s in _SIDE.items():
+        if d == cur.device.index:
+            cur.wait_stream(s)
+
+
 def manual_seed(seed, device="cuda"):
     RNG.seed(int(seed), device)
 
@@ -733,7 +758,7 @@ def rnn_layer(cell, x, w_ih, w_hh, b_ih, b_hh):
     with torch.no_grad():
         gx = linear(x, w_ih, b_ih)
         out = torch.empty(B, L, H, device=x.device, dtype=_F32)
-        c = torch.empty(B, H, device=x.device, dtype=_F32) if cell == "lstm" else None
+        c = torch.empty(LIB.raw("bmhrl_rnn_ws_floats")(B, H), device=x.device, dtype=_F32)
         LIB.call("bmhrl_rnn_layer_f32", 0 if cell == "lstm" else 1, _p(gx), _p(_c(w_hh, "w_hh")), _p(_c(b_hh, "b_hh")),
                  _p(out), _p(c), B, L, H, _stream())
     return out

@@ -93,6 +93,7 @@ class BMHRLTrainer:
         n_tokens = self._global_tokens((y != self.pad_idx).sum())
         loss = self.ls.row_sums(pred, y).sum() / n_tokens
         loss.backward()
+        ops.join_side_streams(loss.device)
         self._sync(self.cap_opt)
         self.cap_opt.step()
         return loss.detach()
@@ -146,6 +147,7 @@ class BMHRLTrainer:
         vopt.zero_grad()
         cap_loss, value_loss, _, _, _ = self.rl_losses(batch, train_worker, stabilize, exp_noise)
         cap_loss.backward()
+        ops.join_side_streams(cap_loss.device)
         self._sync(self.cap_opt)
         self.cap_opt.step()
         value_loss.backward()

@@ -126,8 +126,12 @@ int bmhrl_reinforce_gather_bwd_f32(const float* probs, const long long* action, 
 /* ---- frozen SegmentCritic recurrences, forward only (rnn.cu) ------------------------------------------------- */
 /* One nn.LSTM (cell 0, gates i,f,g,o) or nn.GRU (cell 1, gates r,z,n) layer, batch_first, zero initial state
  * (model/bm_hrl_agent.py:192-193,206,209).  gx (B,L,NG*H) = x W_ih^T + b_ih for all steps (bmhrl_linear_fwd_f32);
- * out (B,L,H); c_ws (B,H) cell-state workspace (LSTM only).  Launches L kernels. */
-int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* c_ws, int B,
+ * out (B,L,H); ws: bmhrl_rnn_ws_floats(B,H) floats (cell state + the grid-barrier counter).  One cooperative launch
+ * per layer: W_hh stays resident in shared memory across all L steps (falls back to one launch per step when the
+ * layer does not fit one co-resident grid, or after bmhrl_rnn_set_persistent(0); both give identical bits). */
+long long bmhrl_rnn_ws_floats(int B, int H);
+int bmhrl_rnn_set_persistent(int on);
+int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B,
                         int L, int H, void* stream);
 /* AReLU model/bm_hrl_agent.py:13-23 (alpha, beta: device scalars). */
 int bmhrl_arelu_f32(const float* x, const float* alpha, const float* beta, float* y, long long n, void* stream);
