@@ -94,11 +94,15 @@ class BMFusionLayer(nn.Module):
         Av, Va = memory
 
         C = self.res_layer_self_att(C, AttentionSublayer(self.self_att, None, None, masks['C_mask']))
-        Ca = self.res_layer_enc_att_A(C, AttentionSublayer(self.enc_att_A, Av, Av, masks['A_mask']))
-        Cv = self.res_layer_enc_att_V(C, AttentionSublayer(self.enc_att_V, Va, Va, masks['V_mask']))
+        def branch_a():
+            Ca = self.res_layer_enc_att_A(C, AttentionSublayer(self.enc_att_A, Av, Av, masks['A_mask']))
+            return ops.layer_norm(Ca, self.normCA.weight, self.normCA.bias, self.normCA.eps)
 
-        Ca = ops.layer_norm(Ca, self.normCA.weight, self.normCA.bias, self.normCA.eps)
-        Cv = ops.layer_norm(Cv, self.normCV.weight, self.normCV.bias, self.normCV.eps)
+        def branch_v():
+            Cv = self.res_layer_enc_att_V(C, AttentionSublayer(self.enc_att_V, Va, Va, masks['V_mask']))
+            return ops.layer_norm(Cv, self.normCV.weight, self.normCV.bias, self.normCV.eps)
+
+        Cv, Ca = ops.parallel(C.device, branch_v, branch_a)
 
         # sigmoid(clamp(a_v_constant, -2, 2)) * Cv + (1 - .) * Ca
         fused_features = ops.gated_mix(Cv, Ca, self.a_v_constant)
@@ -240,14 +244,20 @@ class BMEncoderLayer(nn.Module):
         M1_mask, M2_mask = masks
 
         # 1. self attention
-        M1 = self.res_layers_M1[0](M1, AttentionSublayer(self.self_att_M1, None, None, M1_mask))
-        M2 = self.res_layers_M2[0](M2, AttentionSublayer(self.self_att_M2, None, None, M2_mask))
-        # 2. bimodal attention: queries are normed, keys / values are the un-normed other modality
-        M1m2 = self.res_layers_M1[1](M1, AttentionSublayer(self.bi_modal_att_M1, M2, M2, M2_mask))
-        M2m1 = self.res_layers_M2[1](M2, AttentionSublayer(self.bi_modal_att_M2, M1, M1, M1_mask))
-        # 3. position-wise feed forward
-        M1m2 = self.res_layers_M1[2](M1m2, self.feed_forward_M1)
-        M2m1 = self.res_layers_M2[2](M2m1, self.feed_forward_M2)
+        # (the two modalities are independent inside each stage: they run as concurrent branches)
+        dev = M1.device
+        M1, M2 = ops.parallel(
+            dev, lambda: self.res_layers_M1[0](M1, AttentionSublayer(self.self_att_M1, None, None, M1_mask)),
+            lambda: self.res_layers_M2[0](M2, AttentionSublayer(self.self_att_M2, None, None, M2_mask)))
+        # 2. bimodal attention (queries are normed, keys / values are the un-normed other modality), then
+        # 3. position-wise feed forward of the same modality
+        M1m2, M2m1 = ops.parallel(
+            dev, lambda: self.res_layers_M1[2](
+                self.res_layers_M1[1](M1, AttentionSublayer(self.bi_modal_att_M1, M2, M2, M2_mask)),
+                self.feed_forward_M1),
+            lambda: self.res_layers_M2[2](
+                self.res_layers_M2[1](M2, AttentionSublayer(self.bi_modal_att_M2, M1, M1, M1_mask)),
+                self.feed_forward_M2))
         return M1m2, M2m1
 
 
@@ -476,7 +486,7 @@ class BMHrlAgent(nn.Module):
     def predict_with_features(self, C, V, A, mask):
         """:637-651.  The frozen critic (depends only on the caption embedding) and the worker fusion stack
         (independent of the manager one, model/bm_hrl_agent.py:646-647) are forked onto side streams."""
-        if not self.concurrent_branches:
+        if not (self.concurrent_branches and ops.CONCURRENT):
             _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
             C = self.pos_enc_C(C)
             Va, Av = self.bm_enc((V, A), mask)
@@ -484,7 +494,7 @@ class BMHrlAgent(nn.Module):
             manager_feat = self.bm_manager_fus((C, (Av, Va)), mask)
         else:
             cur = torch.cuda.current_stream(C.device)
-            s_critic, s_worker = ops.side_stream(C.device, 0), ops.side_stream(C.device, 1)
+            s_critic, s_worker = ops.side_stream(C.device, 8), ops.side_stream(C.device, 9)
             s_critic.wait_stream(cur)
             with torch.cuda.stream(s_critic):
                 _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)

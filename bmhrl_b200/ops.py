@@ -82,25 +82,60 @@ RNG = _Rng()
 # side streams: independent branches of the agent (frozen critic, worker fusion stack) run concurrently with the main
 # stream; fork/join is plain event ordering, so it is captured into the step's CUDA graph as parallel branches.
 # ----------------------------------------------------------------------------------------------------------------
-_SIDE = {}
+_SIDE = {}        # slot key -> stream; keys are paths ("main", i, j, ...) so nested forks get their own streams
+_SIDE_KEY = {}    # cuda_stream handle -> slot key
+_DIRTY = set()    # side streams that received work since the last join_side_streams()
+CONCURRENT = True  # False: every branch runs on the caller's stream (debugging / profiling aid)
 
 
 def side_stream(device, slot):
+    """Side stream number `slot` of the stream that is current on `device` (created on first use)."""
     dev = torch.device(device)
-    key = (dev.index if dev.index is not None else torch.cuda.current_device(), slot)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    cur = torch.cuda.current_stream(idx)
+    key = _SIDE_KEY.get((idx, cur.cuda_stream), (idx, "main")) + (slot,)
     if key not in _SIDE:
-        _SIDE[key] = torch.cuda.Stream(device=key[0])
+        _SIDE[key] = torch.cuda.Stream(device=idx)
+        _SIDE_KEY[(idx, _SIDE[key].cuda_stream)] = key
+    _DIRTY.add(key)
     return _SIDE[key]
 
 
-def join_side_streams(device=None):
-    """Makes the current stream wait for everything enqueued on the side streams.  Backward kernels that accumulate
-    straight into a FusedAdam flat buffer run on the stream of their forward op and hand autograd no gradient tensor,
-    so the trainer joins explicitly before the optimiser step."""
+def parallel(device, *thunks):
+    """Runs independent branches concurrently: thunk 0 on the current stream, the others on side streams that are
+    forked from / joined back into it.  Returns the list of results.  (Same kernels, same arithmetic: only the
+    stream each branch is enqueued on differs.)"""
+    if not CONCURRENT or len(thunks) == 1:
+        return [t() for t in thunks]
     cur = torch.cuda.current_stream(device)
-    for (d, _), s in _SIDE.items():
-        if d == cur.device.index:
-            cur.wait_stream(s)
+    out = [None] * len(thunks)
+    sides = []
+    for i in range(1, len(thunks)):
+        s = side_stream(device, i)
+        s.wait_stream(cur)
+        with torch.cuda.stream(s):
+            out[i] = thunks[i]()
+        sides.append(s)
+    out[0] = thunks[0]()
+    eager = not torch.cuda.is_current_stream_capturing()
+    for i, s in enumerate(sides, 1):
+        cur.wait_stream(s)
+        if eager:
+            for t in (out[i] if isinstance(out[i], (tuple, list)) else (out[i],)):
+                if torch.is_tensor(t):
+                    t.record_stream(cur)
+    return out
+
+
+def join_side_streams(device=None):
+    """Makes the current stream wait for everything enqueued on the side streams since the last join.  Backward
+    kernels that accumulate straight into a FusedAdam flat buffer run on the stream of their forward op and hand
+    autograd no gradient tensor, so the trainer joins explicitly before the optimiser step."""
+    cur = torch.cuda.current_stream(device)
+    for key in sorted(_DIRTY, key=len, reverse=True):
+        if key[0] == cur.device.index:
+            cur.wait_stream(_SIDE[key])
+            _DIRTY.discard(key)
 
 
 def manual_seed(seed, device="cuda"):
