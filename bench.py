@@ -269,6 +269,10 @@ def run_gpu(args):
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[args.workload]()
     ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode(args.math)
+    if os.environ.get("BMHRL_ATTN_FUSED") is not None:  # experiment switches (default: fused tcgen05 attention, on)
+        _lib.LIB.call("bmhrl_attn_tuning", int(os.environ["BMHRL_ATTN_FUSED"]))
+    if os.environ.get("BMHRL_CONCURRENT") is not None:
+        ops.CONCURRENT = bool(int(os.environ["BMHRL_CONCURRENT"]))
 
     # pinned host batches (a different one per rank and per step slot), H2D'd inside the e2e region
     n_host = 4

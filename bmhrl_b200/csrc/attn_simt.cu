@@ -80,10 +80,30 @@ __global__ void __launch_bounds__(128) masked_softmax_bwd_kernel(float* __restri
 // the PV GEMM epilogue: idx = ((b*H + h)*Sq + s)*dk + d.
 __global__ void attn_dropout_bwd_kernel(const float* __restrict__ dO, long long ldo, long long bso,
                                         float* __restrict__ out, int B, int H, int Sq, int dk, float p,
-                                        const unsigned long long* __restrict__ rng, unsigned int salt) {
+                                        const unsigned long long* __restrict__ rng, unsigned int salt, int vec) {
     const long long n = (long long)B * H * Sq * dk;
     const float ks = 1.f / (1.f - p);
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (vec) {  // dk % 4 == 0 and 16-byte aligned rows: 4 elements = one Philox block, one 128-bit access
+        for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < (n >> 2); i4 += stride) {
+            const long long i = i4 << 2;
+            int d = (int)(i % dk);
+            long long t = i / dk;
+            int s = (int)(t % Sq);
+            t /= Sq;
+            int h = (int)(t % H);
+            int b = (int)(t / H);
+            float4 g = ld_f4(dO + (long long)b * bso + (long long)s * ldo + h * dk + d);
+            const Philox4 rb = philox_block(rng, salt, (unsigned long long)i4);
+            g.x = u32_to_unit(rb.x) >= p ? g.x * ks : 0.f;
+            g.y = u32_to_unit(rb.y) >= p ? g.y * ks : 0.f;
+            g.z = u32_to_unit(rb.z) >= p ? g.z * ks : 0.f;
+            g.w = u32_to_unit(rb.w) >= p ? g.w * ks : 0.f;
+            st_f4(out + ((long long)b * Sq + s) * ((long long)H * dk) + h * dk + d, g);
+        }
+        return;
+    }
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         int d = (int)(i % dk);
         long long t = i / dk;
         int s = (int)(t % Sq);
@@ -121,14 +141,18 @@ extern "C" int bmhrl_mha_core_fwd_f32(const float* Q, long long ldq, long long b
     // a causal mask without an explicit mask is still a mask: the reference only applies tril when mask is given,
     // callers pass mask_kind 0 + causal 0 for "mask is None".
     int rc;
+    if (math_mode() == 1) {  // tensor-core mode: one fused tcgen05 kernel (attn_tc.cu)
+        rc = launch_attn_fwd_tc(Q, ldq, bsq, K, ldk, bsk, V, ldv, bsv, mask, mask_kind, causal, O, ldo, bso, P, ldp, B, H,
+                                Sq, Sk, dk, drop_p, rng_state, salt, st);
+        if (rc != 1) return rc;
+    }
     {   // S = scale * Q K^T
         GemmParams p{};
         p.A = Q; p.sAm = ldq; p.sAk = 1; p.bAo = bsq; p.bAi = dk;
         p.B = K; p.sBk = 1; p.sBn = ldk; p.bBo = bsk; p.bBi = dk;
         p.C = P; p.ldc = ldp; p.bCo = (long long)H * Sq * ldp; p.bCi = (long long)Sq * ldp;
         p.M = Sq; p.N = Sk; p.K = dk; p.Hdiv = H; p.alpha = scale; p.beta = 0.f;
-        gemm_set_vec_flags(p);
-        if ((rc = launch_gemm_simt(p, B * H, st)) != BMHRL_OK) return rc;
+        if ((rc = launch_gemm_auto(p, B * H, st)) != BMHRL_OK) return rc;
     }
     {
         long long rows = (long long)B * H * Sq;
@@ -143,8 +167,7 @@ extern "C" int bmhrl_mha_core_fwd_f32(const float* Q, long long ldq, long long b
         p.C = O; p.ldc = ldo; p.bCo = bso; p.bCi = dk;
         p.M = Sq; p.N = dk; p.K = Sk; p.Hdiv = H; p.alpha = 1.f; p.beta = 0.f;
         p.drop_p = drop_p; p.rng = rng_state; p.salt = salt;
-        gemm_set_vec_flags(p);
-        if ((rc = launch_gemm_simt(p, B * H, st)) != BMHRL_OK) return rc;
+        if ((rc = launch_gemm_auto(p, B * H, st)) != BMHRL_OK) return rc;
     }
     return BMHRL_OK;
 }
@@ -168,9 +191,11 @@ extern "C" int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long 
     long long ldg = ldo, bsg = bso;
     if (drop_p > 0.f) {
         long long n = (long long)B * H * Sq * dk;
-        int blocks = (int)((n + 255) / 256);
+        const int vec = (dk % 4 == 0) && (ldo % 4 == 0) && (bso % 4 == 0) && aligned16(dO) && aligned16(ws_dO);
+        const long long items = vec ? n / 4 : n;
+        int blocks = (int)((items + 255) / 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        attn_dropout_bwd_kernel<<<blocks, 256, 0, st>>>(dO, ldo, bso, ws_dO, B, H, Sq, dk, drop_p, rng_state, salt);
+        attn_dropout_bwd_kernel<<<blocks, 256, 0, st>>>(dO, ldo, bso, ws_dO, B, H, Sq, dk, drop_p, rng_state, salt, vec);
         BMHRL_POST_LAUNCH("attn_dropout_bwd");
         g = ws_dO; ldg = (long long)H * dk; bsg = (long long)Sq * H * dk;
     }
@@ -180,8 +205,7 @@ extern "C" int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long 
         p.B = g; p.sBk = ldg; p.sBn = 1; p.bBo = bsg; p.bBi = dk;
         p.C = dV; p.ldc = lddv; p.bCo = bsdv; p.bCi = dk;
         p.M = Sk; p.N = dk; p.K = Sq; p.Hdiv = H; p.alpha = 1.f;
-        gemm_set_vec_flags(p);
-        if ((rc = launch_gemm_simt(p, B * H, st)) != BMHRL_OK) return rc;
+        if ((rc = launch_gemm_auto(p, B * H, st)) != BMHRL_OK) return rc;
     }
     {   // dP = g V^T     (Sq x Sk) = (Sq x dk)(dk x Sk)
         GemmParams p{};
@@ -189,8 +213,7 @@ extern "C" int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long 
         p.B = V; p.sBk = 1; p.sBn = ldv; p.bBo = bsv; p.bBi = dk;
         p.C = ws_dP; p.ldc = ldp; p.bCo = pbo; p.bCi = pbi;
         p.M = Sq; p.N = Sk; p.K = dk; p.Hdiv = H; p.alpha = 1.f;
-        gemm_set_vec_flags(p);
-        if ((rc = launch_gemm_simt(p, B * H, st)) != BMHRL_OK) return rc;
+        if ((rc = launch_gemm_auto(p, B * H, st)) != BMHRL_OK) return rc;
     }
     {
         long long rows = (long long)B * H * Sq;
@@ -204,8 +227,7 @@ extern "C" int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long 
         p.B = K; p.sBk = ldk; p.sBn = 1; p.bBo = bsk; p.bBi = dk;
         p.C = dQ; p.ldc = lddq; p.bCo = bsdq; p.bCi = dk;
         p.M = Sq; p.N = dk; p.K = Sk; p.Hdiv = H; p.alpha = 1.f;
-        gemm_set_vec_flags(p);
-        if ((rc = launch_gemm_simt(p, B * H, st)) != BMHRL_OK) return rc;
+        if ((rc = launch_gemm_auto(p, B * H, st)) != BMHRL_OK) return rc;
     }
     {   // dK = dS^T Q    (Sk x dk) = (Sk x Sq)(Sq x dk)
         GemmParams p{};
@@ -213,8 +235,7 @@ extern "C" int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long 
         p.B = Q; p.sBk = ldq; p.sBn = 1; p.bBo = bsq; p.bBi = dk;
         p.C = dK; p.ldc = lddk; p.bCo = bsdk; p.bCi = dk;
         p.M = Sk; p.N = dk; p.K = Sq; p.Hdiv = H; p.alpha = 1.f;
-        gemm_set_vec_flags(p);
-        if ((rc = launch_gemm_simt(p, B * H, st)) != BMHRL_OK) return rc;
+        if ((rc = launch_gemm_auto(p, B * H, st)) != BMHRL_OK) return rc;
     }
     return BMHRL_OK;
 }

@@ -45,7 +45,19 @@ struct TcGemmArgs {
     float alpha, beta;
     const float* bias; int act; const float* resid; long long ldr;
     float drop_p; const unsigned long long* rng; unsigned int salt;
+    // batched problems: z in [0, batch): outer = z / Hdiv, inner = z % Hdiv; operand offsets outer*b?o + inner*b?i
+    // elements (batch <= 1: a single problem, everything below ignored)
+    int batch, Hdiv;
+    long long bAo, bAi, bBo, bBi, bCo, bCi;
 };
+// Routes a GemmParams problem to the tensor-core kernel when the math mode asks for it and TMA can address the
+// operands, else to the fp32 SIMT kernel.
+int launch_gemm_auto(GemmParams& p, int batch, cudaStream_t st);
+// fused tcgen05 attention forward (attn_tc.cu); returns 1 when the shape is outside what the fused kernel handles
+int launch_attn_fwd_tc(const float* Q, long long ldq, long long bsq, const float* K, long long ldk, long long bsk,
+                       const float* V, long long ldv, long long bsv, const unsigned char* mask, int mask_kind, int causal,
+                       float* O, long long ldo, long long bso, float* P, int ldp, int B, int H, int Sq, int Sk, int dk,
+                       float drop_p, const unsigned long long* rng, unsigned int salt, cudaStream_t st);
 int math_mode();                                  // 0 exact fp32 (SIMT), 1 tf32 (tcgen05)
 bool tc_gemm_supported(const TcGemmArgs& a);      // alignment / pitch constraints of TMA
 int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st);

@@ -16,6 +16,7 @@
 // CTA = 192 threads: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer (one elected thread), warps 2-5
 // epilogue (tcgen05.ld -> registers -> global).  Tile 128 x BN x 32 (32 fp32 = one 128-byte swizzle row),
 // STAGES-deep mbarrier ring.  One output tile (x one K split) per CTA.
+#include <stdio.h>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "gemm_simt.cuh"
@@ -43,6 +44,8 @@ struct TcEpilogue {
     const unsigned long long* rng;
     unsigned int salt;
     int vec_ok;  // C (and resid) rows allow 128-bit access
+    int batched, Hdiv;       // blockIdx.z = z * split_k + split; z -> (outer = z / Hdiv, inner = z % Hdiv)
+    long long bCo, bCi;      // C offset of batch entry z, elements
 };
 
 template <int BN, int STAGES>
@@ -62,8 +65,10 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
-    const int kb0 = blockIdx.z * p.kb_per_split;
+    const int zb = blockIdx.z / p.split_k;                 // batch entry
+    const int kb0 = (blockIdx.z - zb * p.split_k) * p.kb_per_split;
     const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+    const int z_out = zb / p.Hdiv, z_in = zb - z_out * p.Hdiv;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -91,6 +96,23 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
                 mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
                 const uint32_t sA = base + s * STAGE_BYTES, sB = sA + TC_A_BYTES;
                 const int k = kb * TC_BK;
+                if (p.batched) {
+                    if (!p.a_mn) {
+                        tma_load_4d(sA, &tmA, full_bar(s), k, m0, z_in, z_out);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < TC_BM / 32; ++c)
+                            tma_load_4d(sA + c * (TC_BK * 128), &tmA, full_bar(s), m0 + c * 32, k, z_in, z_out);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_4d(sB, &tmB, full_bar(s), k, n0, z_in, z_out);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BN / 32; ++c)
+                            tma_load_4d(sB + c * (TC_BK * 128), &tmB, full_bar(s), n0 + c * 32, k, z_in, z_out);
+                    }
+                    continue;
+                }
                 if (!p.a_mn) {
                     tma_load_2d(sA, &tmA, full_bar(s), k, m0);  // box {32 k, 128 m}
                 } else {
@@ -141,7 +163,7 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
             tmem_ld_wait();
             const int nb = n0 + c0;
             if (m < p.M && nb < p.N) {
-                float* crow = p.C + (long long)m * p.ldc + nb;
+                float* crow = p.C + (long long)z_out * p.bCo + (long long)z_in * p.bCi + (long long)m * p.ldc + nb;
                 const float* rrow = p.resid ? p.resid + (long long)m * p.ldr + nb : nullptr;
                 if (p.split_k > 1) {
 #pragma unroll
@@ -151,14 +173,21 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
 #pragma unroll
                     for (int j4 = 0; j4 < 32; j4 += 4) {
                         float v[4];
+                        const unsigned long long e0 = ((unsigned long long)zb * p.M + m) * p.N + nb + j4;
+                        const bool one_block = p.drop_p > 0.f && (e0 & 3ull) == 0;  // 4 elements, one Philox block
+                        Philox4 rb{};
+                        if (one_block) rb = philox_block(p.rng, p.salt, e0 >> 2);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             const int n = nb + j4 + j;
                             float x = p.alpha * __uint_as_float(r[j4 + j]);
                             if (p.bias && n < p.N) x += p.bias[n];
                             if (p.act == 1) x = fmaxf(x, 0.f);
-                            if (p.drop_p > 0.f)
-                                x = dropout_keep(p.rng, p.salt, (unsigned long long)m * p.N + n, p.drop_p) ? x * ks : 0.f;
+                            if (p.drop_p > 0.f) {
+                                const uint32_t u = one_block ? (j == 0 ? rb.x : j == 1 ? rb.y : j == 2 ? rb.z : rb.w)
+                                                             : philox_u32(p.rng, p.salt, e0 + j);
+                                x = u32_to_unit(u) >= p.drop_p ? x * ks : 0.f;
+                            }
                             v[j] = x;
                         }
                         const int n = nb + j4;
@@ -196,11 +225,18 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
 // ---------------------------------------------------------------------------------------------- host side
 static int g_math_mode = 0;  // 0: exact fp32 SIMT; 1: TF32 tensor cores (tcgen05)
 static int g_force_bn = 0, g_force_split = 0;
+static long long g_tc_batched_min_macs = 4ll << 20;
 
 static bool tc_operand_ok(const float* p, long long ld) { return aligned16(p) && ld > 0 && (ld & 3) == 0; }
 
 bool tc_gemm_supported(const TcGemmArgs& a) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return false;
+    if (a.batch > 1) {
+        if (a.resid || a.bias) return false;
+        if (((a.bAo | a.bAi | a.bBo | a.bBi) & 3) != 0 || a.bAo < 0 || a.bAi < 0 || a.bBo < 0 || a.bBi < 0) return false;
+        if (a.Hdiv < 1 || a.batch % a.Hdiv != 0) return false;
+        if ((a.Hdiv > 1 && (a.bAi == 0 || a.bBi == 0)) || (a.batch > a.Hdiv && (a.bAo == 0 || a.bBo == 0))) return false;
+    }
     return tc_operand_ok(a.A, a.lda) && tc_operand_ok(a.B, a.ldb) && get_encode_fn() != nullptr;
 }
 
@@ -226,16 +262,17 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
     const int tiles_m = (a.M + TC_BM - 1) / TC_BM;
     const int num_kb = (a.K + TC_BK - 1) / TC_BK;
     // tile width: the widest BN that still gives >= ~1 CTA per SM; narrow tiles re-read A but fill the machine
+    const int nbatch = a.batch > 1 ? a.batch : 1;
     int BN = 128;
     if (g_force_bn) BN = g_force_bn;
     else {
-        while (BN > 32 && (long long)tiles_m * ((a.N + BN - 1) / BN) < 120) BN >>= 1;
+        while (BN > 32 && (long long)nbatch * tiles_m * ((a.N + BN - 1) / BN) < 120) BN >>= 1;
         if (a.N <= 32) BN = 32; else if (a.N <= 64 && BN > 64) BN = 64;
     }
     const int tiles_n = (a.N + BN - 1) / BN;
     const bool plain = !a.bias && a.act == 0 && !a.resid && a.drop_p == 0.f;
     int split = 1;
-    if (plain) {
+    if (plain && nbatch == 1) {
         if (g_force_split) split = g_force_split;
         else {
             const long long tiles = (long long)tiles_m * tiles_n;
@@ -248,6 +285,18 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
 
     CUtensorMap tmA, tmB;
     bool ok;
+    const CUtensorMapDataType TF = CU_TENSOR_MAP_DATA_TYPE_TFLOAT32;
+    if (nbatch > 1) {
+        const unsigned long long hd = a.Hdiv, ob = nbatch / a.Hdiv;
+        if (!a.a_mn) ok = encode_4d(&tmA, TF, 4, a.A, a.K, a.M, a.lda, hd, a.bAi, ob, a.bAo, TC_BK, TC_BM);
+        else ok = encode_4d(&tmA, TF, 4, a.A, a.M, a.K, a.lda, hd, a.bAi, ob, a.bAo, 32, TC_BK,
+                            CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+        if (ok) {
+            if (!a.b_mn) ok = encode_4d(&tmB, TF, 4, a.B, a.K, a.N, a.ldb, hd, a.bBi, ob, a.bBo, TC_BK, BN);
+            else ok = encode_4d(&tmB, TF, 4, a.B, a.N, a.K, a.ldb, hd, a.bBi, ob, a.bBo, 32, TC_BK,
+                                CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+        }
+    } else {
     if (!a.a_mn) ok = encode_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 4, a.A, a.K, a.M, a.lda, TC_BK, TC_BM);
     else ok = encode_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 4, a.A, a.M, a.K, a.lda, 32, TC_BK,
                         CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
@@ -256,8 +305,13 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
         else ok = encode_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 4, a.B, a.N, a.K, a.ldb, 32, TC_BK,
                             CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
     }
+    }
     if (!ok) {
-        bmhrl_set_error("cuTensorMapEncodeTiled failed");
+        char msg[384];
+        snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d batch=%d Hdiv=%d a_mn=%d b_mn=%d lda=%lld "
+                 "ldb=%lld bAo=%lld bAi=%lld bBo=%lld bBi=%lld BN=%d rc=%d ptr=%p A=%p B=%p)", a.M, a.N, a.K, nbatch, a.Hdiv, a.a_mn, a.b_mn, a.lda,
+                 a.ldb, a.bAo, a.bAi, a.bBo, a.bBi, BN, g_last_encode_rc, g_last_encode_ptr, (const void*)a.A, (const void*)a.B);
+        bmhrl_set_error(msg);
         return BMHRL_ERR_CUDA;
     }
     TcEpilogue ep{};
@@ -266,7 +320,9 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
     ep.a_mn = a.a_mn; ep.b_mn = a.b_mn; ep.alpha = a.alpha; ep.beta = a.beta;
     ep.bias = a.bias; ep.act = a.act; ep.resid = a.resid; ep.ldr = a.ldr;
     ep.drop_p = a.drop_p; ep.rng = a.rng; ep.salt = a.salt;
-    ep.vec_ok = aligned16(a.C) && (a.ldc & 3) == 0 && (!a.resid || (aligned16(a.resid) && (a.ldr & 3) == 0));
+    ep.vec_ok = aligned16(a.C) && (a.ldc & 3) == 0 && (!a.resid || (aligned16(a.resid) && (a.ldr & 3) == 0)) &&
+                (nbatch == 1 || (((a.bCo | a.bCi) & 3) == 0));
+    ep.batched = nbatch > 1; ep.Hdiv = nbatch > 1 ? a.Hdiv : 1; ep.bCo = a.bCo; ep.bCi = a.bCi;
     if (split > 1 && a.beta == 0.f) {  // partial sums are accumulated atomically into a zeroed C
         if (a.ldc == a.N) {
             if (cudaMemsetAsync(a.C, 0, sizeof(float) * (size_t)a.M * a.N, st) != cudaSuccess) return BMHRL_ERR_CUDA;
@@ -275,13 +331,32 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
                 return BMHRL_ERR_CUDA;
         }
     }
-    dim3 grid(tiles_n, tiles_m, split);
+    dim3 grid(tiles_n, tiles_m, split * nbatch);
     if (BN == 128) return launch_tc<128, 4>(tmA, tmB, ep, grid, st);
     if (BN == 64) return launch_tc<64, 4>(tmA, tmB, ep, grid, st);
     return launch_tc<32, 5>(tmA, tmB, ep, grid, st);
 }
 
 int math_mode() { return g_math_mode; }
+
+int launch_gemm_auto(GemmParams& p, int batch, cudaStream_t st) {
+    if (g_math_mode == 1 && !p.bias && !p.resid && p.act == 0 && (p.sAk == 1 || p.sAm == 1) &&
+        (p.sBk == 1 || p.sBn == 1) && (p.beta == 0.f || (p.beta == 1.f && p.drop_p == 0.f))) {
+        TcGemmArgs t{};
+        t.A = p.A; t.a_mn = (p.sAk == 1) ? 0 : 1; t.lda = t.a_mn ? p.sAk : p.sAm;
+        t.B = p.B; t.b_mn = (p.sBk == 1) ? 0 : 1; t.ldb = t.b_mn ? p.sBk : p.sBn;
+        t.C = p.C; t.ldc = p.ldc; t.M = p.M; t.N = p.N; t.K = p.K; t.alpha = p.alpha; t.beta = p.beta;
+        t.drop_p = p.drop_p; t.rng = p.rng; t.salt = p.salt;
+        t.batch = batch; t.Hdiv = p.Hdiv < 1 ? 1 : p.Hdiv;
+        t.bAo = p.bAo; t.bAi = p.bAi; t.bBo = p.bBo; t.bBi = p.bBi; t.bCo = p.bCo; t.bCi = p.bCi;
+        // batched attention-sized contractions: below ~4 M MACs per entry a tensor-core CTA is all prologue /
+        // epilogue latency and the SIMT kernel (48 KB of shared memory, many CTAs per SM) is faster
+        const bool tiny = batch > 1 && (long long)p.M * p.N * p.K < g_tc_batched_min_macs;
+        if (!tiny && tc_gemm_supported(t)) return launch_gemm_tc(t, st);
+    }
+    gemm_set_vec_flags(p);
+    return launch_gemm_simt(p, batch, st);
+}
 
 }  // namespace bmhrl
 
@@ -298,5 +373,6 @@ extern "C" int bmhrl_tc_tuning(int force_bn, int force_split) {
     BMHRL_CHECK_ARG(force_split >= 0, "bmhrl_tc_tuning: split");
     g_force_bn = force_bn;
     g_force_split = force_split;
+    g_tc_batched_min_macs = (force_bn || force_split) ? 0 : (4ll << 20);  // forced tiling: always the tensor-core kernel
     return BMHRL_OK;
 }

@@ -309,11 +309,18 @@ __global__ void __launch_bounds__(256) linear_bwd_prep_kernel(const float* __res
                 g[0] = dY[(long long)m * lddy + n0];
                 if (act == 1) y[0] = Y[(long long)m * ldy + n0];
             }
+            if (act != 1 && drop_p > 0.f && CPT == 4) {  // N % 4 == 0 here: the 4 columns share one Philox block
+                const Philox4 rb = philox_block(rng, salt, ((unsigned long long)m * N + n0) >> 2);
+                g[0] = u32_to_unit(rb.x) >= drop_p ? g[0] * ks : 0.f;
+                g[1 % CPT] = u32_to_unit(rb.y) >= drop_p ? g[1 % CPT] * ks : 0.f;
+                g[2 % CPT] = u32_to_unit(rb.z) >= drop_p ? g[2 % CPT] * ks : 0.f;
+                g[3 % CPT] = u32_to_unit(rb.w) >= drop_p ? g[3 % CPT] * ks : 0.f;
+            }
 #pragma unroll
             for (int j = 0; j < CPT; ++j) {
                 if (act == 1) {
                     g[j] = (y[j] > 0.f) ? g[j] * ks : 0.f;
-                } else if (drop_p > 0.f) {
+                } else if (drop_p > 0.f && CPT != 4) {
                     g[j] = dropout_keep(rng, salt, (unsigned long long)m * N + n0 + j, drop_p) ? g[j] * ks : 0.f;
                 }
                 acc[j] += g[j];

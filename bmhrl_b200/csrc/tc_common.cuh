@@ -59,6 +59,15 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, 
         : "memory");
 }
 
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2,
+                                            int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        :
+        : "r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
 // ------------------------------------------------------------------ tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {  // whole warp; cols: power of 2 >= 32
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols)
@@ -139,6 +148,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static thread_local int g_last_encode_rc = 0;   // CUresult of the last cuTensorMapEncodeTiled call (diagnostics)
+static thread_local const void* g_last_encode_ptr = nullptr;
+
 static inline EncodeTiledFn get_encode_fn() {
     static EncodeTiledFn fn = nullptr;
     if (!fn) {
@@ -162,9 +174,47 @@ static inline bool encode_2d(CUtensorMap* map, CUtensorMapDataType dt, int elem_
     cuuint64_t strides[1] = {ld * (unsigned long long)elem_bytes};
     cuuint32_t box[2] = {box_inner, box_outer};
     cuuint32_t estr[2] = {1, 1};
-    return fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    CUresult rc = fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc == CUDA_ERROR_INVALID_CONTEXT) {  // see encode_4d
+        cudaFree(0);
+        rc = fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    g_last_encode_rc = (int)rc;
+    g_last_encode_ptr = base;
+    return rc == CUDA_SUCCESS;
+}
+
+// 4-D view of a batched row-major operand: element (z_outer, z_inner, row, col) at
+// base + z_outer*so + z_inner*si + row*ld + col (all in elements; ld, si, so multiples of 16 bytes).  Out-of-range
+// rows / columns of a box are zero-filled per batch entry, so batch members never bleed into each other.
+static inline bool encode_4d(CUtensorMap* map, CUtensorMapDataType dt, int elem_bytes, const void* base,
+                             unsigned long long inner, unsigned long long outer, unsigned long long ld,
+                             unsigned long long n_in, unsigned long long si, unsigned long long n_out,
+                             unsigned long long so, unsigned box_inner, unsigned box_outer,
+                             CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return false;
+    if (n_in <= 1) { n_in = 1; si = ld * outer; }
+    if (n_out <= 1) { n_out = 1; so = (si ? si : ld * outer) * n_in; }
+    cuuint64_t dims[4] = {inner, outer, n_in, n_out};
+    cuuint64_t strides[3] = {ld * (unsigned long long)elem_bytes, si * (unsigned long long)elem_bytes,
+                             so * (unsigned long long)elem_bytes};
+    cuuint32_t box[4] = {box_inner, box_outer, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult rc = fn(map, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc == CUDA_ERROR_INVALID_CONTEXT) {
+        // a thread that has not touched the runtime yet (e.g. an autograd worker) has no current driver context:
+        // bind the primary context through the runtime and retry
+        cudaFree(0);
+        rc = fn(map, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    g_last_encode_rc = (int)rc;
+    g_last_encode_ptr = base;
+    return rc == CUDA_SUCCESS;
 }
 
 }  // namespace tc

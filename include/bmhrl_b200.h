@@ -42,6 +42,9 @@ int bmhrl_get_math_mode(void);
 /* tuning / test hook of the tensor-core GEMM: force the tile width (0 = heuristic, 32, 64, 128) and the split-K factor
  * (0 = heuristic). */
 int bmhrl_tc_tuning(int force_bn, int force_split);
+/* test hook: 0 = run the attention core as separate (batched tcgen05) contractions + softmax kernels even in math
+ * mode 1; 1 (default) = the fused tcgen05 attention kernel. */
+int bmhrl_attn_tuning(int fused);
 
 /* ---- contractions (fp32 SIMT path, gemm_simt.cu) ------------------------------------------------------------ */
 /* C[z](m,n) = beta*C + alpha * sum_k A[z](m,k) B[z](k,n);  A(m,k) at A + m*sAm + k*sAk, B(k,n) at B + k*sBk + n*sBn.

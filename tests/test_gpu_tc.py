@@ -106,3 +106,42 @@ def test_agent_tf32_vs_reference_golden(tf32, golden, agent_sd, tag):
     errs["grads_worst"] = worst
     print("tf32 errors", tag, {k: f"{v:.2e}" for k, v in errs.items()})
     assert max(errs.values()) < 2e-2, errs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,H,Sq,Sk,D,kind,p", [
+    (3, 4, 30, 30, 1024, 1, 0.0), (2, 4, 20, 80, 1024, 1, 0.0), (2, 2, 20, 20, 1024, 2, 0.0),
+    (2, 4, 150, 131, 512, 1, 0.0), (2, 4, 33, 47, 1024, 1, 0.2), (1, 4, 300, 300, 1024, 1, 0.0)])
+def test_tc_attention_core_matches_fp32(tf32, B, H, Sq, Sk, D, kind, p):
+    """mha_core in tensor-core mode (tcgen05 contractions) against the exact-fp32 path: outputs and all three input
+    gradients, ragged key padding, one fully masked row, full (B,Sq,Sk) masks, dropout with the shared Philox mask."""
+    g = torch.Generator().manual_seed(B * 1000 + Sq * 10 + Sk)
+    q, k, v = (torch.randn(B, S, D, generator=g).cuda() for S in (Sq, Sk, Sk))
+    if kind == 1:
+        lens = torch.randint(1, Sk + 1, (B,), generator=g)
+        lens[0] = Sk
+        mask = (torch.arange(Sk)[None, :] < lens[:, None])[:, None, :]
+        if B > 1:
+            mask[1] = False  # fully masked clip: uniform attention over every key (reference semantics)
+    else:
+        mask = torch.tril(torch.ones(Sq, Sk, dtype=torch.bool))[None].repeat(B, 1, 1)
+        mask[0, :, Sk // 2:] = False
+    mask = mask.cuda()
+    do = torch.randn(B, Sq, D, generator=g).cuda()
+    from bmhrl_b200._lib import LIB
+    outs = {}
+    for mode in ("fp32", "tf32"):
+        tf32.set_math_mode(mode)
+        # small cases: force the batched tcgen05 GEMMs for the backward contractions (default heuristic keeps
+        # contractions below 4 M MACs per (b, h) on the SIMT kernel)
+        LIB.call("bmhrl_tc_tuning", 32 if (mode == "tf32" and Sq <= 33) else 0, 0)
+        tf32.manual_seed(11)
+        tf32.new_rng_epoch("cuda")
+        qq, kk, vv = (t.clone().requires_grad_(True) for t in (q, k, v))
+        o = tf32.mha_core(qq, kk, vv, mask, H, drop_p=p, salt=5)
+        o.backward(do)
+        outs[mode] = (o.detach(), qq.grad, kk.grad, vv.grad)
+    tf32.set_math_mode("tf32")
+    LIB.call("bmhrl_tc_tuning", 0, 0)
+    for a, b, name in zip(outs["tf32"], outs["fp32"], ("o", "dq", "dk", "dv")):
+        assert rel(a, b) < 3e-3, (name, rel(a, b))

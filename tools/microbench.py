@@ -76,7 +76,9 @@ def ln():
         timeit(lambda: torch.autograd.grad(ops.layer_norm(x, g, b), (x, g, b), dy), name="   fwd + bwd (dx, dgamma, dbeta)")
 
 
-def attn():
+def attn(mode="tf32"):
+    ops.set_math_mode(mode)
+    print(f"-- attention core, math mode {mode}")
     for (B, H, Sq, Sk, D) in [(16, 4, 30, 30, 1024), (16, 4, 80, 80, 1024), (16, 4, 20, 80, 1024), (16, 2, 20, 20, 1024),
                               (64, 4, 300, 300, 1024)]:
         q = torch.randn(B, Sq, D, device=dev, requires_grad=True)

@@ -1,0 +1,93 @@
+"""Kernel timeline of one CUDA-graph replay of the training step (torch.profiler / CUPTI): per-kernel totals, union
+busy time per stream and overall, and the gaps.  usage: python tools/trace_step.py [workload] > gpurun_out/trace.txt"""
+import json
+import os
+import sys
+import collections
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+import bench  # noqa: E402
+from types import SimpleNamespace as NS  # noqa: E402
+
+
+def main():
+    workload = sys.argv[1] if len(sys.argv) > 1 else "warmstart"
+    from bmhrl_b200 import ops, synth, _lib
+    from bmhrl_b200.model.bm_hrl_agent import BMHrlAgent, BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, StepRunner
+    dev = torch.device("cuda", 0)
+    shapes, vshapes = bench.agent_shapes()
+    sd = synth.fill_state_dict(shapes, seed=1234)
+    cfg = bench.cfg_ns("cuda")
+    ds = NS(trg_voc_size=bench.VOC, train_vocab=NS(vectors=sd["emb_C.embedder.weight"].clone()), pad_idx=1, start_idx=2,
+            end_idx=3)
+    model = BMHrlAgent(cfg, ds)
+    model.load_state_dict(sd)
+    model = model.to(dev)
+    wv, mv = BMWorkerValueFunction(cfg), BMManagerValueFunction(cfg)
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7)
+    {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[workload]()
+    ops.manual_seed(1234, dev)
+    ops.set_math_mode(os.environ.get("BMHRL_MATH", "tf32"))
+    if os.environ.get("BMHRL_CONCURRENT") is not None:
+        ops.CONCURRENT = bool(int(os.environ["BMHRL_CONCURRENT"]))
+    b = synth.synthetic_batch(V=bench.VOC, seed=1234, **bench.SHAPE)
+    runner = StepRunner(tr, workload, b, use_graph=True, warmup=3)
+    for _ in range(5):
+        runner.replay()
+    torch.cuda.synchronize()
+    from torch.profiler import profile, ProfilerActivity
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for _ in range(3):
+            runner.replay()
+        torch.cuda.synchronize()
+    path = os.path.join(ROOT, "gpurun_out", "trace.json")
+    prof.export_chrome_trace(path)
+    ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") == "kernel"]
+    ev.sort(key=lambda e: e["ts"])
+    # split into replays: find the adam kernel ends
+    ends = [i for i, e in enumerate(ev) if "adam_multi" in e["name"]]
+    lo = ends[-2] + 1 if len(ends) >= 2 else 0
+    hi = ends[-1] + 1
+    step = ev[lo:hi]
+    t0 = step[0]["ts"]
+    t1 = max(e["ts"] + e["dur"] for e in step)
+    print(f"# one graph replay, workload {workload}: {len(step)} kernels, span {t1 - t0:.1f} us")
+    by = collections.defaultdict(lambda: [0, 0.0])
+    streams = collections.defaultdict(list)
+    for e in step:
+        n = e["name"].split("(")[0][:70]
+        by[n][0] += 1
+        by[n][1] += e["dur"]
+        streams[e["args"].get("stream")].append((e["ts"], e["ts"] + e["dur"]))
+
+    def union(iv):
+        iv = sorted(iv)
+        tot, cs, ce = 0.0, None, None
+        for s, e in iv:
+            if cs is None:
+                cs, ce = s, e
+            elif s <= ce:
+                ce = max(ce, e)
+            else:
+                tot += ce - cs
+                cs, ce = s, e
+        return tot + (ce - cs if cs is not None else 0)
+    allv = [iv for v in streams.values() for iv in v]
+    print(f"# GPU busy (union over streams): {union(allv):.1f} us; sum of kernel durations {sum(e['dur'] for e in step):.1f} us")
+    for sid, v in sorted(streams.items(), key=lambda kv: -len(kv[1])):
+        print(f"#   stream {sid}: {len(v)} kernels, busy {union(v):.1f} us, first {min(s for s, _ in v) - t0:.1f}, last {max(e for _, e in v) - t0:.1f}")
+    print(f"{'total_us':>10} {'count':>5} {'avg_us':>8}  kernel")
+    for n, (c, t) in sorted(by.items(), key=lambda kv: -kv[1][1]):
+        print(f"{t:10.1f} {c:5d} {t / c:8.2f}  {n}")
+    if os.environ.get("BMHRL_TIMELINE"):
+        print("# timeline: start_us dur_us stream kernel")
+        for e in step:
+            print(f"{e['ts'] - t0:9.1f} {e['dur']:7.1f} {e['args'].get('stream')} {e['name'].split('(')[0][:60]}")
+    os.remove(path)
+
+
+if __name__ == "__main__":
+    main()
