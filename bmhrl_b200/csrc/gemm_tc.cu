@@ -17,6 +17,7 @@
 // epilogue (tcgen05.ld -> registers -> global).  Tile 128 x BN x 32 (32 fp32 = one 128-byte swizzle row),
 // STAGES-deep mbarrier ring.  One output tile (x one K split) per CTA.
 #include <stdio.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "gemm_simt.cuh"
@@ -44,6 +45,8 @@ struct TcEpilogue {
     const unsigned long long* rng;
     unsigned int salt;
     int vec_ok;  // C (and resid) rows allow 128-bit access
+    int cluster;             // > 1: the split_k CTAs of a tile form a thread-block cluster along z and reduce their
+                             // partial accumulators through distributed shared memory (no atomics, any epilogue)
     int batched, Hdiv;       // blockIdx.z = z * split_k + split; z -> (outer = z / Hdiv, inner = z % Hdiv)
     long long bCo, bCi;      // C offset of batch entry z, elements
 };
@@ -57,7 +60,8 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
     constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B tiles need 1024-byte alignment
-    const uint32_t bars = base + STAGES * STAGE_BYTES;            // full[STAGES], empty[STAGES], tmem_full, tmem ptr
+    const uint32_t recv = base + STAGES * STAGE_BYTES;            // cluster mode: [src rank][col/4][row] float4 partials
+    const uint32_t bars = recv + (p.cluster > 1 ? TC_BM * BN * 4 : 0);  // full[STAGES], empty[STAGES], tmem_full, tmem ptr
     auto full_bar = [&](int s) { return bars + 8u * s; };
     auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
     const uint32_t tmem_full_bar = bars + 8u * (2 * STAGES);
@@ -84,6 +88,7 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (p.cluster > 1) cluster_sync_all();  // every CTA of the cluster is running before anyone writes into its smem
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
@@ -150,22 +155,67 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
             }
             tc_commit(tmem_full_bar);  // accumulator complete
         }
-    } else {  // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4
-        const int q = warp & 3;
-        const int m = m0 + q * 32 + lane;
+    }
+    // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4, thread = output row
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int m = m0 + row;
+    const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int csz = p.cluster > 1 ? p.cluster : 1;
+    const int W = BN / csz;                         // columns of the tile this CTA finishes (cluster mode)
+    const uint32_t rank = p.cluster > 1 ? cluster_ctarank() : 0u;
+    if (warp >= 2) {
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
+        if (p.cluster > 1) {
+            // reduce-scatter, send side: slice r of my partial accumulator goes to CTA r's receive buffer, slot `rank`
+            for (uint32_t r = 0; r < (uint32_t)csz; ++r) {
+                if (r == rank) continue;
+                const uint32_t rbase = mapa_shared(recv, r) + (rank * (uint32_t)(W / 4)) * (TC_BM * 16u);
+#pragma unroll 1
+                for (int c0 = 0; c0 < W; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(lane_taddr + (uint32_t)(r * W + c0), v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i4 = 0; i4 < 8; ++i4)
+                        st_shared_cluster_v4(rbase + ((uint32_t)(c0 / 4 + i4) * TC_BM + row) * 16u, v[4 * i4],
+                                             v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                }
+            }
+        }
+    }
+    if (p.cluster > 1) {
+        __syncwarp();
+        cluster_sync_all();  // release / acquire: all partial slices have landed
+    }
+    if (warp >= 2) {
         const float ks = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int cc = 0; cc < W; cc += 32) {
+            const int c0 = (int)rank * W + cc;
             uint32_t r[32];
-            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+            tmem_ld_32x32(lane_taddr + (uint32_t)c0, r);
             tmem_ld_wait();
+            if (p.cluster > 1) {
+                for (uint32_t src = 0; src < (uint32_t)csz; ++src) {
+                    if (src == rank) continue;
+                    const uint32_t sb = recv + (src * (uint32_t)(W / 4)) * (TC_BM * 16u);
+#pragma unroll
+                    for (int i4 = 0; i4 < 8; ++i4) {
+                        float4 t = ld_shared_v4(sb + ((uint32_t)(cc / 4 + i4) * TC_BM + row) * 16u);
+                        r[4 * i4] = __float_as_uint(__uint_as_float(r[4 * i4]) + t.x);
+                        r[4 * i4 + 1] = __float_as_uint(__uint_as_float(r[4 * i4 + 1]) + t.y);
+                        r[4 * i4 + 2] = __float_as_uint(__uint_as_float(r[4 * i4 + 2]) + t.z);
+                        r[4 * i4 + 3] = __float_as_uint(__uint_as_float(r[4 * i4 + 3]) + t.w);
+                    }
+                }
+            }
             const int nb = n0 + c0;
             if (m < p.M && nb < p.N) {
                 float* crow = p.C + (long long)z_out * p.bCo + (long long)z_in * p.bCi + (long long)m * p.ldc + nb;
                 const float* rrow = p.resid ? p.resid + (long long)m * p.ldr + nb : nullptr;
-                if (p.split_k > 1) {
+                if (p.split_k > 1 && p.cluster <= 1) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
                         if (nb + j < p.N) atomicAdd(crow + j, p.alpha * __uint_as_float(r[j]));
@@ -242,18 +292,40 @@ bool tc_gemm_supported(const TcGemmArgs& a) {
 
 template <int BN, int STAGES>
 static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcEpilogue& ep, dim3 grid, cudaStream_t st) {
-    constexpr int SMEM = STAGES * (TC_A_BYTES + BN * 128) + 1024 + 8 * (2 * STAGES + 2);
+    constexpr int SMEM_BASE = STAGES * (TC_A_BYTES + BN * 128) + 1024 + 8 * (2 * STAGES + 2);
+    constexpr int SMEM_MAX = SMEM_BASE + TC_BM * BN * 4;  // + the cluster receive buffer
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tf32_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             SMEM);
+                                             SMEM_MAX);
         if (e != cudaSuccess) {
             bmhrl_set_error(cudaGetErrorString(e));
             return BMHRL_ERR_CUDA;
         }
         attr = true;
     }
-    gemm_tf32_tc_kernel<BN, STAGES><<<grid, 192, SMEM, st>>>(tmA, tmB, ep);
+    if (ep.cluster > 1) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(192);
+        cfg.dynamicSmemBytes = SMEM_MAX;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 1;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = ep.cluster;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tf32_tc_kernel<BN, STAGES>, tmA, tmB, ep);
+        if (e != cudaSuccess) {
+            bmhrl_set_error(cudaGetErrorString(e));
+            return BMHRL_ERR_CUDA;
+        }
+        bmhrl_count_launch(1);
+        return BMHRL_OK;
+    }
+    gemm_tf32_tc_kernel<BN, STAGES><<<grid, 192, SMEM_BASE, st>>>(tmA, tmB, ep);
     BMHRL_POST_LAUNCH("gemm_tf32_tc");
     return BMHRL_OK;
 }
@@ -263,25 +335,52 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
     const int num_kb = (a.K + TC_BK - 1) / TC_BK;
     // tile width: the widest BN that still gives >= ~1 CTA per SM; narrow tiles re-read A but fill the machine
     const int nbatch = a.batch > 1 ? a.batch : 1;
-    int BN = 128;
-    if (g_force_bn) BN = g_force_bn;
-    else {
-        while (BN > 32 && (long long)nbatch * tiles_m * ((a.N + BN - 1) / BN) < 120) BN >>= 1;
-        if (a.N <= 32) BN = 32; else if (a.N <= 64 && BN > 64) BN = 64;
-    }
-    const int tiles_n = (a.N + BN - 1) / BN;
+    // Configuration: every SM ingests ~70 GB/s from L2 (measured), so the time of these small GEMMs is
+    //   slots_per_SM * bytes_per_CTA / 70 GB/s + fixed costs,  bytes_per_CTA = (128 + BN) * 128 B * k-blocks per CTA.
+    // Wide tiles cut the bytes, a cluster of `cs` CTAs along K (DSMEM reduce-scatter in the epilogue) keeps all SMs busy.
     const bool plain = !a.bias && a.act == 0 && !a.resid && a.drop_p == 0.f;
-    int split = 1;
-    if (plain && nbatch == 1) {
-        if (g_force_split) split = g_force_split;
+    int BN = 128, split = 1, cluster = 1;
+    if (g_force_bn || g_force_split) {
+        if (g_force_bn) BN = g_force_bn;
         else {
-            const long long tiles = (long long)tiles_m * tiles_n;
-            while (tiles * split < 100 && num_kb / (split * 2) >= 4) split *= 2;
+            while (BN > 32 && (long long)nbatch * tiles_m * ((a.N + BN - 1) / BN) < 120) BN >>= 1;
+            if (a.N <= 32) BN = 32; else if (a.N <= 64 && BN > 64) BN = 64;
         }
-        if (split > num_kb) split = num_kb;
+        if (g_force_split < 0 && nbatch == 1) {  // forced cluster size
+            cluster = -g_force_split;
+            while (cluster > 1 && (BN / cluster < 32 || num_kb < cluster)) cluster >>= 1;
+            split = cluster;
+        } else if (g_force_split > 0 && plain && nbatch == 1) {
+            split = g_force_split;  // atomic split-K
+        }
+    } else {
+        // Measured on B200 (tools/microbench.py gemm): a lone CTA per SM ingests ~70 GB/s from L2, so when 128-wide
+        // tiles alone would leave most SMs idle and K is long, a cluster of 2 / 4 CTAs splits K of each 128x128 tile
+        // (2.5x fewer bytes per SM than 128x32 tiles); otherwise narrow tiles with 2 co-resident CTAs per SM win.
+        const long long t128 = (long long)tiles_m * ((a.N + 127) / 128);
+        static const int allow_cluster = getenv("BMHRL_TC_CLUSTER") ? atoi(getenv("BMHRL_TC_CLUSTER")) : 0;
+        static const int min_tiles = getenv("BMHRL_TC_MIN_TILES") ? atoi(getenv("BMHRL_TC_MIN_TILES")) : 120;
+        if (allow_cluster && nbatch == 1 && a.N > 64 && num_kb >= 16 && t128 * 2 <= 148) {
+            BN = 128;
+            cluster = t128 * 4 <= 160 ? 4 : 2;
+            split = cluster;
+        } else {
+            while (BN > 32 && (long long)nbatch * tiles_m * ((a.N + BN - 1) / BN) < min_tiles) BN >>= 1;
+            if (a.N <= 32) BN = 32; else if (a.N <= 64 && BN > 64) BN = 64;
+            if (plain && nbatch == 1) {
+                const long long tiles = (long long)tiles_m * ((a.N + BN - 1) / BN);
+                while (tiles * split < 100 && num_kb / (split * 2) >= 4) split *= 2;
+            }
+        }
     }
+    if (split > num_kb) split = num_kb;
+    const int tiles_n = (a.N + BN - 1) / BN;
     int kb_per = (num_kb + split - 1) / split;
-    split = (num_kb + kb_per - 1) / kb_per;  // no empty splits
+    if (cluster > 1) {
+        if ((long long)kb_per * (cluster - 1) >= num_kb) { cluster = 1; split = 1; kb_per = num_kb; }  // no empty CTA
+    } else {
+        split = (num_kb + kb_per - 1) / kb_per;  // no empty splits
+    }
 
     CUtensorMap tmA, tmB;
     bool ok;
@@ -322,8 +421,9 @@ int launch_gemm_tc(const TcGemmArgs& a, cudaStream_t st) {
     ep.drop_p = a.drop_p; ep.rng = a.rng; ep.salt = a.salt;
     ep.vec_ok = aligned16(a.C) && (a.ldc & 3) == 0 && (!a.resid || (aligned16(a.resid) && (a.ldr & 3) == 0)) &&
                 (nbatch == 1 || (((a.bCo | a.bCi) & 3) == 0));
+    ep.cluster = cluster;
     ep.batched = nbatch > 1; ep.Hdiv = nbatch > 1 ? a.Hdiv : 1; ep.bCo = a.bCo; ep.bCi = a.bCi;
-    if (split > 1 && a.beta == 0.f) {  // partial sums are accumulated atomically into a zeroed C
+    if (split > 1 && cluster <= 1 && a.beta == 0.f) {  // partial sums are accumulated atomically into a zeroed C
         if (a.ldc == a.N) {
             if (cudaMemsetAsync(a.C, 0, sizeof(float) * (size_t)a.M * a.N, st) != cudaSuccess) return BMHRL_ERR_CUDA;
         } else {
@@ -370,7 +470,7 @@ extern "C" int bmhrl_set_math_mode(int mode) {
 extern "C" int bmhrl_get_math_mode(void) { return g_math_mode; }
 extern "C" int bmhrl_tc_tuning(int force_bn, int force_split) {
     BMHRL_CHECK_ARG(force_bn == 0 || force_bn == 32 || force_bn == 64 || force_bn == 128, "bmhrl_tc_tuning: BN");
-    BMHRL_CHECK_ARG(force_split >= 0, "bmhrl_tc_tuning: split");
+    BMHRL_CHECK_ARG(force_split >= -4 && force_split != -3, "bmhrl_tc_tuning: split (>0 atomic split-K, -2/-4 cluster)");
     g_force_bn = force_bn;
     g_force_split = force_split;
     g_tc_batched_min_macs = (force_bn || force_split) ? 0 : (4ll << 20);  // forced tiling: always the tensor-core kernel

@@ -65,9 +65,11 @@ class MultiheadedAttention(nn.Module):
         if Q.dim() != 3:
             raise RuntimeError("MultiheadedAttention expects (B, S, D) inputs")
         s_core, s_out = self._call_salts()
-        q = ops.linear(Q, self.linear_Q2d.weight, self.linear_Q2d.bias)
-        k = ops.linear(K, self.linear_K2d.weight, self.linear_K2d.bias)
-        v = ops.linear(V, self.linear_V2d.weight, self.linear_V2d.bias)
+        # the three projections are independent: concurrent branches (and so are their backward passes)
+        q, k, v = ops.parallel(Q.device,
+                               lambda: ops.linear(Q, self.linear_Q2d.weight, self.linear_Q2d.bias),
+                               lambda: ops.linear(K, self.linear_K2d.weight, self.linear_K2d.bias),
+                               lambda: ops.linear(V, self.linear_V2d.weight, self.linear_V2d.bias))
         p = self.dropout.p if self.training else 0.0
         o = ops.mha_core(q, k, v, mask, self.H, causal=causal, drop_p=p, salt=s_core)
         return ops.linear(o, self.linear_d2Q.weight, self.linear_d2Q.bias, resid=resid, drop_p=resid_drop_p,

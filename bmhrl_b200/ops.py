@@ -127,15 +127,34 @@ def parallel(device, *thunks):
     return out
 
 
+_WGRAD_KEEP = []   # operands of weight-gradient GEMMs in flight on the wgrad streams (kept alive until the join)
+_WGRAD_RR = [0]
+
+
+def wgrad_stream(device):
+    """Weight-gradient GEMMs that accumulate straight into a FusedAdam flat buffer have no consumer before the
+    optimiser step: they are forked onto two round-robin side streams, off the critical path of backward."""
+    cur = torch.cuda.current_stream(device)
+    _WGRAD_RR[0] ^= 1
+    key = (cur.device.index, "wgrad", _WGRAD_RR[0])
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=cur.device.index)
+    _DIRTY.add(key)
+    s = _SIDE[key]
+    s.wait_stream(cur)
+    return s
+
+
 def join_side_streams(device=None):
     """Makes the current stream wait for everything enqueued on the side streams since the last join.  Backward
     kernels that accumulate straight into a FusedAdam flat buffer run on the stream of their forward op and hand
     autograd no gradient tensor, so the trainer joins explicitly before the optimiser step."""
     cur = torch.cuda.current_stream(device)
-    for key in sorted(_DIRTY, key=len, reverse=True):
+    for key in sorted(_DIRTY, key=lambda k: (len(k), str(k)), reverse=True):
         if key[0] == cur.device.index:
             cur.wait_stream(_SIDE[key])
             _DIRTY.discard(key)
+    _WGRAD_KEEP.clear()
 
 
 def manual_seed(seed, device="cuda"):
@@ -236,7 +255,12 @@ class _Linear(torch.autograd.Function):
             gemm(dz, N, 1, weight, K, 1, dx, K, M, K, N)
         if need_w:  # dW = dZ^T X : (N,M)(M,K)
             if wgrad is not None:  # accumulate into the parameter's slice of the flat gradient buffer (beta = 1)
-                gemm(dz, 1, N, x, K, 1, wgrad, K, N, K, M, beta=1.0)
+                if CONCURRENT:
+                    _WGRAD_KEEP.append((dz, x))
+                    with torch.cuda.stream(wgrad_stream(dy.device)):
+                        gemm(dz, 1, N, x, K, 1, wgrad, K, N, K, M, beta=1.0)
+                else:
+                    gemm(dz, 1, N, x, K, 1, wgrad, K, N, K, M, beta=1.0)
             else:
                 dw = torch.empty(N, K, device=dy.device, dtype=_F32)
                 gemm(dz, 1, N, x, K, 1, dw, K, N, K, M)

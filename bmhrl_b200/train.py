@@ -151,6 +151,7 @@ class BMHRLTrainer:
         self._sync(self.cap_opt)
         self.cap_opt.step()
         value_loss.backward()
+        ops.join_side_streams(value_loss.device)
         self._sync(vopt, mean=True)  # the value loss is a .mean() over the global (B,L) batch (:874-875)
         vopt.step()
         return cap_loss.detach(), value_loss.detach()

@@ -39,8 +39,9 @@ void bmhrl_reset_launch_count(void);
  *    fp32 operands, fp32 accumulation in TMEM; parity bound 2e-2 like the north_star's reduced-precision bound). */
 int bmhrl_set_math_mode(int mode);
 int bmhrl_get_math_mode(void);
-/* tuning / test hook of the tensor-core GEMM: force the tile width (0 = heuristic, 32, 64, 128) and the split-K factor
- * (0 = heuristic). */
+/* tuning / test hook of the tensor-core GEMM: force the tile width (0 = cost model, 32, 64, 128) and the K split
+ * (0 = cost model; > 0: split-K with RED accumulation, plain GEMMs only; -2 / -4: thread-block cluster of that many
+ * CTAs along K, partial accumulators reduce-scattered through distributed shared memory, any epilogue). */
 int bmhrl_tc_tuning(int force_bn, int force_split);
 /* test hook: 0 = run the attention core as separate (batched tcgen05) contractions + softmax kernels even in math
  * mode 1; 1 (default) = the fused tcgen05 attention kernel. */

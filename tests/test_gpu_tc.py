@@ -28,9 +28,11 @@ def _g(seed):
 
 @pytest.mark.parametrize("M,K,N", [(128, 32, 32), (128, 128, 128), (37, 300, 64), (320, 364, 10172), (480, 1024, 1024),
                                    (1280, 128, 1024), (5, 64, 1024), (129, 128, 512), (320, 1024, 300)])
-@pytest.mark.parametrize("bn", [0, 32, 64, 128])
-def test_tc_linear_forward(tf32, gpu_lib, M, K, N, bn):
-    gpu_lib.call("bmhrl_tc_tuning", bn, 0)
+@pytest.mark.parametrize("bn,split", [(0, 0), (32, 0), (64, 0), (128, 0), (128, -2), (128, -4), (64, -2)])
+def test_tc_linear_forward(tf32, gpu_lib, M, K, N, bn, split):
+    """split < 0: the K range is split over a thread-block cluster of -split CTAs whose partial accumulators are
+    reduce-scattered through distributed shared memory before the fused epilogue."""
+    gpu_lib.call("bmhrl_tc_tuning", bn, split)
     g = _g(M + K + N)
     x, w, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / math.sqrt(K), torch.randn(N, generator=g)
     r = torch.randn(M, N, generator=g)
@@ -44,7 +46,7 @@ def test_tc_linear_forward(tf32, gpu_lib, M, K, N, bn):
 
 
 @pytest.mark.parametrize("M,K,N", [(37, 300, 64), (320, 364, 10172), (480, 1024, 1024), (129, 128, 512)])
-@pytest.mark.parametrize("split", [0, 1, 3])
+@pytest.mark.parametrize("split", [0, 1, 3, -2, -4])
 def test_tc_linear_backward(tf32, gpu_lib, M, K, N, split):
     """dX = dZ W (B operand MN-major, split-K over N) and dW = dZ^T X (both operands MN-major), bias grad."""
     gpu_lib.call("bmhrl_tc_tuning", 0, split)
