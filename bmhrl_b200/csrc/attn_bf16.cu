@@ -1,0 +1,430 @@
+// K1, bf16 operands (config 5: long-clip encoder attention sweep, B=64, S=300..800, d_k=256): fused masked multi-head
+// attention forward as ONE persistent kernel on the 5th-gen tensor cores (sm_100a).
+// Reference: attention() model/multihead_attention.py:7-31 -- softmax(mask_replace(Q K^T / sqrt(d_k), -1e9)) V on the
+// head-merged (B, S, H*d_k) tensors the projections produce.  Flash-style: the (B,H,Sq,Sk) score tensor never exists
+// in HBM (the reference materialises it and sweeps it three times); the per-row log-sum-exp is kept instead.
+//
+// Grid = one CTA per SM; CTA c walks the work items c, c+grid, ... ; item = (batch, head, 128-query tile).  192 threads:
+//   warp 0     TMA producer.  Q tile (128 x d_k bf16, resident for the whole item) + a 5-deep ring of 32 KB stages that
+//              carries K tiles (128 keys x 128 d_k columns) and V tiles (64 keys x d_k) in the order the MMA warp
+//              consumes them.  It runs ahead across items, so the next item's Q/K arrive under this item's P V.
+//   warp 1     TMEM allocator + tcgen05.mma issuer (one thread).  S = Q K^T (kind::f16, bf16 x bf16 -> fp32, both
+//              operands K-major in shared memory) into a double-buffered 128-column TMEM tile; O += P V with P read
+//              FROM TMEM (bf16, two keys per 32-bit cell) and V MN-major in shared memory, accumulator 128 x d_k fp32.
+//              Issue order S0 S1 PV0 S2 PV1 ... keeps Q K^T of tile j+1 under the softmax of tile j.
+//   warps 2-5  softmax + epilogue, thread = query row = TMEM lane: no cross-thread traffic for row max / row sum.
+//              ONE pass over the keys: probabilities are taken against a running maximum that is only raised when the
+//              new tile maximum exceeds it by more than 2^8 (exact arithmetic -- the normaliser carries the same
+//              offset); only then is the O accumulator rescaled through registers.
+// Masked scores are REPLACED by -1e9 (not added to), so a fully masked row is uniform over all Sk keys, exactly like
+// the reference.  TMEM: 2 x 128 columns S/P + 256 columns O = 512.
+#include <cuda_bf16.h>
+#include "common.cuh"
+#include "tc_common.cuh"
+#include "../../include/bmhrl_b200.h"
+
+namespace bmhrl {
+
+using namespace tc;
+
+constexpr int AB_BM = 128;   // queries per item
+constexpr int AB_BN = 128;   // keys per S tile
+constexpr int AB_STAGES = 5;
+constexpr int AB_STAGE_BYTES = 32 * 1024;
+constexpr int AB_Q_BYTES = 64 * 1024;  // 128 x 256 bf16
+constexpr int AB_SMEM = AB_Q_BYTES + AB_STAGES * AB_STAGE_BYTES + 1024 + 256;
+constexpr float AB_LAZY = 8.f;  // log2 of the growth the running maximum may lag behind by
+
+struct AttnBf16Params {
+    __nv_bfloat16* O; long long ldo, bso;
+    float* lse;                        // (B,H,Sq) natural-log sum of exp of the (masked, scaled) scores
+    const unsigned char* mask; int mask_kind, causal;
+    int B, H, Sq, Sk, dk;
+    int nqt, n_items;
+    float scale;
+};
+
+__device__ __forceinline__ void tmem_st_32x32_b(uint32_t taddr, const uint32_t* v) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        :
+        : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+          "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]),
+          "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]),
+          "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32_b(uint32_t taddr, uint32_t* v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait_b() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// D[tmem] (+)= A[tmem] * B[smem], kind::f16: A holds two bf16 per 32-bit TMEM cell (row = lane, k pair = column)
+__device__ __forceinline__ void mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        :
+        : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));  // first source -> upper half
+    return r;
+}
+
+__global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_constant__ CUtensorMap tmQ,
+                                                               const __grid_constant__ CUtensorMap tmK,
+                                                               const __grid_constant__ CUtensorMap tmV,
+                                                               const AttnBf16Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t sQ = base;
+    const uint32_t ring = base + AB_Q_BYTES;
+    const uint32_t bars = ring + AB_STAGES * AB_STAGE_BYTES;
+    auto full_bar = [&](int s) { return bars + 8u * s; };
+    auto empty_bar = [&](int s) { return bars + 8u * (AB_STAGES + s); };
+    auto s_full = [&](int i) { return bars + 8u * (2 * AB_STAGES + i); };     // MMA -> softmax: S tile complete
+    auto s_rel = [&](int i) { return bars + 8u * (2 * AB_STAGES + 2 + i); };  // softmax -> MMA: P written (O rescaled)
+    const uint32_t q_full = bars + 8u * (2 * AB_STAGES + 4);
+    const uint32_t q_empty = bars + 8u * (2 * AB_STAGES + 5);
+    const uint32_t pv_bar = bars + 8u * (2 * AB_STAGES + 6);   // MMA -> softmax: P V of one tile complete
+    const uint32_t o_free = bars + 8u * (2 * AB_STAGES + 7);   // epilogue -> MMA: O accumulator drained
+    const uint32_t tmem_slot = bars + 8u * (2 * AB_STAGES + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nkt = (p.Sk + AB_BN - 1) / AB_BN;
+    const int kcols = p.dk < 128 ? p.dk : 128;   // d_k columns of one K stage
+    const int nkh = p.dk / kcols;                // K stages per key tile
+    const int ncs = kcols >> 6;                  // 64-column (128-byte) chunks per K stage
+    const int nvc = p.dk >> 6;                   // 64-column chunks of a V stage / of the Q tile
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        for (int s = 0; s < AB_STAGES; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        mbar_init(s_full(0), 1);
+        mbar_init(s_full(1), 1);
+        mbar_init(s_rel(0), 128);
+        mbar_init(s_rel(1), 128);
+        mbar_init(q_full, 1);
+        mbar_init(q_empty, 1);
+        mbar_init(pv_bar, 1);
+        mbar_init(o_free, 128);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    const uint32_t tmem_o = tmem_base + 256;
+
+    if (warp == 0) {
+        if (lane == 0) {  // ===== TMA producer (same op order as the MMA issuer)
+            int it = 0;
+            for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
+                const int bh = w / p.nqt, qt = w - bh * p.nqt;
+                const int b = bh / p.H, h = bh - b * p.H;
+                const int q0 = qt * AB_BM, col_q = h * p.dk;
+                mbar_wait(q_empty, ((uint32_t)i & 1u) ^ 1u);
+                mbar_arrive_expect_tx(q_full, (uint32_t)(AB_BM * p.dk * 2));
+                for (int c = 0; c < nvc; ++c) tma_load_4d(sQ + c * 16384, &tmQ, q_full, col_q + c * 64, q0, 0, b);
+                auto load_k = [&](int j) {
+                    for (int hf = 0; hf < nkh; ++hf, ++it) {
+                        const int s = it % AB_STAGES;
+                        mbar_wait(empty_bar(s), (((uint32_t)(it / AB_STAGES)) & 1u) ^ 1u);
+                        mbar_arrive_expect_tx(full_bar(s), (uint32_t)(ncs * 16384));
+                        const uint32_t sK = ring + s * AB_STAGE_BYTES;
+                        for (int cc = 0; cc < ncs; ++cc)
+                            tma_load_4d(sK + cc * 16384, &tmK, full_bar(s), col_q + hf * kcols + cc * 64, j * AB_BN, 0, b);
+                    }
+                };
+                auto load_v = [&](int j) {
+                    const int nkc = (min(AB_BN, p.Sk - j * AB_BN) + 63) >> 6;
+                    for (int kc = 0; kc < nkc; ++kc, ++it) {
+                        const int s = it % AB_STAGES;
+                        mbar_wait(empty_bar(s), (((uint32_t)(it / AB_STAGES)) & 1u) ^ 1u);
+                        mbar_arrive_expect_tx(full_bar(s), (uint32_t)(nvc * 8192));
+                        const uint32_t sV = ring + s * AB_STAGE_BYTES;
+                        for (int n = 0; n < nvc; ++n)
+                            tma_load_4d(sV + n * 8192, &tmV, full_bar(s), col_q + n * 64, j * AB_BN + kc * 64, 0, b);
+                    }
+                };
+                load_k(0);
+                if (nkt > 1) load_k(1);
+                for (int j = 0; j < nkt; ++j) {
+                    load_v(j);
+                    if (j + 2 < nkt) load_k(j + 2);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {  // ===== MMA issuer
+            const uint32_t idesc_s = make_idesc(1, AB_BM, AB_BN, 0, 0);
+            const uint32_t idesc_o = make_idesc(1, AB_BM, p.dk, 0, 1);
+            int it = 0, ns = 0, np = 0;  // ring position, S tiles issued, P V tiles issued (all items)
+            for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
+                mbar_wait(q_full, (uint32_t)i & 1u);
+                tc_fence_after();
+                auto s_op = [&](bool last) {  // S[ns & 1] = Q K_j^T; in-order execution behind the P V that read this buffer
+                    const int buf = ns & 1;
+                    for (int hf = 0; hf < nkh; ++hf, ++it) {
+                        const int s = it % AB_STAGES;
+                        mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
+                        tc_fence_after();
+                        const uint32_t sK = ring + s * AB_STAGE_BYTES;
+                        for (int cc = 0; cc < ncs; ++cc) {
+                            const uint32_t a0 = sQ + (hf * ncs + cc) * 16384, b0 = sK + cc * 16384;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                mma_bf16_ss(tmem_base + buf * AB_BN, make_smem_desc(a0 + k * 32, 16, 1024),
+                                            make_smem_desc(b0 + k * 32, 16, 1024), idesc_s,
+                                            (hf > 0 || cc > 0 || k > 0) ? 1u : 0u);
+                        }
+                        tc_commit(empty_bar(s));
+                    }
+                    tc_commit(s_full(buf));
+                    if (last) tc_commit(q_empty);  // every Q K^T of this item has completed: Q may be overwritten
+                    ++ns;
+                };
+                auto pv_op = [&](int j) {  // O += P_j V_j
+                    const int buf = np & 1;
+                    mbar_wait(s_rel(buf), ((uint32_t)(np >> 1)) & 1u);
+                    if (j == 0 && i > 0) mbar_wait(o_free, ((uint32_t)(i - 1)) & 1u);
+                    tc_fence_after();
+                    const int nkc = (min(AB_BN, p.Sk - j * AB_BN) + 63) >> 6;
+                    for (int kc = 0; kc < nkc; ++kc, ++it) {
+                        const int s = it % AB_STAGES;
+                        mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
+                        tc_fence_after();
+                        const uint32_t sV = ring + s * AB_STAGE_BYTES;
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk)
+                            mma_bf16_ts(tmem_o, tmem_base + buf * AB_BN + kc * 32 + kk * 8,
+                                        make_smem_desc(sV + kk * 2048, 8192, 1024), idesc_o,
+                                        (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
+                        tc_commit(empty_bar(s));
+                    }
+                    tc_commit(pv_bar);
+                    ++np;
+                };
+                s_op(nkt == 1);
+                if (nkt > 1) s_op(nkt == 2);
+                for (int j = 0; j < nkt; ++j) {
+                    pv_op(j);
+                    if (j + 2 < nkt) s_op(j + 3 == nkt);
+                }
+            }
+        }
+    } else {  // ===== softmax / epilogue warps: TMEM lane quarter = warp % 4, thread = query row
+        const int qtr = warp & 3;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(qtr * 32) << 16);
+        constexpr float LOG2E = 1.4426950408889634f;
+        const float sl2 = p.scale * LOG2E;
+        const float neg2 = kNegFill * LOG2E;  // the replaced score, in the log2 domain
+        int n = 0;                            // tiles consumed (all items) == index of the next P V
+        for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
+            const int bh = w / p.nqt, qt = w - bh * p.nqt;
+            const int b = bh / p.H, h = bh - b * p.H;
+            const int q = qt * AB_BM + qtr * 32 + lane;
+            const bool row_ok = q < p.Sq;
+            float m = -INFINITY, l = 0.f;
+            for (int j = 0; j < nkt; ++j, ++n) {
+                const int buf = n & 1;
+                const int keys = min(AB_BN, p.Sk - j * AB_BN);
+                uint32_t vis[4];  // visibility bits of this row for the 128 keys of tile j
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int kk0 = c * 32;
+                    uint32_t v = keys - kk0 >= 32 ? 0xffffffffu : (keys - kk0 <= 0 ? 0u : ((1u << (keys - kk0)) - 1u));
+                    if (p.mask_kind == 1) {
+                        const int kk = j * AB_BN + kk0 + lane;
+                        const bool on = kk < p.Sk && p.mask[(long long)b * p.Sk + kk] != 0;
+                        v = __ballot_sync(0xffffffffu, on);
+                    } else if (p.mask_kind == 2) {
+                        v = 0u;
+                        if (row_ok) {
+                            const unsigned char* mr = p.mask + ((long long)b * p.Sq + q) * p.Sk + j * AB_BN + kk0;
+                            const int cnt = min(32, keys - kk0);
+                            for (int t = 0; t < cnt; ++t) v |= (mr[t] != 0 ? 1u : 0u) << t;
+                        }
+                    }
+                    if (p.causal) {
+                        const int lim = q - (j * AB_BN + kk0);
+                        if (lim < 0) v = 0u;
+                        else if (lim < 31) v &= (2u << lim) - 1u;
+                    }
+                    vis[c] = v;
+                }
+                mbar_wait(s_full(buf), ((uint32_t)(n >> 1)) & 1u);
+                tc_fence_after();
+                const uint32_t taddr = lane_base + buf * AB_BN;
+                uint32_t r[128];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) tmem_ld_32x32_b(taddr + c * 32, r + c * 32);
+                tmem_ld_wait();
+                float mt = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                    for (int t = 0; t < 32; ++t) {
+                        float x = ((vis[c] >> t) & 1u) ? __uint_as_float(r[c * 32 + t]) * sl2 : neg2;
+                        x = (c * 32 + t) < keys ? x : -INFINITY;
+                        r[c * 32 + t] = __float_as_uint(x);
+                        mt = fmaxf(mt, x);
+                    }
+                }
+                const bool raise = mt > m + AB_LAZY;  // first tile: m = -inf
+                float alpha = 1.f;
+                if (raise) {
+                    alpha = ex2_approx(m - mt);
+                    m = mt;
+                    l *= alpha;
+                }
+                float acc = 0.f;
+#pragma unroll
+                for (int t = 0; t < 128; t += 2) {
+                    const float p0 = ex2_approx(__uint_as_float(r[t]) - m);
+                    const float p1 = ex2_approx(__uint_as_float(r[t + 1]) - m);
+                    acc += p0 + p1;
+                    r[t >> 1] = pack_bf16x2(p0, p1);
+                }
+                l += acc;
+                if (j > 0) {  // P V of the previous tile: every phase of pv_bar is waited for, in order
+                    mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+                    tc_fence_after();
+                    if (__any_sync(0xffffffffu, raise)) {  // rare: bring the accumulator to the new offset
+                        for (int c = 0; c < (p.dk >> 5); ++c) {
+                            uint32_t o[32];
+                            tmem_ld_32x32_b(lane_base + 256 + c * 32, o);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int t = 0; t < 32; ++t) o[t] = __float_as_uint(__uint_as_float(o[t]) * alpha);
+                            tmem_st_32x32_b(lane_base + 256 + c * 32, o);
+                        }
+                    }
+                }
+                tmem_st_32x32_b(taddr, r);
+                tmem_st_32x32_b(taddr + 32, r + 32);
+                tmem_st_wait_b();
+                tc_fence_before();
+                mbar_arrive(s_rel(buf));
+            }
+            // ---- epilogue: O tile (TMEM) / l -> bf16 -> global, head-merged layout; log-sum-exp
+            mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+            tc_fence_after();
+            const float inv_l = 1.f / l;
+            __nv_bfloat16* orow = p.O + (long long)b * p.bso + (long long)q * p.ldo + h * p.dk;
+            for (int c = 0; c < (p.dk >> 5); ++c) {
+                uint32_t o[32];
+                tmem_ld_32x32_b(lane_base + 256 + c * 32, o);
+                tmem_ld_wait();
+                if (row_ok) {
+#pragma unroll
+                    for (int t = 0; t < 32; t += 8) {
+                        uint4 u;
+                        u.x = pack_bf16x2(__uint_as_float(o[t]) * inv_l, __uint_as_float(o[t + 1]) * inv_l);
+                        u.y = pack_bf16x2(__uint_as_float(o[t + 2]) * inv_l, __uint_as_float(o[t + 3]) * inv_l);
+                        u.z = pack_bf16x2(__uint_as_float(o[t + 4]) * inv_l, __uint_as_float(o[t + 5]) * inv_l);
+                        u.w = pack_bf16x2(__uint_as_float(o[t + 6]) * inv_l, __uint_as_float(o[t + 7]) * inv_l);
+                        *reinterpret_cast<uint4*>(orow + c * 32 + t) = u;
+                    }
+                }
+            }
+            if (row_ok && p.lse) p.lse[(long long)bh * p.Sq + q] = (m + log2f(l)) * 0.6931471805599453f;
+            tc_fence_before();
+            mbar_arrive(o_free);
+        }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace bmhrl
+
+extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, const void* K, long long ldk,
+                                   long long bsk, const void* V, long long ldv, long long bsv,
+                                   const unsigned char* mask, int mask_kind, int causal, void* O, long long ldo,
+                                   long long bso, float* lse, int B, int H, int Sq, int Sk, int dk, void* stream) {
+    using namespace bmhrl;
+    using namespace bmhrl::tc;
+    BMHRL_CHECK_ARG(Q && K && V && O, "attn_fwd_bf16: null tensor");
+    BMHRL_CHECK_ARG(B > 0 && H > 0 && Sq > 0 && Sk > 0, "attn_fwd_bf16: empty shape");
+    BMHRL_CHECK_ARG(mask_kind >= 0 && mask_kind <= 2 && (mask_kind == 0 || mask), "attn_fwd_bf16: bad mask");
+    if (dk != 64 && dk != 128 && dk != 256) {
+        bmhrl_set_error("attn_fwd_bf16: d_k must be 64, 128 or 256");
+        return BMHRL_ERR_UNSUPPORTED;
+    }
+    auto ok8 = [](long long v) { return v > 0 && (v & 7) == 0; };
+    if (!ok8(ldq) || !ok8(ldk) || !ok8(ldv) || !ok8(ldo) || (B > 1 && (!ok8(bsq) || !ok8(bsk) || !ok8(bsv) || !ok8(bso))) ||
+        !aligned16(Q) || !aligned16(K) || !aligned16(V) || !aligned16(O)) {
+        bmhrl_set_error("attn_fwd_bf16: tensors must be 16-byte aligned with pitches that are multiples of 8 elements");
+        return BMHRL_ERR_UNSUPPORTED;
+    }
+    if (get_encode_fn() == nullptr) {
+        bmhrl_set_error("attn_fwd_bf16: cuTensorMapEncodeTiled unavailable");
+        return BMHRL_ERR_CUDA;
+    }
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    CUtensorMap tmQ, tmK, tmV;
+    const unsigned long long D = (unsigned long long)H * dk;
+    bool ok = encode_4d(&tmQ, BF, 2, Q, D, Sq, ldq, 1, 0, B, bsq, 64, AB_BM) &&
+              encode_4d(&tmK, BF, 2, K, D, Sk, ldk, 1, 0, B, bsk, 64, AB_BN) &&
+              encode_4d(&tmV, BF, 2, V, D, Sk, ldv, 1, 0, B, bsv, 64, 64);
+    if (!ok) {
+        bmhrl_set_error("attn_fwd_bf16: cuTensorMapEncodeTiled failed");
+        return BMHRL_ERR_CUDA;
+    }
+    static bool attr = false;
+    static int n_sm = 0;
+    if (!attr) {
+        if (cudaFuncSetAttribute(attn_fwd_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM) !=
+            cudaSuccess) {
+            bmhrl_set_error("attn_fwd_bf16: cannot raise the shared-memory limit");
+            return BMHRL_ERR_CUDA;
+        }
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        if (n_sm <= 0) n_sm = 148;
+        attr = true;
+    }
+    AttnBf16Params p{};
+    p.O = (__nv_bfloat16*)O; p.ldo = ldo; p.bso = bso; p.lse = lse; p.mask = mask; p.mask_kind = mask_kind;
+    p.causal = causal; p.B = B; p.H = H; p.Sq = Sq; p.Sk = Sk; p.dk = dk;
+    p.nqt = (Sq + AB_BM - 1) / AB_BM;
+    p.n_items = B * H * p.nqt;
+    p.scale = 1.0f / sqrtf((float)dk);
+    const int grid = p.n_items < n_sm ? p.n_items : n_sm;
+    attn_fwd_bf16_kernel<<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
+    BMHRL_POST_LAUNCH("attn_fwd_bf16");
+    return BMHRL_OK;
+}

@@ -449,6 +449,32 @@ def mha_core(q, k, v, mask, H, causal=False, drop_p=0.0, salt=0, rng=None):
     return _MhaCore.apply(q, k, v, m, kind, int(bool(causal)), H, float(drop_p), int(salt), rng)
 
 
+def mha_core_bf16(q, k, v, mask, H, causal=False, return_lse=False):
+    """bf16 flash-style attention core, forward only (BASELINE.json config 5, the long-clip encoder attention sweep).
+    q (B,Sq,D), k/v (B,Sk,D) bf16 projected tensors -> head-merged (B,Sq,D) bf16 (+ fp32 (B,H,Sq) log-sum-exp).
+    Same masking semantics as `mha_core` (model/multihead_attention.py:7-31); no dropout, no autograd."""
+    for t, name in ((q, "q"), (k, "k"), (v, "v")):
+        if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous()):
+            raise RuntimeError(f"mha_core_bf16: {name} must be a contiguous CUDA bf16 tensor (there is no CPU fallback)")
+    if q.requires_grad or k.requires_grad or v.requires_grad:
+        if torch.is_grad_enabled():
+            raise RuntimeError("mha_core_bf16 is forward-only: call it under torch.no_grad()")
+    B, Sq, D = q.shape
+    Sk = k.shape[1]
+    if D % H != 0:
+        raise RuntimeError("mha_core_bf16: d_model must be divisible by H")
+    m, kind = _mask_args(mask, B, Sq, Sk)
+    if kind == 0:
+        causal = False
+    if causal and Sq != Sk:
+        raise RuntimeError("mha_core_bf16: causal attention needs Sq == Sk")
+    o = torch.empty_like(q)
+    lse = torch.empty(B, H, Sq, device=q.device, dtype=_F32) if return_lse else None
+    LIB.call("bmhrl_attn_fwd_bf16", _p(q), D, Sq * D, _p(k), D, Sk * D, _p(v), D, Sk * D, _p(m), kind,
+             int(bool(causal)), _p(o), D, Sq * D, _p(lse), B, H, Sq, Sk, D // H, _stream())
+    return (o, lse) if return_lse else o
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # K4 / K5
 # ----------------------------------------------------------------------------------------------------------------

@@ -103,6 +103,18 @@ int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long bso, const 
                            long long lddv, long long bsdv, float* ws_dP, float* ws_dO, int B, int H, int Sq, int Sk,
                            int dk, float drop_p, const unsigned long long* rng_state, unsigned int salt, void* stream);
 
+/* ---- K1, bf16 operands: fused flash-style forward (attn_bf16.cu) --------------------------------------------- */
+/* attention() model/multihead_attention.py:7-31 on bf16 head-merged (B, S, H*dk) tensors (BASELINE.json config 5: the
+ * long-clip encoder attention sweep).  One persistent tcgen05 kernel: S = Q K^T and O += P V on the tensor cores
+ * (bf16 x bf16 -> fp32 in TMEM), one-pass softmax with the reference's REPLACE-by--1e9 masking; the (B,H,Sq,Sk)
+ * score tensor is never written.  Pitches ld?/bs? in ELEMENTS (multiples of 8).  mask_kind / causal as above.
+ * O bf16 (B,Sq,H*dk); lse (may be NULL): fp32 (B,H,Sq) log-sum-exp of the masked scaled scores.  dk in {64,128,256};
+ * no dropout (inference / sweep path). */
+int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, const void* K, long long ldk, long long bsk,
+                        const void* V, long long ldv, long long bsv, const unsigned char* mask, int mask_kind,
+                        int causal, void* O, long long ldo, long long bso, float* lse, int B, int H, int Sq, int Sk,
+                        int dk, void* stream);
+
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
 int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */
 int bmhrl_log_softmax_bwd_f32(const float* dy, const float* y, float* dx, long long rows, int V, void* stream);
