@@ -69,6 +69,37 @@ __device__ __forceinline__ void tmem_ld_32x32_b(uint32_t taddr, uint32_t* v) {
         : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait_b() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st_32x32_x16(uint32_t taddr, const uint32_t* v) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        :
+        : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+          "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait_b() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// rare path of the lazy softmax: multiply this warp's 32 accumulator rows (nchunks x 32 fp32 columns) by alpha[row]
+__device__ __noinline__ void rescale_o(uint32_t taddr, int nchunks, float alpha) {
+    for (int c = 0; c < nchunks; ++c) {
+        uint32_t o[32];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3]), "=r"(o[4]), "=r"(o[5]), "=r"(o[6]), "=r"(o[7]), "=r"(o[8]),
+              "=r"(o[9]), "=r"(o[10]), "=r"(o[11]), "=r"(o[12]), "=r"(o[13]), "=r"(o[14]), "=r"(o[15]), "=r"(o[16]),
+              "=r"(o[17]), "=r"(o[18]), "=r"(o[19]), "=r"(o[20]), "=r"(o[21]), "=r"(o[22]), "=r"(o[23]), "=r"(o[24]),
+              "=r"(o[25]), "=r"(o[26]), "=r"(o[27]), "=r"(o[28]), "=r"(o[29]), "=r"(o[30]), "=r"(o[31])
+            : "r"(taddr + c * 32)
+            : "memory");
+        tmem_ld_wait_b();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) o[t] = __float_as_uint(__uint_as_float(o[t]) * alpha);
+        tmem_st_32x32_b(taddr + c * 32, o);
+    }
+    tmem_st_wait_b();
+}
 
 // D[tmem] (+)= A[tmem] * B[smem], kind::f16: A holds two bf16 per 32-bit TMEM cell (row = lane, k pair = column)
 __device__ __forceinline__ void mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
@@ -284,53 +315,99 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 mbar_wait(s_full(buf), ((uint32_t)(n >> 1)) & 1u);
                 tc_fence_after();
                 const uint32_t taddr = lane_base + buf * AB_BN;
-                uint32_t r[128];
-#pragma unroll
-                for (int c = 0; c < 4; ++c) tmem_ld_32x32_b(taddr + c * 32, r + c * 32);
-                tmem_ld_wait();
-                float mt = -INFINITY;
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-#pragma unroll
-                    for (int t = 0; t < 32; ++t) {
-                        float x = ((vis[c] >> t) & 1u) ? __uint_as_float(r[c * 32 + t]) * sl2 : neg2;
-                        x = (c * 32 + t) < keys ? x : -INFINITY;
-                        r[c * 32 + t] = __float_as_uint(x);
-                        mt = fmaxf(mt, x);
-                    }
-                }
-                const bool raise = mt > m + AB_LAZY;  // first tile: m = -inf
+                // Scores stay in the raw domain: max over raw scores, one FFMA (score * scale*log2e - m) feeds ex2.
+                const bool fast = __all_sync(0xffffffffu, keys == AB_BN && (vis[0] & vis[1] & vis[2] & vis[3]) == 0xffffffffu);
+                const int nch = ((keys + 63) >> 6) << 1;  // 32-key chunks covered by the V stages of this tile
+                bool raise;
                 float alpha = 1.f;
-                if (raise) {
-                    alpha = ex2_approx(m - mt);
-                    m = mt;
-                    l *= alpha;
-                }
-                float acc = 0.f;
+                if (fast) {  // every key of the tile visible to every row of the warp: straight-line, one TMEM read
+                    uint32_t r[128];
 #pragma unroll
-                for (int t = 0; t < 128; t += 2) {
-                    const float p0 = ex2_approx(__uint_as_float(r[t]) - m);
-                    const float p1 = ex2_approx(__uint_as_float(r[t + 1]) - m);
-                    acc += p0 + p1;
-                    r[t >> 1] = pack_bf16x2(p0, p1);
-                }
-                l += acc;
-                if (j > 0) {  // P V of the previous tile: every phase of pv_bar is waited for, in order
-                    mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
-                    tc_fence_after();
-                    if (__any_sync(0xffffffffu, raise)) {  // rare: bring the accumulator to the new offset
-                        for (int c = 0; c < (p.dk >> 5); ++c) {
-                            uint32_t o[32];
-                            tmem_ld_32x32_b(lane_base + 256 + c * 32, o);
-                            tmem_ld_wait();
+                    for (int c = 0; c < 4; ++c) tmem_ld_32x32_b(taddr + c * 32, r + c * 32);
+                    tmem_ld_wait();
+                    float mx = __uint_as_float(r[0]);
 #pragma unroll
-                            for (int t = 0; t < 32; ++t) o[t] = __float_as_uint(__uint_as_float(o[t]) * alpha);
-                            tmem_st_32x32_b(lane_base + 256 + c * 32, o);
+                    for (int t = 1; t < 128; ++t) mx = fmaxf(mx, __uint_as_float(r[t]));
+                    const float mt = mx * sl2;
+                    raise = mt > m + AB_LAZY;  // first tile: m = -inf
+                    if (raise) {
+                        alpha = ex2_approx(m - mt);
+                        m = mt;
+                        l *= alpha;
+                    }
+                    const float nm = -m;
+                    float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+                    for (int t = 0; t < 128; t += 2) {
+                        const float p0 = ex2_approx(fmaf(__uint_as_float(r[t]), sl2, nm));
+                        const float p1 = ex2_approx(fmaf(__uint_as_float(r[t + 1]), sl2, nm));
+                        acc0 += p0;
+                        acc1 += p1;
+                        r[t >> 1] = pack_bf16x2(p0, p1);
+                    }
+                    l += acc0 + acc1;
+                    if (j > 0) {  // P V of the previous tile: every phase of pv_bar is waited for, in order
+                        mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+                        tc_fence_after();
+                    }
+                    if (j > 0 && __any_sync(0xffffffffu, raise)) rescale_o(lane_base + 256, p.dk >> 5, alpha);
+                    tmem_st_32x32_b(taddr, r);
+                    tmem_st_32x32_b(taddr + 32, r + 32);
+                } else {  // masked / partial tile: two rolled sweeps over 32-key chunks (small code, selects per element)
+                    const float neg_raw = kNegFill / p.scale;  // * scale*log2e gives the replaced score in the log2 domain
+                    float mx = -INFINITY;
+#pragma unroll 1
+                    for (int c = 0; c < nch; ++c) {
+                        const uint32_t v = c == 0 ? vis[0] : c == 1 ? vis[1] : c == 2 ? vis[2] : vis[3];
+                        const int rem = keys - c * 32;
+                        const uint32_t valid = rem >= 32 ? 0xffffffffu : (rem <= 0 ? 0u : ((1u << rem) - 1u));
+                        uint32_t r[32];
+                        tmem_ld_32x32_b(taddr + c * 32, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int t = 0; t < 32; ++t) {
+                            float x = ((v >> t) & 1u) ? __uint_as_float(r[t]) : neg_raw;
+                            x = ((valid >> t) & 1u) ? x : -INFINITY;
+                            mx = fmaxf(mx, x);
                         }
                     }
+                    const float mt = mx * sl2;
+                    raise = mt > m + AB_LAZY;
+                    if (raise) {
+                        alpha = ex2_approx(m - mt);
+                        m = mt;
+                        l *= alpha;
+                    }
+                    const float nm = -m;
+                    if (j > 0) {
+                        mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+                        tc_fence_after();
+                    }
+                    if (j > 0 && __any_sync(0xffffffffu, raise)) rescale_o(lane_base + 256, p.dk >> 5, alpha);
+                    float acc = 0.f;
+#pragma unroll 1
+                    for (int c = 0; c < nch; ++c) {
+                        const uint32_t v = c == 0 ? vis[0] : c == 1 ? vis[1] : c == 2 ? vis[2] : vis[3];
+                        const int rem = keys - c * 32;
+                        const uint32_t valid = rem >= 32 ? 0xffffffffu : (rem <= 0 ? 0u : ((1u << rem) - 1u));
+                        uint32_t r[32];
+                        tmem_ld_32x32_b(taddr + c * 32, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int t = 0; t < 32; t += 2) {
+                            float x0 = ((v >> t) & 1u) ? __uint_as_float(r[t]) : neg_raw;
+                            float x1 = ((v >> (t + 1)) & 1u) ? __uint_as_float(r[t + 1]) : neg_raw;
+                            x0 = ((valid >> t) & 1u) ? x0 : -INFINITY;
+                            x1 = ((valid >> (t + 1)) & 1u) ? x1 : -INFINITY;
+                            const float p0 = ex2_approx(fmaf(x0, sl2, nm));
+                            const float p1 = ex2_approx(fmaf(x1, sl2, nm));
+                            acc += p0 + p1;
+                            r[t >> 1] = pack_bf16x2(p0, p1);
+                        }
+                        tmem_st_32x32_x16(taddr + c * 16, r);  // packed P never reaches the unread S chunks
+                    }
+                    l += acc;
                 }
-                tmem_st_32x32_b(taddr, r);
-                tmem_st_32x32_b(taddr + 32, r + 32);
                 tmem_st_wait_b();
                 tc_fence_before();
                 mbar_arrive(s_rel(buf));
@@ -340,13 +417,15 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             tc_fence_after();
             const float inv_l = 1.f / l;
             __nv_bfloat16* orow = p.O + (long long)b * p.bso + (long long)q * p.ldo + h * p.dk;
-            for (int c = 0; c < (p.dk >> 5); ++c) {
-                uint32_t o[32];
+#pragma unroll 1
+            for (int c = 0; c < (p.dk >> 5); c += 2) {
+                uint32_t o[64];
                 tmem_ld_32x32_b(lane_base + 256 + c * 32, o);
+                tmem_ld_32x32_b(lane_base + 256 + c * 32 + 32, o + 32);
                 tmem_ld_wait();
                 if (row_ok) {
 #pragma unroll
-                    for (int t = 0; t < 32; t += 8) {
+                    for (int t = 0; t < 64; t += 8) {
                         uint4 u;
                         u.x = pack_bf16x2(__uint_as_float(o[t]) * inv_l, __uint_as_float(o[t + 1]) * inv_l);
                         u.y = pack_bf16x2(__uint_as_float(o[t + 2]) * inv_l, __uint_as_float(o[t + 3]) * inv_l);

@@ -26,6 +26,7 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // Bounded spin: a pipeline bug must surface as a launch failure (trap), never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok = 0;
+#pragma unroll 1  // one compact spin loop per call site (the unrolled form made the kernels 5x larger)
     for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
