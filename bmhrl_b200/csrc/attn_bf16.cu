@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
     const uint32_t tmem_o = tmem_base + 256;
 
     if (warp == 0) {
-        if (lane == 0) {  // ===== TMA producer (same op order as the MMA issuer)
+        if (elect_one()) {  // ===== TMA producer (same op order as the MMA issuer)
             int it = 0;
             for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
                 const int bh = w / p.nqt, qt = w - bh * p.nqt;
@@ -215,9 +215,12 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ===== MMA issuer
+        if (elect_one()) {  // ===== MMA issuer
             const uint32_t idesc_s = make_idesc(1, AB_BM, AB_BN, 0, 0);
             const uint32_t idesc_o = make_idesc(1, AB_BM, p.dk, 0, 1);
+            const uint64_t q_desc = make_smem_desc(sQ, 16, 1024);        // K-major, 128-byte rows, 8-row groups
+            const uint64_t ring_desc = make_smem_desc(ring, 16, 1024);   // K tiles, same layout
+            const uint64_t v_desc = make_smem_desc(ring, 8192, 1024);    // V tiles: MN-major, 64-column chunks 8 KB apart
             int it = 0, ns = 0, np = 0;  // ring position, S tiles issued, P V tiles issued (all items)
             for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
                 mbar_wait(q_full, (uint32_t)i & 1u);
@@ -228,14 +231,13 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                         const int s = it % AB_STAGES;
                         mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
                         tc_fence_after();
-                        const uint32_t sK = ring + s * AB_STAGE_BYTES;
                         for (int cc = 0; cc < ncs; ++cc) {
-                            const uint32_t a0 = sQ + (hf * ncs + cc) * 16384, b0 = sK + cc * 16384;
+                            const uint64_t a0 = desc_advance(q_desc, (hf * ncs + cc) * 16384);
+                            const uint64_t b0 = desc_advance(ring_desc, s * AB_STAGE_BYTES + cc * 16384);
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                mma_bf16_ss(tmem_base + buf * AB_BN, make_smem_desc(a0 + k * 32, 16, 1024),
-                                            make_smem_desc(b0 + k * 32, 16, 1024), idesc_s,
-                                            (hf > 0 || cc > 0 || k > 0) ? 1u : 0u);
+                                mma_bf16_ss(tmem_base + buf * AB_BN, desc_advance(a0, k * 32), desc_advance(b0, k * 32),
+                                            idesc_s, (hf > 0 || cc > 0 || k > 0) ? 1u : 0u);
                         }
                         tc_commit(empty_bar(s));
                     }
@@ -253,12 +255,11 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                         const int s = it % AB_STAGES;
                         mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
                         tc_fence_after();
-                        const uint32_t sV = ring + s * AB_STAGE_BYTES;
+                        const uint64_t v0 = desc_advance(v_desc, s * AB_STAGE_BYTES);
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk)
-                            mma_bf16_ts(tmem_o, tmem_base + buf * AB_BN + kc * 32 + kk * 8,
-                                        make_smem_desc(sV + kk * 2048, 8192, 1024), idesc_o,
-                                        (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
+                            mma_bf16_ts(tmem_o, tmem_base + buf * AB_BN + kc * 32 + kk * 8, desc_advance(v0, kk * 2048),
+                                        idesc_o, (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
                         tc_commit(empty_bar(s));
                     }
                     tc_commit(pv_bar);
