@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(192) attn_fwd_tc_kernel(const __grid_constant_
     const uint32_t tmem_o = tmem_base + 256;
 
     if (warp == 0) {
-        if (lane == 0) {  // ===== TMA producer: same op order as the MMA issuer below
+        if (elect_one()) {  // ===== TMA producer: same op order as the MMA issuer below
             int it = 0;
             auto load_qk = [&](int j) {
                 for (int c = 0; c < ncq; ++c, ++it) {
@@ -146,9 +146,11 @@ __global__ void __launch_bounds__(192) attn_fwd_tc_kernel(const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ===== MMA issuer
+        if (elect_one()) {  // ===== MMA issuer
             const uint32_t idesc_s = make_idesc(2, AT_BM, AT_BN, 0, 0);
             const uint32_t idesc_o = make_idesc(2, AT_BM, p.dvt, 0, 1);
+            const uint64_t qk_desc = make_smem_desc(base, 16, 1024);      // stage 0, K-major; later stages: desc_advance
+            const uint64_t v_desc = make_smem_desc(base, 4096, 512, 1);   // stage 0, MN-major fp32 (BASE32B layout)
             int it = 0, n = 0;
             int waited[2] = {0, 0};
             auto wait_rel = [&](int buf, int count) {
@@ -165,11 +167,11 @@ __global__ void __launch_bounds__(192) attn_fwd_tc_kernel(const __grid_constant_
                     const int s = it % AT_STAGES;
                     mbar_wait(full_bar(s), ((uint32_t)(it / AT_STAGES)) & 1u);
                     tc_fence_after();
-                    const uint32_t sA = base + s * AT_STAGE_BYTES, sB = sA + AT_BM * 128;
+                    const uint64_t da = desc_advance(qk_desc, s * AT_STAGE_BYTES), db = desc_advance(da, AT_BM * 128);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        mma_tf32_ss(tmem_base + buf * AT_BN, make_smem_desc(sA + k * 32, 16, 1024),
-                                    make_smem_desc(sB + k * 32, 16, 1024), idesc_s, (c > 0 || k > 0) ? 1u : 0u);
+                        mma_tf32_ss(tmem_base + buf * AT_BN, desc_advance(da, k * 32), desc_advance(db, k * 32), idesc_s,
+                                    (c > 0 || k > 0) ? 1u : 0u);
                     tc_commit(empty_bar(s));
                 }
                 tc_commit(s_full(buf));
@@ -183,12 +185,11 @@ __global__ void __launch_bounds__(192) attn_fwd_tc_kernel(const __grid_constant_
                     const int s = it % AT_STAGES;
                     mbar_wait(full_bar(s), ((uint32_t)(it / AT_STAGES)) & 1u);
                     tc_fence_after();
-                    const uint32_t sV = base + s * AT_STAGE_BYTES;
+                    const uint64_t dv = desc_advance(v_desc, s * AT_STAGE_BYTES);
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk)
-                        mma_tf32_ts(tmem_o, tmem_base + buf * AT_BN + kc * 32 + kk * 8,
-                                    make_smem_desc(sV + kk * 1024, 4096, 512, 1), idesc_o,
-                                    (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
+                        mma_tf32_ts(tmem_o, tmem_base + buf * AT_BN + kc * 32 + kk * 8, desc_advance(dv, kk * 1024),
+                                    idesc_o, (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
                     tc_commit(empty_bar(s));
                 }
             };

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
     if (warp == 0) {
-        if (lane == 0) {  // ===== TMA producer
+        if (elect_one()) {  // ===== TMA producer
             for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
                 const int s = it % STAGES;
                 const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
@@ -135,22 +135,23 @@ __global__ void __launch_bounds__(192) gemm_tf32_tc_kernel(const __grid_constant
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ===== MMA issuer
+        if (elect_one()) {  // ===== MMA issuer
             const uint32_t idesc = make_idesc(2, TC_BM, BN, p.a_mn, p.b_mn);
+            // stage-0 descriptors; a stage / K step further on is one add (see desc_advance)
+            const uint64_t ad0 = p.a_mn ? make_smem_desc(base, TC_BK * 128, 512, 1) : make_smem_desc(base, 16, 1024);
+            const uint64_t bd0 = p.b_mn ? make_smem_desc(base + TC_A_BYTES, TC_BK * 128, 512, 1)
+                                        : make_smem_desc(base + TC_A_BYTES, 16, 1024);
+            const uint32_t a_step = p.a_mn ? 1024u : 32u, b_step = p.b_mn ? 1024u : 32u;
             for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
                 const int s = it % STAGES;
                 const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
                 mbar_wait(full_bar(s), ph);
                 tc_fence_after();
-                const uint32_t sA = base + s * STAGE_BYTES, sB = sA + TC_A_BYTES;
+                const uint64_t ad = desc_advance(ad0, s * STAGE_BYTES), bd = desc_advance(bd0, s * STAGE_BYTES);
 #pragma unroll
-                for (int k = 0; k < TC_BK / 8; ++k) {  // UMMA_K = 8 for tf32 (32 bytes of K)
-                    const uint64_t ad = p.a_mn ? make_smem_desc(sA + k * 1024, TC_BK * 128, 512, 1)
-                                               : make_smem_desc(sA + k * 32, 16, 1024);
-                    const uint64_t bd = p.b_mn ? make_smem_desc(sB + k * 1024, TC_BK * 128, 512, 1)
-                                               : make_smem_desc(sB + k * 32, 16, 1024);
-                    mma_tf32_ss(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
-                }
+                for (int k = 0; k < TC_BK / 8; ++k)  // UMMA_K = 8 for tf32 (32 bytes of K)
+                    mma_tf32_ss(tmem_base, desc_advance(ad, k * a_step), desc_advance(bd, k * b_step), idesc,
+                                (it > 0 || k > 0) ? 1u : 0u);
                 tc_commit(empty_bar(s));  // frees the smem slot once these MMAs have read it
             }
             tc_commit(tmem_full_bar);  // accumulator complete
