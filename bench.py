@@ -366,9 +366,15 @@ def run_gpu(args):
                                     "kind": "port",
                                     "sample": "5 full B=16 steps (median, 1 warm-up) of the oracle port of the "
                                               "reference step on the host cores: fwd + loss + bwd + Adam, fp32"}
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # The step graph holds captured NCCL work: tearing the communicator down (destroy_process_group, or the
+        # interpreter's own teardown order) with it alive hangs.  Everything is measured and printed; leave together.
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def step_bytes(workload):
