@@ -21,11 +21,13 @@ class GradSync:
         self.value_fn_mean = value_fn_mean
         self.calls = 0
 
-    def ranges(self, opt):
-        """Contiguous [start, end) element ranges of opt.flat_grad that hold currently-trainable tensors, merged
-        and then split into buckets of at most bucket_elems."""
+    def ranges(self, opt, only=None):
+        """Contiguous [start, end) element ranges of opt.flat_grad that hold currently-trainable tensors (of the
+        parameter indices in `only`, when given), merged and then split into buckets of at most bucket_elems."""
         spans = []
         for i in opt.active:
+            if only is not None and i not in only:
+                continue
             s = opt.offsets[i]
             e = s + opt.params[i].numel()
             if spans and spans[-1][1] == s:
@@ -40,10 +42,10 @@ class GradSync:
                 s += n
         return out
 
-    def __call__(self, opt, mean=False):
+    def __call__(self, opt, mean=False, only=None):
         if self.world == 1:
             return
-        for s, e in self.ranges(opt):
+        for s, e in self.ranges(opt, only):
             dist.all_reduce(opt.flat_grad[s:e], op=dist.ReduceOp.SUM, group=self.group)
             self.calls += 1
         if mean:

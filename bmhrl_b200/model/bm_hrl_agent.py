@@ -483,6 +483,16 @@ class BMHrlAgent(nn.Module):
 
     concurrent_branches = True  # critic / worker fusion stack on side streams (same results, fewer idle SMs)
 
+    # data-parallel hook (set by the trainer): called in backward once every gradient of the modules AFTER the encoder
+    # has been enqueued, so their all-reduce overlaps the encoder's backward (bmhrl_b200/ddp.py)
+    grad_ready_callback = None
+
+    def _mark_encoder_outputs(self, Va, Av):
+        cb = self.grad_ready_callback
+        if cb is None:
+            return Va, Av
+        return ops.grad_marker(Va, cb), ops.grad_marker(Av, cb)
+
     def predict_with_features(self, C, V, A, mask):
         """:637-651.  The frozen critic (depends only on the caption embedding) and the worker fusion stack
         (independent of the manager one, model/bm_hrl_agent.py:646-647) are forked onto side streams."""
@@ -490,6 +500,7 @@ class BMHrlAgent(nn.Module):
             _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
             C = self.pos_enc_C(C)
             Va, Av = self.bm_enc((V, A), mask)
+            Va, Av = self._mark_encoder_outputs(Va, Av)
             worker_feat = self.bm_worker_fus((C, (Av, Va)), mask)
             manager_feat = self.bm_manager_fus((C, (Av, Va)), mask)
         else:
@@ -500,6 +511,7 @@ class BMHrlAgent(nn.Module):
                 _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
             C = self.pos_enc_C(C)
             Va, Av = self.bm_enc((V, A), mask)
+            Va, Av = self._mark_encoder_outputs(Va, Av)
             s_worker.wait_stream(cur)
             with torch.cuda.stream(s_worker):
                 worker_feat = self.bm_worker_fus((C, (Av, Va)), mask)

@@ -157,6 +157,38 @@ def join_side_streams(device=None):
     _WGRAD_KEEP.clear()
 
 
+def wait_dirty_side_streams(stream, device=None):
+    """`stream` waits for everything enqueued so far on the side streams that received work since the last join
+    (they stay marked: the trainer's final join still covers what they get afterwards)."""
+    idx = stream.device.index
+    for key in list(_DIRTY):
+        if key[0] == idx and _SIDE[key] is not stream:
+            stream.wait_stream(_SIDE[key])
+
+
+class _GradMarker(torch.autograd.Function):
+    """Identity whose backward calls `callback()` first.  Autograd runs ready nodes in reverse creation order, so when
+    the marker placed on the encoder outputs fires, the backward kernels of everything created AFTER it (fusion
+    stacks, manager / worker heads, loss) have all been enqueued: their gradients can start their all-reduce while
+    the encoder's backward is still running."""
+
+    @staticmethod
+    def forward(ctx, x, callback):
+        ctx.callback = callback
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.callback()
+        return g, None
+
+
+def grad_marker(x, callback):
+    if callback is None or not (torch.is_grad_enabled() and x.requires_grad):
+        return x
+    return _GradMarker.apply(x, callback)
+
+
 def manual_seed(seed, device="cuda"):
     RNG.seed(int(seed), device)
 
@@ -224,13 +256,16 @@ class _Linear(torch.autograd.Function):
             RECORD.append(("linear", M, N, K))
         LIB.call("bmhrl_linear_fwd_f32", _p(x), K, _p(weight), _p(b), _p(r), N, _p(y), N, M, N, K, act, drop_p,
                  _p(rng) if drop_p > 0 else None, salt, _stream())
-        ctx.save_for_backward(x, weight, y if act == 1 else None, rng if drop_p > 0 else None, wgrad, bgrad)
+        ctx.save_for_backward(x, weight, y if act == 1 else None, rng if drop_p > 0 else None)
+        ctx.gbufs = (wgrad, bgrad)  # destination slices of the flat gradient buffer: not autograd-saved (the
+        # data-parallel all-reduce updates other slices of that buffer in place while backward is still running)
         ctx.cfg = (act, drop_p, salt, M, N, K, bias is not None, resid is not None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, weight, y, rng, wgrad, bgrad = ctx.saved_tensors
+        x, weight, y, rng = ctx.saved_tensors
+        wgrad, bgrad = ctx.gbufs
         act, drop_p, salt, M, N, K, has_bias, has_resid = ctx.cfg
         dy = _c(dy, "dy")
         need_x, need_w, need_b, need_r = ctx.needs_input_grad[0], ctx.needs_input_grad[1], \
@@ -289,12 +324,14 @@ class _LayerNorm(torch.autograd.Function):
         rstd = torch.empty(rows, device=x.device, dtype=_F32)
         LIB.call("bmhrl_layernorm_fwd_f32", _p(x), None, _p(gamma), _p(beta), None, _p(y), _p(mean), _p(rstd), rows, D,
                  eps, _stream())
-        ctx.save_for_backward(x, gamma, mean, rstd, ggrad, bgrad)
+        ctx.save_for_backward(x, gamma, mean, rstd)
+        ctx.gbufs = (ggrad, bgrad)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, gamma, mean, rstd, ggrad, bgrad = ctx.saved_tensors
+        x, gamma, mean, rstd = ctx.saved_tensors
+        ggrad, bgrad = ctx.gbufs
         dy = _c(dy, "dy")
         D = x.shape[-1]
         rows = x.numel() // D
@@ -323,12 +360,14 @@ class _GatedMix(torch.autograd.Function):
         gate = _c(gate, "gate")
         out = torch.empty_like(v)
         LIB.call("bmhrl_gated_mix_fwd_f32", _p(v), _p(a), _p(gate), _p(out), v.numel(), _stream())
-        ctx.save_for_backward(v, a, gate, ggrad)
+        ctx.save_for_backward(v, a, gate)
+        ctx.gbufs = (ggrad,)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        v, a, gate, ggrad = ctx.saved_tensors
+        v, a, gate = ctx.saved_tensors
+        (ggrad,) = ctx.gbufs
         g = _c(g, "g")
         dv = torch.empty_like(v)
         da = torch.empty_like(a)

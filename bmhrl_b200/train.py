@@ -44,6 +44,17 @@ class BMHRLTrainer:
         self.mv_opt = ops.FusedAdam(mv_model.parameters(), lr=lr)
         self.grad_sync = grad_sync  # data-parallel hook: callable(optimizer) all-reducing optimizer.flat_grad
         self.loss_factor = 4.0 / 20.0  # captioning_bmrl_loops.py:831-833
+        # Overlap of the gradient all-reduce with backward: parameters of everything after the encoder (fusion stacks,
+        # heads) are final when the marker on the encoder outputs fires in backward; their buckets are reduced on a
+        # communication stream while the encoder's backward runs, the encoder's own buckets after the final join.
+        ids = {id(p): n for n, p in cap_model.named_parameters()}
+        self._early = frozenset(i for i, p in enumerate(self.cap_opt.params) if not ids[id(p)].startswith("bm_enc."))
+        self._late = frozenset(range(len(self.cap_opt.params))) - self._early
+        self._early_done = False
+        self._comm_stream = None
+        self.overlap_grad_sync = True
+        if grad_sync is not None and getattr(grad_sync, "world", 1) > 1 and hasattr(cap_model, "predict_with_features"):
+            cap_model.grad_ready_callback = self._early_sync
 
     # ---- phase switching (captioning_bmrl_loops.py:809-820, :1144) ------------------------------------------------
     def teach_warmstart(self):
@@ -72,9 +83,30 @@ class BMHRLTrainer:
                            self.modality, self.pad_idx)
         return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y.contiguous(), masks
 
+    def _early_sync(self):
+        """Backward-time callback (ops.grad_marker on the encoder outputs): all-reduce the post-encoder gradients on
+        the communication stream, behind everything enqueued so far on this stream and on the side streams."""
+        if self.grad_sync is None or self._early_done or not self.overlap_grad_sync:
+            return
+        self._early_done = True
+        dev = self.cap_opt.flat_grad.device
+        if self._comm_stream is None:
+            self._comm_stream = torch.cuda.Stream(device=dev)
+        comm = self._comm_stream
+        comm.wait_stream(torch.cuda.current_stream(dev))
+        ops.wait_dirty_side_streams(comm)
+        with torch.cuda.stream(comm):
+            self.grad_sync(self.cap_opt, only=self._early)
+
     def _sync(self, opt, mean=False):
-        if self.grad_sync is not None:
-            self.grad_sync(opt, mean=mean)
+        if self.grad_sync is None:
+            return
+        if opt is self.cap_opt and self._early_done:
+            self._early_done = False
+            self.grad_sync(opt, mean=mean, only=self._late)
+            torch.cuda.current_stream(opt.flat_grad.device).wait_stream(self._comm_stream)
+            return
+        self.grad_sync(opt, mean=mean)
 
     def _global_tokens(self, n_tokens):
         """The reference computes the loss once over the gathered global batch (DataParallel), so the normaliser is

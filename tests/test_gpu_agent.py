@@ -181,3 +181,76 @@ def test_padding_invariance_full_size(gpu_lib, agent_sd):
     assert rel(out2[0], out[0]) < 1e-5 and torch.equal(out2[4], out[4])
     lse = torch.logsumexp(out[0], -1)
     assert float(lse.abs().max()) < 1e-4  # rows are log-probabilities
+
+
+class _FakeSync:
+    """Stands in for ddp.GradSync with world = 2 and identical ranks on ONE GPU: the 'all-reduce' of a bucket doubles
+    it in place (on the current stream) and counts how often every element was reduced."""
+
+    def __init__(self):
+        from bmhrl_b200.ddp import GradSync
+        self._gs = GradSync.__new__(GradSync)
+        self._gs.bucket_elems, self._gs.world, self._gs.group, self._gs.calls = 1 << 20, 2, None, 0
+        self.world = 2
+        self.count = {}
+        self.log = []
+
+    def __call__(self, opt, mean=False, only=None):
+        cnt = self.count.setdefault(id(opt), torch.zeros_like(opt.flat_grad))
+        for s, e in self._gs.ranges(opt, only):
+            opt.flat_grad[s:e].mul_(2.0)
+            cnt[s:e] += 1
+        self.log.append((None if only is None else len(only), torch.cuda.current_stream().cuda_stream))
+        if mean:
+            opt.flat_grad.div_(2)
+
+    def all_reduce_scalar(self, t):
+        return t * 2
+
+
+@pytest.mark.parametrize("kind,use_graph", [("warmstart", False), ("warmstart", True), ("worker", True)])
+def test_overlapped_grad_sync_reduces_every_gradient_once(gpu_lib, agent_sd, kind, use_graph):
+    """Data-parallel overlap (train.BMHRLTrainer._early_sync): the post-encoder buckets are reduced from the backward
+    marker on a communication stream, the encoder buckets after the join -- every trainable element exactly once,
+    and the step result equals the non-overlapped order."""
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, StepRunner
+    b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=3, ragged=True)
+    res = []
+    from bmhrl_b200 import ops
+    for overlap in (False, True):
+        ops.manual_seed(11, "cuda")  # same sampling draws in both runs ...
+        ops.RNG.salt = 1000           # ... and the same call-site salts
+        model, cfg = build_agent(agent_sd)
+        sync = _FakeSync()
+        tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD,
+                          grad_sync=sync)
+        tr.overlap_grad_sync = overlap
+        (tr.teach_warmstart if kind == "warmstart" else tr.teach_worker)()
+        model.manager.exploration = False
+        run = StepRunner(tr, kind, b, use_graph=use_graph, warmup=1 if use_graph else 0)
+        sync.count.clear()
+        sync.log.clear()
+        if use_graph:  # the count tensors are not part of the graph: check them on one extra eager step
+            run._eager()
+        else:
+            run.step(b)
+        torch.cuda.synchronize()
+        cnt = sync.count[id(tr.cap_opt)]
+        act = torch.zeros_like(cnt)
+        for i in tr.cap_opt.active:
+            o = tr.cap_opt.offsets[i]
+            act[o:o + tr.cap_opt.params[i].numel()] = 1
+        assert torch.equal(cnt, act), "a gradient element was reduced twice or not at all"
+        cap_calls = [l for l in sync.log if l[0] is not None]
+        if overlap:
+            assert len(cap_calls) == 2 and cap_calls[0][1] != cap_calls[1][1]  # early part on the communication stream
+            assert cap_calls[0][0] == len(tr._early) and cap_calls[1][0] == len(tr._late)
+        else:
+            assert not cap_calls
+        for _ in range(2):
+            run.step(b)
+        torch.cuda.synchronize()
+        res.append((model.worker.core.projection.weight.detach().clone(),
+                    model.bm_enc.encoder.layers[0].self_att_M1.linear_Q2d.weight.detach().clone()))
+    assert rel(res[1][0], res[0][0]) < 1e-6 and rel(res[1][1], res[0][1]) < 1e-6
