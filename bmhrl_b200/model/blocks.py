@@ -15,9 +15,16 @@ class LayerStack(nn.Module):
         super(LayerStack, self).__init__()
         self.layers = clone(layer, N)
 
+    # optional callable(i, x) -> x applied to the output of layer i < N-1 (the data-parallel trainer marks the layer
+    # boundaries so that gradient buckets of finished layers can be reduced while backward continues below them)
+    layer_boundary_hook = None
+
     def forward(self, x, masks):
-        for layer in self.layers:
+        hook = self.layer_boundary_hook
+        for i, layer in enumerate(self.layers):
             x = layer(x, masks)
+            if hook is not None and i + 1 < len(self.layers):
+                x = hook(i, x)
         return x
 
 

@@ -1003,17 +1003,40 @@ class FusedAdam:
         self._ct = torch.tensor(ct, device=dev, dtype=torch.int32)
         self._cs = torch.tensor(cs, device=dev, dtype=torch.int32)
         self.n_chunks = len(ct)
+        self._subsets = {}  # frozenset of parameter indices -> (act, ct, cs, n_act, n_chunks) device tables
+
+    def _subset_tables(self, only):
+        """Chunk tables of the active parameters whose index is in `only` (built on first use: call once eagerly
+        before capturing a CUDA graph -- StepRunner's warm-up steps do)."""
+        key = only if isinstance(only, frozenset) else frozenset(only)
+        t = self._subsets.get(key)
+        if t is None:
+            dev = self.flat_grad.device
+            act = [i for i in self.active if i in key]
+            ct, cs = [], []
+            for i in act:
+                for s in range(0, self.params[i].numel(), self.chunk):
+                    ct.append(i)
+                    cs.append(s)
+            i32 = dict(device=dev, dtype=torch.int32)
+            t = (torch.tensor(act, **i32), torch.tensor(ct, **i32), torch.tensor(cs, **i32), len(act), len(ct))
+            self._subsets[key] = t
+        return t
 
     def zero_grad(self, set_to_none=False):
         self.flat_grad.zero_()
         for i in self.active:
             self.params[i].grad = self.grad_views[i]
 
-    def step(self):
+    def step(self, only=None):
+        """One Adam update of every active parameter, or of those whose index is in `only` (the data-parallel trainer
+        updates the parameters whose gradients are already reduced while backward is still running)."""
         st = _stream()
-        if self.n_chunks == 0:
+        act, ct, cs, n_act, n_chunks = (self._act, self._ct, self._cs, len(self.active), self.n_chunks) \
+            if only is None else self._subset_tables(only)
+        if n_chunks == 0:
             return
-        LIB.call("bmhrl_tick", _p(self.step_counts), _p(self._act), len(self.active), None, st)
+        LIB.call("bmhrl_tick", _p(self.step_counts), _p(act), n_act, None, st)
         LIB.call("bmhrl_adam_multi_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne),
-                 _p(self._ct), _p(self._cs), self.n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
+                 _p(ct), _p(cs), n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
                  self.eps, self.grad_scale, st)

@@ -44,17 +44,25 @@ class BMHRLTrainer:
         self.mv_opt = ops.FusedAdam(mv_model.parameters(), lr=lr)
         self.grad_sync = grad_sync  # data-parallel hook: callable(optimizer) all-reducing optimizer.flat_grad
         self.loss_factor = 4.0 / 20.0  # captioning_bmrl_loops.py:831-833
-        # Overlap of the gradient all-reduce with backward: parameters of everything after the encoder (fusion stacks,
-        # heads) are final when the marker on the encoder outputs fires in backward; their buckets are reduced on a
-        # communication stream while the encoder's backward runs, the encoder's own buckets after the final join.
+        # Overlap of the gradient all-reduce (and of Adam) with backward.  Autograd runs ready nodes in reverse creation
+        # order, so when a marker placed on the output of a module fires in backward, the backward kernels of everything
+        # created after it have been enqueued.  Stage 0 = everything after the encoder (fusion stacks, heads), fired by
+        # the marker on the encoder outputs; stage k = encoder layer N-k, fired by the marker on the output of layer
+        # N-k-1.  A fired stage is reduced and Adam-stepped on a communication stream while backward continues; what is
+        # left (encoder layer 0) follows the final join.
         ids = {id(p): n for n, p in cap_model.named_parameters()}
-        self._early = frozenset(i for i, p in enumerate(self.cap_opt.params) if not ids[id(p)].startswith("bm_enc."))
-        self._late = frozenset(range(len(self.cap_opt.params))) - self._early
-        self._early_done = False
+        pnames = [ids[id(p)] for p in self.cap_opt.params]
+        n_enc = len(cap_model.bm_enc.encoder.layers) if hasattr(cap_model, "bm_enc") else 0
+        self._stages = [frozenset(i for i, n in enumerate(pnames) if not n.startswith("bm_enc."))]
+        for k in range(1, n_enc):
+            pre = f"bm_enc.encoder.layers.{n_enc - k}."
+            self._stages.append(frozenset(i for i, n in enumerate(pnames) if n.startswith(pre)))
+        self._fired = []          # stages already handed to the communication stream in this backward
         self._comm_stream = None
         self.overlap_grad_sync = True
-        if grad_sync is not None and getattr(grad_sync, "world", 1) > 1 and hasattr(cap_model, "predict_with_features"):
-            cap_model.grad_ready_callback = self._early_sync
+        if grad_sync is not None and getattr(grad_sync, "world", 1) > 1 and n_enc > 0:
+            cap_model.grad_ready_callback = lambda: self._early_sync(0)
+            cap_model.bm_enc.encoder.layer_boundary_hook = self._mark_layer_boundary
 
     # ---- phase switching (captioning_bmrl_loops.py:809-820, :1144) ------------------------------------------------
     def teach_warmstart(self):
@@ -83,12 +91,20 @@ class BMHRLTrainer:
                            self.modality, self.pad_idx)
         return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y.contiguous(), masks
 
-    def _early_sync(self):
-        """Backward-time callback (ops.grad_marker on the encoder outputs): all-reduce the post-encoder gradients on
-        the communication stream, behind everything enqueued so far on this stream and on the side streams."""
-        if self.grad_sync is None or self._early_done or not self.overlap_grad_sync:
+    def _mark_layer_boundary(self, i, x):
+        """LayerStack hook of the encoder: output (M1, M2) of layer i -> marked copies; the marker fires in backward
+        when layer i+1 is done, i.e. stage n_enc - (i+1)."""
+        n_enc = len(self.cap_model.bm_enc.encoder.layers)
+        stage = n_enc - (i + 1)
+        cb = lambda: self._early_sync(stage)
+        return tuple(ops.grad_marker(t, cb) for t in x)
+
+    def _early_sync(self, stage):
+        """Backward-time callback (ops.grad_marker): all-reduce + Adam of one finished stage on the communication
+        stream, behind everything enqueued so far on this stream and on the side streams."""
+        if self.grad_sync is None or not self.overlap_grad_sync or stage in self._fired or stage >= len(self._stages):
             return
-        self._early_done = True
+        self._fired.append(stage)
         dev = self.cap_opt.flat_grad.device
         if self._comm_stream is None:
             self._comm_stream = torch.cuda.Stream(device=dev)
@@ -96,17 +112,22 @@ class BMHRLTrainer:
         comm.wait_stream(torch.cuda.current_stream(dev))
         ops.wait_dirty_side_streams(comm)
         with torch.cuda.stream(comm):
-            self.grad_sync(self.cap_opt, only=self._early)
+            self.grad_sync(self.cap_opt, only=self._stages[stage])
+            self.cap_opt.step(only=self._stages[stage])
 
-    def _sync(self, opt, mean=False):
-        if self.grad_sync is None:
-            return
-        if opt is self.cap_opt and self._early_done:
-            self._early_done = False
-            self.grad_sync(opt, mean=mean, only=self._late)
+    def _sync_and_step(self, opt, mean=False):
+        """All-reduce (data parallel) + Adam of whatever has not been handled from a backward marker."""
+        if opt is self.cap_opt and self._fired:
+            done = frozenset().union(*(self._stages[k] for k in self._fired))
+            rest = frozenset(range(len(opt.params))) - done
+            self._fired = []
+            self.grad_sync(opt, mean=mean, only=rest)
+            opt.step(only=rest)
             torch.cuda.current_stream(opt.flat_grad.device).wait_stream(self._comm_stream)
             return
-        self.grad_sync(opt, mean=mean)
+        if self.grad_sync is not None:
+            self.grad_sync(opt, mean=mean)
+        opt.step()
 
     def _global_tokens(self, n_tokens):
         """The reference computes the loss once over the gathered global batch (DataParallel), so the normaliser is
@@ -126,8 +147,7 @@ class BMHRLTrainer:
         loss = self.ls.row_sums(pred, y).sum() / n_tokens
         loss.backward()
         ops.join_side_streams(loss.device)
-        self._sync(self.cap_opt)
-        self.cap_opt.step()
+        self._sync_and_step(self.cap_opt)
         return loss.detach()
 
     # ---- RL step -----------------------------------------------------------------------------------------------------
@@ -180,12 +200,10 @@ class BMHRLTrainer:
         cap_loss, value_loss, _, _, _ = self.rl_losses(batch, train_worker, stabilize, exp_noise)
         cap_loss.backward()
         ops.join_side_streams(cap_loss.device)
-        self._sync(self.cap_opt)
-        self.cap_opt.step()
+        self._sync_and_step(self.cap_opt)
         value_loss.backward()
         ops.join_side_streams(value_loss.device)
-        self._sync(vopt, mean=True)  # the value loss is a .mean() over the global (B,L) batch (:874-875)
-        vopt.step()
+        self._sync_and_step(vopt, mean=True)  # the value loss is a .mean() over the global (B,L) batch (:874-875)
         return cap_loss.detach(), value_loss.detach()
 
 

@@ -210,8 +210,8 @@ class _FakeSync:
 
 @pytest.mark.parametrize("kind,use_graph", [("warmstart", False), ("warmstart", True), ("worker", True)])
 def test_overlapped_grad_sync_reduces_every_gradient_once(gpu_lib, agent_sd, kind, use_graph):
-    """Data-parallel overlap (train.BMHRLTrainer._early_sync): the post-encoder buckets are reduced from the backward
-    marker on a communication stream, the encoder buckets after the join -- every trainable element exactly once,
+    """Data-parallel overlap (train.BMHRLTrainer._early_sync): finished stages (post-encoder modules, then encoder
+    layer 1) are reduced + Adam-stepped from backward markers on a communication stream, the rest after the join -- every trainable element exactly once,
     and the step result equals the non-overlapped order."""
     from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
     from bmhrl_b200.train import BMHRLTrainer, StepRunner
@@ -243,9 +243,10 @@ def test_overlapped_grad_sync_reduces_every_gradient_once(gpu_lib, agent_sd, kin
             act[o:o + tr.cap_opt.params[i].numel()] = 1
         assert torch.equal(cnt, act), "a gradient element was reduced twice or not at all"
         cap_calls = [l for l in sync.log if l[0] is not None]
-        if overlap:
-            assert len(cap_calls) == 2 and cap_calls[0][1] != cap_calls[1][1]  # early part on the communication stream
-            assert cap_calls[0][0] == len(tr._early) and cap_calls[1][0] == len(tr._late)
+        if overlap:  # post-encoder stage, encoder layer 1 (both on the communication stream), then the rest
+            assert len(cap_calls) == 3 and cap_calls[0][1] == cap_calls[1][1] != cap_calls[2][1]
+            assert cap_calls[0][0] == len(tr._stages[0]) and cap_calls[1][0] == len(tr._stages[1])
+            assert cap_calls[2][0] == len(tr.cap_opt.params) - len(tr._stages[0]) - len(tr._stages[1])
         else:
             assert not cap_calls
         for _ in range(2):
