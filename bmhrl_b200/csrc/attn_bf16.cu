@@ -42,7 +42,32 @@ struct AttnBf16Params {
     int B, H, Sq, Sk, dk;
     int nqt, n_items;
     float scale;
+    // key-padding masks only (mask_kind 1, not causal), from attn_mask_pack_kernel: keys beyond the last visible one of a
+    // batch row get probability exactly 0 (unless the whole row is masked: sk_eff = Sk), so their tiles are skipped
+    const int* sk_eff;          // (B) or NULL
+    const uint32_t* mbits;      // (B, mwords) visibility bits, 4 words per 128-key tile, or NULL
+    int mwords;
 };
+
+// One CTA per batch row: bit-packs the (B,Sk) key-padding mask and finds the effective key count.
+__global__ void attn_mask_pack_kernel(const unsigned char* __restrict__ mask, int Sk, int mwords, int* __restrict__ sk_eff,
+                                      uint32_t* __restrict__ mbits) {
+    const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    __shared__ int last;
+    if (threadIdx.x == 0) last = -1;
+    __syncthreads();
+    int mine = -1;
+    for (int wd = warp; wd < mwords; wd += nw) {
+        const int k = wd * 32 + lane;
+        const bool on = k < Sk && mask[(long long)b * Sk + k] != 0;
+        const uint32_t bits = __ballot_sync(0xffffffffu, on);
+        if (lane == 0) mbits[(long long)b * mwords + wd] = bits;
+        if (bits) mine = max(mine, wd * 32 + 31 - __clz(bits));
+    }
+    if (lane == 0 && mine >= 0) atomicMax(&last, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) sk_eff[b] = last >= 0 ? last + 1 : Sk;
+}
 
 __device__ __forceinline__ void tmem_st_32x32_b(uint32_t taddr, const uint32_t* v) {
     asm volatile(
@@ -143,7 +168,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
     const uint32_t tmem_slot = bars + 8u * (2 * AB_STAGES + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nkt = (p.Sk + AB_BN - 1) / AB_BN;
+    auto item_sk = [&](int b) { return p.sk_eff ? __ldg(p.sk_eff + b) : p.Sk; };  // keys that can get weight
     const int kcols = p.dk < 128 ? p.dk : 128;   // d_k columns of one K stage
     const int nkh = p.dk / kcols;                // K stages per key tile
     const int ncs = kcols >> 6;                  // 64-column (128-byte) chunks per K stage
@@ -182,6 +207,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 const int bh = w / p.nqt, qt = w - bh * p.nqt;
                 const int b = bh / p.H, h = bh - b * p.H;
                 const int q0 = qt * AB_BM, col_q = h * p.dk;
+                const int Sk = item_sk(b), nkt = (Sk + AB_BN - 1) / AB_BN;
                 mbar_wait(q_empty, ((uint32_t)i & 1u) ^ 1u);
                 mbar_arrive_expect_tx(q_full, (uint32_t)(AB_BM * p.dk * 2));
                 for (int c = 0; c < nvc; ++c) tma_load_4d(sQ + c * 16384, &tmQ, q_full, col_q + c * 64, q0, 0, b);
@@ -196,7 +222,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                     }
                 };
                 auto load_v = [&](int j) {
-                    const int nkc = (min(AB_BN, p.Sk - j * AB_BN) + 63) >> 6;
+                    const int nkc = (min(AB_BN, Sk - j * AB_BN) + 63) >> 6;
                     for (int kc = 0; kc < nkc; ++kc, ++it) {
                         const int s = it % AB_STAGES;
                         mbar_wait(empty_bar(s), (((uint32_t)(it / AB_STAGES)) & 1u) ^ 1u);
@@ -223,6 +249,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             const uint64_t v_desc = make_smem_desc(ring, 8192, 1024);    // V tiles: MN-major, 64-column chunks 8 KB apart
             int it = 0, ns = 0, np = 0;  // ring position, S tiles issued, P V tiles issued (all items)
             for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
+                const int Sk = item_sk((w / p.nqt) / p.H), nkt = (Sk + AB_BN - 1) / AB_BN;
                 mbar_wait(q_full, (uint32_t)i & 1u);
                 tc_fence_after();
                 auto s_op = [&](bool last) {  // S[ns & 1] = Q K_j^T; in-order execution behind the P V that read this buffer
@@ -250,7 +277,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                     mbar_wait(s_rel(buf), ((uint32_t)(np >> 1)) & 1u);
                     if (j == 0 && i > 0) mbar_wait(o_free, ((uint32_t)(i - 1)) & 1u);
                     tc_fence_after();
-                    const int nkc = (min(AB_BN, p.Sk - j * AB_BN) + 63) >> 6;
+                    const int nkc = (min(AB_BN, Sk - j * AB_BN) + 63) >> 6;
                     for (int kc = 0; kc < nkc; ++kc, ++it) {
                         const int s = it % AB_STAGES;
                         mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
@@ -286,15 +313,24 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             const int q = qt * AB_BM + qtr * 32 + lane;
             const bool row_ok = q < p.Sq;
             float m = -INFINITY, l = 0.f;
+            const int Sk = item_sk(b), nkt = (Sk + AB_BN - 1) / AB_BN;
+            const uint32_t* mrow = p.mbits ? p.mbits + (long long)b * p.mwords : nullptr;
+            uint32_t vw[4] = {0u, 0u, 0u, 0u};  // packed key-padding bits of the NEXT tile (loaded one tile ahead)
+            if (mrow) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) vw[c] = __ldg(mrow + c);
+            }
             for (int j = 0; j < nkt; ++j, ++n) {
                 const int buf = n & 1;
-                const int keys = min(AB_BN, p.Sk - j * AB_BN);
+                const int keys = min(AB_BN, Sk - j * AB_BN);
                 uint32_t vis[4];  // visibility bits of this row for the 128 keys of tile j
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const int kk0 = c * 32;
                     uint32_t v = keys - kk0 >= 32 ? 0xffffffffu : (keys - kk0 <= 0 ? 0u : ((1u << (keys - kk0)) - 1u));
-                    if (p.mask_kind == 1) {
+                    if (mrow) {
+                        v &= vw[c];
+                    } else if (p.mask_kind == 1) {
                         const int kk = j * AB_BN + kk0 + lane;
                         const bool on = kk < p.Sk && p.mask[(long long)b * p.Sk + kk] != 0;
                         v = __ballot_sync(0xffffffffu, on);
@@ -312,6 +348,10 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                         else if (lim < 31) v &= (2u << lim) - 1u;
                     }
                     vis[c] = v;
+                }
+                if (mrow && j + 1 < nkt) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) vw[c] = __ldg(mrow + (j + 1) * 4 + c);
                 }
                 mbar_wait(s_full(buf), ((uint32_t)(n >> 1)) & 1u);
                 tc_fence_after();
@@ -450,10 +490,15 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
 
 }  // namespace bmhrl
 
+extern "C" long long bmhrl_attn_fwd_bf16_ws_bytes(int B, int Sk) {
+    return 4ll * (((B + 3) & ~3) + (long long)B * 4 * ((Sk + 127) / 128));
+}
+
 extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, const void* K, long long ldk,
                                    long long bsk, const void* V, long long ldv, long long bsv,
                                    const unsigned char* mask, int mask_kind, int causal, void* O, long long ldo,
-                                   long long bso, float* lse, int B, int H, int Sq, int Sk, int dk, void* stream) {
+                                   long long bso, float* lse, int B, int H, int Sq, int Sk, int dk, void* ws,
+                                   void* stream) {
     using namespace bmhrl;
     using namespace bmhrl::tc;
     BMHRL_CHECK_ARG(Q && K && V && O, "attn_fwd_bf16: null tensor");
@@ -503,6 +548,15 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
     p.nqt = (Sq + AB_BM - 1) / AB_BM;
     p.n_items = B * H * p.nqt;
     p.scale = 1.0f / sqrtf((float)dk);
+    if (ws && mask_kind == 1 && !causal) {  // key-padding mask: bit-pack it and trim fully masked tail tiles per batch row
+        p.mwords = 4 * ((Sk + AB_BN - 1) / AB_BN);
+        int* sk_eff = (int*)ws;
+        uint32_t* mbits = (uint32_t*)ws + ((B + 3) & ~3);
+        attn_mask_pack_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(mask, Sk, p.mwords, sk_eff, mbits);
+        BMHRL_POST_LAUNCH("attn_mask_pack");
+        p.sk_eff = sk_eff;
+        p.mbits = mbits;
+    }
     const int grid = p.n_items < n_sm ? p.n_items : n_sm;
     attn_fwd_bf16_kernel<<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
     BMHRL_POST_LAUNCH("attn_fwd_bf16");

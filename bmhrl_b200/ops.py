@@ -488,7 +488,7 @@ def mha_core(q, k, v, mask, H, causal=False, drop_p=0.0, salt=0, rng=None):
     return _MhaCore.apply(q, k, v, m, kind, int(bool(causal)), H, float(drop_p), int(salt), rng)
 
 
-def mha_core_bf16(q, k, v, mask, H, causal=False, return_lse=False):
+def mha_core_bf16(q, k, v, mask, H, causal=False, return_lse=False, use_ws=True):
     """bf16 flash-style attention core, forward only (BASELINE.json config 5, the long-clip encoder attention sweep).
     q (B,Sq,D), k/v (B,Sk,D) bf16 projected tensors -> head-merged (B,Sq,D) bf16 (+ fp32 (B,H,Sq) log-sum-exp).
     Same masking semantics as `mha_core` (model/multihead_attention.py:7-31); no dropout, no autograd."""
@@ -509,8 +509,11 @@ def mha_core_bf16(q, k, v, mask, H, causal=False, return_lse=False):
         raise RuntimeError("mha_core_bf16: causal attention needs Sq == Sk")
     o = torch.empty_like(q)
     lse = torch.empty(B, H, Sq, device=q.device, dtype=_F32) if return_lse else None
+    ws = None
+    if kind == 1 and not causal and use_ws:  # bit-packed mask + per-row trimming of fully masked tail tiles
+        ws = torch.empty(LIB.raw("bmhrl_attn_fwd_bf16_ws_bytes")(B, Sk), device=q.device, dtype=torch.uint8)
     LIB.call("bmhrl_attn_fwd_bf16", _p(q), D, Sq * D, _p(k), D, Sk * D, _p(v), D, Sk * D, _p(m), kind,
-             int(bool(causal)), _p(o), D, Sq * D, _p(lse), B, H, Sq, Sk, D // H, _stream())
+             int(bool(causal)), _p(o), D, Sq * D, _p(lse), B, H, Sq, Sk, D // H, _p(ws), _stream())
     return (o, lse) if return_lse else o
 
 

@@ -113,7 +113,11 @@ int bmhrl_mha_core_bwd_f32(const float* dO, long long ldo, long long bso, const 
 int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, const void* K, long long ldk, long long bsk,
                         const void* V, long long ldv, long long bsv, const unsigned char* mask, int mask_kind,
                         int causal, void* O, long long ldo, long long bso, float* lse, int B, int H, int Sq, int Sk,
-                        int dk, void* stream);
+                        int dk, void* ws, void* stream);
+/* ws (may be NULL): bmhrl_attn_fwd_bf16_ws_bytes() bytes.  With a key-padding mask the kernel then reads the mask
+ * bit-packed and skips, per batch row, the key tiles behind the last visible key (their probabilities are exactly 0
+ * unless the whole row is masked, which keeps all Sk keys like the reference). */
+long long bmhrl_attn_fwd_bf16_ws_bytes(int B, int Sk);
 
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
 int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */

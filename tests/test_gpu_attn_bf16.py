@@ -37,11 +37,11 @@ def _oracle(q, k, v, mask4, H, causal=False):
     return o.transpose(1, 2).reshape(B, Sq, D), torch.logsumexp(s, -1)
 
 
-def _run(gpu_lib, q, k, v, mask, H, causal=False):
+def _run(gpu_lib, q, k, v, mask, H, causal=False, use_ws=True):
     from bmhrl_b200 import ops
     with torch.no_grad():
         o, lse = ops.mha_core_bf16(q.cuda(), k.cuda(), v.cuda(), None if mask is None else mask.cuda(), H, causal,
-                                   return_lse=True)
+                                   return_lse=True, use_ws=use_ws)
     torch.cuda.synchronize()
     return o.float().cpu(), lse.cpu()
 
@@ -71,6 +71,23 @@ def test_key_padding_mask(gpu_lib, Sq, Sk):
     ro, rl = _oracle(q, k, v, mask[:, None], H)
     assert rel(o, ro) < BF16_TOL, rel(o, ro)
     assert rel(o[2], ro[2]) < BF16_TOL  # the fully masked row: mean of V over ALL keys, like the reference
+    assert torch.allclose(lse.double(), rl, rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("use_ws", [True, False])
+def test_trimmed_tail_tiles(gpu_lib, use_ws):
+    """Per batch row the kernel skips the key tiles behind the last visible key (workspace given); rows with NO visible
+    key keep all Sk keys (uniform attention like the reference); ragged lengths across the batch; ws = NULL path."""
+    B, H, Sq, Sk, dk = 6, 2, 200, 700, 256
+    q, k, v = _inputs(B, H, Sq, Sk, dk, seed=41)
+    mask = torch.zeros(B, 1, Sk, dtype=torch.bool)
+    for b, n in enumerate([700, 1, 128, 129, 0, 385]):
+        mask[b, :, :n] = True
+    mask[3, :, 5:100] = False  # holes before the last visible key
+    o, lse = _run(gpu_lib, q, k, v, mask, H, use_ws=use_ws)
+    ro, rl = _oracle(q, k, v, mask[:, None], H)
+    for b in range(B):
+        assert rel(o[b], ro[b]) < BF16_TOL, (b, rel(o[b], ro[b]))
     assert torch.allclose(lse.double(), rl, rtol=1e-3, atol=1e-3)
 
 

@@ -70,7 +70,9 @@ def main():
             fl = 4.0 * B * H * Sq * Sk * dk
             line = {"kernel": "attn_fwd_bf16_kernel", "B": B, "H": H, "Sq": Sq, "Sk": Sk, "dk": dk, "mask": mname,
                     "us": t * 1e6, "tflops": fl / t / 1e12, "peak_tflops": pk, "frac": fl / t / 1e12 / pk,
-                    "peak_source": src, "dtype": "bf16", "pass": "fwd"}
+                    "peak_source": src, "dtype": "bf16", "pass": "fwd",
+                    "flops": "nominal 4*B*H*Sq*Sk*dk" + (" (key tiles behind the last visible key are skipped: their "
+                                                          "probabilities are exactly 0)" if mname == "pad50" else "")}
             print(json.dumps(line), flush=True)
         if not quick:
             ops.set_math_mode("tf32")
