@@ -232,6 +232,34 @@ def gemm_roofline(recorded, iters=20):
     return flops / n, sec / n, n
 
 
+def attention_roofline(pk):
+    """BASELINE.json config 5 (bf16 long-clip encoder attention, B=64, H=4, d_k=256) timed live: the fused tcgen05
+    forward kernel attn_fwd_bf16_kernel, CUDA events around 10 back-to-back launches (68-105 MB of Q/K/V/O per call)."""
+    from bmhrl_b200 import ops
+    dev = torch.device("cuda")
+    out = []
+    for S in (800, 300):
+        B, H, dk = 64, 4, 256
+        q, k, v = (torch.randn(B, S, H * dk, device=dev).bfloat16() for _ in range(3))
+        with torch.no_grad():
+            for _ in range(3):
+                ops.mha_core_bf16(q, k, v, None, H)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(10):
+                ops.mha_core_bf16(q, k, v, None, H)
+            e1.record()
+            torch.cuda.synchronize()
+        sec = e0.elapsed_time(e1) / 1e3 / 10
+        fl = 4.0 * B * H * S * S * dk
+        out.append({"kernel": "attn_fwd_bf16_kernel", "shape": f"B=64 H=4 Sq=Sk={S} d_k=256 bf16 fwd", "bound": "tensor",
+                    "achieved": fl / sec / 1e12, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                    "frac": fl / sec / 1e12 / pk["bf16_tflops"], "us": sec * 1e6})
+        del q, k, v
+    return out
+
+
 def run_gpu(args):
     import torch.distributed as dist
     from bmhrl_b200 import ops, synth, _lib
@@ -359,6 +387,7 @@ def run_gpu(args):
                          "launches_per_step": ng, "avg_launch_us": sl * 1e6, "flops_per_launch": fl},
             "step_hbm_roofline": {"algorithmic_bytes": step_bytes(args.workload), "peak_gbs": pk["hbm_gbs"],
                                   "frac": step_bytes(args.workload) / (sec / args.steps) / 1e9 / pk["hbm_gbs"]},
+            "attention_roofline": attention_roofline(pk),
             "loss": last,
         }
         if cpu_med is not None:
