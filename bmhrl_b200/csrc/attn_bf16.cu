@@ -29,10 +29,11 @@ using namespace tc;
 
 constexpr int AB_BM = 128;   // queries per item
 constexpr int AB_BN = 128;   // keys per S tile
-constexpr int AB_STAGES = 5;
+constexpr int AB_STAGES = 4;
 constexpr int AB_STAGE_BYTES = 32 * 1024;
 constexpr int AB_Q_BYTES = 64 * 1024;  // 128 x 256 bf16
-constexpr int AB_SMEM = AB_Q_BYTES + AB_STAGES * AB_STAGE_BYTES + 1024 + 256;
+constexpr int AB_OST_BYTES = 4 * 4096;  // per softmax warp: 32 rows x 128 B of output, transposed for full-line global stores
+constexpr int AB_SMEM = AB_Q_BYTES + AB_STAGES * AB_STAGE_BYTES + 1024 + 256 + AB_OST_BYTES;
 constexpr float AB_LAZY = 8.f;  // log2 of the growth the running maximum may lag behind by
 
 struct AttnBf16Params {
@@ -457,23 +458,36 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
             tc_fence_after();
             const float inv_l = 1.f / l;
-            __nv_bfloat16* orow = p.O + (long long)b * p.bso + (long long)q * p.ldo + h * p.dk;
+            // thread = row out of TMEM, but a row-per-thread 16-byte store touches 32 different lines per instruction
+            // (the LSU then costs more than the MMAs of a short item): transpose 64-column chunks through shared
+            // memory (16-byte units XOR-swizzled by row) and store 4 rows x 128 B = 4 full lines per instruction.
+            uint8_t* ost = smem_raw + (bars - smem_u32(smem_raw)) + 256 + qtr * 4096;
+            const int q_w0 = qt * AB_BM + qtr * 32;  // first query row of this warp
+            __nv_bfloat16* obase = p.O + (long long)b * p.bso + h * p.dk;
 #pragma unroll 1
             for (int c = 0; c < (p.dk >> 5); c += 2) {
                 uint32_t o[64];
                 tmem_ld_32x32_b(lane_base + 256 + c * 32, o);
                 tmem_ld_32x32_b(lane_base + 256 + c * 32 + 32, o + 32);
                 tmem_ld_wait();
-                if (row_ok) {
+                __syncwarp();  // the previous chunk has been read out of the staging tile
 #pragma unroll
-                    for (int t = 0; t < 64; t += 8) {
-                        uint4 u;
-                        u.x = pack_bf16x2(__uint_as_float(o[t]) * inv_l, __uint_as_float(o[t + 1]) * inv_l);
-                        u.y = pack_bf16x2(__uint_as_float(o[t + 2]) * inv_l, __uint_as_float(o[t + 3]) * inv_l);
-                        u.z = pack_bf16x2(__uint_as_float(o[t + 4]) * inv_l, __uint_as_float(o[t + 5]) * inv_l);
-                        u.w = pack_bf16x2(__uint_as_float(o[t + 6]) * inv_l, __uint_as_float(o[t + 7]) * inv_l);
-                        *reinterpret_cast<uint4*>(orow + c * 32 + t) = u;
-                    }
+                for (int u8 = 0; u8 < 8; ++u8) {
+                    const int t = u8 * 8;
+                    uint4 u;
+                    u.x = pack_bf16x2(__uint_as_float(o[t]) * inv_l, __uint_as_float(o[t + 1]) * inv_l);
+                    u.y = pack_bf16x2(__uint_as_float(o[t + 2]) * inv_l, __uint_as_float(o[t + 3]) * inv_l);
+                    u.z = pack_bf16x2(__uint_as_float(o[t + 4]) * inv_l, __uint_as_float(o[t + 5]) * inv_l);
+                    u.w = pack_bf16x2(__uint_as_float(o[t + 6]) * inv_l, __uint_as_float(o[t + 7]) * inv_l);
+                    *reinterpret_cast<uint4*>(ost + lane * 128 + ((u8 ^ (lane & 7)) << 4)) = u;
+                }
+                __syncwarp();
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int r = it * 4 + (lane >> 3), u8 = lane & 7;
+                    const uint4 u = *reinterpret_cast<const uint4*>(ost + r * 128 + ((u8 ^ (r & 7)) << 4));
+                    if (q_w0 + r < p.Sq)
+                        *reinterpret_cast<uint4*>(obase + (long long)(q_w0 + r) * p.ldo + c * 32 + u8 * 8) = u;
                 }
             }
             if (row_ok && p.lse) p.lse[(long long)bh * p.Sq + q] = (m + log2f(l)) * 0.6931471805599453f;
