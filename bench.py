@@ -232,6 +232,15 @@ def gemm_roofline(recorded, iters=20):
     return flops / n, sec / n, n
 
 
+def gemm_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch (average over the GEMM launches of one training step),
+    from the committed ncu capture profiles/r01_gemm_traffic.json (see its `command`); None when absent."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")))["avg_dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def attention_roofline(pk):
     """BASELINE.json config 5 (bf16 long-clip encoder attention, B=64, H=4, d_k=256) timed live: the fused tcgen05
     forward kernel attn_fwd_bf16_kernel, CUDA events around 10 back-to-back launches (68-105 MB of Q/K/V/O per call)."""
@@ -383,7 +392,7 @@ def run_gpu(args):
                                     "kind::tf32, TMEM accumulators)") if args.math == "tf32" else
                                    "projection/FFN/vocab/gradient GEMMs (gemm_simt_kernel, fp32 SIMT)",
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
-                         "traffic": None, "peak_source": f"{pk_src} bf16_tflops_sustained",
+                         "traffic": gemm_traffic(), "peak_source": f"{pk_src} bf16_tflops_sustained",
                          "launches_per_step": ng, "avg_launch_us": sl * 1e6, "flops_per_launch": fl},
             "step_hbm_roofline": {"algorithmic_bytes": step_bytes(args.workload), "peak_gbs": pk["hbm_gbs"],
                                   "frac": step_bytes(args.workload) / (sec / args.steps) / 1e9 / pk["hbm_gbs"]},
