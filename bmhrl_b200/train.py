@@ -136,14 +136,39 @@ class BMHRLTrainer:
             return self.grad_sync.all_reduce_scalar(n_tokens)
         return n_tokens
 
+    def _global_tokens_early(self, y):
+        """The token count depends on the captions only: with more than one rank its all-reduce is issued on the
+        communication stream BEFORE the forward pass (the ranks have just left the previous step's gradient
+        all-reduce together), instead of as a rendezvous in the middle of the step.  Returns a thunk that makes the
+        current stream wait for it and yields the global count."""
+        local = (y != self.pad_idx).sum()
+        world = getattr(self.grad_sync, "world", 1) if self.grad_sync is not None else 1
+        if world <= 1 or not self.overlap_grad_sync or not local.is_cuda:
+            return lambda: self._global_tokens(local)
+        dev = local.device
+        if self._comm_stream is None:
+            self._comm_stream = torch.cuda.Stream(device=dev)
+        comm = self._comm_stream
+        comm.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(comm):
+            total = self.grad_sync.all_reduce_scalar(local)
+        done = torch.cuda.Event()
+        done.record(comm)
+
+        def get():
+            torch.cuda.current_stream(dev).wait_event(done)
+            return total
+        return get
+
     # ---- warm-start step -------------------------------------------------------------------------------------------
     def warmstart_step(self, batch):
         """captioning_bmrl_loops.py:1148-1160.  Returns the scalar loss tensor (device)."""
         ops.new_rng_epoch(batch["rgb"].device)
         self.cap_opt.zero_grad()
         x, cap_in, y, masks = self._inputs(batch)
+        n_tokens = self._global_tokens_early(y)
         pred = self.cap_model(x, cap_in, masks)[0]
-        n_tokens = self._global_tokens((y != self.pad_idx).sum())
+        n_tokens = n_tokens()
         loss = self.ls.row_sums(pred, y).sum() / n_tokens
         loss.backward()
         ops.join_side_streams(loss.device)
@@ -154,9 +179,10 @@ class BMHRLTrainer:
     def rl_losses(self, batch, train_worker, stabilize=False, exp_noise=None):
         """Forward part of train_bimodal_bl (:843-862, :873-875): returns (cap_loss, value_loss, tokens, score)."""
         x, cap_in, y, masks = self._inputs(batch)
+        n_tokens = self._global_tokens_early(y)
         pred, worker_feat, manager_feat, goal_feat, seg = self.cap_model(x, cap_in, masks)
         loss_mask = y != self.pad_idx
-        n_tokens = self._global_tokens(loss_mask.sum())
+        n_tokens = n_tokens()
         if train_worker:
             ev = self.wv_model((worker_feat.detach(), goal_feat.detach())).squeeze(-1)
         else:
