@@ -152,3 +152,38 @@ def test_rejects_bad_inputs(gpu_lib):
     q, k, v = _inputs(1, 2, 8, 8, 96, seed=0)
     with pytest.raises(RuntimeError):
         ops.mha_core_bf16(q.cuda(), k.cuda(), v.cuda(), None, 2)  # d_k = 96 unsupported
+
+
+def test_full_size_properties(gpu_lib):
+    """BASELINE config 5 sizes (B=64, H=4, S=300, d_k=256), size-independent properties instead of the oracle:
+    (1) V = 1 -> every output is exactly 1 (the probabilities of a row sum to 1 against the same normaliser);
+    (2) masked key padding does not change the un-padded result, and neither does the workspace (tile trimming);
+    (3) permuting the keys (and values) leaves the output unchanged up to bf16 summation order;
+    (4) log-sum-exp of a row with identical scores = score + log(Sk)."""
+    from bmhrl_b200 import ops
+    B, H, S, dk = 64, 4, 300, 256
+    D = H * dk
+    g = torch.Generator(device="cuda").manual_seed(5)
+    q = torch.randn(B, S, D, device="cuda", generator=g).bfloat16()
+    k = torch.randn(B, S, D, device="cuda", generator=g).bfloat16()
+    v = torch.randn(B, S, D, device="cuda", generator=g).bfloat16()
+    with torch.no_grad():
+        o1 = ops.mha_core_bf16(q, k, torch.ones_like(v), None, H)
+        assert float((o1.float() - 1).abs().max()) <= 2 ** -7  # bf16 rounding of P and of the output only
+        o = ops.mha_core_bf16(q, k, v, None, H)
+        # (2) 300 -> 500 keys, the tail masked
+        kp = torch.cat([k, torch.randn(B, 200, D, device="cuda", generator=g).bfloat16()], 1)
+        vp = torch.cat([v, torch.randn(B, 200, D, device="cuda", generator=g).bfloat16()], 1)
+        mask = torch.zeros(B, 1, 500, dtype=torch.bool, device="cuda")
+        mask[:, :, :S] = True
+        for use_ws in (True, False):
+            op = ops.mha_core_bf16(q, kp, vp, mask, H, use_ws=use_ws)
+            assert rel(op, o) < 2e-3, (use_ws, rel(op, o))
+        # (3) key permutation
+        perm = torch.randperm(S, device="cuda", generator=g)
+        opm = ops.mha_core_bf16(q, k[:, perm].contiguous(), v[:, perm].contiguous(), None, H)
+        assert rel(opm, o) < 5e-3, rel(opm, o)
+        # (4) constant scores
+        _, lse = ops.mha_core_bf16(torch.zeros_like(q), k, v, None, H, return_lse=True)
+        assert torch.allclose(lse, torch.full_like(lse, math.log(S)), atol=1e-4)
+    torch.cuda.synchronize()
