@@ -34,6 +34,9 @@ constexpr int AB_STAGE_BYTES = 32 * 1024;
 constexpr int AB_Q_BYTES = 64 * 1024;  // 128 x 256 bf16
 constexpr int AB_OST_BYTES = 4 * 4096;  // per softmax warp: 32 rows x 128 B of output, transposed for full-line global stores
 constexpr int AB_SMEM = AB_Q_BYTES + AB_STAGES * AB_STAGE_BYTES + 1024 + 256 + AB_OST_BYTES;
+// automatic choice: never the CTA-pair form yet -- measured 270 us vs 183 us at B=64, S=800 (the softmax warps, not the
+// K / V delivery, bound the kernel, and the pair adds cross-CTA hand-offs to that chain); bmhrl_attn_bf16_tuning(2) selects it
+constexpr int AB_PAIR_MIN_QTILES = 1 << 30;
 constexpr float AB_LAZY = 8.f;  // log2 of the growth the running maximum may lag behind by
 
 struct AttnBf16Params {
@@ -138,6 +141,69 @@ __device__ __forceinline__ void mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
         : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// ---- CTA pair (cta_group::2): one MMA spans the two SMs of a cluster; only the leader CTA (cluster rank 0) issues
+__device__ __forceinline__ void mma2_bf16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :
+        : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mma2_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        :
+        : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrives once on the barrier at the same shared-memory offset in BOTH CTAs when the MMAs issued so far have completed
+__device__ __forceinline__ void tc_commit2(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((unsigned short)3) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem, uint32_t cols) {  // one warp in EACH CTA of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// TMA load into MY shared memory whose completion bytes are counted on a barrier of the LEADER CTA (cluster address)
+__device__ __forceinline__ void tma2_load_4d(uint32_t dst, const CUtensorMap* m, uint32_t cluster_bar, int c0, int c1,
+                                             int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5, %6}], [%2];"
+        :
+        : "r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(cluster_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {  // barrier possibly in the peer CTA
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+// wait on a LOCAL barrier whose arrivals may come from the peer CTA (acquire at cluster scope); bounded like mbar_wait
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+#pragma unroll 1
+    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -149,6 +215,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     return r;
 }
 
+// PAIR: two CTAs of a cluster (one SM pair) work on two neighbouring query tiles of the same (batch, head) with
+// cta_group::2 MMAs (M = 256): every K tile is split by keys and every V tile by value columns between the two shared
+// memories, so each SM takes in HALF of the K / V bytes -- the delivery of K / V from L2 is what bounds the one-CTA form
+// at long sequences.  Only the leader (cluster rank 0) issues MMAs; completion is multicast to the barriers of both
+// CTAs; TMA loads of both CTAs are counted on the leader's barriers; softmax threads of the peer arrive remotely.
+template <bool PAIR>
 __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_constant__ CUtensorMap tmQ,
                                                                const __grid_constant__ CUtensorMap tmK,
                                                                const __grid_constant__ CUtensorMap tmV,
@@ -170,6 +242,18 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     auto item_sk = [&](int b) { return p.sk_eff ? __ldg(p.sk_eff + b) : p.Sk; };  // keys that can get weight
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;            // 0 = leader of the pair
+    const int w_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;   // first item / item stride of this CTA (pair)
+    const int w_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int tiles_bh = PAIR ? (p.nqt + 1) >> 1 : p.nqt;           // items per (batch, head)
+    auto item_qt = [&](int tq) { return PAIR ? 2 * tq + (int)rank : tq; };  // query tile of THIS CTA inside the item
+    // the leader's copy of a barrier of mine (same offset), as a shared::cluster address
+    const uint32_t lead_bars = PAIR ? mapa_shared(bars, 0) : bars;
+    auto lead = [&](uint32_t bar) { return lead_bars + (bar - bars); };
+    auto wait_x = [&](uint32_t bar, uint32_t parity) {  // barriers that the leader's multicast commits arrive on
+        if (PAIR) mbar_wait_cluster(bar, parity);
+        else mbar_wait(bar, parity);
+    };
     const int kcols = p.dk < 128 ? p.dk : 128;   // d_k columns of one K stage
     const int nkh = p.dk / kcols;                // K stages per key tile
     const int ncs = kcols >> 6;                  // 64-column (128-byte) chunks per K stage
@@ -185,17 +269,21 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
         }
         mbar_init(s_full(0), 1);
         mbar_init(s_full(1), 1);
-        mbar_init(s_rel(0), 128);
-        mbar_init(s_rel(1), 128);
+        mbar_init(s_rel(0), PAIR ? 256 : 128);   // softmax threads of both CTAs arrive on the leader's copy
+        mbar_init(s_rel(1), PAIR ? 256 : 128);
         mbar_init(q_full, 1);
         mbar_init(q_empty, 1);
         mbar_init(pv_bar, 1);
-        mbar_init(o_free, 128);
+        mbar_init(o_free, PAIR ? 256 : 128);
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    if (warp == 1) {
+        if (PAIR) tmem_alloc2(tmem_slot, 512);
+        else tmem_alloc(tmem_slot, 512);
+    }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled on them
+    else __syncthreads();
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
@@ -204,12 +292,41 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
     if (warp == 0) {
         if (elect_one()) {  // ===== TMA producer (same op order as the MMA issuer)
             int it = 0;
-            for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
-                const int bh = w / p.nqt, qt = w - bh * p.nqt;
+            for (int i = 0, w = w_first; w < p.n_items; ++i, w += w_step) {
+                const int bh = w / tiles_bh, qt = item_qt(w - bh * tiles_bh);
                 const int b = bh / p.H, h = bh - b * p.H;
                 const int q0 = qt * AB_BM, col_q = h * p.dk;
                 const int Sk = item_sk(b), nkt = (Sk + AB_BN - 1) / AB_BN;
-                mbar_wait(q_empty, ((uint32_t)i & 1u) ^ 1u);
+                wait_x(q_empty, ((uint32_t)i & 1u) ^ 1u);
+                if (PAIR) {
+                    // K stage: MY 64 keys of the tile x d_k; V stage: the 128 keys of the tile x MY half of the columns
+                    if (rank == 0) mbar_arrive_expect_tx(q_full, (uint32_t)(2 * AB_BM * p.dk * 2));
+                    for (int c = 0; c < nvc; ++c)
+                        tma2_load_4d(sQ + c * 16384, &tmQ, lead(q_full), col_q + c * 64, q0, 0, b);
+                    auto load2 = [&](bool is_k, int j) {
+                        const int s = it % AB_STAGES;
+                        mbar_wait_cluster(empty_bar(s), (((uint32_t)(it / AB_STAGES)) & 1u) ^ 1u);
+                        if (rank == 0) mbar_arrive_expect_tx(full_bar(s), (uint32_t)(2 * 64 * p.dk * 2));
+                        const uint32_t st = ring + s * AB_STAGE_BYTES;
+                        if (is_k) {
+                            for (int c = 0; c < nvc; ++c)
+                                tma2_load_4d(st + c * 8192, &tmK, lead(full_bar(s)), col_q + c * 64,
+                                             j * AB_BN + (int)rank * 64, 0, b);
+                        } else {
+                            for (int c = 0; c < (nvc >> 1); ++c)
+                                tma2_load_4d(st + c * 16384, &tmV, lead(full_bar(s)),
+                                             col_q + (int)rank * (p.dk >> 1) + c * 64, j * AB_BN, 0, b);
+                        }
+                        ++it;
+                    };
+                    load2(true, 0);
+                    if (nkt > 1) load2(true, 1);
+                    for (int j = 0; j < nkt; ++j) {
+                        load2(false, j);
+                        if (j + 2 < nkt) load2(true, j + 2);
+                    }
+                    continue;
+                }
                 mbar_arrive_expect_tx(q_full, (uint32_t)(AB_BM * p.dk * 2));
                 for (int c = 0; c < nvc; ++c) tma_load_4d(sQ + c * 16384, &tmQ, q_full, col_q + c * 64, q0, 0, b);
                 auto load_k = [&](int j) {
@@ -242,15 +359,70 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             }
         }
     } else if (warp == 1) {
-        if (elect_one()) {  // ===== MMA issuer
+        if (PAIR && rank == 0 && elect_one()) {  // ===== MMA issuer of the pair (leader only): M = 256 over both CTAs
+            const uint32_t idesc_s = make_idesc(1, 2 * AB_BM, AB_BN, 0, 0);
+            const uint32_t idesc_o = make_idesc(1, 2 * AB_BM, p.dk, 0, 1);
+            const uint64_t q_desc = make_smem_desc(sQ, 16, 1024);         // per CTA: its 128 query rows, K-major
+            const uint64_t k_desc = make_smem_desc(ring, 16, 1024);       // per CTA: its 64 keys, K-major, 8 KB per 64 columns
+            const uint64_t v_desc = make_smem_desc(ring, 16384, 1024);    // per CTA: its d_k/2 columns, MN-major, 16 KB chunks
+            int it = 0, ns = 0, np = 0;
+            for (int i = 0, w = w_first; w < p.n_items; ++i, w += w_step) {
+                const int Sk = item_sk((w / tiles_bh) / p.H), nkt = (Sk + AB_BN - 1) / AB_BN;
+                mbar_wait_cluster(q_full, (uint32_t)i & 1u);
+                tc_fence_after();
+                auto s_op = [&](bool last) {
+                    const int buf = ns & 1;
+                    const int s = it % AB_STAGES;
+                    mbar_wait_cluster(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
+                    tc_fence_after();
+                    for (int c = 0; c < nvc; ++c) {
+                        const uint64_t a0 = desc_advance(q_desc, c * 16384);
+                        const uint64_t b0 = desc_advance(k_desc, s * AB_STAGE_BYTES + c * 8192);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            mma2_bf16_ss(tmem_base + buf * AB_BN, desc_advance(a0, k * 32), desc_advance(b0, k * 32),
+                                         idesc_s, (c > 0 || k > 0) ? 1u : 0u);
+                    }
+                    tc_commit2(empty_bar(s));
+                    ++it;
+                    tc_commit2(s_full(buf));
+                    if (last) tc_commit2(q_empty);
+                    ++ns;
+                };
+                auto pv_op = [&](int j) {
+                    const int buf = np & 1;
+                    mbar_wait_cluster(s_rel(buf), ((uint32_t)(np >> 1)) & 1u);
+                    if (j == 0 && i > 0) mbar_wait_cluster(o_free, ((uint32_t)(i - 1)) & 1u);
+                    tc_fence_after();
+                    const int nk16 = (min(AB_BN, Sk - j * AB_BN) + 15) >> 4;  // 16-key MMA steps
+                    const int s = it % AB_STAGES;
+                    mbar_wait_cluster(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
+                    tc_fence_after();
+                    const uint64_t v0 = desc_advance(v_desc, s * AB_STAGE_BYTES);
+                    for (int kk = 0; kk < nk16; ++kk)
+                        mma2_bf16_ts(tmem_o, tmem_base + buf * AB_BN + kk * 8, desc_advance(v0, kk * 2048), idesc_o,
+                                     (j > 0 || kk > 0) ? 1u : 0u);
+                    tc_commit2(empty_bar(s));
+                    ++it;
+                    tc_commit2(pv_bar);
+                    ++np;
+                };
+                s_op(nkt == 1);
+                if (nkt > 1) s_op(nkt == 2);
+                for (int j = 0; j < nkt; ++j) {
+                    pv_op(j);
+                    if (j + 2 < nkt) s_op(j + 3 == nkt);
+                }
+            }
+        } else if (!PAIR && elect_one()) {  // ===== MMA issuer
             const uint32_t idesc_s = make_idesc(1, AB_BM, AB_BN, 0, 0);
             const uint32_t idesc_o = make_idesc(1, AB_BM, p.dk, 0, 1);
             const uint64_t q_desc = make_smem_desc(sQ, 16, 1024);        // K-major, 128-byte rows, 8-row groups
             const uint64_t ring_desc = make_smem_desc(ring, 16, 1024);   // K tiles, same layout
             const uint64_t v_desc = make_smem_desc(ring, 8192, 1024);    // V tiles: MN-major, 64-column chunks 8 KB apart
             int it = 0, ns = 0, np = 0;  // ring position, S tiles issued, P V tiles issued (all items)
-            for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
-                const int Sk = item_sk((w / p.nqt) / p.H), nkt = (Sk + AB_BN - 1) / AB_BN;
+            for (int i = 0, w = w_first; w < p.n_items; ++i, w += w_step) {
+                const int Sk = item_sk((w / tiles_bh) / p.H), nkt = (Sk + AB_BN - 1) / AB_BN;
                 mbar_wait(q_full, (uint32_t)i & 1u);
                 tc_fence_after();
                 auto s_op = [&](bool last) {  // S[ns & 1] = Q K_j^T; in-order execution behind the P V that read this buffer
@@ -308,8 +480,8 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
         const float sl2 = p.scale * LOG2E;
         const float neg2 = kNegFill * LOG2E;  // the replaced score, in the log2 domain
         int n = 0;                            // tiles consumed (all items) == index of the next P V
-        for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
-            const int bh = w / p.nqt, qt = w - bh * p.nqt;
+        for (int i = 0, w = w_first; w < p.n_items; ++i, w += w_step) {
+            const int bh = w / tiles_bh, qt = item_qt(w - bh * tiles_bh);
             const int b = bh / p.H, h = bh - b * p.H;
             const int q = qt * AB_BM + qtr * 32 + lane;
             const bool row_ok = q < p.Sq;
@@ -354,7 +526,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
 #pragma unroll
                     for (int c = 0; c < 4; ++c) vw[c] = __ldg(mrow + (j + 1) * 4 + c);
                 }
-                mbar_wait(s_full(buf), ((uint32_t)(n >> 1)) & 1u);
+                wait_x(s_full(buf), ((uint32_t)(n >> 1)) & 1u);
                 tc_fence_after();
                 const uint32_t taddr = lane_base + buf * AB_BN;
                 // Scores stay in the raw domain: max over raw scores, one FFMA (score * scale*log2e - m) feeds ex2.
@@ -389,7 +561,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                     }
                     l += acc0 + acc1;
                     if (j > 0) {  // P V of the previous tile: every phase of pv_bar is waited for, in order
-                        mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+                        wait_x(pv_bar, ((uint32_t)(n - 1)) & 1u);
                         tc_fence_after();
                     }
                     if (j > 0 && __any_sync(0xffffffffu, raise)) rescale_o(lane_base + 256, p.dk >> 5, alpha);
@@ -422,7 +594,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                     }
                     const float nm = -m;
                     if (j > 0) {
-                        mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+                        wait_x(pv_bar, ((uint32_t)(n - 1)) & 1u);
                         tc_fence_after();
                     }
                     if (j > 0 && __any_sync(0xffffffffu, raise)) rescale_o(lane_base + 256, p.dk >> 5, alpha);
@@ -452,10 +624,11 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 }
                 tmem_st_wait_b();
                 tc_fence_before();
-                mbar_arrive(s_rel(buf));
+                if (PAIR) mbar_arrive_cluster(lead(s_rel(buf)));
+                else mbar_arrive(s_rel(buf));
             }
             // ---- epilogue: O tile (TMEM) / l -> bf16 -> global, head-merged layout; log-sum-exp
-            mbar_wait(pv_bar, ((uint32_t)(n - 1)) & 1u);
+            wait_x(pv_bar, ((uint32_t)(n - 1)) & 1u);
             tc_fence_after();
             const float inv_l = 1.f / l;
             // thread = row out of TMEM, but a row-per-thread 16-byte store touches 32 different lines per instruction
@@ -492,17 +665,29 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             }
             if (row_ok && p.lse) p.lse[(long long)bh * p.Sq + q] = (m + log2f(l)) * 0.6931471805599453f;
             tc_fence_before();
-            mbar_arrive(o_free);
+            if (PAIR) mbar_arrive_cluster(lead(o_free));
+            else mbar_arrive(o_free);
         }
     }
-    __syncthreads();
+    tc_fence_before();
+    if (PAIR) cluster_sync_all();  // the leader's MMAs read the peer's shared / tensor memory: leave together
+    else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        if (PAIR) tmem_dealloc2(tmem_base, 512);
+        else tmem_dealloc(tmem_base, 512);
     }
 }
 
 }  // namespace bmhrl
+
+static int g_attn_bf16_pair = 0;
+/* test / tuning hook: 0 = automatic, 1 = always the one-CTA kernel, 2 = the CTA-pair kernel whenever d_k allows */
+extern "C" int bmhrl_attn_bf16_tuning(int pair_mode) {
+    BMHRL_CHECK_ARG(pair_mode >= 0 && pair_mode <= 2, "bmhrl_attn_bf16_tuning: mode 0..2");
+    g_attn_bf16_pair = pair_mode;
+    return BMHRL_OK;
+}
 
 extern "C" long long bmhrl_attn_fwd_bf16_ws_bytes(int B, int Sk) {
     return 4ll * (((B + 3) & ~3) + (long long)B * 4 * ((Sk + 127) / 128));
@@ -545,8 +730,10 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
     static bool attr = false;
     static int n_sm = 0;
     if (!attr) {
-        if (cudaFuncSetAttribute(attn_fwd_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM) !=
-            cudaSuccess) {
+        if (cudaFuncSetAttribute(attn_fwd_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM) !=
+                cudaSuccess ||
+            cudaFuncSetAttribute(attn_fwd_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM) !=
+                cudaSuccess) {
             bmhrl_set_error("attn_fwd_bf16: cannot raise the shared-memory limit");
             return BMHRL_ERR_CUDA;
         }
@@ -571,8 +758,38 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
         p.sk_eff = sk_eff;
         p.mbits = mbits;
     }
+    const bool use_pair = (dk == 128 || dk == 256) && n_sm >= 2 &&
+                          (g_attn_bf16_pair == 2 || (g_attn_bf16_pair == 0 && p.nqt >= AB_PAIR_MIN_QTILES));
+    if (use_pair) {  // CTA pairs: K split by keys (box 64 x 64), V by columns (box 64 x 128), two query tiles per item
+        ok = encode_4d(&tmK, BF, 2, K, D, Sk, ldk, 1, 0, B, bsk, 64, 64) &&
+             encode_4d(&tmV, BF, 2, V, D, Sk, ldv, 1, 0, B, bsv, 64, AB_BN);
+        if (!ok) {
+            bmhrl_set_error("attn_fwd_bf16: cuTensorMapEncodeTiled failed (pair)");
+            return BMHRL_ERR_CUDA;
+        }
+        p.n_items = B * H * ((p.nqt + 1) >> 1);
+        const int pairs = p.n_items < (n_sm >> 1) ? p.n_items : (n_sm >> 1);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * pairs);
+        cfg.blockDim = dim3(192);
+        cfg.dynamicSmemBytes = AB_SMEM;
+        cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        if (cudaLaunchKernelEx(&cfg, attn_fwd_bf16_kernel<true>, tmQ, tmK, tmV, p) != cudaSuccess) {
+            bmhrl_set_error(cudaGetErrorString(cudaGetLastError()));
+            return BMHRL_ERR_CUDA;
+        }
+        bmhrl_count_launch(1);
+        return BMHRL_OK;
+    }
     const int grid = p.n_items < n_sm ? p.n_items : n_sm;
-    attn_fwd_bf16_kernel<<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
+    attn_fwd_bf16_kernel<false><<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
     BMHRL_POST_LAUNCH("attn_fwd_bf16");
     return BMHRL_OK;
 }

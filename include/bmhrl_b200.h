@@ -118,6 +118,10 @@ int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, const void*
  * bit-packed and skips, per batch row, the key tiles behind the last visible key (their probabilities are exactly 0
  * unless the whole row is masked, which keeps all Sk keys like the reference). */
 long long bmhrl_attn_fwd_bf16_ws_bytes(int B, int Sk);
+/* test / tuning hook: 0 = automatic (currently always one CTA per query tile: it is the faster form), 1 = one CTA per
+ * query tile, 2 = CTA pairs (cta_group::2 MMAs over two SMs, K / V tiles split between their shared memories) whenever
+ * d_k is 128 or 256. */
+int bmhrl_attn_bf16_tuning(int pair_mode);
 
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
 int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */

@@ -13,6 +13,15 @@ pytestmark = pytest.mark.gpu
 BF16_TOL = 1e-2
 
 
+@pytest.fixture(autouse=True, params=["one_cta", "cta_pair"])
+def kernel_variant(request, gpu_lib):
+    """Every test runs on both forms of the kernel: one CTA per query tile, and CTA pairs (cta_group::2 MMAs with the
+    K / V tiles split between the two shared memories); d_k = 64 always takes the one-CTA form."""
+    gpu_lib.call("bmhrl_attn_bf16_tuning", 1 if request.param == "one_cta" else 2)
+    yield request.param
+    gpu_lib.call("bmhrl_attn_bf16_tuning", 0)
+
+
 def _inputs(B, H, Sq, Sk, dk, seed, scale=1.0):
     g = torch.Generator().manual_seed(seed)
     D = H * dk
