@@ -185,7 +185,9 @@ __device__ __forceinline__ void tma2_load_4d(uint32_t dst, const CUtensorMap* m,
         : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {  // barrier possibly in the peer CTA
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+    // default semantics (as CUTLASS' ClusterBarrier::arrive): what crosses the CTAs is tensor memory, ordered by the
+    // tcgen05 fences around the barrier; an explicit .release.cluster costs a MEMBAR / ERRBAR per arrival
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 // wait on a LOCAL barrier whose arrivals may come from the peer CTA (acquire at cluster scope); bounded like mbar_wait
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
@@ -194,7 +196,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
     for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"  // .acquire.cluster would invalidate L1 (CCTL.IVALL) per poll
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(ok)
             : "r"(bar), "r"(parity)
@@ -220,7 +222,8 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // memories, so each SM takes in HALF of the K / V bytes -- the delivery of K / V from L2 is what bounds the one-CTA form
 // at long sequences.  Only the leader (cluster rank 0) issues MMAs; completion is multicast to the barriers of both
 // CTAs; TMA loads of both CTAs are counted on the leader's barriers; softmax threads of the peer arrive remotely.
-template <bool PAIR>
+// MASKED = false: no mask and not causal -- the visibility code (and its instruction-cache footprint) is compiled out.
+template <bool PAIR, bool MASKED>
 __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_constant__ CUtensorMap tmQ,
                                                                const __grid_constant__ CUtensorMap tmK,
                                                                const __grid_constant__ CUtensorMap tmV,
@@ -487,7 +490,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             const bool row_ok = q < p.Sq;
             float m = -INFINITY, l = 0.f;
             const int Sk = item_sk(b), nkt = (Sk + AB_BN - 1) / AB_BN;
-            const uint32_t* mrow = p.mbits ? p.mbits + (long long)b * p.mwords : nullptr;
+            const uint32_t* mrow = (MASKED && p.mbits) ? p.mbits + (long long)b * p.mwords : nullptr;
             uint32_t vw[4] = {0u, 0u, 0u, 0u};  // packed key-padding bits of the NEXT tile (loaded one tile ahead)
             if (mrow) {
 #pragma unroll
@@ -501,6 +504,10 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 for (int c = 0; c < 4; ++c) {
                     const int kk0 = c * 32;
                     uint32_t v = keys - kk0 >= 32 ? 0xffffffffu : (keys - kk0 <= 0 ? 0u : ((1u << (keys - kk0)) - 1u));
+                    if (!MASKED) {
+                        vis[c] = v;
+                        continue;
+                    }
                     if (mrow) {
                         v &= vw[c];
                     } else if (p.mask_kind == 1) {
@@ -530,7 +537,8 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 tc_fence_after();
                 const uint32_t taddr = lane_base + buf * AB_BN;
                 // Scores stay in the raw domain: max over raw scores, one FFMA (score * scale*log2e - m) feeds ex2.
-                const bool fast = __all_sync(0xffffffffu, keys == AB_BN && (vis[0] & vis[1] & vis[2] & vis[3]) == 0xffffffffu);
+                const bool fast = MASKED ? __all_sync(0xffffffffu, keys == AB_BN && (vis[0] & vis[1] & vis[2] & vis[3]) == 0xffffffffu)
+                                         : keys == AB_BN;
                 const int nch = ((keys + 63) >> 6) << 1;  // 32-key chunks covered by the V stages of this tile
                 bool raise;
                 float alpha = 1.f;
@@ -539,9 +547,13 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
 #pragma unroll
                     for (int c = 0; c < 4; ++c) tmem_ld_32x32_b(taddr + c * 32, r + c * 32);
                     tmem_ld_wait();
-                    float mx = __uint_as_float(r[0]);
+                    float mx4[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
 #pragma unroll
-                    for (int t = 1; t < 128; ++t) mx = fmaxf(mx, __uint_as_float(r[t]));
+                    for (int t = 4; t < 128; t += 4) {  // four independent chains instead of one 127-deep one
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) mx4[u] = fmaxf(mx4[u], __uint_as_float(r[t + u]));
+                    }
+                    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
                     const float mt = mx * sl2;
                     raise = mt > m + AB_LAZY;  // first tile: m = -inf
                     if (raise) {
@@ -550,16 +562,21 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                         l *= alpha;
                     }
                     const float nm = -m;
-                    float acc0 = 0.f, acc1 = 0.f;
+                    float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                    for (int t = 0; t < 128; t += 2) {
+                    for (int t = 0; t < 128; t += 4) {
                         const float p0 = ex2_approx(fmaf(__uint_as_float(r[t]), sl2, nm));
                         const float p1 = ex2_approx(fmaf(__uint_as_float(r[t + 1]), sl2, nm));
-                        acc0 += p0;
-                        acc1 += p1;
+                        const float p2 = ex2_approx(fmaf(__uint_as_float(r[t + 2]), sl2, nm));
+                        const float p3 = ex2_approx(fmaf(__uint_as_float(r[t + 3]), sl2, nm));
+                        acc[0] += p0;
+                        acc[1] += p1;
+                        acc[2] += p2;
+                        acc[3] += p3;
                         r[t >> 1] = pack_bf16x2(p0, p1);
+                        r[(t >> 1) + 1] = pack_bf16x2(p2, p3);
                     }
-                    l += acc0 + acc1;
+                    l += (acc[0] + acc[1]) + (acc[2] + acc[3]);
                     if (j > 0) {  // P V of the previous tile: every phase of pv_bar is waited for, in order
                         wait_x(pv_bar, ((uint32_t)(n - 1)) & 1u);
                         tc_fence_after();
@@ -637,30 +654,39 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
             uint8_t* ost = smem_raw + (bars - smem_u32(smem_raw)) + 256 + qtr * 4096;
             const int q_w0 = qt * AB_BM + qtr * 32;  // first query row of this warp
             __nv_bfloat16* obase = p.O + (long long)b * p.bso + h * p.dk;
-#pragma unroll 1
-            for (int c = 0; c < (p.dk >> 5); c += 2) {
+            {
+                const int nc64 = p.dk >> 6;  // 64-column chunks; the TMEM read of chunk c+1 is in flight under the stores of c
                 uint32_t o[64];
-                tmem_ld_32x32_b(lane_base + 256 + c * 32, o);
-                tmem_ld_32x32_b(lane_base + 256 + c * 32 + 32, o + 32);
-                tmem_ld_wait();
-                __syncwarp();  // the previous chunk has been read out of the staging tile
+                tmem_ld_32x32_b(lane_base + 256, o);
+                tmem_ld_32x32_b(lane_base + 256 + 32, o + 32);
+#pragma unroll 1
+                for (int c = 0; c < nc64; ++c) {
+                    uint4 u[8];
+                    tmem_ld_wait();
 #pragma unroll
-                for (int u8 = 0; u8 < 8; ++u8) {
-                    const int t = u8 * 8;
-                    uint4 u;
-                    u.x = pack_bf16x2(__uint_as_float(o[t]) * inv_l, __uint_as_float(o[t + 1]) * inv_l);
-                    u.y = pack_bf16x2(__uint_as_float(o[t + 2]) * inv_l, __uint_as_float(o[t + 3]) * inv_l);
-                    u.z = pack_bf16x2(__uint_as_float(o[t + 4]) * inv_l, __uint_as_float(o[t + 5]) * inv_l);
-                    u.w = pack_bf16x2(__uint_as_float(o[t + 6]) * inv_l, __uint_as_float(o[t + 7]) * inv_l);
-                    *reinterpret_cast<uint4*>(ost + lane * 128 + ((u8 ^ (lane & 7)) << 4)) = u;
-                }
-                __syncwarp();
+                    for (int u8 = 0; u8 < 8; ++u8) {
+                        const int t = u8 * 8;
+                        u[u8].x = pack_bf16x2(__uint_as_float(o[t]) * inv_l, __uint_as_float(o[t + 1]) * inv_l);
+                        u[u8].y = pack_bf16x2(__uint_as_float(o[t + 2]) * inv_l, __uint_as_float(o[t + 3]) * inv_l);
+                        u[u8].z = pack_bf16x2(__uint_as_float(o[t + 4]) * inv_l, __uint_as_float(o[t + 5]) * inv_l);
+                        u[u8].w = pack_bf16x2(__uint_as_float(o[t + 6]) * inv_l, __uint_as_float(o[t + 7]) * inv_l);
+                    }
+                    if (c + 1 < nc64) {
+                        tmem_ld_32x32_b(lane_base + 256 + (c + 1) * 64, o);
+                        tmem_ld_32x32_b(lane_base + 256 + (c + 1) * 64 + 32, o + 32);
+                    }
+                    __syncwarp();  // the previous chunk has been read out of the staging tile
 #pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int r = it * 4 + (lane >> 3), u8 = lane & 7;
-                    const uint4 u = *reinterpret_cast<const uint4*>(ost + r * 128 + ((u8 ^ (r & 7)) << 4));
-                    if (q_w0 + r < p.Sq)
-                        *reinterpret_cast<uint4*>(obase + (long long)(q_w0 + r) * p.ldo + c * 32 + u8 * 8) = u;
+                    for (int u8 = 0; u8 < 8; ++u8)
+                        *reinterpret_cast<uint4*>(ost + lane * 128 + ((u8 ^ (lane & 7)) << 4)) = u[u8];
+                    __syncwarp();
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) {
+                        const int r = it * 4 + (lane >> 3), u8 = lane & 7;
+                        const uint4 v4 = *reinterpret_cast<const uint4*>(ost + r * 128 + ((u8 ^ (r & 7)) << 4));
+                        if (q_w0 + r < p.Sq)
+                            *reinterpret_cast<uint4*>(obase + (long long)(q_w0 + r) * p.ldo + c * 64 + u8 * 8) = v4;
+                    }
                 }
             }
             if (row_ok && p.lse) p.lse[(long long)bh * p.Sq + q] = (m + log2f(l)) * 0.6931471805599453f;
@@ -730,10 +756,11 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
     static bool attr = false;
     static int n_sm = 0;
     if (!attr) {
-        if (cudaFuncSetAttribute(attn_fwd_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM) !=
-                cudaSuccess ||
-            cudaFuncSetAttribute(attn_fwd_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM) !=
-                cudaSuccess) {
+        const cudaFuncAttribute A = cudaFuncAttributeMaxDynamicSharedMemorySize;
+        if (cudaFuncSetAttribute(attn_fwd_bf16_kernel<false, false>, A, AB_SMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(attn_fwd_bf16_kernel<false, true>, A, AB_SMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(attn_fwd_bf16_kernel<true, false>, A, AB_SMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(attn_fwd_bf16_kernel<true, true>, A, AB_SMEM) != cudaSuccess) {
             bmhrl_set_error("attn_fwd_bf16: cannot raise the shared-memory limit");
             return BMHRL_ERR_CUDA;
         }
@@ -758,6 +785,7 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
         p.sk_eff = sk_eff;
         p.mbits = mbits;
     }
+    const bool masked = mask_kind != 0 || causal != 0;
     const bool use_pair = (dk == 128 || dk == 256) && n_sm >= 2 &&
                           (g_attn_bf16_pair == 2 || (g_attn_bf16_pair == 0 && p.nqt >= AB_PAIR_MIN_QTILES));
     if (use_pair) {  // CTA pairs: K split by keys (box 64 x 64), V by columns (box 64 x 128), two query tiles per item
@@ -781,7 +809,9 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
         at[0].val.clusterDim.z = 1;
         cfg.attrs = at;
         cfg.numAttrs = 1;
-        if (cudaLaunchKernelEx(&cfg, attn_fwd_bf16_kernel<true>, tmQ, tmK, tmV, p) != cudaSuccess) {
+        const cudaError_t e = masked ? cudaLaunchKernelEx(&cfg, attn_fwd_bf16_kernel<true, true>, tmQ, tmK, tmV, p)
+                                     : cudaLaunchKernelEx(&cfg, attn_fwd_bf16_kernel<true, false>, tmQ, tmK, tmV, p);
+        if (e != cudaSuccess) {
             bmhrl_set_error(cudaGetErrorString(cudaGetLastError()));
             return BMHRL_ERR_CUDA;
         }
@@ -789,7 +819,8 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
         return BMHRL_OK;
     }
     const int grid = p.n_items < n_sm ? p.n_items : n_sm;
-    attn_fwd_bf16_kernel<false><<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
+    if (masked) attn_fwd_bf16_kernel<false, true><<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
+    else attn_fwd_bf16_kernel<false, false><<<grid, 192, AB_SMEM, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p);
     BMHRL_POST_LAUNCH("attn_fwd_bf16");
     return BMHRL_OK;
 }

@@ -49,6 +49,9 @@ def main():
     except Exception:
         pk, src = 1590.0, "fallback"
     B, H, dk = 64, 4, 256
+    if os.environ.get("ATTN_PAIR"):  # 1 = one CTA per query tile, 2 = CTA pairs (cta_group::2)
+        from bmhrl_b200._lib import LIB
+        LIB.call("bmhrl_attn_bf16_tuning", int(os.environ["ATTN_PAIR"]))
     D = H * dk
     shapes = [(300, 300), (800, 800), (300, 800), (800, 300)] if not quick else [(300, 300)]
     if os.environ.get("ATTN_SHAPES"):  # e.g. ATTN_SHAPES=800x800,300x300

@@ -1,6 +1,9 @@
-ATTN_SHAPES=${ATTN_SHAPES:-300x300,800x800} timeout 300 python tools/attn_sweep.py --quick > gpurun_out/attn/quick.jsonl 2> gpurun_out/attn/quick.err; echo "exit $?"
-python - <<'PY'
-import json
-for l in open("gpurun_out/attn/quick.jsonl"):
-    d=json.loads(l); print(d["kernel"][:22], d["Sq"], d["Sk"], d["mask"], round(d["us"],1), "us", round(d["tflops"],1), "TF", round(d["frac"],3))
-PY
+mkdir -p gpurun_out/attn
+for g in 148 111 74 37; do
+echo "grid cap $g"
+BMHRL_ATTN_GRID=$g ATTN_SHAPES=800x800 timeout 300 python tools/attn_sweep.py --quick 2> gpurun_out/attn/quick.err | head -1 | python -c "
+import json,sys
+for l in sys.stdin:
+    d=json.loads(l); print(d['Sq'], d['Sk'], d['mask'], round(d['us'],1), 'us', round(d['tflops'],1), 'TF')
+"
+done
