@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 }
             }
         } else if (!PAIR && elect_one()) {  // ===== MMA issuer
-            const uint32_t idesc_s = make_idesc(1, AB_BM, AB_BN, 0, 0);
+            const uint32_t idesc_full = make_idesc(1, AB_BM, AB_BN, 0, 0);
             const uint32_t idesc_o = make_idesc(1, AB_BM, p.dk, 0, 1);
             const uint64_t q_desc = make_smem_desc(sQ, 16, 1024);        // K-major, 128-byte rows, 8-row groups
             const uint64_t ring_desc = make_smem_desc(ring, 16, 1024);   // K tiles, same layout
@@ -428,8 +428,11 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                 const int Sk = item_sk((w / tiles_bh) / p.H), nkt = (Sk + AB_BN - 1) / AB_BN;
                 mbar_wait(q_full, (uint32_t)i & 1u);
                 tc_fence_after();
-                auto s_op = [&](bool last) {  // S[ns & 1] = Q K_j^T; in-order execution behind the P V that read this buffer
+                auto s_op = [&](int j) {  // S[ns & 1] = Q K_j^T; in-order execution behind the P V that read this buffer
                     const int buf = ns & 1;
+                    // a partial last tile only computes the score columns of its keys (N rounded up to 16)
+                    const int keys = min(AB_BN, Sk - j * AB_BN);
+                    const uint32_t idesc_s = keys == AB_BN ? idesc_full : make_idesc(1, AB_BM, (keys + 15) & ~15, 0, 0);
                     for (int hf = 0; hf < nkh; ++hf, ++it) {
                         const int s = it % AB_STAGES;
                         mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
@@ -445,7 +448,7 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                         tc_commit(empty_bar(s));
                     }
                     tc_commit(s_full(buf));
-                    if (last) tc_commit(q_empty);  // every Q K^T of this item has completed: Q may be overwritten
+                    if (j == nkt - 1) tc_commit(q_empty);  // every Q K^T of this item has completed: Q may be overwritten
                     ++ns;
                 };
                 auto pv_op = [&](int j) {  // O += P_j V_j
@@ -453,7 +456,8 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                     mbar_wait(s_rel(buf), ((uint32_t)(np >> 1)) & 1u);
                     if (j == 0 && i > 0) mbar_wait(o_free, ((uint32_t)(i - 1)) & 1u);
                     tc_fence_after();
-                    const int nkc = (min(AB_BN, Sk - j * AB_BN) + 63) >> 6;
+                    const int keys = min(AB_BN, Sk - j * AB_BN);
+                    const int nkc = (keys + 63) >> 6, nk16 = (keys + 15) >> 4;  // V stages; 16-key MMA steps
                     for (int kc = 0; kc < nkc; ++kc, ++it) {
                         const int s = it % AB_STAGES;
                         mbar_wait(full_bar(s), ((uint32_t)(it / AB_STAGES)) & 1u);
@@ -461,18 +465,19 @@ __global__ void __launch_bounds__(192, 1) attn_fwd_bf16_kernel(const __grid_cons
                         const uint64_t v0 = desc_advance(v_desc, s * AB_STAGE_BYTES);
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk)
-                            mma_bf16_ts(tmem_o, tmem_base + buf * AB_BN + kc * 32 + kk * 8, desc_advance(v0, kk * 2048),
-                                        idesc_o, (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
+                            if (kc * 4 + kk < nk16)
+                                mma_bf16_ts(tmem_o, tmem_base + buf * AB_BN + kc * 32 + kk * 8, desc_advance(v0, kk * 2048),
+                                            idesc_o, (j > 0 || kc > 0 || kk > 0) ? 1u : 0u);
                         tc_commit(empty_bar(s));
                     }
                     tc_commit(pv_bar);
                     ++np;
                 };
-                s_op(nkt == 1);
-                if (nkt > 1) s_op(nkt == 2);
+                s_op(0);
+                if (nkt > 1) s_op(1);
                 for (int j = 0; j < nkt; ++j) {
                     pv_op(j);
-                    if (j + 2 < nkt) s_op(j + 3 == nkt);
+                    if (j + 2 < nkt) s_op(j + 2);
                 }
             }
         }
