@@ -21,6 +21,7 @@
 #include <cuda_bf16.h>
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "attn_bf16_common.cuh"
 #include "../../include/bmhrl_b200.h"
 
 namespace bmhrl {
@@ -73,41 +74,10 @@ __global__ void attn_mask_pack_kernel(const unsigned char* __restrict__ mask, in
     if (threadIdx.x == 0) sk_eff[b] = last >= 0 ? last + 1 : Sk;
 }
 
-__device__ __forceinline__ void tmem_st_32x32_b(uint32_t taddr, const uint32_t* v) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
-        :
-        : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
-          "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]),
-          "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]),
-          "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-        : "memory");
+void attn_mask_pack(const unsigned char* mask, int B, int Sk, int mwords, int* sk_eff, uint32_t* mbits, cudaStream_t stream) {
+    attn_mask_pack_kernel<<<B, 128, 0, stream>>>(mask, Sk, mwords, sk_eff, mbits);
 }
-__device__ __forceinline__ void tmem_ld_32x32_b(uint32_t taddr, uint32_t* v) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait_b() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tmem_st_32x32_x16(uint32_t taddr, const uint32_t* v) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
-        :
-        : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
-          "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait_b() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 // rare path of the lazy softmax: multiply this warp's 32 accumulator rows (nchunks x 32 fp32 columns) by alpha[row]
 __device__ __noinline__ void rescale_o(uint32_t taddr, int nchunks, float alpha) {
     for (int c = 0; c < nchunks; ++c) {
@@ -130,17 +100,6 @@ __device__ __noinline__ void rescale_o(uint32_t taddr, int nchunks, float alpha)
     tmem_st_wait_b();
 }
 
-// D[tmem] (+)= A[tmem] * B[smem], kind::f16: A holds two bf16 per 32-bit TMEM cell (row = lane, k pair = column)
-__device__ __forceinline__ void mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
-                                            uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        :
-        : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
 // ---- CTA pair (cta_group::2): one MMA spans the two SMs of a cluster; only the leader CTA (cluster rank 0) issues
 __device__ __forceinline__ void mma2_bf16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                              uint32_t accumulate) {
@@ -204,17 +163,6 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
         if (ok) return;
     }
     __trap();
-}
-
-__device__ __forceinline__ float ex2_approx(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-    uint32_t r;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));  // first source -> upper half
-    return r;
 }
 
 // PAIR: two CTAs of a cluster (one SM pair) work on two neighbouring query tiles of the same (batch, head) with
@@ -785,7 +733,7 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
         p.mwords = 4 * ((Sk + AB_BN - 1) / AB_BN);
         int* sk_eff = (int*)ws;
         uint32_t* mbits = (uint32_t*)ws + ((B + 3) & ~3);
-        attn_mask_pack_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(mask, Sk, p.mwords, sk_eff, mbits);
+        attn_mask_pack(mask, B, Sk, p.mwords, sk_eff, mbits, (cudaStream_t)stream);
         BMHRL_POST_LAUNCH("attn_mask_pack");
         p.sk_eff = sk_eff;
         p.mbits = mbits;

@@ -517,6 +517,49 @@ def mha_core_bf16(q, k, v, mask, H, causal=False, return_lse=False, use_ws=True)
     return (o, lse) if return_lse else o
 
 
+def mha_core_bf16_bwd(q, k, v, o, lse, do, mask, H):
+    """Backward of `mha_core_bf16` (attn_bf16_bwd.cu): (dq, dk, dv) bf16 from the forward's output `o`, its fp32
+    (B,H,Sq) log-sum-exp and the output gradient `do`.  mask: None or a (B,1,Sk) key-padding mask.  The probabilities
+    are recomputed from q, k and lse; what autograd derives from model/multihead_attention.py:22-30 in the reference."""
+    for t, name in ((q, "q"), (k, "k"), (v, "v"), (o, "o"), (do, "do")):
+        if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous()):
+            raise RuntimeError(f"mha_core_bf16_bwd: {name} must be a contiguous CUDA bf16 tensor (there is no CPU fallback)")
+    B, Sq, D = q.shape
+    Sk = k.shape[1]
+    if D % H != 0:
+        raise RuntimeError("mha_core_bf16_bwd: d_model must be divisible by H")
+    if not (lse.is_cuda and lse.dtype == _F32 and lse.is_contiguous() and tuple(lse.shape) == (B, H, Sq)):
+        raise RuntimeError("mha_core_bf16_bwd: lse must be the contiguous fp32 (B,H,Sq) tensor of the forward")
+    m, kind = _mask_args(mask, B, Sq, Sk)
+    dq, dk_, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    ws = torch.empty(LIB.raw("bmhrl_attn_bwd_bf16_ws_bytes")(B, H, Sq, Sk), device=q.device, dtype=torch.uint8)
+    LIB.call("bmhrl_attn_bwd_bf16", _p(q), D, Sq * D, _p(k), D, Sk * D, _p(v), D, Sk * D, _p(o), D, Sq * D,
+             _p(do), D, Sq * D, _p(lse), _p(m), kind, _p(dq), D, Sq * D, _p(dk_), D, Sk * D, _p(dv), D, Sk * D,
+             B, H, Sq, Sk, D // H, _p(ws), _stream())
+    return dq, dk_, dv
+
+
+class _MhaCoreBf16(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, mask, H):
+        with torch.no_grad():
+            o, lse = mha_core_bf16(q, k, v, mask, H, return_lse=True)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.mask, ctx.H = mask, H
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        dq, dk_, dv = mha_core_bf16_bwd(q, k, v, o, lse, do.contiguous(), ctx.mask, ctx.H)
+        return dq, dk_, dv, None, None
+
+
+def mha_core_bf16_train(q, k, v, mask, H):
+    """Differentiable bf16 attention core: `mha_core_bf16` forward, `mha_core_bf16_bwd` backward (key-padding masks)."""
+    return _MhaCoreBf16.apply(q, k, v, mask, H)
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # K4 / K5
 # ----------------------------------------------------------------------------------------------------------------

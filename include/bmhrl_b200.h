@@ -123,6 +123,23 @@ long long bmhrl_attn_fwd_bf16_ws_bytes(int B, int Sk);
  * d_k is 128 or 256. */
 int bmhrl_attn_bf16_tuning(int pair_mode);
 
+/* ---- K1, bf16 operands: flash-style backward (attn_bf16_bwd.cu) ---------------------------------------------- */
+/* Gradients of attention() model/multihead_attention.py:7-31 (what autograd derives from :22-30 in the reference) with
+ * respect to the bf16 head-merged Q (B,Sq,H*dk), K, V (B,Sk,H*dk), given O and lse of bmhrl_attn_fwd_bf16 and dO:
+ *   P = exp(S - lse), dV = P^T dO, dP = dO V^T, dS = P o (dP - rowsum(dO o O)), dQ = dS K / sqrt(dk), dK = dS^T Q / sqrt(dk).
+ * The (B,H,Sq,Sk) probabilities are recomputed on the tensor cores, never stored.  Masked scores were REPLACED by -1e9
+ * in the forward: no gradient reaches them (a batch row with no visible key still sends its uniform weights to dV).
+ * mask_kind 0 (none) or 1 ((B,Sk) key padding); 2 (full (B,Sq,Sk) masks) returns BMHRL_ERR_UNSUPPORTED.  Pitches in
+ * ELEMENTS (multiples of 8); dQ / dK / dV bf16, fully overwritten; ws: bmhrl_attn_bwd_bf16_ws_bytes() bytes, required.
+ * Four launches: rowsum(dO o O), then one persistent tcgen05 kernel per gradient (dQ, dK, dV). */
+int bmhrl_attn_bwd_bf16(const void* Q, long long ldq, long long bsq, const void* K, long long ldk, long long bsk,
+                        const void* V, long long ldv, long long bsv, const void* O, long long ldo, long long bso,
+                        const void* dO, long long lddo, long long bsdo, const float* lse, const unsigned char* mask,
+                        int mask_kind, void* dQ, long long lddq, long long bsdq, void* dK, long long lddk,
+                        long long bsdk, void* dV, long long lddv, long long bsdv, int B, int H, int Sq, int Sk, int dk,
+                        void* ws, void* stream);
+long long bmhrl_attn_bwd_bf16_ws_bytes(int B, int H, int Sq, int Sk);
+
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
 int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */
 int bmhrl_log_softmax_bwd_f32(const float* dy, const float* y, float* dx, long long rows, int V, void* stream);
