@@ -7,17 +7,25 @@
 //
 // One persistent kernel, three instantiations (one launch each), all with the same structure.  An item is a 128-row tile
 // of the gradient being produced; the other sequence is streamed through in 64-column steps:
-//   DQ : rows = queries.  resident Q, dO tiles;  step j streams K_j (X) and V_j (Y):
-//        S = Q K_j^T, dP = dO V_j^T -> TMEM;  dS (bf16) -> TMEM;  dQ += dS K_j        (K_j read again, MN-major)
-//   DK : rows = keys.     resident K, V tiles;   step i streams Q_i (X) and dO_i (Y):
+//   DQ : rows = queries.  resident Q, dO tiles;  step j streams K_j and V_j:
+//        S = Q K_j^T, dP = dO V_j^T -> TMEM;  dS (bf16) -> TMEM;  dQ += dS K_j        (K_j delivered again, MN-major)
+//   DK : rows = keys.     resident K, V tiles;   step i streams Q_i and dO_i:
 //        S^T = K Q_i^T, dP^T = V dO_i^T;  dS^T -> TMEM;  dK += dS^T Q_i
-//   DV : rows = keys.     resident K tile;       step i streams dO_i (X) and Q_i (Y):
+//   DV : rows = keys.     resident K tile;       step i streams Q_i and dO_i:
 //        S^T = K Q_i^T;  P^T (bf16) -> TMEM;  dV += P^T dO_i
 // (dK and dV cannot share a pass at d_k = 256: two 128 x 256 fp32 accumulators are all 512 TMEM columns.)
 // 192 threads: warp 0 TMA producer, warp 1 TMEM allocator + tcgen05.mma issuer, warps 2-5 thread = row: read the S / dP
 // tiles from TMEM, recompute the probabilities, write dS (or P) back as the bf16 A operand of the accumulating MMA.
-// Shared memory: 2 resident 64 KB tiles + X ring (2 x 32 KB, lives until the accumulating MMA has read it) + Y ring
-// (2 half tiles of 16 KB, consumed by the K-major MMA that contracts over d_k).  TMEM: S 2 x 64, dP 2 x 64, accumulator 256.
+// Shared memory (224 KB at d_k = 256): 2 resident 64 KB tiles + two rings of 2 half tiles (16 KB) for the K-major
+// operands of S and dP, freed as soon as those MMAs have read them, + ONE 32 KB tile for the MN-major operand of the
+// accumulating MMA.  That tile is the same data as the S operand, delivered a second time (from L2): holding the first
+// copy until dS exists would leave no room to prefetch the next steps, and the step would wait for a load every time.
+// TMEM: S 2 x 64, dP 2 x 64, accumulator 256.
+// What bounds it (measured, B=64 S=800: ~2.1 us per 64-column step in every pass, unchanged when the Z delivery or the
+// row arithmetic is switched off): shared-memory bandwidth.  An N = 64 MMA re-reads its 4 KB A slice for 2 KB of B every
+// 32 tensor-pipe clocks (192 B/clk against 128 B/clk); per step S + dP read 192 KB, the accumulating MMA 32 KB, and TMA
+// writes 96 KB.  Wider steps (N = 128 halves the A re-reads) do not fit next to two resident 64 KB tiles and a 256-column
+// accumulator; the way out is the CTA-pair form (cta_group::2: M = 256, each SM holds half of every streamed tile).
 #include <cuda_bf16.h>
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -31,9 +39,9 @@ using namespace tc;
 constexpr int BW_BM = 128;  // rows per item
 constexpr int BW_BN = 64;   // streamed columns per step
 constexpr int BW_RES_BYTES = 64 * 1024;
-constexpr int BW_X_BYTES = 32 * 1024;
-constexpr int BW_Y_BYTES = 16 * 1024;
-constexpr int BW_SMEM = 2 * BW_RES_BYTES + 2 * BW_X_BYTES + 2 * BW_Y_BYTES + 1024 + 256;
+constexpr int BW_P_BYTES = 16 * 1024;  // half of a streamed tile (64 rows x 128 columns), K-major operand of S / dP
+constexpr int BW_Z_BYTES = 32 * 1024;  // a streamed tile (64 rows x 256 columns), MN-major operand of the accumulating MMA
+constexpr int BW_SMEM = 2 * BW_RES_BYTES + 4 * BW_P_BYTES + BW_Z_BYTES + 1024 + 256;
 enum { BW_DQ = 0, BW_DK = 1, BW_DV = 2 };
 
 struct AttnBwdParams {
@@ -74,42 +82,46 @@ __global__ void attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ O, long 
 template <int MODE>
 __global__ void __launch_bounds__(192, 1) attn_bwd_bf16_kernel(const __grid_constant__ CUtensorMap tmRA,
                                                                const __grid_constant__ CUtensorMap tmRB,
-                                                               const __grid_constant__ CUtensorMap tmX,
-                                                               const __grid_constant__ CUtensorMap tmY,
+                                                               const __grid_constant__ CUtensorMap tmKA,
+                                                               const __grid_constant__ CUtensorMap tmKB,
+                                                               const __grid_constant__ CUtensorMap tmZ,
                                                                const AttnBwdParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t resA = base, resB = base + BW_RES_BYTES;
-    const uint32_t ringX = base + 2 * BW_RES_BYTES;
-    const uint32_t ringY = ringX + 2 * BW_X_BYTES;
-    const uint32_t bars = ringY + 2 * BW_Y_BYTES;
-    auto full_x = [&](int s) { return bars + 8u * s; };
-    auto empty_x = [&](int s) { return bars + 8u * (2 + s); };
-    auto full_y = [&](int s) { return bars + 8u * (4 + s); };
-    auto empty_y = [&](int s) { return bars + 8u * (6 + s); };
+    const uint32_t ringA = base + 2 * BW_RES_BYTES;   // parts of the streamed tile that pairs with resident A (S)
+    const uint32_t ringB = ringA + 2 * BW_P_BYTES;    // parts of the streamed tile that pairs with resident B (dP)
+    const uint32_t tileZ = ringB + 2 * BW_P_BYTES;    // streamed tile as the MN-major operand of the accumulating MMA
+    const uint32_t bars = tileZ + BW_Z_BYTES;
+    auto full_a = [&](int s) { return bars + 8u * s; };
+    auto empty_a = [&](int s) { return bars + 8u * (2 + s); };
+    auto full_b = [&](int s) { return bars + 8u * (4 + s); };
+    auto empty_b = [&](int s) { return bars + 8u * (6 + s); };
     auto sdp_full = [&](int i) { return bars + 8u * (8 + i); };   // MMA -> row threads: S (and dP) tile complete
     auto ds_ready = [&](int i) { return bars + 8u * (10 + i); };  // row threads -> MMA: dS / P written
     const uint32_t r_full = bars + 8u * 12, r_empty = bars + 8u * 13;
     const uint32_t acc_full = bars + 8u * 14, acc_free = bars + 8u * 15;
-    const uint32_t tmem_slot = bars + 8u * 16;
+    const uint32_t full_z = bars + 8u * 16, empty_z = bars + 8u * 17;
+    const uint32_t tmem_slot = bars + 8u * 18;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nvc = p.dk >> 6;                    // 64-column chunks of a tile
-    const int nyp = p.dk >= 128 ? 2 : 1;          // parts the Y tile is delivered in
-    const int ypc = nvc / nyp;                    // 64-column chunks per Y part
+    const int nyp = p.dk >= 128 ? 2 : 1;          // parts a K-major streamed tile is delivered in
+    const int ypc = nvc / nyp;                    // 64-column chunks per part
     const int nt = (p.cols + BW_BN - 1) / BW_BN;  // steps per item
     constexpr bool TWO_RES = MODE != BW_DV;       // S and dP both computed (two resident operands)
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmRA);
         tma_prefetch_desc(&tmRB);
-        tma_prefetch_desc(&tmX);
-        tma_prefetch_desc(&tmY);
+        tma_prefetch_desc(&tmKA);
+        tma_prefetch_desc(&tmKB);
+        tma_prefetch_desc(&tmZ);
         for (int s = 0; s < 2; ++s) {
-            mbar_init(full_x(s), 1);
-            mbar_init(empty_x(s), 1);
-            mbar_init(full_y(s), 1);
-            mbar_init(empty_y(s), 1);
+            mbar_init(full_a(s), 1);
+            mbar_init(empty_a(s), 1);
+            mbar_init(full_b(s), 1);
+            mbar_init(empty_b(s), 1);
             mbar_init(sdp_full(s), 1);
             mbar_init(ds_ready(s), 128);
         }
@@ -117,6 +129,8 @@ __global__ void __launch_bounds__(192, 1) attn_bwd_bf16_kernel(const __grid_cons
         mbar_init(r_empty, 1);
         mbar_init(acc_full, 1);
         mbar_init(acc_free, 128);
+        mbar_init(full_z, 1);
+        mbar_init(empty_z, 1);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -130,8 +144,8 @@ __global__ void __launch_bounds__(192, 1) attn_bwd_bf16_kernel(const __grid_cons
     auto tmem_dp = [&](int buf) { return tmem_base + 128u + (uint32_t)(buf * BW_BN); };
 
     if (warp == 0) {
-        if (elect_one()) {  // ===== TMA producer
-            int gx = 0, gy = 0;  // X tiles / Y parts loaded so far
+        if (elect_one()) {  // ===== TMA producer: same order as the MMA issuer consumes -- parts(0) parts(1) Z(0) parts(2) Z(1) ...
+            int ga = 0, gb = 0, gz = 0;  // parts / Z tiles loaded so far (all items)
             for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
                 const int bh = w / p.nrt, rt = w - bh * p.nrt;
                 const int b = bh / p.H, h = bh - b * p.H;
@@ -142,23 +156,37 @@ __global__ void __launch_bounds__(192, 1) attn_bwd_bf16_kernel(const __grid_cons
                     tma_load_4d(resA + c * 16384, &tmRA, r_full, col0 + c * 64, row0, 0, b);
                     if (TWO_RES) tma_load_4d(resB + c * 16384, &tmRB, r_full, col0 + c * 64, row0, 0, b);
                 }
-                for (int t = 0; t < nt; ++t) {
-                    {
-                        const int s = gx & 1;
-                        mbar_wait(empty_x(s), (((uint32_t)(gx >> 1)) & 1u) ^ 1u);
-                        mbar_arrive_expect_tx(full_x(s), (uint32_t)(nvc * 8192));
-                        for (int c = 0; c < nvc; ++c)
-                            tma_load_4d(ringX + s * BW_X_BYTES + c * 8192, &tmX, full_x(s), col0 + c * 64, t * BW_BN, 0, b);
-                        ++gx;
-                    }
-                    for (int y = 0; y < nyp; ++y, ++gy) {
-                        const int s = gy & 1;
-                        mbar_wait(empty_y(s), (((uint32_t)(gy >> 1)) & 1u) ^ 1u);
-                        mbar_arrive_expect_tx(full_y(s), (uint32_t)(ypc * 8192));
+                auto load_parts = [&](int t) {
+                    for (int y = 0; y < nyp; ++y, ++ga) {
+                        const int s = ga & 1;
+                        mbar_wait(empty_a(s), (((uint32_t)(ga >> 1)) & 1u) ^ 1u);
+                        mbar_arrive_expect_tx(full_a(s), (uint32_t)(ypc * 8192));
                         for (int c = 0; c < ypc; ++c)
-                            tma_load_4d(ringY + s * BW_Y_BYTES + c * 8192, &tmY, full_y(s), col0 + (y * ypc + c) * 64,
+                            tma_load_4d(ringA + s * BW_P_BYTES + c * 8192, &tmKA, full_a(s), col0 + (y * ypc + c) * 64,
                                         t * BW_BN, 0, b);
                     }
+                    if (TWO_RES) {
+                        for (int y = 0; y < nyp; ++y, ++gb) {
+                            const int s = gb & 1;
+                            mbar_wait(empty_b(s), (((uint32_t)(gb >> 1)) & 1u) ^ 1u);
+                            mbar_arrive_expect_tx(full_b(s), (uint32_t)(ypc * 8192));
+                            for (int c = 0; c < ypc; ++c)
+                                tma_load_4d(ringB + s * BW_P_BYTES + c * 8192, &tmKB, full_b(s), col0 + (y * ypc + c) * 64,
+                                            t * BW_BN, 0, b);
+                        }
+                    }
+                };
+                auto load_z = [&](int t) {
+                    mbar_wait(empty_z, ((uint32_t)gz & 1u) ^ 1u);
+                    mbar_arrive_expect_tx(full_z, (uint32_t)(nvc * 8192));
+                    for (int c = 0; c < nvc; ++c) tma_load_4d(tileZ + c * 8192, &tmZ, full_z, col0 + c * 64, t * BW_BN, 0, b);
+                    ++gz;
+                };
+                load_parts(0);
+                if (nt > 1) load_parts(1);
+                for (int t = 0; t < nt; ++t) {
+                    load_z(t);
+                    if (t + 2 < nt) load_parts(t + 2);
                 }
             }
         }
@@ -168,64 +196,49 @@ __global__ void __launch_bounds__(192, 1) attn_bwd_bf16_kernel(const __grid_cons
             const uint32_t idesc_f = make_idesc(1, BW_BM, p.dk, 0, 1);
             const uint64_t ra_desc = make_smem_desc(resA, 16, 1024);     // K-major, 128-byte rows, 16 KB per 64 columns
             const uint64_t rb_desc = make_smem_desc(resB, 16, 1024);
-            const uint64_t xk_desc = make_smem_desc(ringX, 16, 1024);    // X tile as K-major B (N = its 64 rows)
-            const uint64_t xm_desc = make_smem_desc(ringX, 8192, 1024);  // X tile as MN-major B (K = its 64 rows, N = d_k)
-            const uint64_t y_desc = make_smem_desc(ringY, 16, 1024);     // Y part, K-major B
-            int gy = 0, ns = 0, nf = 0;  // Y parts consumed; S(+dP) tiles issued; accumulating MMAs issued (all items)
+            const uint64_t ka_desc = make_smem_desc(ringA, 16, 1024);    // parts: K-major B (N = 64 rows), 8 KB per 64 columns
+            const uint64_t kb_desc = make_smem_desc(ringB, 16, 1024);
+            const uint64_t z_desc = make_smem_desc(tileZ, 8192, 1024);   // MN-major B (K = 64 rows, N = d_k)
+            int ga = 0, gb = 0, ns = 0, nf = 0;  // parts consumed; S(+dP) tiles issued; accumulating MMAs issued (all items)
             for (int i = 0, w = blockIdx.x; w < p.n_items; ++i, w += gridDim.x) {
                 mbar_wait(r_full, (uint32_t)i & 1u);
                 tc_fence_after();
-                // contraction over d_k of a resident operand (A) with the Y parts (B), into tmem_d
-                auto y_mma = [&](uint64_t a_desc, uint32_t tmem_d) {
-                    for (int y = 0; y < nyp; ++y, ++gy) {
-                        const int s = gy & 1;
-                        mbar_wait(full_y(s), ((uint32_t)(gy >> 1)) & 1u);
+                // contraction over d_k of a resident operand (A) with the parts of a streamed tile (B), into tmem_d
+                auto parts_mma = [&](uint64_t a_desc, uint64_t k_desc, bool ring_b, int& g, uint32_t tmem_d) {
+                    for (int y = 0; y < nyp; ++y, ++g) {
+                        const int s = g & 1;
+                        mbar_wait(ring_b ? full_b(s) : full_a(s), ((uint32_t)(g >> 1)) & 1u);
                         tc_fence_after();
                         for (int c = 0; c < ypc; ++c) {
                             const uint64_t a0 = desc_advance(a_desc, (y * ypc + c) * 16384);
-                            const uint64_t b0 = desc_advance(y_desc, s * BW_Y_BYTES + c * 8192);
+                            const uint64_t b0 = desc_advance(k_desc, s * BW_P_BYTES + c * 8192);
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 mma_bf16_ss(tmem_d, desc_advance(a0, k * 32), desc_advance(b0, k * 32), idesc_s,
                                             (y > 0 || c > 0 || k > 0) ? 1u : 0u);
                         }
-                        tc_commit(empty_y(s));
+                        tc_commit(ring_b ? empty_b(s) : empty_a(s));
                     }
                 };
                 auto sd_op = [&](int t) {
                     const int buf = ns & 1;
-                    if (MODE == BW_DV) {
-                        y_mma(ra_desc, tmem_s(buf));  // S^T = K Q_i^T, Q_i delivered in parts
-                    } else {
-                        const int s = ns & 1;         // X tile of step ns
-                        mbar_wait(full_x(s), ((uint32_t)(ns >> 1)) & 1u);
-                        tc_fence_after();
-                        for (int c = 0; c < nvc; ++c) {
-                            const uint64_t a0 = desc_advance(ra_desc, c * 16384);
-                            const uint64_t b0 = desc_advance(xk_desc, s * BW_X_BYTES + c * 8192);
-#pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                mma_bf16_ss(tmem_s(buf), desc_advance(a0, k * 32), desc_advance(b0, k * 32), idesc_s,
-                                            (c > 0 || k > 0) ? 1u : 0u);
-                        }
-                        y_mma(rb_desc, tmem_dp(buf));  // dP = dO V_j^T  /  dP^T = V dO_i^T
-                    }
+                    parts_mma(ra_desc, ka_desc, false, ga, tmem_s(buf));              // S = Q K_j^T   /  S^T = K Q_i^T
+                    if (TWO_RES) parts_mma(rb_desc, kb_desc, true, gb, tmem_dp(buf));  // dP = dO V_j^T /  dP^T = V dO_i^T
                     tc_commit(sdp_full(buf));
                     if (t == nt - 1) tc_commit(r_empty);  // the resident tiles have been read for the last time
                     ++ns;
                 };
-                auto f_op = [&](int t) {  // accumulator += dS (or P), from TMEM, times the X tile
-                    const int buf = nf & 1, s = nf & 1;
+                auto f_op = [&](int t) {  // accumulator += dS (or P), from TMEM, times the Z tile
+                    const int buf = nf & 1;
                     mbar_wait(ds_ready(buf), ((uint32_t)(nf >> 1)) & 1u);
                     if (t == 0 && i > 0) mbar_wait(acc_free, ((uint32_t)(i - 1)) & 1u);
-                    mbar_wait(full_x(s), ((uint32_t)(nf >> 1)) & 1u);  // (already seen by sd_op except in the DV form)
+                    mbar_wait(full_z, (uint32_t)nf & 1u);
                     tc_fence_after();
-                    const uint64_t b0 = desc_advance(xm_desc, s * BW_X_BYTES);
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk)
-                        mma_bf16_ts(tmem_acc, tmem_s(buf) + kk * 8, desc_advance(b0, kk * 2048), idesc_f,
+                        mma_bf16_ts(tmem_acc, tmem_s(buf) + kk * 8, desc_advance(z_desc, kk * 2048), idesc_f,
                                     (t > 0 || kk > 0) ? 1u : 0u);
-                    tc_commit(empty_x(s));
+                    tc_commit(empty_z);
                     if (t == nt - 1) tc_commit(acc_full);
                     ++nf;
                 };
@@ -365,6 +378,14 @@ __global__ void __launch_bounds__(192, 1) attn_bwd_bf16_kernel(const __grid_cons
 
 }  // namespace bmhrl
 
+static int g_attn_bwd_passes = 7;
+/* profiling hook: bit mask of the gradient passes bmhrl_attn_bwd_bf16 launches (1 = dQ, 2 = dK, 4 = dV; default 7) */
+extern "C" int bmhrl_attn_bwd_bf16_tuning(int passes) {
+    BMHRL_CHECK_ARG(passes >= 1 && passes <= 7, "bmhrl_attn_bwd_bf16_tuning: pass mask 1..7");
+    g_attn_bwd_passes = passes;
+    return BMHRL_OK;
+}
+
 extern "C" long long bmhrl_attn_bwd_bf16_ws_bytes(int B, int H, int Sq, int Sk) {
     const long long nd = ((long long)B * H * Sq + 3) & ~3ll;
     return 4ll * (nd + ((B + 3) & ~3) + (long long)B * 4 * ((Sk + 127) / 128));
@@ -467,20 +488,26 @@ extern "C" int bmhrl_attn_bwd_bf16(const void* Q, long long ldq, long long bsq, 
         const int grid = a.n_items < n_sm ? a.n_items : n_sm;
         if (mode == BW_DQ) {
             a.out = (__nv_bfloat16*)dQ; a.ldo = lddq; a.bso = bsdq;
-            attn_bwd_bf16_kernel<BW_DQ><<<grid, 192, BW_SMEM, st>>>(rQ, rdO, sK, sV, a);
+            attn_bwd_bf16_kernel<BW_DQ><<<grid, 192, BW_SMEM, st>>>(rQ, rdO, sK, sV, sK, a);
         } else if (mode == BW_DK) {
             a.out = (__nv_bfloat16*)dK; a.ldo = lddk; a.bso = bsdk;
-            attn_bwd_bf16_kernel<BW_DK><<<grid, 192, BW_SMEM, st>>>(rK, rV, sQ, sdO, a);
+            attn_bwd_bf16_kernel<BW_DK><<<grid, 192, BW_SMEM, st>>>(rK, rV, sQ, sdO, sQ, a);
         } else {
             a.out = (__nv_bfloat16*)dV; a.ldo = lddv; a.bso = bsdv;
-            attn_bwd_bf16_kernel<BW_DV><<<grid, 192, BW_SMEM, st>>>(rK, rK, sdO, sQ, a);
+            attn_bwd_bf16_kernel<BW_DV><<<grid, 192, BW_SMEM, st>>>(rK, rK, sQ, sQ, sdO, a);
         }
     };
-    launch(BW_DQ);
-    BMHRL_POST_LAUNCH("attn_bwd_bf16 dQ");
-    launch(BW_DK);
-    BMHRL_POST_LAUNCH("attn_bwd_bf16 dK");
-    launch(BW_DV);
-    BMHRL_POST_LAUNCH("attn_bwd_bf16 dV");
+    if (g_attn_bwd_passes & 1) {
+        launch(BW_DQ);
+        BMHRL_POST_LAUNCH("attn_bwd_bf16 dQ");
+    }
+    if (g_attn_bwd_passes & 2) {
+        launch(BW_DK);
+        BMHRL_POST_LAUNCH("attn_bwd_bf16 dK");
+    }
+    if (g_attn_bwd_passes & 4) {
+        launch(BW_DV);
+        BMHRL_POST_LAUNCH("attn_bwd_bf16 dV");
+    }
     return BMHRL_OK;
 }

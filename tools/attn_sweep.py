@@ -77,6 +77,27 @@ def main():
                     "flops": "nominal 4*B*H*Sq*Sk*dk" + (" (key tiles behind the last visible key are skipped: their "
                                                           "probabilities are exactly 0)" if mname == "pad50" else "")}
             print(json.dumps(line), flush=True)
+        if "--bwd" in sys.argv:  # backward (attn_bf16_bwd.cu): rowsum(dO o O) + the dQ, dK, dV passes; nominal 2.5 x forward FLOPs
+            from bmhrl_b200._lib import LIB
+            do = torch.randn(B, Sq, D, device=dev, generator=g).bfloat16()
+            for mname in ("none", "pad50"):
+                m = None
+                if mname == "pad50":
+                    m = torch.ones(B, 1, Sk, dtype=torch.bool, device=dev)
+                    m[:, :, Sk // 2:] = False
+                with torch.no_grad():
+                    o, lse = ops.mha_core_bf16(q, k, v, m, H, return_lse=True)
+                    fl = 10.0 * B * H * Sq * Sk * dk
+                    for passes, pname in ((7, "bwd (delta + dQ + dK + dV)"), (1, "delta + dQ"), (2, "delta + dK"), (4, "delta + dV")):
+                        LIB.call("bmhrl_attn_bwd_bf16_tuning", passes)
+                        t = timeit(lambda: ops.mha_core_bf16_bwd(q, k, v, o, lse, do, m, H), reps=4, iters=3)
+                        line = {"kernel": "attn_bwd_bf16_kernel", "B": B, "H": H, "Sq": Sq, "Sk": Sk, "dk": dk, "mask": mname,
+                                "pass": pname, "us": t * 1e6, "dtype": "bf16"}
+                        if passes == 7:
+                            line.update({"tflops": fl / t / 1e12, "peak_tflops": pk, "frac": fl / t / 1e12 / pk,
+                                         "flops": "nominal 10*B*H*Sq*Sk*dk (executed: 16, S is recomputed in every pass)"})
+                        print(json.dumps(line), flush=True)
+                    LIB.call("bmhrl_attn_bwd_bf16_tuning", 7)
         if not quick:
             ops.set_math_mode("tf32")
             qf, kf, vf = q.float(), k.float(), v.float()
