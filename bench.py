@@ -265,7 +265,23 @@ def attention_roofline(pk):
         out.append({"kernel": "attn_fwd_bf16_kernel", "shape": f"B=64 H=4 Sq=Sk={S} d_k=256 bf16 fwd", "bound": "tensor",
                     "achieved": fl / sec / 1e12, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                     "frac": fl / sec / 1e12 / pk["bf16_tflops"], "us": sec * 1e6})
-        del q, k, v
+        # backward (attn_bf16_bwd.cu): rowsum(dO o O) + the dQ, dK and dV passes; nominal FLOPs = 2.5 x forward
+        do = torch.randn(B, S, H * dk, device=dev).bfloat16()
+        with torch.no_grad():
+            o, lse = ops.mha_core_bf16(q, k, v, None, H, return_lse=True)
+            for _ in range(2):
+                ops.mha_core_bf16_bwd(q, k, v, o, lse, do, None, H)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(5):
+                ops.mha_core_bf16_bwd(q, k, v, o, lse, do, None, H)
+            e1.record()
+            torch.cuda.synchronize()
+        bsec = e0.elapsed_time(e1) / 1e3 / 5
+        out.append({"kernel": "attn_bwd_bf16_kernel x3 + delta", "shape": f"B=64 H=4 Sq=Sk={S} d_k=256 bf16 bwd",
+                    "bound": "tensor", "achieved": 2.5 * fl / bsec / 1e12, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                    "frac": 2.5 * fl / bsec / 1e12 / pk["bf16_tflops"], "us": bsec * 1e6})
+        del q, k, v, do, o, lse
     return out
 
 
