@@ -4,8 +4,10 @@ Restates the bodies of the reference's epoch loops as fixed-shape device program
   * warm-start step  epoch_loops/captioning_bmrl_loops.py:1148-1160  (fwd + LabelSmoothing + bwd + Adam)
   * RL step          epoch_loops/captioning_bmrl_loops.py:837-877    (fwd + value fn + biased_kl() + BiasedKL +
                      bwd + Adam + value-function MSE bwd + Adam), worker and manager phases (F4-free).
-The reward scorer (host Python n-gram code in the reference, metrics/cider.py) is OUTSIDE this path: a step takes
-the (B, L) score tensor as an input (synthetic rewards in the timed runs).
+The timed step takes the (B, L) score tensor as an input (synthetic rewards in the timed
+runs).  With `scorer=` (bmhrl_b200.metrics.CiderScorer, the host C++ restatement of metrics/cider.py) and
+batch["trg_caption"] (list of strings) the eager step scores the sampled tokens on the host between sampling and the
+loss like the reference does; that variant has a host round trip and is not graph-captured.
 
 Every step can be captured into ONE CUDA graph (`StepRunner.capture`): the library's entry points never
 synchronise or allocate, dropout/sampling counters and Adam step counts advance on the device.  No CPU fallback.
@@ -29,12 +31,22 @@ def used_parameters(model):
                     or n.startswith("manager.core."))]
 
 
+def get_score(train_worker, scorer, predicted_tokens, caption, mask, segments):
+    """captioning_bmrl_loops.py:219-230 for the CIDEr scorer (METEOR needs nltk + WordNet, BLEU: not built)."""
+    if scorer.type != "CIDER":
+        raise NotImplementedError(f"scorer type {scorer.type!r}: only the CIDEr reward scorer is implemented")
+    if train_worker:
+        return scorer.delta_cider_worker(predicted_tokens, caption)
+    return scorer.delta_cider_manager(predicted_tokens, caption, mask, segments)
+
+
 class BMHRLTrainer:
     """Holds the agent, the two value functions, their fused Adam optimisers (torch.optim.Adam defaults,
     scripts/train_rl_captioning_module.py:81-83) and the criteria (:66-67, :132)."""
 
     def __init__(self, cap_model, wv_model, mv_model, pad_idx=1, smoothing=0.7, lr=1e-4, modality="audio_video",
-                 grad_sync=None):
+                 grad_sync=None, scorer=None):
+        self.scorer = scorer  # bmhrl_b200.metrics.CiderScorer; None = the step takes batch["score"] (synthetic rewards)
         self.cap_model, self.wv_model, self.mv_model = cap_model, wv_model, mv_model
         self.pad_idx, self.modality = pad_idx, modality
         self.ls = LabelSmoothing(smoothing, pad_idx)
@@ -188,15 +200,26 @@ class BMHRLTrainer:
         else:
             ev = self.mv_model(manager_feat.detach()).squeeze(-1)
         # biased_kl() :271-334
-        score = batch["score"].to(pred.dtype)
         lm = loss_mask.to(pred.dtype)
         expected = ev.detach()
         if train_worker:
             mode = "noise" if exp_noise is not None else "philox"
             tok, sp = ops.sample_tokens(pred, mode, exp_noise, salt=self._sample_salt())
-            norm = lm.sum(-1, keepdim=True)
         else:
             tok, sp = ops.sample_tokens(pred, "argmax")
+        if self.scorer is not None and "trg_caption" in batch:
+            # get_score() :219-230, :287 on the host (libbmhrl_reward.so): D2H of the (B, L) tokens, H2D of the scores.
+            # Not graph-capturable (host round trip); the reference's manager scorer closes `segments` in place at the
+            # reference caption length (metrics/cider.py:74-77) and every later use sees that edit -- done on a copy
+            # here because the forward pass has saved `seg` for backward.
+            seg = seg.clone()
+            score = get_score(train_worker, self.scorer, tok, batch["trg_caption"], loss_mask, seg)[0]
+            score = score.to(pred.device, pred.dtype)
+        else:
+            score = batch["score"].to(pred.dtype)
+        if train_worker:
+            norm = lm.sum(-1, keepdim=True)
+        else:
             segf = seg.to(pred.dtype)
             norm = segf.sum(-1, keepdim=True)
             score = score * segf

@@ -1,5 +1,7 @@
 """GPU: the whole hot path (BMHrlAgent forward/backward, warm-start and RL training steps, greedy decode) against
 golden vectors produced by the UNMODIFIED reference, plus CUDA-graph and size-independent property checks."""
+from types import SimpleNamespace as NS
+
 import pytest
 import torch
 
@@ -255,3 +257,64 @@ def test_overlapped_grad_sync_reduces_every_gradient_once(gpu_lib, agent_sd, kin
         res.append((model.worker.core.projection.weight.detach().clone(),
                     model.bm_enc.encoder.layers[0].self_att_M1.linear_Q2d.weight.detach().clone()))
     assert rel(res[1][0], res[0][0]) < 1e-6 and rel(res[1][1], res[0][1]) < 1e-6
+
+
+@pytest.mark.parametrize("train_worker", [True, False])
+def test_rl_losses_with_host_cider_scorer(gpu_lib, golden, agent_sd, train_worker):
+    """The eager RL step with the real reward scorer between sampling and the loss (captioning_bmrl_loops.py:287):
+    the scores the step used are the oracle's CIDEr rewards of the tokens it sampled; a worker step fed those scores
+    as batch["score"] gives the same losses; the manager step sees `segments` closed at the reference length."""
+    import numpy as np
+    from oracle import reward_oracle as RO
+    from bmhrl_b200.metrics import CiderScorer
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer
+    B, L, gamma = 4, 9, 0.9
+    model, cfg = build_agent(agent_sd)
+    wv, mv = BMWorkerValueFunction(cfg), BMManagerValueFunction(cfg)
+    vsd = synth.fill_state_dict(golden["value_fn_shapes"], seed=3)
+    (wv if train_worker else mv).load_state_dict(vsd)
+    itos = ["<unk>", "<pad>", "<s>", "</s>"] + [f"w{i}" for i in range(4, VOC)]
+    b = synth.synthetic_batch(B=B, Sv=6, Sa=10, L=L, V=VOC, seed=11, ragged=True)
+    cap = b["caption"]
+    targets = [" ".join(itos[int(t)] for t in row[1:] if int(t) not in (PAD, 2, 3))[: 10 ** 6] for row in cap]
+    targets = [" ".join(t.split()[: L - 3]) for t in targets]          # reference length < L (the closing edit)
+    gen = torch.Generator().manual_seed(5)
+    corpus = [[itos[int(t)] for t in row[1:] if int(t) not in (PAD, 2, 3)] for row in cap] * 2
+    corpus += [[itos[int(i)] for i in torch.randint(4, 60, (12,), generator=gen)] for _ in range(200)]
+    scorer = CiderScorer(NS(itos=itos), corpus, "cuda", gamma, gamma)
+    tr = BMHRLTrainer(model, wv.cuda(), mv.cuda(), pad_idx=PAD, smoothing=SMOOTH, scorer=scorer)
+    if train_worker:
+        tr.teach_worker()
+    else:
+        tr.teach_manager()
+        model.manager.exploration = False
+    torch.manual_seed(2)
+    q = torch.empty(B * L, VOC).exponential_(1).view(B, L, VOC).cuda() if train_worker else None
+    db = _dev({k: v for k, v in b.items()})
+    db["trg_caption"] = targets
+    # dout_p = 0 and exploration off: the passes below see the same forward
+    cap_loss, value_loss, tok, score, div = tr.rl_losses(db, train_worker, False, q)
+    assert torch.isfinite(cap_loss) and torch.isfinite(value_loss)
+    df = RO.precook_corpus(corpus)
+    if train_worker:
+        want, _ = RO.worker_reward(itos, df, tok.cpu().numpy(), targets, gamma)
+        assert np.abs(score.cpu().numpy() - want).max() <= 1e-6
+        db2 = {k: v for k, v in db.items() if k != "trg_caption"}
+        db2["score"] = torch.from_numpy(want).cuda()
+        cap2, val2, tok2, score2, div2 = tr.rl_losses(db2, True, False, q)
+        assert torch.equal(tok2, tok)
+        assert rel(cap2, cap_loss) < 1e-4 and rel(val2, value_loss) < 1e-4 and rel(div2, div) < 1e-4
+    else:
+        from bmhrl_b200.model.masking import make_masks
+        cin = db["caption"][:, :-1]
+        with torch.no_grad():
+            seg = model(((db["rgb"], db["flow"]), db["audio"]), cin, make_masks(db, cin, "audio_video", PAD))[4]
+        sec = (seg.cpu().numpy() != 0).astype(np.int64)
+        want = RO.manager_reward(itos, df, tok.cpu().numpy(), targets, sec, gamma)  # closes `sec` in place
+        for r, t in enumerate(targets):
+            e = len(t.split())
+            assert sec[r, e] == 1 and not sec[r, e + 1:].any()
+        assert np.abs(score.cpu().numpy() - want * sec).max() <= 1e-6
+    cap_loss.backward()
+    value_loss.backward()
