@@ -118,6 +118,27 @@ def test_greedy_decode_golden(gpu_lib, golden, agent_sd):
     assert rel(last[:, :, ::101], g["last_slice_fp16in"]) < TOL
 
 
+def test_greedy_decode_encode_once_matches_full_recompute(gpu_lib, golden, agent_sd):
+    """The encode-once decoder (encoder run once, vocabulary projection for the last position only) generates the
+    golden tokens of config 1 and the same last-position log-probabilities as the full-recompute decoder; also on a
+    ragged B=3 batch."""
+    from bmhrl_b200.decode import greedy_decoder, greedy_decoder_cached
+    g = golden["greedy"]
+    model, _ = build_agent(agent_sd)
+    model.eval()
+    model.set_inference_mode(True)
+    fs = {"rgb": g["rgb"].float().cuda(), "flow": g["flow"].float().cuda(), "audio": g["audio"].float().cuda()}
+    trg, last = greedy_decoder_cached(model, fs, g["max_len"], 2, 3, PAD, "audio_video", return_last=True)
+    assert torch.equal(trg.cpu(), g["tokens_fp16in"])
+    assert rel(last[:, :, ::101], g["last_slice_fp16in"]) < TOL
+    b = synth.synthetic_batch(B=3, Sv=9, Sa=20, L=6, V=VOC, seed=21, ragged=True)
+    fs = {k: b[k].cuda() for k in ("rgb", "flow", "audio")}
+    t0, l0 = greedy_decoder(model, fs, 7, 2, 3, PAD, "audio_video", return_last=True)
+    t1, l1 = greedy_decoder_cached(model, fs, 7, 2, 3, PAD, "audio_video", return_last=True)
+    assert torch.equal(t0, t1)
+    assert rel(l1, l0) < 1e-4
+
+
 def test_warmstart_step_matches_oracle_adam(gpu_lib, golden, agent_sd):
     """Two full warm-start steps (fwd + LabelSmoothing + bwd + fused Adam) vs oracle autograd + oracle Adam."""
     from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
