@@ -1,0 +1,63 @@
+"""Config 1 (single-clip greedy captioning, B=1, Sv=14, Sa=36, 30 generated tokens, random-init BMHRL): tokens/s of the
+full-recompute decoder (the reference's algorithm, captioning_bmrl_loops.py:127-152) and of the encode-once decoder,
+timed with CUDA events on the current stream.  Prints one JSON line.
+
+    python tools/bench_decode.py [--B 1] [--tokens 30] [--reps 5]
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--B", type=int, default=1)
+    ap.add_argument("--tokens", type=int, default=30)
+    ap.add_argument("--reps", type=int, default=5)
+    a = ap.parse_args()
+    from bmhrl_b200 import ops, synth
+    from bmhrl_b200.decode import greedy_decoder, greedy_decoder_cached
+    from conftest import PAD, VOC, build_agent
+    golden = torch.load(os.path.join(ROOT, "tests", "golden", "reference_golden.pt"), weights_only=False)
+    sd = synth.fill_state_dict(golden["agent_shapes"], seed=1234)
+    model, _ = build_agent(sd)
+    model.eval()
+    model.set_inference_mode(True)
+    b = synth.synthetic_batch(B=a.B, Sv=14, Sa=36, L=6, V=VOC, seed=3)
+    fs = {k: b[k].cuda() for k in ("rgb", "flow", "audio")}
+    out = {"metric": "greedy_decode_tokens_per_sec", "unit": "tokens/s",
+           "config": {"workload": f"config 1 shape: B={a.B}, Sv=14, Sa=36, {a.tokens} generated tokens, V={VOC}, "
+                                  f"random-init BMHRL, end token disabled so every run generates {a.tokens} tokens"}}
+    for mode in ("fp32", "tf32"):
+        ops.set_math_mode(mode)
+        res = {}
+        toks = {}
+        for name, fn in (("full_recompute", greedy_decoder), ("encode_once", greedy_decoder_cached)):
+            run = lambda: fn(model, fs, a.tokens, 2, -1, PAD, "audio_video")
+            for _ in range(2):
+                toks[name] = run()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(a.reps):
+                run()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / a.reps
+            res[name] = {"ms_per_caption": ms, "tokens_per_s": 1e3 * a.B * a.tokens / ms}
+        res["same_tokens"] = bool(torch.equal(toks["full_recompute"], toks["encode_once"]))
+        res["speedup"] = res["full_recompute"]["ms_per_caption"] / res["encode_once"]["ms_per_caption"]
+        out[mode] = res
+    ops.set_math_mode("fp32")
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
