@@ -196,6 +196,57 @@ void score_row(const Cider& c, const long long* pred, int L, const int* tok_off,
     for (int l = n_scored; l < L; ++l) rewards[l] = last;  // F.pad(..., scores[last_symbol]) :56-59
 }
 
+struct BleuScratch {
+    OrderedMap<int> ref[kMaxN];   // n-gram -> count in the (single) reference (cook_refs_bleu maxcounts)
+    OrderedMap<int> hyp[kMaxN];
+    std::vector<int> hw;
+};
+
+// One row of BleuScorer._bleu_diff (metrics/bleu.py:26-59): BLEU-1..n of every prefix against ONE reference,
+// compute_score (:216-279) with option "average" (one reference), averaged with weights 1/n in fp32 (:276-278).
+// Unlike the CIDEr variant the prefix loop does not stop at "</s>".
+void bleu_row(int N, const long long* pred, int L, const int* tok_off, const int* tok_words, const int* rw, int R,
+              float* rewards, BleuScratch& s) {
+    for (int n = 0; n < N; ++n) {
+        s.ref[n].reserve_pow2((size_t)std::max(R, 1));
+        for (int i = 0; i + n + 1 <= R; ++i) s.ref[n].vals[s.ref[n].find_or_insert(make_key(rw + i, n + 1))] += 1;
+        s.hyp[n].reserve_pow2((size_t)std::max(L, 1));
+    }
+    const double small = 1e-9, tiny = 1e-15;
+    const double reflen = (double)R / 1.0;  // float(sum(reflens)) / len(reflens)
+    long long correct[kMaxN] = {0, 0, 0, 0};
+    s.hw.clear();
+    for (int l = 0; l < L; ++l) {
+        long long t = pred[l];
+        for (int wi = tok_off[t]; wi < tok_off[t + 1]; ++wi) {
+            s.hw.push_back(tok_words[wi]);
+            const int m = (int)s.hw.size();
+            for (int n = 0; n < N && n + 1 <= m; ++n) {
+                Key k = make_key(s.hw.data() + (m - n - 1), n + 1);
+                int32_t r = s.ref[n].find(k);
+                int c = (s.hyp[n].vals[s.hyp[n].find_or_insert(k)] += 1);
+                if (r >= 0 && c <= s.ref[n].vals[r]) correct[n] += 1;  // sum of min(refmax, count) grows by one
+            }
+        }
+        const int testlen = (int)s.hw.size();
+        double bleu = 1.0, bleus[kMaxN];
+        for (int k = 0; k < N; ++k) {
+            double guess = (double)std::max(0, testlen - k);
+            bleu *= ((double)correct[k] + tiny) / (guess + small);
+            bleus[k] = std::pow(bleu, 1.0 / (double)(k + 1));
+        }
+        const double ratio = ((double)testlen + tiny) / (reflen + small);
+        if (ratio < 1.0) {
+            const double bp = std::exp(1.0 - 1.0 / ratio);
+            for (int k = 0; k < N; ++k) bleus[k] *= bp;
+        }
+        const float w = (float)(1.0 / (double)N);
+        float acc = 0.0f;
+        for (int k = 0; k < N; ++k) acc = acc + (float)bleus[k] * w;
+        rewards[l] = acc;
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -295,6 +346,43 @@ int bmhrl_cider_prefix_rewards(void* scorer, const long long* pred, int B, int L
         return 0;
     } catch (const std::exception& e) {
         return fail(-3, std::string("bmhrl_cider_prefix_rewards: ") + e.what());
+    }
+}
+
+int bmhrl_bleu_prefix_rewards(const long long* pred, int B, int L, const int* tok_off, const int* tok_words, int n_tok,
+                              const int* ref_words, const long long* ref_off, int n, float* rewards, float* delta,
+                              int n_threads) {
+    if (n < 1 || n > kMaxN) return fail(-1, "bmhrl_bleu_prefix_rewards: n must be in 1..4");
+    if (B < 0 || L < 1) return fail(-1, "bmhrl_bleu_prefix_rewards: need B >= 0, L >= 1");
+    if (B == 0) return 0;
+    if (!pred || !tok_off || !ref_off || !rewards || !delta) return fail(-1, "bmhrl_bleu_prefix_rewards: null argument");
+    for (long long i = 0; i < (long long)B * L; ++i)
+        if (pred[i] < 0 || pred[i] >= n_tok) return fail(-2, "bmhrl_bleu_prefix_rewards: token id outside the vocabulary");
+    try {
+        int hw = (int)std::thread::hardware_concurrency();
+        int T = n_threads > 0 ? n_threads : std::max(1, std::min(hw > 0 ? hw : 1, B / 8));
+        T = std::min(T, B);
+        auto work = [&](int b0, int b1) {
+            BleuScratch s;
+            for (int b = b0; b < b1; ++b) {
+                float* rw = rewards + (size_t)b * L;
+                bleu_row(n, pred + (size_t)b * L, L, tok_off, tok_words, ref_words + ref_off[b],
+                         (int)(ref_off[b + 1] - ref_off[b]), rw, s);
+                float* d = delta + (size_t)b * L;
+                d[0] = rw[0];
+                for (int l = 1; l < L; ++l) d[l] = rw[l] - rw[l - 1];  // fp32 tensors in the reference (:52-53)
+            }
+        };
+        if (T <= 1) {
+            work(0, B);
+        } else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < T; ++t) th.emplace_back(work, (int)((long long)B * t / T), (int)((long long)B * (t + 1) / T));
+            for (auto& x : th) x.join();
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        return fail(-3, std::string("bmhrl_bleu_prefix_rewards: ") + e.what());
     }
 }
 

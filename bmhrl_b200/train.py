@@ -32,12 +32,16 @@ def used_parameters(model):
 
 
 def get_score(train_worker, scorer, predicted_tokens, caption, mask, segments):
-    """captioning_bmrl_loops.py:219-230 for the CIDEr scorer (METEOR needs nltk + WordNet, BLEU: not built)."""
-    if scorer.type != "CIDER":
-        raise NotImplementedError(f"scorer type {scorer.type!r}: only the CIDEr reward scorer is implemented")
-    if train_worker:
-        return scorer.delta_cider_worker(predicted_tokens, caption)
-    return scorer.delta_cider_manager(predicted_tokens, caption, mask, segments)
+    """captioning_bmrl_loops.py:219-230 for the CIDEr and BLEU scorers (METEOR needs nltk + WordNet: not built)."""
+    if scorer.type == "CIDER":
+        if train_worker:
+            return scorer.delta_cider_worker(predicted_tokens, caption)
+        return scorer.delta_cider_manager(predicted_tokens, caption, mask, segments)
+    if scorer.type == "BLEU":
+        if train_worker:
+            return scorer.delta_bleu_worker(predicted_tokens, caption)
+        return scorer.delta_bleu_manager(predicted_tokens, caption, mask, segments)
+    raise NotImplementedError(f"scorer type {scorer.type!r}: the CIDEr and BLEU reward scorers are implemented")
 
 
 class BMHRLTrainer:

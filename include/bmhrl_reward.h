@@ -45,6 +45,14 @@ int bmhrl_cider_prefix_rewards(void* scorer, const long long* pred, int B, int L
                                const int* tok_words, const unsigned char* tok_is_end, int n_tok, const int* ref_words,
                                const long long* ref_off, double* rewards, float* delta, int n_threads);
 
+/* metrics/bleu.py:26-59 BleuScorer._bleu_diff (BleuScorerObj.compute_score :216-279 for one hypothesis / one
+ * reference, option "average"): BLEU-1..n of every prefix, brevity penalty exp(1 - 1/ratio), mean over the orders
+ * in fp32.  The prefix loop does NOT stop at "</s>".  tok_off / tok_words: CSR of vocab.itos[t].lower().split();
+ * ref_words / ref_off: CSR of target[b].lower().split().  rewards, delta: (B, L) float. */
+int bmhrl_bleu_prefix_rewards(const long long* pred, int B, int L, const int* tok_off, const int* tok_words, int n_tok,
+                              const int* ref_words, const long long* ref_off, int n, float* rewards, float* delta,
+                              int n_threads);
+
 /* metrics/util.py:56-66 discontinue_reward(cider_diff, gamma, n_step) without segments:
  * out[b, l] = sum_{i < n_step} fl32(gamma^i) * diff[b, l+i], accumulated in fp32 in the reference's order. */
 int bmhrl_discount_rewards(const float* diff, int B, int L, double gamma, int n_step, float* out);

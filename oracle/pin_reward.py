@@ -23,7 +23,7 @@ WORDS = ("a man is jumping over the long bar and lands in sand woman runs down t
 
 
 def make_vocab():
-    itos = ["<unk>", "<pad>", "<s>", "</s>"] + sorted(set(WORDS)) + [" ", "n't"]
+    itos = ["<unk>", "<pad>", "<s>", "</s>"] + sorted(set(WORDS)) + [" ", "n't", "Sand"]
     return itos
 
 
@@ -44,7 +44,7 @@ def main():
     if refboot.REF_ROOT not in sys.path:
         sys.path.insert(0, refboot.REF_ROOT)
     with refboot.sink():
-        from metrics import cider as rcider, util as rutil, batched_meteor as rbm
+        from metrics import cider as rcider, util as rutil, batched_meteor as rbm, bleu as rbleu
     rng = random.Random(20261104)
     torch.manual_seed(7)
     itos = make_vocab()
@@ -93,6 +93,14 @@ def main():
             entry[f"sections_in_{name}"] = sec_in
             entry[f"sections_out_{name}"] = sections.clone()
             entry[f"manager_score_{name}"] = m_score.clone()
+        # BLEU scorer on the same predictions (metrics/bleu.py); "Mixed Case" vocabulary entries are lower()ed there
+        with refboot.sink():
+            bl = rbleu.BleuScorer(vocab, "cpu", gamma, gamma)
+            bw, br = bl.delta_bleu_worker(pred.clone(), list(targets))
+            sec_b = entry["sections_in_bool"].clone()
+            bm, _ = bl.delta_bleu_manager(pred.clone(), list(targets), None, sec_b)
+        assert torch.equal(sec_b, entry["sections_in_bool"])
+        entry.update({"bleu_worker_score": bw.clone(), "bleu_rewards": br.clone(), "bleu_manager_score": bm.clone()})
         g["cases"].append(entry)
         # df table spot checks
         if case == 0:

@@ -11,6 +11,9 @@ Follows, function by function:
   discount_segments         metrics/util.py:67-88 (discontinue_reward with segments, in place, quirks kept)
   close_sections            metrics/cider.py:74-77 (delta_cider_manager's in-place edit of `sections`)
   worker_reward / manager_reward   metrics/cider.py:72-109
+  bleu_pair                 metrics/util.py:6-15, :93-139 + metrics/bleu.py:216-279 (ONE hypothesis / ONE reference)
+  bleu_prefix_rewards       metrics/bleu.py:26-59 (_bleu_diff; no stop at "</s>", fp32 rewards)
+  bleu_worker_reward / bleu_manager_reward   metrics/bleu.py:61-92 (the segment variant discounts WITHOUT segments)
 
 Pinned against the UNMODIFIED reference by oracle/pin_reward.py -> tests/golden/reward_golden.pt
 (tests/test_reward_scorer.py::test_oracle_matches_reference_golden).
@@ -149,3 +152,47 @@ def manager_reward(itos, df, pred, targets, sections, gamma, n=4, sigma=6.0):
     step, _ = worker_reward(itos, df, pred, targets, gamma, n, sigma)
     seg = segment_sums(step, sections)
     return discount_segments(seg, sections, gamma)
+
+
+def bleu_pair(hyp_words, ref_words, n=4):
+    ref = ngram_counts(ref_words, n)
+    hyp = ngram_counts(hyp_words, n)
+    testlen, reflen = len(hyp_words), float(len(ref_words)) / 1
+    correct = [0] * n
+    for g, c in hyp.items():
+        correct[len(g) - 1] += min(ref.get(g, 0), c)
+    small, tiny = 1e-9, 1e-15
+    bleus, bleu = [], 1.
+    for k in range(n):
+        bleu *= float(correct[k] + tiny) / (max(0, testlen - k) + small)
+        bleus.append(bleu ** (1. / (k + 1)))
+    ratio = (testlen + tiny) / (reflen + small)
+    if ratio < 1:
+        bleus = [b * math.exp(1 - 1 / ratio) for b in bleus]
+    acc = np.float32(0)
+    for b in bleus:  # torch.sum(torch.tensor(bleus) * torch.tensor(1 / n)) in fp32
+        acc = np.float32(acc + np.float32(np.float32(b) * np.float32(1 / n)))
+    return acc
+
+
+def bleu_prefix_rewards(itos, pred, targets, n=4):
+    pred = np.asarray(pred)
+    B, L = pred.shape
+    rewards = np.zeros((B, L), dtype=np.float32)
+    for b in range(B):
+        hypo = [itos[int(t)] for t in pred[b]]
+        ref = targets[b].lower().split()
+        for l in range(L):
+            rewards[b, l] = bleu_pair(" ".join(hypo[:l + 1]).lower().split(), ref, n)
+    delta = np.concatenate([rewards[:, :1], rewards[:, 1:] - rewards[:, :-1]], axis=1).astype(np.float32)
+    return delta, rewards
+
+
+def bleu_worker_reward(itos, pred, targets, gamma, n=4):
+    delta, rewards = bleu_prefix_rewards(itos, pred, targets, n)
+    return discount(delta, gamma), rewards
+
+
+def bleu_manager_reward(itos, pred, targets, sections, gamma, n=4):
+    step, _ = bleu_worker_reward(itos, pred, targets, gamma, n)
+    return discount(segment_sums(step, sections), gamma)
