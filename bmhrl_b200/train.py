@@ -192,8 +192,9 @@ class BMHRLTrainer:
         return loss.detach()
 
     # ---- RL step -----------------------------------------------------------------------------------------------------
-    def rl_losses(self, batch, train_worker, stabilize=False, exp_noise=None):
-        """Forward part of train_bimodal_bl (:843-862, :873-875): returns (cap_loss, value_loss, tokens, score)."""
+    def rl_forward(self, batch, train_worker, exp_noise=None):
+        """First half of the RL step, up to the sampled tokens (:843-858, biased_kl() :271-285): everything the host
+        reward scorer needs.  Returns the state `rl_tail` continues from."""
         x, cap_in, y, masks = self._inputs(batch)
         n_tokens = self._global_tokens_early(y)
         pred, worker_feat, manager_feat, goal_feat, seg = self.cap_model(x, cap_in, masks)
@@ -201,26 +202,22 @@ class BMHRLTrainer:
         n_tokens = n_tokens()
         if train_worker:
             ev = self.wv_model((worker_feat.detach(), goal_feat.detach())).squeeze(-1)
-        else:
-            ev = self.mv_model(manager_feat.detach()).squeeze(-1)
-        # biased_kl() :271-334
-        lm = loss_mask.to(pred.dtype)
-        expected = ev.detach()
-        if train_worker:
             mode = "noise" if exp_noise is not None else "philox"
             tok, sp = ops.sample_tokens(pred, mode, exp_noise, salt=self._sample_salt())
         else:
+            ev = self.mv_model(manager_feat.detach()).squeeze(-1)
             tok, sp = ops.sample_tokens(pred, "argmax")
-        if self.scorer is not None and "trg_caption" in batch:
-            # get_score() :219-230, :287 on the host (libbmhrl_reward.so): D2H of the (B, L) tokens, H2D of the scores.
-            # Not graph-capturable (host round trip); the reference's manager scorer closes `segments` in place at the
-            # reference caption length (metrics/cider.py:74-77) and every later use sees that edit -- done on a copy
-            # here because the forward pass has saved `seg` for backward.
-            seg = seg.clone()
-            score = get_score(train_worker, self.scorer, tok, batch["trg_caption"], loss_mask, seg)[0]
-            score = score.to(pred.device, pred.dtype)
-        else:
-            score = batch["score"].to(pred.dtype)
+        return {"pred": pred, "y": y, "loss_mask": loss_mask, "n_tokens": n_tokens, "ev": ev, "seg": seg, "tok": tok,
+                "sp": sp}
+
+    def rl_tail(self, st, score, seg, train_worker, stabilize=False):
+        """Second half (biased_kl() :287-334, value function :873-875) given the (B, L) scores and the segment labels
+        the scorer left behind.  Returns (cap_loss, value_loss, tokens, score, divergence row sums)."""
+        pred, y, loss_mask, n_tokens, ev, tok, sp = (st[k] for k in ("pred", "y", "loss_mask", "n_tokens", "ev", "tok",
+                                                                      "sp"))
+        score = score.to(pred.dtype)
+        lm = loss_mask.to(pred.dtype)
+        expected = ev.detach()
         if train_worker:
             norm = lm.sum(-1, keepdim=True)
         else:
@@ -239,6 +236,26 @@ class BMHRLTrainer:
         value_loss = (((ev_used - score.detach()) ** 2) * vmask).mean()
         return cap_loss, value_loss, tok, score.detach(), div.detach()
 
+    def host_score(self, tok, seg, loss_mask, trg_caption, train_worker):
+        """get_score() :219-230, :287 on the host (libbmhrl_reward.so): D2H of the (B, L) tokens (and of the segment
+        labels for the manager), H2D of the scores.  The reference's manager scorer closes `segments` in place at the
+        reference caption length (metrics/cider.py:74-77) and every later use sees that edit; it is done on a copy
+        here because the forward pass has saved `seg` for backward.  Returns (score, seg) on tok's device."""
+        seg_h = seg.detach().to("cpu")
+        score = get_score(train_worker, self.scorer, tok.detach().to("cpu"), trg_caption, loss_mask, seg_h)[0]
+        return score.to(tok.device), seg_h.to(seg.device)
+
+    def rl_losses(self, batch, train_worker, stabilize=False, exp_noise=None):
+        """Forward part of train_bimodal_bl (:843-862, :873-875): returns (cap_loss, value_loss, tokens, score, div).
+        With a scorer and batch["trg_caption"] the sampled tokens are scored on the host (not graph-capturable as one
+        piece: `ScoredStepRunner` splits the step around the host call)."""
+        st = self.rl_forward(batch, train_worker, exp_noise)
+        if self.scorer is not None and "trg_caption" in batch:
+            score, seg = self.host_score(st["tok"], st["seg"], st["loss_mask"], batch["trg_caption"], train_worker)
+        else:
+            score, seg = batch["score"], st["seg"]
+        return self.rl_tail(st, score, seg, train_worker, stabilize)
+
     def _sample_salt(self):
         if not hasattr(self, "_ssalt"):
             self._ssalt = ops.next_salt()
@@ -246,11 +263,17 @@ class BMHRLTrainer:
 
     def rl_step(self, batch, train_worker, stabilize=False, exp_noise=None):
         """captioning_bmrl_loops.py:837-877.  Returns (cap_loss, value_loss) device scalars."""
-        ops.new_rng_epoch(batch["rgb"].device)
-        vopt = self.wv_opt if train_worker else self.mv_opt
-        self.cap_opt.zero_grad()
-        vopt.zero_grad()
+        self.rl_begin(batch, train_worker)
         cap_loss, value_loss, _, _, _ = self.rl_losses(batch, train_worker, stabilize, exp_noise)
+        return self.rl_finish(cap_loss, value_loss, train_worker)
+
+    def rl_begin(self, batch, train_worker):
+        ops.new_rng_epoch(batch["rgb"].device)
+        self.cap_opt.zero_grad()
+        (self.wv_opt if train_worker else self.mv_opt).zero_grad()
+
+    def rl_finish(self, cap_loss, value_loss, train_worker):
+        vopt = self.wv_opt if train_worker else self.mv_opt
         cap_loss.backward()
         ops.join_side_streams(cap_loss.device)
         self._sync_and_step(self.cap_opt)
@@ -303,6 +326,97 @@ class StepRunner:
             self.graph.replay()
         else:
             self.out = self._eager()
+        return self.out
+
+    def step(self, host_batch):
+        self.load(host_batch)
+        return self.replay()
+
+
+class ScoredStepRunner:
+    """The RL step with the REAL reward scorer in the loop (captioning_bmrl_loops.py:837-877 as the reference runs it):
+    two CUDA graphs around one host call.
+
+        graph A   H2D'd batch -> forward, value function, token sampling           (static outputs: tokens, segments)
+        host      D2H tokens (+ segments) -> libbmhrl_reward.so CIDEr / BLEU rewards -> H2D scores (+ closed segments)
+        graph B   biased-KL loss, backward, all-reduce, Adam, value-function step  (reads the static score buffers)
+
+    The autograd graph built while capturing A is consumed while capturing B; both captures share one memory pool, so
+    the saved activations of A stay at fixed addresses.  Replays must alternate A, B like the captures did."""
+
+    def __init__(self, trainer, kind, example_batch, stabilize=False, use_graph=True, warmup=3):
+        if trainer.scorer is None:
+            raise RuntimeError("ScoredStepRunner needs BMHRLTrainer(scorer=...)")
+        if kind not in ("worker", "manager"):
+            raise ValueError("ScoredStepRunner runs the worker or the manager RL step")
+        self.trainer, self.kind, self.stabilize = trainer, kind, stabilize
+        self.train_worker = kind == "worker"
+        dev = next(trainer.cap_model.parameters()).device
+        self.static = {k: torch.empty_like(v, device=dev).copy_(v) for k, v in example_batch.items()
+                       if k in ("rgb", "flow", "audio", "caption")}
+        self.captions = list(example_batch["trg_caption"])
+        self.use_graph = use_graph
+        self.graph_a = self.graph_b = None
+        self.score_buf = self.seg_buf = None
+        self.scorer_seconds = 0.0
+        if not use_graph:
+            return
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        from ._lib import launch_count
+        n0 = launch_count()
+        self.graph_a = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph_a):
+            trainer.rl_begin(self.static, self.train_worker)
+            self.st = trainer.rl_forward(self.static, self.train_worker)
+            ops.join_side_streams(dev)
+            self.tok_out = self.st["tok"]
+            self.seg_out = self.st["seg"]
+        torch.cuda.synchronize(dev)
+        B, L = self.tok_out.shape
+        self.score_buf = torch.zeros(B, L, device=dev, dtype=self.st["pred"].dtype)
+        self.seg_buf = torch.zeros_like(self.seg_out)   # filled by the host part of every replay
+        self.graph_b = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph_b, pool=self.graph_a.pool()):
+            losses = trainer.rl_tail(self.st, self.score_buf, self.seg_buf, self.train_worker, self.stabilize)
+            self.out = trainer.rl_finish(losses[0], losses[1], self.train_worker)
+        self.captured_launches = launch_count() - n0
+        del self.st  # the autograd graph has been consumed by the capture of B
+
+    def _host_part(self):
+        import time
+        t = self.trainer
+        tok_h = self.tok_out  # .to("cpu") inside host_score synchronises with graph A
+        t0 = time.perf_counter()
+        score, seg = t.host_score(tok_h, self.seg_out, None, self.captions, self.train_worker)
+        self.scorer_seconds = time.perf_counter() - t0
+        self.score_buf.copy_(score, non_blocking=True)
+        self.seg_buf.copy_(seg, non_blocking=True)
+
+    def _eager(self):
+        t = self.trainer
+        b = dict(self.static)
+        b["trg_caption"] = self.captions
+        return t.rl_step(b, self.train_worker, self.stabilize)
+
+    def load(self, host_batch, non_blocking=True):
+        for k, buf in self.static.items():
+            buf.copy_(host_batch[k], non_blocking=non_blocking)
+        if "trg_caption" in host_batch:
+            self.captions = list(host_batch["trg_caption"])
+
+    def replay(self):
+        if not self.use_graph:
+            self.out = self._eager()
+            return self.out
+        self.graph_a.replay()
+        self._host_part()
+        self.graph_b.replay()
         return self.out
 
     def step(self, host_batch):

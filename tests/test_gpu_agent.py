@@ -2,6 +2,7 @@
 golden vectors produced by the UNMODIFIED reference, plus CUDA-graph and size-independent property checks."""
 from types import SimpleNamespace as NS
 
+import numpy as np
 import pytest
 import torch
 
@@ -339,3 +340,58 @@ def test_rl_losses_with_host_cider_scorer(gpu_lib, golden, agent_sd, train_worke
         assert np.abs(score.cpu().numpy() - want * sec).max() <= 1e-6
     cap_loss.backward()
     value_loss.backward()
+
+
+@pytest.mark.parametrize("kind", ["worker", "manager"])
+def test_scored_step_two_graphs_equals_eager(gpu_lib, golden, agent_sd, kind):
+    """ScoredStepRunner (graph A: forward + sampling | host CIDEr scorer | graph B: loss, backward, Adam) takes the
+    same two training steps as the eager scored step: same losses, same parameters afterwards."""
+    from bmhrl_b200.metrics import CiderScorer
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, ScoredStepRunner
+    from bmhrl_b200 import ops
+    B, L, gamma = 4, 9, 0.9
+    itos = ["<unk>", "<pad>", "<s>", "</s>"] + [f"w{i}" for i in range(4, VOC)]
+    batches = []
+    for seed in (11, 12):
+        b = synth.synthetic_batch(B=B, Sv=6, Sa=10, L=L, V=VOC, seed=seed)
+        words = [[itos[int(t)] for t in row[1:] if int(t) not in (PAD, 2, 3)][: L - 3] for row in b["caption"]]
+        b["trg_caption"] = [" ".join(w) for w in words]
+        batches.append(b)
+    corpus = [c.split() for b in batches for c in b["trg_caption"]] * 2
+
+    def run(use_graph):
+        model, cfg = build_agent(agent_sd)
+        wv, mv = BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda()
+        vsd = synth.fill_state_dict(golden["value_fn_shapes"], seed=3)
+        wv.load_state_dict(vsd)
+        mv.load_state_dict(vsd)
+        scorer = CiderScorer(NS(itos=itos), corpus, "cuda", gamma, gamma)
+        tr = BMHRLTrainer(model, wv, mv, pad_idx=PAD, smoothing=SMOOTH, scorer=scorer)
+        if kind == "worker":
+            tr.teach_worker()
+        else:
+            tr.teach_manager()
+            model.manager.exploration = False
+        ops.manual_seed(77)   # same device RNG stream and the same lazily drawn salts in both runs
+        ops.RNG.salt = 0
+        # one eager step in both runs (lazily created workspaces / salts settle before the capture); the runner's own
+        # warm-up stays off so that both runs have taken the same number of steps
+        tr.rl_step({**_dev({k: v for k, v in batches[1].items() if k != "trg_caption"}),
+                    "trg_caption": batches[1]["trg_caption"]}, kind == "worker")
+        torch.cuda.synchronize()
+        runner = ScoredStepRunner(tr, kind, batches[0], use_graph=use_graph, warmup=0)
+        losses = []
+        for b in batches:
+            out = runner.step(b)
+            losses.append([float(o) for o in out])
+        torch.cuda.synchronize()
+        flat = torch.cat([p.detach().flatten() for p in model.parameters() if p.requires_grad]).clone()
+        return losses, flat
+
+    l_graph, p_graph = run(True)
+    l_eager, p_eager = run(False)
+    assert all(np.isfinite(v) for l in l_graph + l_eager for v in l)
+    for a, c in zip(l_graph, l_eager):
+        assert abs(a[0] - c[0]) <= 1e-4 * abs(c[0]) + 1e-7 and abs(a[1] - c[1]) <= 1e-4 * abs(c[1]) + 1e-7, (l_graph, l_eager)
+    assert rel(p_graph, p_eager) < 1e-5
