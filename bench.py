@@ -342,7 +342,26 @@ def run_gpu(args):
     eager.replay()
     per_step_gemms, ops.RECORD = ops.RECORD, None
     del eager
-    runner = StepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
+    if args.scorer:
+        # the REAL reward scorer in the loop: synthetic vocabulary, a 37k-caption Zipf
+        # corpus for the document frequencies, the batch's own captions as references; two graphs around the host call
+        import random
+        from bmhrl_b200.metrics import BleuScorer, CiderScorer
+        from bmhrl_b200.train import ScoredStepRunner
+        if args.workload == "warmstart":
+            raise SystemExit("--scorer needs --workload worker|manager (the warm-start step has no rewards)")
+        itos = ["<unk>", "<pad>", "<s>", "</s>"] + [f"w{i}" for i in range(4, VOC)]
+        rng = random.Random(99)
+        corpus = [[itos[4 + min(int(rng.paretovariate(1.1)) - 1, VOC - 5)] for _ in range(rng.randint(6, 22))]
+                  for _ in range(37421)]
+        for b in host:
+            b["trg_caption"] = [" ".join(itos[int(t)] for t in row[1:] if int(t) > 3) for row in b["caption"]]
+            b["trg_caption"] = [" ".join(c.split()[:SHAPE["L"] - 2]) for c in b["trg_caption"]]
+        tr.scorer = (CiderScorer(NS(itos=itos), corpus, "cpu", 0.9, 0.9) if args.scorer == "cider"
+                     else BleuScorer(NS(itos=itos), "cpu", 0.9, 0.9))
+        runner = ScoredStepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
+    else:
+        runner = StepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
 
     def barrier():
         if world > 1:
@@ -415,6 +434,11 @@ def run_gpu(args):
             "attention_roofline": attention_roofline(pk),
             "loss": last,
         }
+        if args.scorer:
+            line["config"]["scorer"] = (f"{args.scorer} reward scorer in the loop (libbmhrl_reward.so on the host between "
+                                        f"graph A forward+sampling and graph B loss+backward+Adam); tokens D2H, scores H2D")
+            line["host_part_ms_last_step"] = runner.scorer_seconds * 1e3  # D2H wait for graph A + scorer + H2D enqueue
+            line["e2e"]["d2h_bytes_per_step"] = 4 + 8 * SHAPE["B"] * SHAPE["L"] + 4 * SHAPE["B"] * SHAPE["L"]
         if cpu_med is not None:
             line["cpu_baseline"] = {"value": SHAPE["B"] / cpu_med, "unit": "clips/s", "cores": cpu_threads,
                                     "kind": "port",
@@ -449,6 +473,8 @@ def main():
                     help="tf32: tcgen05 tensor-core GEMMs (default); fp32: exact SIMT contractions")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--scorer", default=None, choices=["cider", "bleu"],
+                    help="RL workloads: score the sampled tokens with the real host reward scorer inside the step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
