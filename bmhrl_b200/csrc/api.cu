@@ -17,6 +17,23 @@ extern "C" long long bmhrl_launch_count(void) { return g_launches.load(std::memo
 extern "C" void bmhrl_reset_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
 extern "C" int bmhrl_abi_version(void) { return BMHRL_ABI_VERSION; }
 
+// A new non-blocking stream on the current device with a handle no other stream shares (see the header).  Never
+// destroyed: the host layer keeps its side streams for the life of the process.
+extern "C" int bmhrl_stream_create(void** stream) {
+    if (!stream) {
+        bmhrl_set_error("bmhrl_stream_create: null pointer");
+        return BMHRL_ERR_ARG;
+    }
+    cudaStream_t s = nullptr;
+    cudaError_t e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        bmhrl_set_error(cudaGetErrorString(e));
+        return BMHRL_ERR_CUDA;
+    }
+    *stream = (void*)s;
+    return BMHRL_OK;
+}
+
 // Returns 0 when the current device is a Blackwell sm_100 part this library was built for.
 extern "C" int bmhrl_check_device(void) {
     int dev = 0;

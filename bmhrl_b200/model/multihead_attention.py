@@ -49,6 +49,14 @@ class MultiheadedAttention(nn.Module):
 
         assert self.d_model % H == 0
         self._salts = None
+        # inference extension (bmhrl_b200.decode.GraphedGreedyDecoder): (k, v) = the K / V projections of a fixed
+        # memory, computed once per clip; while it is set, forward() skips linear_K2d / linear_V2d
+        self.memory_kv = None
+
+    def project_memory(self, K, V):
+        """linear_K2d(K), linear_V2d(V): what forward() computes from its K / V arguments before the core."""
+        return (ops.linear(K, self.linear_K2d.weight, self.linear_K2d.bias),
+                ops.linear(V, self.linear_V2d.weight, self.linear_V2d.bias))
 
     def _call_salts(self):
         # dropout call-site ids: fixed per module instance so a CUDA-graph replay and an eager run agree
@@ -65,6 +73,13 @@ class MultiheadedAttention(nn.Module):
         if Q.dim() != 3:
             raise RuntimeError("MultiheadedAttention expects (B, S, D) inputs")
         s_core, s_out = self._call_salts()
+        if self.memory_kv is not None:
+            if self.training:
+                raise RuntimeError("MultiheadedAttention.memory_kv is an inference-only cache")
+            k, v = self.memory_kv
+            q = ops.linear(Q, self.linear_Q2d.weight, self.linear_Q2d.bias)
+            o = ops.mha_core(q, k, v, mask, self.H, causal=causal, drop_p=0.0, salt=s_core)
+            return ops.linear(o, self.linear_d2Q.weight, self.linear_d2Q.bias, resid=resid, drop_p=0.0, salt=s_out)
         # the three projections are independent: concurrent branches (and so are their backward passes)
         q, k, v = ops.parallel(Q.device,
                                lambda: ops.linear(Q, self.linear_Q2d.weight, self.linear_Q2d.bias),

@@ -7,6 +7,8 @@ raises.
 """
 import math
 
+import os
+
 import torch
 
 from ._lib import LIB
@@ -88,6 +90,30 @@ _DIRTY = set()    # side streams that received work since the last join_side_str
 CONCURRENT = True  # False: every branch runs on the caller's stream (debugging / profiling aid)
 
 
+def new_stream(device_index):
+    """A CUDA stream of our own (bmhrl_stream_create), wrapped for torch.  torch.cuda.Stream() draws from a pool of 32
+    handles per device and re-issues them round-robin, so two side streams could be ONE CUDA stream; during graph
+    capture (no record_stream) the caching allocator then re-used a block freed on one branch for an unordered branch
+    that happened to share the handle.  Every fork target of this module has a unique handle instead."""
+    import ctypes
+    h = ctypes.c_void_p()
+    with torch.cuda.device(device_index):
+        LIB.call("bmhrl_stream_create", ctypes.byref(h))
+    return torch.cuda.ExternalStream(h.value, device=device_index)
+
+
+_WARMUP = {}
+
+
+def warmup_stream(device):
+    """One private stream per device for the eager passes that precede a graph capture."""
+    idx = torch.device(device).index
+    idx = torch.cuda.current_device() if idx is None else idx
+    if idx not in _WARMUP:
+        _WARMUP[idx] = new_stream(idx)
+    return _WARMUP[idx]
+
+
 def side_stream(device, slot):
     """Side stream number `slot` of the stream that is current on `device` (created on first use)."""
     dev = torch.device(device)
@@ -95,7 +121,7 @@ def side_stream(device, slot):
     cur = torch.cuda.current_stream(idx)
     key = _SIDE_KEY.get((idx, cur.cuda_stream), (idx, "main")) + (slot,)
     if key not in _SIDE:
-        _SIDE[key] = torch.cuda.Stream(device=idx)
+        _SIDE[key] = new_stream(idx)
         _SIDE_KEY[(idx, _SIDE[key].cuda_stream)] = key
     _DIRTY.add(key)
     return _SIDE[key]
@@ -138,7 +164,7 @@ def wgrad_stream(device):
     _WGRAD_RR[0] ^= 1
     key = (cur.device.index, "wgrad", _WGRAD_RR[0])
     if key not in _SIDE:
-        _SIDE[key] = torch.cuda.Stream(device=cur.device.index)
+        _SIDE[key] = new_stream(cur.device.index)
     _DIRTY.add(key)
     s = _SIDE[key]
     s.wait_stream(cur)

@@ -297,7 +297,7 @@ class StepRunner:
         self.graph = None
         self.out = None
         if use_graph:
-            side = torch.cuda.Stream(device=dev)
+            side = ops.warmup_stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
                 for _ in range(warmup):  # lazily-created salts / workspaces / cuBLAS-free paths settle here
@@ -361,7 +361,7 @@ class ScoredStepRunner:
         self.scorer_seconds = 0.0
         if not use_graph:
             return
-        side = torch.cuda.Stream(device=dev)
+        side = ops.warmup_stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             for _ in range(warmup):

@@ -32,6 +32,12 @@ int bmhrl_check_device(void);             /* 0 iff the current device is sm_100 
 const char* bmhrl_last_error(void);       /* thread-local message of the last failing call */
 long long bmhrl_launch_count(void);       /* kernels launched by this library since the last reset */
 void bmhrl_reset_launch_count(void);
+/* A new non-blocking CUDA stream on the current device (cudaStreamCreateWithFlags).  The host layer forks its
+ * concurrent branches onto streams made here instead of framework-pooled ones: a pool hands the same handle out again
+ * after a few dozen requests, and two "different" side streams that are one CUDA stream defeat the per-stream ownership
+ * the caching allocator relies on while a CUDA graph is being captured (a block freed by one branch was re-used by an
+ * unordered branch).  Replaces nothing in the reference (its nn.DataParallel threads share the default stream). */
+int bmhrl_stream_create(void** stream);
 
 /* ---- math mode ------------------------------------------------------------------------------------------------ */
 /* 0 (default): every contraction in exact fp32 on the SIMT pipes (parity bound 1e-3, in practice ~1e-6).

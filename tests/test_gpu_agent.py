@@ -140,6 +140,77 @@ def test_greedy_decode_encode_once_matches_full_recompute(gpu_lib, golden, agent
     assert rel(l1, l0) < 1e-4
 
 
+@pytest.mark.parametrize("use_graph", [True, False])
+def test_graphed_greedy_decoder_matches_encode_once(gpu_lib, golden, agent_sd, use_graph):
+    """GraphedGreedyDecoder (static zero-padded feature buffers, encoder-memory K/V projected once per clip, one CUDA
+    graph per prefix length, completeness read back every k tokens) generates the golden config-1 caption, the tokens /
+    log-probabilities of the eager encode-once decoder on clips SMALLER than its buffers, stops where the reference
+    loop stops, and re-uses its graphs across clips."""
+    from bmhrl_b200.decode import GraphedGreedyDecoder, greedy_decoder_cached
+    g = golden["greedy"]
+    model, _ = build_agent(agent_sd)
+    model.eval()
+    model.set_inference_mode(True)
+    fs = {"rgb": g["rgb"].float().cuda(), "flow": g["flow"].float().cuda(), "audio": g["audio"].float().cuda()}
+    Sv, Sa = fs["rgb"].shape[1], fs["audio"].shape[1]
+    dec = GraphedGreedyDecoder(model, 1, Sv + 6, Sa + 4, g["max_len"], 2, 3, PAD, use_graph=use_graph, check_every=4)
+    trg, last = dec(fs, return_last=True)
+    assert torch.equal(trg.cpu(), g["tokens_fp16in"])
+    assert rel(last[:, :, ::101], g["last_slice_fp16in"]) < TOL
+    n_graphs = len(dec.graphs)
+    assert (n_graphs > 1) == use_graph
+    # a second, different clip through the same graphs, then the first one again
+    b = synth.synthetic_batch(B=1, Sv=9, Sa=20, L=6, V=VOC, seed=22)
+    fs2 = {k: b[k].cuda() for k in ("rgb", "flow", "audio")}
+    t_ref, l_ref = greedy_decoder_cached(model, fs2, g["max_len"], 2, 3, PAD, "audio_video", return_last=True)
+    t2, l2 = dec(fs2, return_last=True)
+    assert torch.equal(t2, t_ref)
+    assert rel(l2, l_ref) < 1e-4
+    captures = dec.captures
+    trg_again = dec(fs)
+    assert torch.equal(trg_again.cpu(), g["tokens_fp16in"])
+    assert dec.captures == captures  # nothing is captured twice
+    # ragged B=3 batch; end token chosen so that the rows finish at different steps and the loop stops early
+    b = synth.synthetic_batch(B=3, Sv=9, Sa=20, L=6, V=VOC, seed=21, ragged=True)
+    fs3 = {k: b[k].cuda() for k in ("rgb", "flow", "audio")}
+    free_run = greedy_decoder_cached(model, fs3, 9, 2, -1, PAD, "audio_video")
+    for end in (int(free_run[0, 2]), int(free_run[2, 5]), -1):
+        t_ref, l_ref = greedy_decoder_cached(model, fs3, 9, 2, end, PAD, "audio_video", return_last=True)
+        for k in (1, 3, 100):
+            dec3 = GraphedGreedyDecoder(model, 3, 12, 24, 9, 2, end, PAD, use_graph=use_graph, check_every=k)
+            t3, l3 = dec3(fs3, return_last=True)
+            assert torch.equal(t3, t_ref), (end, k)
+            assert rel(l3, l_ref) < 1e-4
+    with pytest.raises(ValueError):
+        dec(fs3)
+
+
+def test_graphed_greedy_decoder_refuses_training_mode(gpu_lib, agent_sd):
+    from bmhrl_b200.decode import GraphedGreedyDecoder
+    model, _ = build_agent(agent_sd)
+    with pytest.raises(RuntimeError):
+        GraphedGreedyDecoder(model, 1, 8, 8, 5, 2, 3, PAD)
+
+
+def test_side_streams_do_not_share_cuda_handles(gpu_lib):
+    """ops forks its concurrent branches onto streams from bmhrl_stream_create: unlike torch.cuda.Stream() (a pool of
+    32 handles per device, re-issued round-robin) no two of them -- and no pooled torch stream -- are the same CUDA
+    stream.  Shared handles let the capture-time allocator hand a block freed on one branch to an unordered branch
+    (the graphed decoder produced other captions once enough streams had been created in the process)."""
+    from bmhrl_b200 import ops
+    mine = [ops.side_stream("cuda:0", 40 + i) for i in range(40)] + [ops.warmup_stream("cuda:0")]
+    handles = [s.cuda_stream for s in ops._SIDE.values()] + [mine[-1].cuda_stream]
+    assert len(set(handles)) == len(handles)
+    pooled = {torch.cuda.Stream(device=0).cuda_stream for _ in range(70)}
+    assert len(pooled) <= 32  # the pool wraps around ...
+    assert not (pooled & set(handles))  # ... and never onto one of ours
+    # streams made by the library work as torch streams: fork / join, and the current-stream lookup of nested forks
+    x = torch.ones(1 << 20, device="cuda")
+    y = ops.parallel("cuda:0", lambda: x * 2, lambda: x * 3, lambda: x * 4)
+    torch.cuda.synchronize()
+    assert [float(t[0]) for t in y] == [2.0, 3.0, 4.0]
+
+
 def test_warmstart_step_matches_oracle_adam(gpu_lib, golden, agent_sd):
     """Two full warm-start steps (fwd + LabelSmoothing + bwd + fused Adam) vs oracle autograd + oracle Adam."""
     from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction

@@ -1,5 +1,6 @@
 """Config 1 (single-clip greedy captioning, B=1, Sv=14, Sa=36, 30 generated tokens, random-init BMHRL): tokens/s of the
-full-recompute decoder (the reference's algorithm, captioning_bmrl_loops.py:127-152) and of the encode-once decoder,
+full-recompute decoder (the reference's algorithm, captioning_bmrl_loops.py:127-152), of the encode-once decoder and of
+the graphed decoder (encoder + memory K/V once per clip, one CUDA-graph replay per token),
 timed with CUDA events on the current stream.  Prints one JSON line.
 
     python tools/bench_decode.py [--B 1] [--tokens 30] [--reps 5]
@@ -23,7 +24,7 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     a = ap.parse_args()
     from bmhrl_b200 import ops, synth
-    from bmhrl_b200.decode import greedy_decoder, greedy_decoder_cached
+    from bmhrl_b200.decode import GraphedGreedyDecoder, greedy_decoder, greedy_decoder_cached
     from conftest import PAD, VOC, build_agent
     golden = torch.load(os.path.join(ROOT, "tests", "golden", "reference_golden.pt"), weights_only=False)
     sd = synth.fill_state_dict(golden["agent_shapes"], seed=1234)
@@ -39,8 +40,11 @@ def main():
         ops.set_math_mode(mode)
         res = {}
         toks = {}
-        for name, fn in (("full_recompute", greedy_decoder), ("encode_once", greedy_decoder_cached)):
-            run = lambda: fn(model, fs, a.tokens, 2, -1, PAD, "audio_video")
+        # graphed: static buffers a little larger than the clip (Sv 16, Sa 40), one completeness read-back per caption
+        dec = GraphedGreedyDecoder(model, a.B, 16, 40, a.tokens, 2, -1, PAD, check_every=a.tokens)
+        for name, fn in (("full_recompute", greedy_decoder), ("encode_once", greedy_decoder_cached),
+                         ("graphed", None)):
+            run = (lambda: dec(fs)) if fn is None else (lambda: fn(model, fs, a.tokens, 2, -1, PAD, "audio_video"))
             for _ in range(2):
                 toks[name] = run()
             torch.cuda.synchronize()
@@ -53,7 +57,10 @@ def main():
             ms = e0.elapsed_time(e1) / a.reps
             res[name] = {"ms_per_caption": ms, "tokens_per_s": 1e3 * a.B * a.tokens / ms}
         res["same_tokens"] = bool(torch.equal(toks["full_recompute"], toks["encode_once"]))
+        res["same_tokens_graphed"] = bool(torch.equal(toks["full_recompute"], toks["graphed"]))
         res["speedup"] = res["full_recompute"]["ms_per_caption"] / res["encode_once"]["ms_per_caption"]
+        res["speedup_graphed"] = res["full_recompute"]["ms_per_caption"] / res["graphed"]["ms_per_caption"]
+        res["graphed_launches_per_caption"] = dec.replays // (2 + a.reps)
         out[mode] = res
     ops.set_math_mode("fp32")
     print(json.dumps(out))
