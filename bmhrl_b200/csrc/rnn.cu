@@ -25,7 +25,8 @@ __global__ void __launch_bounds__(RNN_WARPS * 32) rnn_step_kernel(const float* _
                                                                  const float* __restrict__ W_hh,  // (NG*H,H)
                                                                  const float* __restrict__ b_hh,  // (NG*H)
                                                                  float* __restrict__ out,         // (B,L,H)
-                                                                 float* __restrict__ c,           // (B,H) LSTM only
+                                                                 const float* c_prev,             // (B,H) LSTM only
+                                                                 float* c_next,                   // may be c_prev
                                                                  int B, int L, int H, int t) {
     extern __shared__ float hs[];  // RNN_BT x H
     const int b0 = blockIdx.y * RNN_BT;
@@ -73,9 +74,9 @@ __global__ void __launch_bounds__(RNN_WARPS * 32) rnn_step_kernel(const float* _
         float pf = gxr[H + j] + b_hh[H + j] + mine[1];
         float pg = gxr[2 * H + j] + b_hh[2 * H + j] + mine[2];
         float po = gxr[3 * H + j] + b_hh[3 * H + j] + mine[NG - 1];
-        float cprev = t > 0 ? c[(long long)b * H + j] : 0.f;
+        float cprev = t > 0 ? c_prev[(long long)b * H + j] : 0.f;
         float cn = sigmoid_exact(pf) * cprev + sigmoid_exact(pi) * tanhf(pg);
-        c[(long long)b * H + j] = cn;
+        c_next[(long long)b * H + j] = cn;
         hnew = sigmoid_exact(po) * tanhf(cn);
     } else {
         float r = sigmoid_exact(gxr[j] + mine[0] + b_hh[j]);
@@ -355,16 +356,8 @@ extern "C" int bmhrl_rnn_set_persistent(int on) {
     return BMHRL_OK;
 }
 
-extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out,
-                                   float* ws, int B, int L, int H, void* stream) {
-    BMHRL_CHECK_ARG(cell == 0 || cell == 1, "bmhrl_rnn_layer_f32: cell must be 0 (LSTM) or 1 (GRU)");
-    BMHRL_CHECK_ARG(gx && W_hh && b_hh && out, "bmhrl_rnn_layer_f32: null pointer");
-    BMHRL_CHECK_ARG(cell == 1 || ws, "bmhrl_rnn_layer_f32: LSTM needs the workspace (bmhrl_rnn_ws_floats)");
-    BMHRL_CHECK_ARG(B >= 0 && L >= 0 && H > 0, "bmhrl_rnn_layer_f32: bad sizes");
-    if (B == 0 || L == 0) return BMHRL_OK;
-    cudaStream_t st = (cudaStream_t)stream;
-    const size_t smem = (size_t)RNN_BT * H * sizeof(float);
-    BMHRL_CHECK_ARG(smem <= 200 * 1024, "bmhrl_rnn_layer_f32: hidden size too large");
+// rnn_step_kernel needs more than the default 48 KB of dynamic shared memory for H > 768.
+static int rnn_step_smem_attr(int cell, size_t smem) {
     static bool attr_set[2] = {false, false};
     if (smem > 48 * 1024 && !attr_set[cell]) {
         cudaError_t e = cell == 0 ? cudaFuncSetAttribute(rnn_step_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -377,14 +370,45 @@ extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh,
         }
         attr_set[cell] = true;
     }
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_rnn_step_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out,
+                                  const float* c_prev, float* c_next, int B, int L, int H, int t, void* stream) {
+    BMHRL_CHECK_ARG(cell == 0 || cell == 1, "bmhrl_rnn_step_f32: cell must be 0 (LSTM) or 1 (GRU)");
+    BMHRL_CHECK_ARG(gx && W_hh && b_hh && out, "bmhrl_rnn_step_f32: null pointer");
+    BMHRL_CHECK_ARG(cell == 1 || (c_next && (t == 0 || c_prev)), "bmhrl_rnn_step_f32: LSTM needs the cell-state buffers");
+    BMHRL_CHECK_ARG(B > 0 && L > 0 && H > 0 && t >= 0 && t < L, "bmhrl_rnn_step_f32: bad sizes");
+    const size_t smem = (size_t)RNN_BT * H * sizeof(float);
+    BMHRL_CHECK_ARG(smem <= 200 * 1024, "bmhrl_rnn_step_f32: hidden size too large");
+    if (int rc = rnn_step_smem_attr(cell, smem)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid((H + RNN_WARPS - 1) / RNN_WARPS, (B + RNN_BT - 1) / RNN_BT);
+    if (cell == 0) rnn_step_kernel<4><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, c_prev, c_next, B, L, H, t);
+    else rnn_step_kernel<3><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, nullptr, nullptr, B, L, H, t);
+    BMHRL_POST_LAUNCH("rnn_step");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out,
+                                   float* ws, int B, int L, int H, void* stream) {
+    BMHRL_CHECK_ARG(cell == 0 || cell == 1, "bmhrl_rnn_layer_f32: cell must be 0 (LSTM) or 1 (GRU)");
+    BMHRL_CHECK_ARG(gx && W_hh && b_hh && out, "bmhrl_rnn_layer_f32: null pointer");
+    BMHRL_CHECK_ARG(cell == 1 || ws, "bmhrl_rnn_layer_f32: LSTM needs the workspace (bmhrl_rnn_ws_floats)");
+    BMHRL_CHECK_ARG(B >= 0 && L >= 0 && H > 0, "bmhrl_rnn_layer_f32: bad sizes");
+    if (B == 0 || L == 0) return BMHRL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t smem = (size_t)RNN_BT * H * sizeof(float);
+    BMHRL_CHECK_ARG(smem <= 200 * 1024, "bmhrl_rnn_layer_f32: hidden size too large");
+    if (int rc = rnn_step_smem_attr(cell, smem)) return rc;
     if (g_rnn_persistent && ws) {
         int rc = launch_rnn_persistent(cell, gx, W_hh, b_hh, out, ws, B, L, H, st);
         if (rc != 1) return rc;  // 1 = shape does not fit the persistent kernel: use the per-step kernels
     }
     dim3 grid((H + RNN_WARPS - 1) / RNN_WARPS, (B + RNN_BT - 1) / RNN_BT);
     for (int t = 0; t < L; ++t) {
-        if (cell == 0) rnn_step_kernel<4><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, ws, B, L, H, t);
-        else rnn_step_kernel<3><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, nullptr, B, L, H, t);
+        if (cell == 0) rnn_step_kernel<4><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, ws, ws, B, L, H, t);
+        else rnn_step_kernel<3><<<grid, RNN_WARPS * 32, smem, st>>>(gx, W_hh, b_hh, out, nullptr, nullptr, B, L, H, t);
         BMHRL_POST_LAUNCH("rnn_step");
     }
     return BMHRL_OK;

@@ -91,9 +91,10 @@ class GraphedGreedyDecoder:
       * one graph for the encoder, which also projects the encoder memory to the K / V of every caption->audio /
         caption->video attention of both fusion stacks (model/bm_hrl_agent.py:89-94) ONCE per clip instead of once
         per token (`MultiheadedAttention.memory_kv`);
-      * one graph per prefix length t (captured on first use, shared memory pool): critic, both fusion stacks,
-        manager, goal attention, last-position vocabulary projection, argmax written into column t of the static
-        token buffer -- a token is one graph replay instead of ~350 launches from Python;
+      * one graph per prefix length t (captured on first use, shared memory pool): ONE step of the critic's six
+        recurrent layers for the new position (the critic is causal; its states of the earlier positions are kept),
+        both fusion stacks, manager, goal attention, last-position vocabulary projection, argmax written into column
+        t of the static token buffer -- a token is one graph replay instead of ~350 launches from Python;
       * the completeness test of the reference loop (captioning_bmrl_loops.py:137,150: stop once every row has
         produced `end_idx`) read back every `check_every` tokens; tokens generated past the stopping point are cut
         off on the host, so the result has exactly the reference's length.
@@ -124,6 +125,8 @@ class GraphedGreedyDecoder:
         self.audio = torch.zeros(B, Sa, model.d_audio, device=dev)
         self.trg = torch.full((B, max_len + 1), pad_idx, dtype=torch.long, device=dev)
         self.last = torch.zeros(B, max_len, model.voc_size, device=dev)
+        from .model.bm_hrl_agent import SegmentCriticDecodeState
+        self.critic_state = SegmentCriticDecodeState(model.critic, B, max_len, dev)
         self.mem = None
         self.graphs = {}
         self.pool = torch.cuda.graph_pool_handle() if use_graph else None
@@ -156,7 +159,9 @@ class GraphedGreedyDecoder:
             att.memory_kv = pair
         try:
             C = m.emb_C(trg)
-            _, segment_labels = m.critic.scores_and_labels(C, m.critic_score_threshhold)
+            # the critic is causal: only the new position runs through its six recurrent layers
+            m.critic.step_labels(self.critic_state, C[:, t - 1:t], t - 1, m.critic_score_threshhold)
+            segment_labels = self.critic_state.labels[:, :t].contiguous()
             C = m.pos_enc_C(C)
             worker_feat = m.bm_worker_fus((C, (Av, Va)), masks)
             manager_feat = m.bm_manager_fus((C, (Av, Va)), masks)

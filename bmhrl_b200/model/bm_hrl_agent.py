@@ -160,10 +160,50 @@ class SegmentCritic(nn.Module):
         with torch.no_grad():
             return ops.segment_labels(self.hidden(embedded_indices), self.lin.weight, self.lin.bias, 0.0)[0]
 
+    def step_labels(self, state, x_p, p, threshold):
+        """Incremental form of `scores_and_labels` (the critic is causal: zero initial state, unidirectional LSTM / GRU,
+        position-wise AReLU and Linear): x_p (B,1,E) is the embedding of the token at position p, positions 0..p-1 have
+        been fed before.  Writes the label of position p into state.labels[:, p] -- the same bits as running the whole
+        prefix (one `rnn_step` per layer instead of a p+1-step recurrence per layer per generated token)."""
+        with torch.no_grad():
+            h = x_p
+            for l, (gx, out, c) in enumerate(state.lstm):
+                g = ops.linear(h, getattr(self.lstm, f"weight_ih_l{l}"), getattr(self.lstm, f"bias_ih_l{l}"))
+                gx[:, p].copy_(g[:, 0])
+                ops.rnn_step("lstm", gx, getattr(self.lstm, f"weight_hh_l{l}"), getattr(self.lstm, f"bias_hh_l{l}"),
+                             out, c, p)
+                h = out[:, p:p + 1]
+            h = self.relu(h)
+            for l, (gx, out) in enumerate(state.gru):
+                g = ops.linear(h, getattr(self.gru, f"weight_ih_l{l}"), getattr(self.gru, f"bias_ih_l{l}"))
+                gx[:, p].copy_(g[:, 0])
+                ops.rnn_step("gru", gx, getattr(self.gru, f"weight_hh_l{l}"), getattr(self.gru, f"bias_hh_l{l}"),
+                             out, None, p)
+                h = out[:, p:p + 1]
+            h = self.relu2(h)
+            _, labels = ops.segment_labels(h, self.lin.weight, self.lin.bias, threshold)
+            state.labels[:, p].copy_(labels[:, 0])
+
     def scores_and_labels(self, embedded_indices, threshold):
         """(B,L,1) raw scores and int32 (B,L) labels sigmoid(score) > threshold in one pass."""
         with torch.no_grad():
             return ops.segment_labels(self.hidden(embedded_indices), self.lin.weight, self.lin.bias, threshold)
+
+
+class SegmentCriticDecodeState:
+    """Caller-kept buffers of `SegmentCritic.step_labels` (greedy decoding appends one token per step): for every
+    recurrent layer the input contributions gx, the hidden states of all positions and the LSTM cell state after each
+    step; `labels` (B, Lmax) int32 collects the segment labels of the positions seen so far."""
+
+    def __init__(self, critic, B, max_len, device):
+        H = critic.lstm.hidden_size
+        f = dict(device=device, dtype=torch.float32)
+        self.lstm = [(torch.zeros(B, max_len, 4 * H, **f), torch.zeros(B, max_len, H, **f),
+                      torch.zeros(max_len, B, H, **f)) for _ in range(critic.lstm.num_layers)]
+        self.gru = [(torch.zeros(B, max_len, 3 * H, **f), torch.zeros(B, max_len, H, **f))
+                    for _ in range(critic.gru.num_layers)]
+        self.labels = torch.zeros(B, max_len, device=device, dtype=torch.int32)
+        self.max_len = max_len
 
 
 class BMEncoder(nn.Module):

@@ -960,6 +960,26 @@ def rnn_layer(cell, x, w_ih, w_hh, b_ih, b_hh):
     return out
 
 
+def rnn_step(cell, gx, w_hh, b_hh, out, c, t):
+    """Step t of an nn.LSTM / nn.GRU layer IN PLACE on caller-kept buffers gx (B,Lmax,NG*H), out (B,Lmax,H) and, for
+    the LSTM, c (Lmax,B,H) (the cell state after every step, so a step can be repeated): the incremental form of
+    `rnn_layer` for token-by-token decoding."""
+    B, L, H = out.shape
+    NG = 4 if cell == "lstm" else 3
+    if gx.shape != (B, L, NG * H) or not gx.is_contiguous() or not out.is_contiguous():
+        raise RuntimeError("rnn_step: gx / out must be contiguous (B,Lmax,NG*H) / (B,Lmax,H) buffers")
+    _chk(gx, "gx")
+    _chk(out, "out")
+    cp = cn = None
+    if cell == "lstm":
+        if c is None or c.shape != (L, B, H) or not c.is_contiguous():
+            raise RuntimeError("rnn_step: the LSTM needs a contiguous (Lmax,B,H) cell-state buffer")
+        _chk(c, "c")
+        cp, cn = c[max(t - 1, 0)], c[t]
+    LIB.call("bmhrl_rnn_step_f32", 0 if cell == "lstm" else 1, _p(gx), _p(_c(w_hh, "w_hh")), _p(_c(b_hh, "b_hh")),
+             _p(out), _p(cp), _p(cn), B, L, H, int(t), _stream())
+
+
 def arelu(x, alpha, beta):
     x = _c(x, "x")
     y = torch.empty_like(x)

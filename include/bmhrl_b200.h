@@ -182,6 +182,13 @@ long long bmhrl_rnn_ws_floats(int B, int H);
 int bmhrl_rnn_set_persistent(int on);
 int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B,
                         int L, int H, void* stream);
+/* ONE time step t of the same layer on caller-kept buffers laid out for L steps: reads h_{t-1} from out[:, t-1, :] and
+ * the LSTM cell state from c_prev (B,H) (both taken as zero at t == 0), gx[:, t, :]; writes out[:, t, :] and the new
+ * cell state to c_next (B,H; may be c_prev; GRU: both null).  Distinct c_prev / c_next make the step repeatable.
+ * Greedy decoding appends one token per step (captioning_bmrl_loops.py:127-152), and the critic is causal: calling this
+ * for t = 0, 1, ... gives the bits bmhrl_rnn_layer_f32 gives for the whole prefix, at the cost of one step per token. */
+int bmhrl_rnn_step_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, const float* c_prev,
+                       float* c_next, int B, int L, int H, int t, void* stream);
 /* AReLU model/bm_hrl_agent.py:13-23 (alpha, beta: device scalars). */
 int bmhrl_arelu_f32(const float* x, const float* alpha, const float* beta, float* y, long long n, void* stream);
 /* scores[row] = x[row,:] . w + b; labels[row] = sigmoid(score) > threshold (model/bm_hrl_agent.py:213,638-640). */

@@ -347,9 +347,13 @@ def test_overlapped_grad_sync_reduces_every_gradient_once(gpu_lib, agent_sd, kin
         for _ in range(2):
             run.step(b)
         torch.cuda.synchronize()
-        res.append((model.worker.core.projection.weight.detach().clone(),
-                    model.bm_enc.encoder.layers[0].self_att_M1.linear_Q2d.weight.detach().clone()))
-    assert rel(res[1][0], res[0][0]) < 1e-6 and rel(res[1][1], res[0][1]) < 1e-6
+        res.append({k: v.detach().clone() for k, v in model.named_parameters() if v.requires_grad})
+    # Tolerance: two runs of the SAME configuration (serial, eager, no overlap) already differ by up to 1.5e-5 in this
+    # norm on a B200 (measured): bias / LayerNorm / embedding gradients are reduced with float atomics, and Adam's
+    # g / (|g| + eps) turns round-off into O(lr) steps wherever the true gradient is zero (key biases, near-uniform
+    # attention's Q / K weights).  A stage stepped on incomplete gradients would differ by ~1e-3 or more.
+    worst = max(rel(res[1][k], res[0][k]) for k in res[0])
+    assert worst < 1e-4, worst
 
 
 @pytest.mark.parametrize("train_worker", [True, False])

@@ -306,6 +306,46 @@ def test_segment_critic(gpu_lib, agent_sd):
         assert rel(crit(x.cuda()), ref) < 1e-4
 
 
+def test_segment_critic_incremental_steps_equal_whole_prefix(gpu_lib, agent_sd):
+    """SegmentCritic.step_labels (one rnn_step per layer per appended position, states kept by the caller) gives the
+    labels AND hidden states of the whole-prefix recurrence bit for bit; a repeated step changes nothing (the LSTM cell
+    state is kept per step)."""
+    from types import SimpleNamespace as NS
+    from bmhrl_b200 import ops
+    from bmhrl_b200.model.bm_hrl_agent import SegmentCritic, SegmentCriticDecodeState
+    g = _g(23)
+    crit = SegmentCritic(NS(d_model_caps=300, rl_critic_path=None))
+    crit.load_state_dict({k[len("critic."):]: v for k, v in agent_sd.items() if k.startswith("critic.")})
+    crit = crit.cuda()
+    for B, L, Lmax in ((3, 7, 10), (1, 12, 12), (17, 4, 6)):
+        x = (torch.randn(B, L, 300, generator=g) * math.sqrt(300) * 0.3).cuda()
+        state = SegmentCriticDecodeState(crit, B, Lmax, "cuda")
+        for p in range(L):
+            crit.step_labels(state, x[:, p:p + 1], p, 0.25)
+            if p % 3 == 1:
+                crit.step_labels(state, x[:, p:p + 1], p, 0.25)  # a repeated step (warm-up, then capture) is harmless
+            _, labels = crit.scores_and_labels(x[:, :p + 1].contiguous(), 0.25)
+            assert torch.equal(state.labels[:, :p + 1], labels), (B, p)
+        assert torch.equal(state.gru[-1][1][:, :L], _critic_last_gru(crit, x))
+    with pytest.raises(RuntimeError):
+        ops.rnn_step("lstm", state.lstm[0][0], crit.lstm.weight_hh_l0, crit.lstm.bias_hh_l0, state.lstm[0][1], None, 0)
+    with pytest.raises(RuntimeError):
+        ops.rnn_step("gru", state.gru[0][0], crit.gru.weight_hh_l0, crit.gru.bias_hh_l0, state.gru[0][1], None, Lmax)
+
+
+def _critic_last_gru(crit, x):
+    from bmhrl_b200 import ops
+    h = x
+    for l in range(crit.lstm.num_layers):
+        h = ops.rnn_layer("lstm", h, getattr(crit.lstm, f"weight_ih_l{l}"), getattr(crit.lstm, f"weight_hh_l{l}"),
+                          getattr(crit.lstm, f"bias_ih_l{l}"), getattr(crit.lstm, f"bias_hh_l{l}"))
+    h = crit.relu(h)
+    for l in range(crit.gru.num_layers):
+        h = ops.rnn_layer("gru", h, getattr(crit.gru, f"weight_ih_l{l}"), getattr(crit.gru, f"weight_hh_l{l}"),
+                          getattr(crit.gru, f"bias_ih_l{l}"), getattr(crit.gru, f"bias_hh_l{l}"))
+    return h
+
+
 def test_detr_layers_golden(gpu_lib, golden):
     from bmhrl_b200.model.encoder import TransformerEncoder, TransformerEncoderLayer
     from bmhrl_b200.model.decoder import TransformerDecoder, TransformerDecoderLayer

@@ -22,6 +22,10 @@ def main():
     ap.add_argument("--B", type=int, default=1)
     ap.add_argument("--tokens", type=int, default=30)
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--only", default="", help="comma list of decoders to time (full_recompute,encode_once,graphed)")
+    ap.add_argument("--modes", default="fp32,tf32")
+    ap.add_argument("--profile", action="store_true",
+                    help="bracket ONE graphed caption with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     a = ap.parse_args()
     from bmhrl_b200 import ops, synth
     from bmhrl_b200.decode import GraphedGreedyDecoder, greedy_decoder, greedy_decoder_cached
@@ -36,7 +40,8 @@ def main():
     out = {"metric": "greedy_decode_tokens_per_sec", "unit": "tokens/s",
            "config": {"workload": f"config 1 shape: B={a.B}, Sv=14, Sa=36, {a.tokens} generated tokens, V={VOC}, "
                                   f"random-init BMHRL, end token disabled so every run generates {a.tokens} tokens"}}
-    for mode in ("fp32", "tf32"):
+    only = set(filter(None, a.only.split(",")))
+    for mode in a.modes.split(","):
         ops.set_math_mode(mode)
         res = {}
         toks = {}
@@ -44,6 +49,8 @@ def main():
         dec = GraphedGreedyDecoder(model, a.B, 16, 40, a.tokens, 2, -1, PAD, check_every=a.tokens)
         for name, fn in (("full_recompute", greedy_decoder), ("encode_once", greedy_decoder_cached),
                          ("graphed", None)):
+            if only and name not in only:
+                continue
             run = (lambda: dec(fs)) if fn is None else (lambda: fn(model, fs, a.tokens, 2, -1, PAD, "audio_video"))
             for _ in range(2):
                 toks[name] = run()
@@ -56,11 +63,18 @@ def main():
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / a.reps
             res[name] = {"ms_per_caption": ms, "tokens_per_s": 1e3 * a.B * a.tokens / ms}
-        res["same_tokens"] = bool(torch.equal(toks["full_recompute"], toks["encode_once"]))
-        res["same_tokens_graphed"] = bool(torch.equal(toks["full_recompute"], toks["graphed"]))
-        res["speedup"] = res["full_recompute"]["ms_per_caption"] / res["encode_once"]["ms_per_caption"]
-        res["speedup_graphed"] = res["full_recompute"]["ms_per_caption"] / res["graphed"]["ms_per_caption"]
-        res["graphed_launches_per_caption"] = dec.replays // (2 + a.reps)
+        if a.profile:
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
+            dec(fs)
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
+        if not only:
+            res["same_tokens"] = bool(torch.equal(toks["full_recompute"], toks["encode_once"]))
+            res["same_tokens_graphed"] = bool(torch.equal(toks["full_recompute"], toks["graphed"]))
+            res["speedup"] = res["full_recompute"]["ms_per_caption"] / res["encode_once"]["ms_per_caption"]
+            res["speedup_graphed"] = res["full_recompute"]["ms_per_caption"] / res["graphed"]["ms_per_caption"]
+            res["graph_replays_per_caption"] = dec.replays // (2 + a.reps)
         out[mode] = res
     ops.set_math_mode("fp32")
     print(json.dumps(out))
