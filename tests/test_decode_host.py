@@ -39,3 +39,18 @@ def test_stop_length_ignores_the_start_column_and_empty_prefix():
     assert reference_stop_length(torch.tensor([[3, 5, 3]]), 3) == 3
     assert reference_stop_length(torch.tensor([[2, 3, 3], [2, 4, 3]]), 3) == 3
     assert reference_stop_length(torch.tensor([[2, 3, 9], [2, 4, 9]]), 3) is None
+
+
+def test_graphed_decoder_has_no_cpu_path(agent_sd):
+    """The product path fails loudly without a CUDA device: no CPU fallback, no oracle behind it."""
+    import pytest
+    from conftest import PAD, build_agent
+    from bmhrl_b200.decode import GraphedGreedyDecoder
+    model, _ = build_agent(agent_sd, device="cpu")
+    model.eval()
+    model.set_inference_mode(True)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        GraphedGreedyDecoder(model, 1, 8, 8, 5, 2, 3, PAD)
+    model.train()
+    with pytest.raises(RuntimeError, match="eval"):
+        GraphedGreedyDecoder(model, 1, 8, 8, 5, 2, 3, PAD)
