@@ -180,6 +180,90 @@ int launch_gemm_simt(const GemmParams& p, int batch, cudaStream_t st) {
 }
 
 
+// ------------------------------------------------------------------------------------------------------------------
+// Skinny linear layer: y = act(x W^T + b) + resid for M <= 32 rows (token-by-token decoding: M = B * prefix length or
+// M = B).  The tcgen05 GEMM pays its fixed costs (tensor-map fetch, TMEM allocation, barrier set-up, a 128-row MMA
+// tile that is > 75 % padding) on every one of the ~45 projections per generated token; here one warp owns one output
+// column: it streams its row of W once (128-bit loads), the <= 32 rows of x sit in shared memory in K chunks, and the
+// lanes' partial sums are reduced with shuffles.  Exact fp32 (FMA), so it is at least as accurate as the tf32 path it
+// stands in for.  Tensor-core math mode only: in fp32 mode every linear layer stays on ONE kernel so that row results
+// do not depend on how many rows a call has (the incremental critic relies on that, rnn.cu).
+constexpr int SK_WARPS = 8;  // output columns per CTA
+constexpr int SK_KC = 256;   // K chunk staged in shared memory
+
+template <int MT>
+__global__ void __launch_bounds__(SK_WARPS * 32) linear_skinny_kernel(const float* __restrict__ X, long long ldx,
+                                                                     const float* __restrict__ W,
+                                                                     const float* __restrict__ bias,
+                                                                     const float* __restrict__ resid, long long ldr,
+                                                                     float* __restrict__ Y, long long ldy, int M, int N,
+                                                                     int K, int act) {
+    __shared__ float4 xs[MT][SK_KC / 4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = blockIdx.x * SK_WARPS + warp;
+    const bool valid = n < N;
+    const float* wrow = W + (long long)(valid ? n : 0) * K;
+    float acc[MT];
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[m] = 0.f;
+    for (int k0 = 0; k0 < K; k0 += SK_KC) {
+        const int q = min(SK_KC, K - k0) >> 2;  // float4 per row in this chunk (K % 4 == 0)
+        __syncthreads();
+        for (int i = threadIdx.x; i < MT * (SK_KC / 4); i += SK_WARPS * 32) {
+            const int m = i / (SK_KC / 4), c = i % (SK_KC / 4);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (m < M && c < q) v = ld_f4(X + (long long)m * ldx + k0 + 4 * c);
+            xs[m][c] = v;
+        }
+        __syncthreads();
+        for (int c = lane; c < q; c += 32) {
+            const float4 w = ld_f4(wrow + k0 + 4 * c);
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+                const float4 x = xs[m][c];
+                acc[m] = fmaf(w.x, x.x, acc[m]);
+                acc[m] = fmaf(w.y, x.y, acc[m]);
+                acc[m] = fmaf(w.z, x.z, acc[m]);
+                acc[m] = fmaf(w.w, x.w, acc[m]);
+            }
+        }
+    }
+    float mine = 0.f;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+        const float s = warp_sum(acc[m]);
+        if (lane == m) mine = s;
+    }
+    if (!valid || lane >= M) return;
+    float v = mine + (bias ? bias[n] : 0.f);
+    if (act == 1) v = fmaxf(v, 0.f);
+    if (resid) v += resid[(long long)lane * ldr + n];
+    Y[(long long)lane * ldy + n] = v;
+}
+
+static int g_skinny_linear = -1;  // -1: not read yet (BMHRL_SKINNY_LINEAR=0 disables)
+
+static bool skinny_linear_enabled() {
+    if (g_skinny_linear < 0) {
+        const char* e = getenv("BMHRL_SKINNY_LINEAR");
+        g_skinny_linear = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_skinny_linear == 1;
+}
+
+static int launch_linear_skinny(const float* X, long long ldx, const float* W, const float* bias, const float* resid,
+                                long long ldr, float* Y, long long ldy, int M, int N, int K, int act, cudaStream_t st) {
+    if (M <= 0 || N <= 0) return BMHRL_OK;
+    const dim3 grid((N + SK_WARPS - 1) / SK_WARPS);
+    if (M <= 8) linear_skinny_kernel<8><<<grid, SK_WARPS * 32, 0, st>>>(X, ldx, W, bias, resid, ldr, Y, ldy, M, N, K, act);
+    else if (M <= 16)
+        linear_skinny_kernel<16><<<grid, SK_WARPS * 32, 0, st>>>(X, ldx, W, bias, resid, ldr, Y, ldy, M, N, K, act);
+    else linear_skinny_kernel<32><<<grid, SK_WARPS * 32, 0, st>>>(X, ldx, W, bias, resid, ldr, Y, ldy, M, N, K, act);
+    BMHRL_POST_LAUNCH("linear_skinny");
+    return BMHRL_OK;
+}
+
+
 }  // namespace bmhrl
 
 using namespace bmhrl;
@@ -206,6 +290,11 @@ extern "C" int bmhrl_gemm_f32(const float* A, long long sAm, long long sAk, cons
     return launch_gemm_simt(p, batch, (cudaStream_t)stream);
 }
 
+extern "C" int bmhrl_set_skinny_linear(int on) {
+    g_skinny_linear = on ? 1 : 0;
+    return BMHRL_OK;
+}
+
 extern "C" int bmhrl_linear_fwd_f32(const float* X, long long ldx, const float* W, const float* bias,
                                     const float* resid, long long ldr, float* Y, long long ldy, int M, int N,
                                     int K, int act, float drop_p, const unsigned long long* rng_state,
@@ -221,6 +310,9 @@ extern "C" int bmhrl_linear_fwd_f32(const float* X, long long ldx, const float* 
     p.Hdiv = 1;
     p.alpha = 1.f; p.beta = 0.f; p.bias = bias; p.act = act; p.resid = resid; p.ldr = ldr;
     p.drop_p = drop_p; p.rng = rng_state; p.salt = salt;
+    if (math_mode() == 1 && M <= 32 && K > 0 && drop_p == 0.f && (K & 3) == 0 && (ldx & 3) == 0 &&
+        ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W)) & 15) == 0 && skinny_linear_enabled())
+        return launch_linear_skinny(X, ldx, W, bias, resid, ldr, Y, ldy, M, N, K, act, (cudaStream_t)stream);
     if (math_mode() == 1) {
         TcGemmArgs t{};
         t.A = X; t.lda = ldx; t.a_mn = 0; t.B = W; t.ldb = K; t.b_mn = 0; t.C = Y; t.ldc = ldy;

@@ -61,6 +61,10 @@ int bmhrl_gemm_f32(const float* A, long long sAm, long long sAk, const float* B,
                    float* C, long long ldc, int M, int N, int K, int batch, int Hdiv, long long bAo, long long bAi,
                    long long bBo, long long bBi, long long bCo, long long bCi, float alpha, float beta, void* stream);
 
+/* Tensor-core math mode only: linear layers with M <= 32 rows and no dropout (token-by-token decoding) run on a
+ * one-warp-per-output-column exact-fp32 kernel instead of a mostly empty 128-row tcgen05 tile.  1 (default) / 0; the
+ * environment variable BMHRL_SKINNY_LINEAR=0 sets the initial value. */
+int bmhrl_set_skinny_linear(int on);
 /* Y = resid + dropout(act(X W^T + bias)); W is (N,K) like nn.Linear.weight.  act: 0 none, 1 ReLU.
  * Replaces linear_Q2d/K2d/V2d/d2Q (model/multihead_attention.py:70-72,89), fc1/fc2 (model/blocks.py:175-187,
  * with the ResidualConnection add of model/blocks.py:144 fused), Manager.linear (model/bm_hrl_agent.py:439-440),

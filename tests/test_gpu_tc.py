@@ -19,6 +19,7 @@ def tf32(gpu_lib):
     ops.set_math_mode("tf32")
     yield ops
     gpu_lib.call("bmhrl_tc_tuning", 0, 0)
+    gpu_lib.call("bmhrl_set_skinny_linear", 1)
     ops.set_math_mode("fp32")
 
 
@@ -33,6 +34,7 @@ def test_tc_linear_forward(tf32, gpu_lib, M, K, N, bn, split):
     """split < 0: the K range is split over a thread-block cluster of -split CTAs whose partial accumulators are
     reduce-scattered through distributed shared memory before the fused epilogue."""
     gpu_lib.call("bmhrl_tc_tuning", bn, split)
+    gpu_lib.call("bmhrl_set_skinny_linear", 0)  # M = 5 must exercise the tensor-core kernel here
     g = _g(M + K + N)
     x, w, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / math.sqrt(K), torch.randn(N, generator=g)
     r = torch.randn(M, N, generator=g)
@@ -43,6 +45,30 @@ def test_tc_linear_forward(tf32, gpu_lib, M, K, N, bn, split):
     assert rel(y2, torch.relu(ref) + r.double()) < TF32_TOL
     y3 = tf32.linear(x.cuda(), w.cuda(), None)
     assert rel(y3, ref - b.double()) < TF32_TOL
+
+
+@pytest.mark.parametrize("M,K,N", [(1, 300, 2400), (1, 364, 10172), (7, 1024, 1024), (8, 64, 300), (9, 128, 1024),
+                                   (16, 600, 1800), (17, 1024, 300), (30, 1024, 1024), (32, 300, 64), (3, 1024, 1030)])
+def test_skinny_linear_forward(tf32, gpu_lib, M, K, N):
+    """Tensor-core math mode, M <= 32 rows, no dropout: linear_skinny_kernel (exact fp32, one warp per output column).
+    Its error is at fp32 round-off level, which the tf32 kernel cannot reach -- so the tight bound also proves which
+    kernel ran; with the switch off the same call goes through the tcgen05 kernel again."""
+    g = _g(M * 7 + K + N)
+    x, w, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / math.sqrt(K), torch.randn(N, generator=g)
+    r = torch.randn(M, N, generator=g)
+    ref = torch.nn.functional.linear(x.double(), w.double(), b.double())
+    xc, wc, bc, rc = x.cuda(), w.cuda(), b.cuda(), r.cuda()
+    assert rel(tf32.linear(xc, wc, bc), ref) < 2e-6
+    assert rel(tf32.linear(xc, wc, bc, resid=rc, act=1), torch.relu(ref) + r.double()) < 2e-6
+    assert rel(tf32.linear(xc, wc, None), ref - b.double()) < 2e-6
+    assert rel(tf32.linear(xc.view(1, M, K), wc, bc), ref.view(1, M, N)) < 2e-6
+    gpu_lib.call("bmhrl_set_skinny_linear", 0)
+    assert 2e-6 < rel(tf32.linear(xc, wc, bc), ref) < TF32_TOL
+    gpu_lib.call("bmhrl_set_skinny_linear", 1)
+    # one row more than the kernel takes: tensor-core path
+    x33 = torch.randn(33, K, generator=g)
+    y33 = tf32.linear(x33.cuda(), wc, bc)
+    assert 2e-6 < rel(y33, torch.nn.functional.linear(x33.double(), w.double(), b.double())) < TF32_TOL
 
 
 @pytest.mark.parametrize("M,K,N", [(37, 300, 64), (320, 364, 10172), (480, 1024, 1024), (129, 128, 512)])
