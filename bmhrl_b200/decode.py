@@ -1,5 +1,12 @@
 """Greedy caption decoding, config 1 (epoch_loops/captioning_bmrl_loops.py:127-152 with the 3-argument
-`model.inference` form).  Like the reference the whole model is re-run for every generated token."""
+`model.inference` form).
+
+  greedy_decoder           the reference's algorithm: the whole model is re-run for every generated token
+  greedy_decoder_cached    encoder once per clip batch, vocabulary projection for the last position only
+  GraphedGreedyDecoder     for a stream of clips: static buffers, encoder + encoder-memory K/V once per clip, one CUDA
+                           graph replay and one recurrent step of the critic per token
+
+All three generate the same tokens (tests/test_gpu_agent.py); none has a CPU path."""
 import torch
 
 from .model.masking import c_mask, make_masks
