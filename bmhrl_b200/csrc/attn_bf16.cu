@@ -706,9 +706,9 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
         bmhrl_set_error("attn_fwd_bf16: cuTensorMapEncodeTiled failed");
         return BMHRL_ERR_CUDA;
     }
-    static bool attr = false;
-    static int n_sm = 0;
-    if (!attr) {
+    static DeviceOnce attr;
+    const int n_sm = device_sm_count();
+    if (needs_setup(attr)) {
         const cudaFuncAttribute A = cudaFuncAttributeMaxDynamicSharedMemorySize;
         if (cudaFuncSetAttribute(attn_fwd_bf16_kernel<false, false>, A, AB_SMEM) != cudaSuccess ||
             cudaFuncSetAttribute(attn_fwd_bf16_kernel<false, true>, A, AB_SMEM) != cudaSuccess ||
@@ -717,11 +717,7 @@ extern "C" int bmhrl_attn_fwd_bf16(const void* Q, long long ldq, long long bsq, 
             bmhrl_set_error("attn_fwd_bf16: cannot raise the shared-memory limit");
             return BMHRL_ERR_CUDA;
         }
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        if (n_sm <= 0) n_sm = 148;
-        attr = true;
+        mark_done(attr);
     }
     AttnBf16Params p{};
     p.O = (__nv_bfloat16*)O; p.ldo = ldo; p.bso = bso; p.lse = lse; p.mask = mask; p.mask_kind = mask_kind;

@@ -442,9 +442,9 @@ extern "C" int bmhrl_attn_bwd_bf16(const void* Q, long long ldq, long long bsq, 
         bmhrl_set_error("attn_bwd_bf16: cuTensorMapEncodeTiled failed");
         return BMHRL_ERR_CUDA;
     }
-    static bool attr = false;
-    static int n_sm = 0;
-    if (!attr) {
+    static DeviceOnce attr;
+    const int n_sm = device_sm_count();
+    if (needs_setup(attr)) {
         const cudaFuncAttribute A = cudaFuncAttributeMaxDynamicSharedMemorySize;
         if (cudaFuncSetAttribute(attn_bwd_bf16_kernel<BW_DQ>, A, BW_SMEM) != cudaSuccess ||
             cudaFuncSetAttribute(attn_bwd_bf16_kernel<BW_DK>, A, BW_SMEM) != cudaSuccess ||
@@ -452,11 +452,7 @@ extern "C" int bmhrl_attn_bwd_bf16(const void* Q, long long ldq, long long bsq, 
             bmhrl_set_error("attn_bwd_bf16: cannot raise the shared-memory limit");
             return BMHRL_ERR_CUDA;
         }
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        if (n_sm <= 0) n_sm = 148;
-        attr = true;
+        mark_done(attr);
     }
     cudaStream_t st = (cudaStream_t)stream;
     float* delta = (float*)ws;
@@ -497,17 +493,26 @@ extern "C" int bmhrl_attn_bwd_bf16(const void* Q, long long ldq, long long bsq, 
             attn_bwd_bf16_kernel<BW_DV><<<grid, 192, BW_SMEM, st>>>(rK, rK, sQ, sQ, sdO, a);
         }
     };
+    // A gradient whose pass is switched off by the profiling hook comes back as zeros, never as uninitialised memory.
+    auto zero_out = [&](void* g, long long ld, long long bs, int rows) -> bool {
+        const size_t width = sizeof(__nv_bfloat16) * (size_t)H * dk;
+        for (int b = 0; b < B; ++b)
+            if (cudaMemset2DAsync((char*)g + sizeof(__nv_bfloat16) * (size_t)b * bs, sizeof(__nv_bfloat16) * (size_t)ld, 0,
+                                  width, rows, st) != cudaSuccess)
+                return false;
+        return true;
+    };
     if (g_attn_bwd_passes & 1) {
         launch(BW_DQ);
         BMHRL_POST_LAUNCH("attn_bwd_bf16 dQ");
-    }
+    } else if (!zero_out(dQ, lddq, bsdq, Sq)) return BMHRL_ERR_CUDA;
     if (g_attn_bwd_passes & 2) {
         launch(BW_DK);
         BMHRL_POST_LAUNCH("attn_bwd_bf16 dK");
-    }
+    } else if (!zero_out(dK, lddk, bsdk, Sk)) return BMHRL_ERR_CUDA;
     if (g_attn_bwd_passes & 4) {
         launch(BW_DV);
         BMHRL_POST_LAUNCH("attn_bwd_bf16 dV");
-    }
+    } else if (!zero_out(dV, lddv, bsdv, Sk)) return BMHRL_ERR_CUDA;
     return BMHRL_OK;
 }

@@ -365,13 +365,13 @@ int launch_attn_fwd_tc(const float* Q, long long ldq, long long bsq, const float
         bmhrl_set_error("attention: cuTensorMapEncodeTiled failed");
         return BMHRL_ERR_CUDA;
     }
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    if (needs_setup(attr)) {
         if (cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM) != cudaSuccess) {
             bmhrl_set_error("attention: cannot raise the shared-memory limit");
             return BMHRL_ERR_CUDA;
         }
-        attr = true;
+        mark_done(attr);
     }
     AttnFwdParams p{};
     p.O = O; p.ldo = ldo; p.bso = bso; p.P = P; p.ldp = ldp; p.mask = mask; p.mask_kind = mask_kind; p.causal = causal;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
+#include <atomic>
 
 #define BMHRL_OK 0
 #define BMHRL_ERR_ARG (-1)
@@ -32,6 +33,36 @@ extern "C" void bmhrl_count_launch(int n);
     } while (0)
 
 namespace bmhrl {
+
+// ---------------------------------------------------------------- per-device one-time set-up (host)
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) and the SM count are PER DEVICE: a process that uses several
+// devices (tests on cuda:1, single-process multi-GPU) must repeat the set-up on each.  The flags are atomics and the
+// set-up calls idempotent, so two threads racing through the first call on a device are harmless.
+constexpr int kMaxDevices = 64;
+struct DeviceOnce {
+    std::atomic<unsigned char> done[kMaxDevices];
+};
+inline int current_device_slot() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return (d < 0 || d >= kMaxDevices) ? 0 : d;
+}
+// true when `once` has not been completed on the current device yet; call mark_done(once) after a successful set-up
+inline bool needs_setup(DeviceOnce& once) { return once.done[current_device_slot()].load(std::memory_order_acquire) == 0; }
+inline void mark_done(DeviceOnce& once) { once.done[current_device_slot()].store(1, std::memory_order_release); }
+inline int device_sm_count() {
+    static std::atomic<int> n[kMaxDevices];
+    const int slot = current_device_slot();
+    int v = n[slot].load(std::memory_order_relaxed);
+    if (v <= 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        if (v <= 0) v = 148;
+        n[slot].store(v, std::memory_order_relaxed);
+    }
+    return v;
+}
 
 constexpr float kNegFill = -1e9f;  // reference replaces masked scores by -1e9 (model/multihead_attention.py:21-22)
 

@@ -295,15 +295,15 @@ template <int BN, int STAGES>
 static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcEpilogue& ep, dim3 grid, cudaStream_t st) {
     constexpr int SMEM_BASE = STAGES * (TC_A_BYTES + BN * 128) + 1024 + 8 * (2 * STAGES + 2);
     constexpr int SMEM_MAX = SMEM_BASE + TC_BM * BN * 4;  // + the cluster receive buffer
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    if (needs_setup(attr)) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tf32_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              SMEM_MAX);
         if (e != cudaSuccess) {
             bmhrl_set_error(cudaGetErrorString(e));
             return BMHRL_ERR_CUDA;
         }
-        attr = true;
+        mark_done(attr);
     }
     if (ep.cluster > 1) {
         cudaLaunchConfig_t cfg = {};

@@ -62,13 +62,21 @@ __device__ __forceinline__ float kl_target(const KlRow& r, int v) {
 
 __device__ __forceinline__ float xlogy(float t) { return t == 0.f ? 0.f : t * logf(t); }
 
+// Rows whose target is pad are zeroed by the reference only `if mask.sum() > 0` where mask holds the flat row INDICES
+// of the pad targets (loss/label_smoothing.py:26-30, loss/biased_kl.py:46-50): when flat row 0 is the only pad row,
+// nothing is zeroed.  Only the CTA of row 0 ever has to look at the other rows.
 __device__ __forceinline__ KlRow make_row(int mode, const long long* trg, const long long* samp, const float* offset,
-                                          long long row, int V, float smoothing, int pad_idx) {
+                                          long long row, long long rows, int V, float smoothing, int pad_idx) {
     KlRow r;
     r.mode = mode;
     r.trg = (int)trg[row];
     r.pad_idx = pad_idx;
     r.pad_row = (r.trg == pad_idx);
+    if (r.pad_row && row == 0) {
+        bool later = false;
+        for (long long i = 1; i < rows && !later; ++i) later = ((int)trg[i] == pad_idx);
+        r.pad_row = later;
+    }
     r.u = smoothing / (float)(V - 2);
     if (mode == 0) {
         r.samp = -1;
@@ -92,10 +100,10 @@ __global__ void __launch_bounds__(ROW_THREADS) kl_fwd_kernel(int mode, const flo
                                                              const long long* __restrict__ samp,
                                                              const float* __restrict__ offset,
                                                              float* __restrict__ out, float* __restrict__ rowsum,
-                                                             int V, float smoothing, int pad_idx) {
+                                                             long long rows, int V, float smoothing, int pad_idx) {
     __shared__ float red[32];
     const long long row = blockIdx.x;
-    const KlRow r = make_row(mode, trg, samp, offset, row, V, smoothing, pad_idx);
+    const KlRow r = make_row(mode, trg, samp, offset, row, rows, V, smoothing, pad_idx);
     const float* pr = pred + row * V;
     float acc = 0.f;
     for (int v = threadIdx.x; v < V; v += ROW_THREADS) {
@@ -120,9 +128,9 @@ __global__ void __launch_bounds__(ROW_THREADS) kl_bwd_kernel(int mode, const flo
                                                              const float* __restrict__ dout,
                                                              const float* __restrict__ drow,
                                                              float* __restrict__ dpred, float* __restrict__ doffset,
-                                                             int V, float smoothing, int pad_idx) {
+                                                             long long rows, int V, float smoothing, int pad_idx) {
     const long long row = blockIdx.x;
-    const KlRow r = make_row(mode, trg, samp, offset, row, V, smoothing, pad_idx);
+    const KlRow r = make_row(mode, trg, samp, offset, row, rows, V, smoothing, pad_idx);
     const float grow = drow ? drow[row] : 0.f;
     if (dpred) {
         for (int v = threadIdx.x; v < V; v += ROW_THREADS) {
@@ -251,7 +259,7 @@ extern "C" int bmhrl_kl_loss_fwd_f32(int mode, const float* pred, const long lon
     BMHRL_CHECK_ARG(mode == 0 || (biased_trg && biased_offset), "bmhrl_kl_loss_fwd_f32: biased KL needs trg/offset");
     if (rows == 0) return BMHRL_OK;
     kl_fwd_kernel<<<(unsigned)rows, ROW_THREADS, 0, (cudaStream_t)stream>>>(mode, pred, trg, biased_trg, biased_offset,
-                                                                           out, rowsum, V, smoothing, pad_idx);
+                                                                           out, rowsum, rows, V, smoothing, pad_idx);
     BMHRL_POST_LAUNCH("kl_fwd");
     return BMHRL_OK;
 }
@@ -265,7 +273,7 @@ extern "C" int bmhrl_kl_loss_bwd_f32(int mode, const float* pred, const long lon
     BMHRL_CHECK_ARG(mode == 0 || (biased_trg && biased_offset), "bmhrl_kl_loss_bwd_f32: biased KL needs trg/offset");
     if (rows == 0) return BMHRL_OK;
     kl_bwd_kernel<<<(unsigned)rows, ROW_THREADS, 0, (cudaStream_t)stream>>>(
-        mode, pred, trg, biased_trg, biased_offset, dout, drow, dpred, doffset, V, smoothing, pad_idx);
+        mode, pred, trg, biased_trg, biased_offset, dout, drow, dpred, doffset, rows, V, smoothing, pad_idx);
     BMHRL_POST_LAUNCH("kl_bwd");
     return BMHRL_OK;
 }

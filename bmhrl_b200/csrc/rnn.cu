@@ -295,20 +295,15 @@ static int g_rnn_persistent = 1;
 template <int NG>
 static int launch_rnn_persistent_t(const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B,
                                    int L, int H, cudaStream_t st) {
-    static int n_sm = 0;
-    static bool attr = false;
-    if (!n_sm) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    }
-    if (!attr) {
+    const int n_sm = device_sm_count();
+    static DeviceOnce attr;
+    if (needs_setup(attr)) {
         if (cudaFuncSetAttribute(rnn_layer_persistent_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  220 * 1024) != cudaSuccess) {
             bmhrl_set_error("rnn persistent: cannot raise the shared-memory limit");
             return BMHRL_ERR_CUDA;
         }
-        attr = true;
+        mark_done(attr);
     }
     // smallest units-per-block whose grid is co-resident (1 CTA per SM is assumed; smaller smem only helps)
     int upb = (H + n_sm - 1) / n_sm;
@@ -358,8 +353,8 @@ extern "C" int bmhrl_rnn_set_persistent(int on) {
 
 // rnn_step_kernel needs more than the default 48 KB of dynamic shared memory for H > 768.
 static int rnn_step_smem_attr(int cell, size_t smem) {
-    static bool attr_set[2] = {false, false};
-    if (smem > 48 * 1024 && !attr_set[cell]) {
+    static DeviceOnce attr_set[2];
+    if (smem > 48 * 1024 && needs_setup(attr_set[cell])) {
         cudaError_t e = cell == 0 ? cudaFuncSetAttribute(rnn_step_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                          200 * 1024)
                                   : cudaFuncSetAttribute(rnn_step_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -368,7 +363,7 @@ static int rnn_step_smem_attr(int cell, size_t smem) {
             bmhrl_set_error(cudaGetErrorString(e));
             return BMHRL_ERR_CUDA;
         }
-        attr_set[cell] = true;
+        mark_done(attr_set[cell]);
     }
     return BMHRL_OK;
 }

@@ -155,14 +155,26 @@ def parallel(device, *thunks):
 
 _WGRAD_KEEP = []   # operands of weight-gradient GEMMs in flight on the wgrad streams (kept alive until the join)
 _WGRAD_RR = [0]
+_WGRAD_DEST = {}   # (device, destination data_ptr) -> wgrad stream index: ONE stream per destination, for good
 
 
-def wgrad_stream(device):
+def wgrad_stream(device, dest=None):
     """Weight-gradient GEMMs that accumulate straight into a FusedAdam flat buffer have no consumer before the
-    optimiser step: they are forked onto two round-robin side streams, off the critical path of backward."""
+    optimiser step: they are forked onto two side streams, off the critical path of backward.  The beta = 1 epilogue
+    is a plain read-add-write, so two GEMMs into the SAME destination (a module used twice in one forward, two
+    forwards before one backward) must never run concurrently: the stream is chosen by the destination, round-robin
+    only over destinations seen for the first time, and work on one stream is ordered."""
     cur = torch.cuda.current_stream(device)
-    _WGRAD_RR[0] ^= 1
-    key = (cur.device.index, "wgrad", _WGRAD_RR[0])
+    if dest is None:
+        _WGRAD_RR[0] ^= 1
+        idx = _WGRAD_RR[0]
+    else:
+        k = (cur.device.index, dest.data_ptr())
+        idx = _WGRAD_DEST.get(k)
+        if idx is None:
+            _WGRAD_RR[0] ^= 1
+            idx = _WGRAD_DEST[k] = _WGRAD_RR[0]
+    key = (cur.device.index, "wgrad", idx)
     if key not in _SIDE:
         _SIDE[key] = new_stream(cur.device.index)
     _DIRTY.add(key)
@@ -318,7 +330,7 @@ class _Linear(torch.autograd.Function):
             if wgrad is not None:  # accumulate into the parameter's slice of the flat gradient buffer (beta = 1)
                 if CONCURRENT:
                     _WGRAD_KEEP.append((dz, x))
-                    with torch.cuda.stream(wgrad_stream(dy.device)):
+                    with torch.cuda.stream(wgrad_stream(dy.device, wgrad)):
                         gemm(dz, 1, N, x, K, 1, wgrad, K, N, K, M, beta=1.0)
                 else:
                     gemm(dz, 1, N, x, K, 1, wgrad, K, N, K, M, beta=1.0)

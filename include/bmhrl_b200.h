@@ -149,7 +149,8 @@ int bmhrl_attn_bwd_bf16(const void* Q, long long ldq, long long bsq, const void*
                         long long bsdk, void* dV, long long lddv, long long bsdv, int B, int H, int Sq, int Sk, int dk,
                         void* ws, void* stream);
 long long bmhrl_attn_bwd_bf16_ws_bytes(int B, int H, int Sq, int Sk);
-/* profiling hook: bit mask of the gradient passes to launch (1 = dQ, 2 = dK, 4 = dV); default 7 = all */
+/* profiling hook: bit mask of the gradient passes to launch (1 = dQ, 2 = dK, 4 = dV); default 7 = all.  The gradient of
+ * a pass that is switched off is returned as ZEROS (never uninitialised memory). */
 int bmhrl_attn_bwd_bf16_tuning(int passes);
 
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */

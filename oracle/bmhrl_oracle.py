@@ -346,6 +346,18 @@ def _xlogy_kl(pred, dist):
     return torch.xlogy(dist, dist) - dist * pred
 
 
+def _keep_rows(target, pad_idx):
+    """loss/label_smoothing.py:26-30, loss/biased_kl.py:46-50: rows whose target is pad are zeroed -- but only
+    `if mask.sum() > 0 and len(mask) > 0`, where `mask = nonzero(target == pad)` holds the flat ROW INDICES.  When
+    the only padded target is flat row 0 the index sum is 0 and the reference zeroes nothing: that row keeps its
+    smoothed distribution (minus the pad column) and contributes loss and gradient."""
+    is_pad = target == pad_idx
+    idx = torch.nonzero(is_pad).reshape(-1)
+    if idx.numel() > 0 and int(idx.sum()) > 0:
+        return ~is_pad
+    return torch.ones_like(is_pad)
+
+
 def label_smoothing_kl(pred, target, smoothing, pad_idx):
     """loss/label_smoothing.py:12-32.  Returns the (B*L, V) element-wise divergence."""
     V = pred.shape[-1]
@@ -354,7 +366,7 @@ def label_smoothing_kl(pred, target, smoothing, pad_idx):
     dist = torch.full_like(pred, smoothing / (V - 2))
     dist.scatter_(1, target[:, None], 1 - smoothing)
     dist[:, pad_idx] = 0
-    dist = dist * (target != pad_idx)[:, None].to(dist.dtype)
+    dist = dist * _keep_rows(target, pad_idx)[:, None].to(dist.dtype)
     return _xlogy_kl(pred, dist)
 
 
@@ -372,7 +384,7 @@ def biased_kl_divergence(pred, trg, biased_trg, biased_offset, smoothing, pad_id
     colmask[pad_idx] = 0
     dist = dist * colmask[None, :]
     dist = dist + torch.zeros_like(p2).scatter(1, biased_trg.reshape(-1, 1), (biased_offset * tf).reshape(-1, 1))
-    dist = dist * (t != pad_idx)[:, None].to(dist.dtype)
+    dist = dist * _keep_rows(t, pad_idx)[:, None].to(dist.dtype)
     return _xlogy_kl(p2, dist + 1e-8)
 
 

@@ -185,6 +185,33 @@ def pin_losses(ref, gold):
                         "value": value, "critic": cv_r.detach().clone()}
     res["inputs"] = {"logits": logits, "trg": trg, "samp": samp, "off": off}
     gold["losses"] = res
+    # the reference's `if mask.sum() > 0` quirk: flat row 0 is the ONLY pad target -> no row is zeroed
+    trg0 = torch.randint(2, V, (B, L), generator=g)
+    trg0[0, 0] = PAD
+    res0 = {}
+    for name in ("ls", "bkl"):
+        lp_r = torch.log_softmax(logits.clone().requires_grad_(True), -1)
+        lp_r.retain_grad()
+        lp_o = torch.log_softmax(logits.clone().requires_grad_(True), -1)
+        lp_o.retain_grad()
+        off_r = off.clone().requires_grad_(True)
+        off_o = off.clone().requires_grad_(True)
+        with refboot.sink():
+            if name == "ls":
+                r = ref.label_smoothing.LabelSmoothing(SMOOTH, PAD)(lp_r, trg0)
+                o = O.label_smoothing_kl(lp_o, trg0, SMOOTH, PAD)
+            else:
+                r = ref.biased_kl.BiasedKL(SMOOTH, PAD)(lp_r, trg0, samp, off_r)
+                o = O.biased_kl_divergence(lp_o, trg0, samp, off_o, SMOOTH, PAD)
+        w = torch.randn(r.shape, generator=torch.Generator().manual_seed(9))
+        (r * w).sum().backward()
+        (o * w).sum().backward()
+        check(f"{name} value (only row 0 pad)", o.detach(), r.detach())
+        check(f"{name} dpred (only row 0 pad)", lp_o.grad, lp_r.grad)
+        assert float(r[0].abs().sum()) > 0, "the reference is expected to keep row 0 here"
+        res0[name] = {"out": r.detach().clone(), "dpred": lp_r.grad.clone(), "w": w}
+    res0["inputs"] = {"logits": logits, "trg": trg0, "samp": samp, "off": off}
+    gold["losses_row0"] = res0
 
 
 def pin_expand_goals(ref, gold):

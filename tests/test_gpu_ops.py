@@ -158,6 +158,29 @@ def test_kl_losses_golden(gpu_lib, golden):
     assert rel(out, r["out"]) < TIGHT and rel(probs.grad, r["dprobs"]) < TIGHT and rel(cv.grad, r["dcritic"]) < TIGHT
 
 
+def test_kl_losses_only_row0_padded(gpu_lib, golden):
+    """Reference quirk (loss/label_smoothing.py:26-30): pad rows are zeroed only when the flat row indices of the pad
+    targets sum to > 0 -- a lone pad target in flat row 0 keeps its distribution.  Kernel vs the reference's output."""
+    from bmhrl_b200.loss.label_smoothing import LabelSmoothing
+    from bmhrl_b200.loss.biased_kl import BiasedKL
+    from bmhrl_b200 import ops
+    gl = golden["losses_row0"]
+    i = gl["inputs"]
+    for name in ("ls", "bkl"):
+        lp = ops.log_softmax(i["logits"].clone().cuda().requires_grad_(True))
+        lp.retain_grad()
+        if name == "ls":
+            out = LabelSmoothing(SMOOTH, PAD)(lp, i["trg"].cuda())
+            rs = LabelSmoothing(SMOOTH, PAD).row_sums(lp, i["trg"].cuda())
+        else:
+            out = BiasedKL(SMOOTH, PAD)(lp, i["trg"].cuda(), i["samp"].cuda(), i["off"].clone().cuda())
+            rs = BiasedKL(SMOOTH, PAD).row_sums(lp, i["trg"].cuda(), i["samp"].cuda(), i["off"].clone().cuda())
+        (out * gl[name]["w"].cuda()).sum().backward()
+        assert rel(out, gl[name]["out"]) < TIGHT
+        assert rel(lp.grad, gl[name]["dpred"]) < TIGHT
+        assert rel(rs, gl[name]["out"].sum(-1)) < TIGHT
+
+
 def test_kl_rowsum_backward_full_vocab(gpu_lib):
     from bmhrl_b200 import ops
     g = _g(8)

@@ -41,6 +41,25 @@ def test_losses(golden):
     assert rel(o, r["out"]) < TOL and rel(probs.grad, r["dprobs"]) < TOL and rel(cv.grad, r["dcritic"]) < TOL
 
 
+def test_losses_only_row0_padded(golden):
+    """The reference zeroes pad rows only `if mask.sum() > 0` over the flat row INDICES of the pad targets
+    (loss/label_smoothing.py:26-30): a lone pad target in flat row 0 keeps its smoothed distribution."""
+    g = golden["losses_row0"]
+    i = g["inputs"]
+    assert int(i["trg"][0, 0]) == PAD and int((i["trg"] == PAD).sum()) == 1
+    for name in ("ls", "bkl"):
+        lp = torch.log_softmax(i["logits"].clone().requires_grad_(True), -1)
+        lp.retain_grad()
+        if name == "ls":
+            o = O.label_smoothing_kl(lp, i["trg"], SMOOTH, PAD)
+        else:
+            o = O.biased_kl_divergence(lp, i["trg"], i["samp"], i["off"].clone(), SMOOTH, PAD)
+        (o * g[name]["w"]).sum().backward()
+        assert float(g[name]["out"][0].abs().sum()) > 0  # row 0 was NOT zeroed by the reference
+        assert rel(o, g[name]["out"]) < TOL
+        assert rel(lp.grad, g[name]["dpred"]) < TOL
+
+
 def test_expand_goals(golden):
     for c in golden["expand_goals"]:
         x = c["x"].clone().requires_grad_(True)
