@@ -173,3 +173,30 @@ def test_tc_attention_core_matches_fp32(tf32, B, H, Sq, Sk, D, kind, p):
     LIB.call("bmhrl_tc_tuning", 0, 0)
     for a, b, name in zip(outs["tf32"], outs["fp32"], ("o", "dq", "dk", "dv")):
         assert rel(a, b) < 3e-3, (name, rel(a, b))
+
+
+def test_linear_used_twice_accumulates_both_weight_gradients(tf32):
+    """One nn.Linear applied twice in one forward (the reference's mixed_prediction path does that with the embedder):
+    both dW GEMMs accumulate with beta = 1 into the SAME FusedAdam slice.  They must be ordered (one wgrad stream per
+    destination), otherwise the plain read-add-write epilogue loses updates.  Checked against torch in both modes."""
+    import torch.nn as nn
+    g = _g(17)
+    M, K, N = 2048, 1024, 1024
+    for mode in ("tf32", "fp32"):
+        tf32.set_math_mode(mode)
+        lin = nn.Linear(K, N).cuda()
+        opt = tf32.FusedAdam(lin.parameters())
+        x1, x2 = torch.randn(M, K, generator=g).cuda(), torch.randn(M, K, generator=g).cuda()
+        w1, w2 = torch.randn(M, N, generator=g).cuda(), torch.randn(M, N, generator=g).cuda()
+        ref = w1.t() @ x1 + w2.t() @ x2
+        refb = w1.sum(0) + w2.sum(0)
+        assert tf32.CONCURRENT
+        for _ in range(8):
+            opt.zero_grad()
+            y = (tf32.linear(x1, lin.weight, lin.bias) * w1).sum() + (tf32.linear(x2, lin.weight, lin.bias) * w2).sum()
+            y.backward()
+            tf32.join_side_streams(x1.device)
+            torch.cuda.synchronize()
+            assert rel(lin.weight.grad, ref) < (TF32_TOL if mode == "tf32" else 2e-5)
+            assert rel(lin.bias.grad, refb) < 2e-5
+    tf32.set_math_mode("tf32")
