@@ -55,6 +55,7 @@ def cpu_step_fn(workload, threads):
     as the reported CPU baseline."""
     from oracle import bmhrl_oracle as O
     from bmhrl_b200 import synth
+    O.DROPOUT_P = 0.1  # the benchmark's dropout, at the reference's dropout sites (timing only)
     torch.set_num_threads(threads)
     shapes, vshapes = agent_shapes()
     sd = synth.fill_state_dict(shapes, seed=1234)
@@ -117,6 +118,12 @@ def time_cpu(workload, steps, warmup, threads):
     return ts[len(ts) // 2]
 
 
+CPU_PORT_NOTE = ("CPU arm = oracle/bmhrl_oracle.py, a functional-PyTorch restatement of the reference step (kind 'port') with "
+                 "dropout 0.1 at the reference's dropout sites: no nn.Module overhead, no debug prints, no per-call "
+                 "fp64 positional table copy -- it is FASTER than the reference's own modules on the same cores (survey "
+                 "probe: 15-23 clips/s on 8 threads), so ratios against it are conservative")
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -127,21 +134,22 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "clips/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": med * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.workload),
+            "config": dict(workload_config(args.workload), note=CPU_PORT_NOTE),
             "cpu_baseline": {"value": val, "unit": "clips/s", "cores": threads, "kind": "port",
                              "sample": f"{args.steps} full B=16 steps (median) of the oracle port of the reference "
-                                       f"step: fwd + loss + bwd + Adam, fp32, torch CPU, {threads} threads"},
+                                       f"step: fwd + loss + bwd + Adam, fp32, torch CPU, {threads} threads, "
+                                       f"dropout 0.1 at the reference's dropout sites"},
             "e2e": {"value": val, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
-def workload_config(workload):
+def workload_config(workload, dropout=0.1):
     names = {"warmstart": "warm-start KL (label-smoothing) caption train step",
              "worker": "BMHRL RL step, worker phase (REINFORCE-biased KL + value fn)",
              "manager": "BMHRL RL step, manager phase (REINFORCE-biased KL + value fn)"}
     return {"workload": f"{names[workload]}, B=16/GPU, Sv=30, Sa=80, L=20, V=10172, d_model=1024, H=4, N=2, "
-                        f"synthetic I3D(1024 rgb+flow)+VGGish(128), random-init BMHRL, dropout 0.1, Adam lr 1e-4",
-            "phase": workload, "batch_per_gpu": SHAPE["B"],
+                        f"synthetic I3D(1024 rgb+flow)+VGGish(128), random-init BMHRL, dropout {dropout}, Adam lr 1e-4",
+            "phase": workload, "batch_per_gpu": SHAPE["B"], "dropout": dropout,
             "l2": "no explicit flush: parameters + Adam state + gradients touched every step (~1 GB) exceed the 126 MB L2"}
 
 
@@ -230,6 +238,10 @@ def gemm_roofline(recorded, iters=20):
     sec = e0.elapsed_time(e1) / 1e3 / iters
     n = len(calls)
     return flops / n, sec / n, n
+
+
+TRAFFIC_SOURCE = ("profiles/r01_gemm_traffic.json (committed ncu capture of the same command, dram__bytes_read.sum + "
+                  "dram__bytes_write.sum per GEMM launch; not re-measured in this run: ncu cannot run inside a timed bench)")
 
 
 def gemm_traffic():
@@ -403,6 +415,45 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     sec, sec_e2e = float(t[0]), float(t[1])
 
+    # ---- BASELINE config 3: the worker and manager RL steps, same model / process, their own graphs (all ranks)
+    phases = {}
+    if args.workload == "warmstart" and not args.scorer and not args.no_phases:
+        main_runner = runner
+        for ph in ("worker", "manager"):
+            {"worker": tr.teach_worker, "manager": tr.teach_manager}[ph]()
+            r2 = StepRunner(tr, ph, host[0], use_graph=not args.no_graph, warmup=3)
+            for _ in range(args.warmup):
+                r2.replay()
+            barrier()
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
+            for _ in range(args.steps):
+                r2.replay()
+            p1.record()
+            barrier()
+            psec = p0.elapsed_time(p1) / 1e3
+            for i in range(args.warmup):
+                float(r2.step(host[i % n_host])[0])
+            barrier()
+            p0.record()
+            for i in range(args.steps):
+                float(r2.step(host[i % n_host])[0])
+            p1.record()
+            barrier()
+            psec_e2e = p0.elapsed_time(p1) / 1e3
+            tt = torch.tensor([psec, psec_e2e], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            psec, psec_e2e = float(tt[0]), float(tt[1])
+            nclips = SHAPE["B"] * world * args.steps
+            phases[ph] = {"ms_per_step": psec / args.steps * 1e3, "value": nclips / psec, "unit": "clips/s",
+                          "e2e": {"value": nclips / psec_e2e, "ms_per_step": psec_e2e / args.steps * 1e3},
+                          "launches_per_step": getattr(r2, "captured_launches", None),
+                          "config": workload_config(ph)["workload"]}
+            del r2
+        tr.teach_warmstart()
+        runner = main_runner
+
     if rank == 0:
         pk, pk_src = peaks()
         graph_launches = getattr(runner, "captured_launches", None)
@@ -410,7 +461,10 @@ def run_gpu(args):
         ach = fl / sl / 1e12 if sl > 0 else 0.0
         peak = pk["bf16_tflops_sustained"]
         cpu_threads = os.cpu_count() or 1
-        cpu_med = time_cpu(args.workload, 5, 1, cpu_threads) if not args.no_cpu else None
+        # N > 1: torchrun pins OMP_NUM_THREADS=1 and the other ranks would idle in the barrier for minutes: the CPU
+        # baseline is an N=1 number (rank 0 of a single-GPU run), as the bench contract says
+        do_cpu = not args.no_cpu and world == 1
+        cpu_med = time_cpu(args.workload, 5, 1, cpu_threads) if do_cpu else None
         clips = SHAPE["B"] * world * args.steps
         line = {
             "metric": METRIC, "value": clips / sec, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
@@ -427,7 +481,7 @@ def run_gpu(args):
                                     "kind::tf32, TMEM accumulators)") if args.math == "tf32" else
                                    "projection/FFN/vocab/gradient GEMMs (gemm_simt_kernel, fp32 SIMT)",
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
-                         "traffic": gemm_traffic(), "peak_source": f"{pk_src} bf16_tflops_sustained",
+                         "traffic": gemm_traffic(), "traffic_source": TRAFFIC_SOURCE, "peak_source": f"{pk_src} bf16_tflops_sustained",
                          "launches_per_step": ng, "avg_launch_us": sl * 1e6, "flops_per_launch": fl},
             "step_hbm_roofline": {"algorithmic_bytes": step_bytes(args.workload), "peak_gbs": pk["hbm_gbs"],
                                   "frac": step_bytes(args.workload) / (sec / args.steps) / 1e9 / pk["hbm_gbs"]},
@@ -441,9 +495,20 @@ def run_gpu(args):
             line["e2e"]["d2h_bytes_per_step"] = 4 + 8 * SHAPE["B"] * SHAPE["L"] + 4 * SHAPE["B"] * SHAPE["L"]
         if cpu_med is not None:
             line["cpu_baseline"] = {"value": SHAPE["B"] / cpu_med, "unit": "clips/s", "cores": cpu_threads,
-                                    "kind": "port",
+                                    "kind": "port", "dropout": 0.1, "note": CPU_PORT_NOTE,
                                     "sample": "5 full B=16 steps (median, 1 warm-up) of the oracle port of the "
                                               "reference step on the host cores: fwd + loss + bwd + Adam, fp32"}
+        for ph, rec in phases.items():
+            rec["step_hbm_roofline"] = {"algorithmic_bytes": step_bytes(ph), "peak_gbs": pk["hbm_gbs"],
+                                        "frac": step_bytes(ph) / (rec["ms_per_step"] / 1e3) / 1e9 / pk["hbm_gbs"]}
+            if do_cpu:
+                med = time_cpu(ph, 3, 1, cpu_threads)
+                rec["cpu_port"] = {"value": SHAPE["B"] / med, "unit": "clips/s", "cores": cpu_threads, "dropout": 0.1,
+                                   "sample": "3 full B=16 steps (median, 1 warm-up) of the oracle port of this phase"}
+        if phases:
+            line["phases"] = phases
+        if world == 1 and not args.no_eager:
+            line["eager_module_swap"] = eager_module_swap(args, cfg, ds, sd, host, dev)
         print(json.dumps(line), flush=True)
     if world > 1:
         # The step graph holds captured NCCL work: tearing the communicator down (destroy_process_group, or the
@@ -453,6 +518,49 @@ def run_gpu(args):
         sys.stdout.flush()
         sys.stderr.flush()
         os._exit(0)
+
+
+def eager_module_swap(args, cfg, ds, sd, host, dev, steps=10):
+    """INTEGRATION.md section 1 as a maintainer of the reference gets it: the reference's own warm-start loop body
+    (epoch_loops/captioning_bmrl_loops.py:1148-1160) over the swapped-in modules -- eager launches through
+    Python + ctypes, the materialising LabelSmoothing.forward, torch.optim.Adam, no StepRunner, no CUDA graph."""
+    from bmhrl_b200 import ops
+    from bmhrl_b200.loss.label_smoothing import LabelSmoothing
+    from bmhrl_b200.model.bm_hrl_agent import BMHrlAgent
+    from bmhrl_b200.model.masking import make_masks
+    model = BMHrlAgent(cfg, ds)
+    model.load_state_dict(sd)
+    model = model.to(dev).train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    crit = LabelSmoothing(SMOOTH, PAD)
+    b = {k: v.to(dev) for k, v in host[0].items()}
+
+    def step():
+        ops.new_rng_epoch(dev)
+        opt.zero_grad()
+        cap = b["caption"]
+        cin, y = cap[:, :-1], cap[:, 1:]
+        masks = make_masks({"rgb": b["rgb"], "flow": b["flow"], "audio": b["audio"]}, cin, "audio_video", PAD)
+        pred = model((b["rgb"] + b["flow"], b["audio"]), cin, masks)[0]
+        n_tokens = (y != PAD).sum()
+        loss = torch.sum(crit(pred, y)) / n_tokens
+        loss.backward()
+        ops.join_side_streams(dev)
+        opt.step()
+        return loss
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss = step()
+    last = float(loss)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / steps * 1e3
+    del model, opt
+    return {"ms_per_step": ms, "value": SHAPE["B"] / ms * 1e3, "unit": "clips/s", "steps": steps, "loss": last,
+            "what": "reference loop body over the swapped-in bmhrl_b200 modules: eager, torch.optim.Adam, materialised "
+                    "(B*L,V) loss, wall clock incl. Python/ctypes overhead (math mode " + args.math + ")"}
 
 
 def step_bytes(workload):
@@ -473,6 +581,8 @@ def main():
                     help="tf32: tcgen05 tensor-core GEMMs (default); fp32: exact SIMT contractions")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-phases", action="store_true", help="skip the worker / manager RL-step phases (config 3)")
+    ap.add_argument("--no-eager", action="store_true", help="skip the eager module-swap measurement")
     ap.add_argument("--scorer", default=None, choices=["cider", "bleu"],
                     help="RL workloads: score the sampled tokens with the real host reward scorer inside the step")
     args = ap.parse_args()

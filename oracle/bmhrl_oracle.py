@@ -38,10 +38,21 @@ def positional_table(seq_len, d_model):
     return torch.where(even, torch.sin(ang), torch.cos(ang))
 
 
+# Dropout probability at the reference's dropout sites (PositionalEncoder model/blocks.py:112, attention output
+# model/multihead_attention.py:29-30, ResidualConnection model/blocks.py:142-144, FFN model/blocks.py:183, Manager
+# model/bm_hrl_agent.py:440).  0 for every parity check (the goldens are dropout-free); bench.py's timed CPU arm sets
+# it to the benchmark's 0.1 so that both arms do the same work (torch's own CPU RNG: timing only, no parity claim).
+DROPOUT_P = 0.0
+
+
+def _drop(x):
+    return F.dropout(x, DROPOUT_P, training=True) if DROPOUT_P > 0 else x
+
+
 def add_positional(x):
-    """model/blocks.py:105-112 with dropout p=0 (table cast to x's dtype by type_as)."""
+    """model/blocks.py:105-112 (table cast to x's dtype by type_as), dropout p = DROPOUT_P."""
     S, D = x.shape[-2], x.shape[-1]
-    return x + positional_table(S, D).to(x.dtype)[None]
+    return _drop(x + positional_table(S, D).to(x.dtype)[None])
 
 
 def embed_tokens(sd, tokens, prefix="emb_C.embedder."):
@@ -63,7 +74,7 @@ def layer_norm(sd, prefix, x, eps=1e-5):
 
 def ffn(sd, prefix, x):
     """model/blocks.py:175-187 with dropout p=0: fc2(relu(fc1(x)))."""
-    return linear(sd, prefix + "fc2.", torch.relu(linear(sd, prefix + "fc1.", x)))
+    return linear(sd, prefix + "fc2.", _drop(torch.relu(linear(sd, prefix + "fc1.", x))))
 
 
 # --------------------------------------------------------------------------------------------------
@@ -95,7 +106,7 @@ def attention_core(q, k, v, mask, causal=False):
             tril = torch.tril(torch.ones(Sk, Sk, dtype=torch.bool))
             s = s.masked_fill(~tril[None, None], NEG_FILL)
         s = s.masked_fill(~mask, NEG_FILL)
-    return torch.softmax(s, dim=-1) @ v
+    return _drop(torch.softmax(s, dim=-1) @ v)
 
 
 def mha(sd, prefix, Q, K, V, mask, H, causal=False):
@@ -122,7 +133,7 @@ def bm_encoder_layer(sd, p, M1, M2, M1_mask, M2_mask, H):
     """model/bm_hrl_agent.py:344-384: pre-LN residual blocks; cross attention uses LN(query) but the
     UN-normed other modality as key/value."""
     def res(i, mod, x, f):  # model/blocks.py:135-144
-        return x + f(layer_norm(sd, f"{p}res_layers_{mod}.{i}.norm.", x))
+        return x + _drop(f(layer_norm(sd, f"{p}res_layers_{mod}.{i}.norm.", x)))
 
     M1 = res(0, "M1", M1, lambda n: mha(sd, p + "self_att_M1.", n, n, n, M1_mask, H))
     M2 = res(0, "M2", M2, lambda n: mha(sd, p + "self_att_M2.", n, n, n, M2_mask, H))
@@ -144,11 +155,11 @@ def bm_encoder(sd, p, V, A, masks, H, N):
 def bm_fusion_layer(sd, p, C, mem_A, mem_V, masks, H):
     """model/bm_hrl_agent.py:73-117.  feed_forward exists but is never called (F11)."""
     n = layer_norm(sd, p + "res_layer_self_att.norm.", C)
-    C = C + mha(sd, p + "self_att.", n, n, n, masks["C_mask"], H)
-    Ca = C + mha(sd, p + "enc_att_A.", layer_norm(sd, p + "res_layer_enc_att_A.norm.", C), mem_A, mem_A,
-                 masks["A_mask"], H)
-    Cv = C + mha(sd, p + "enc_att_V.", layer_norm(sd, p + "res_layer_enc_att_V.norm.", C), mem_V, mem_V,
-                 masks["V_mask"], H)
+    C = C + _drop(mha(sd, p + "self_att.", n, n, n, masks["C_mask"], H))
+    Ca = C + _drop(mha(sd, p + "enc_att_A.", layer_norm(sd, p + "res_layer_enc_att_A.norm.", C), mem_A, mem_A,
+                       masks["A_mask"], H))
+    Cv = C + _drop(mha(sd, p + "enc_att_V.", layer_norm(sd, p + "res_layer_enc_att_V.norm.", C), mem_V, mem_V,
+                       masks["V_mask"], H))
     Ca = layer_norm(sd, p + "normCA.", Ca)
     Cv = layer_norm(sd, p + "normCV.", Cv)
     g = torch.sigmoid(torch.clamp(sd[p + "a_v_constant"], min=-2, max=2))
@@ -262,7 +273,7 @@ def expand_goals(x, seg):
 def manager_head(sd, manager_feat, seg, noise=None, p="manager."):
     """model/bm_hrl_agent.py:437-454 with dropout p=0.  `noise`: the explicit 64-d exploration vector
     (already including the -0.5*mean shift), or None when exploration is off."""
-    g = linear(sd, p + "linear.", manager_feat)
+    g = _drop(linear(sd, p + "linear.", manager_feat))
     if noise is not None:
         g = g + noise
     return expand_goals(g, seg)
