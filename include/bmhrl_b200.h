@@ -79,6 +79,44 @@ int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const float* Y, l
                               int M, int N, int act, float drop_p, const unsigned long long* rng_state,
                               unsigned int salt, int accumulate_db, void* stream);
 
+/* ---- contractions, bf16 operands (gemm_bf16.cu): the library's bf16 math mode ------------------------------------ */
+/* One problem of a grouped launch.  Every pointer is a device pointer; bf16 operands are 16-byte aligned with row pitches
+ * (lda / ldb, in ELEMENTS) that are multiples of 8; tails of M / N / K need no padding (TMA zero-fills them).
+ *   v(m,n) = alpha * sum_k A(m,k) B(n,k) + bias[n];  act (1 = ReLU);  gate: v = gate(m,n) > 0 ? v * gate_scale : 0
+ *            (the ReLU / dropout gradient gate: the saved forward output drop(relu(z)) is > 0 exactly where both let
+ *            the gradient through);  Philox dropout with element index m*N + n;  + resid(m,n);  + beta * C32(m,n)
+ *   C32 (fp32, optional) and / or C16 (bf16, optional) receive v.
+ * a_mn = 0: A(m,k) at A + m*lda + k (activations; dZ in dX = dZ W);  a_mn = 1: A(m,k) at A + k*lda + m (dZ^T in
+ * dW = dZ^T X).  b_mn = 0: B(n,k) at B + n*ldb + k (nn.Linear.weight (N,K));  b_mn = 1: B(n,k) at B + k*ldb + n (the
+ * weight in dX, X in dW).  seg_rows > 0: row m of the fp32 output goes to C32 / C32_seg1 / C32_seg2 for m / seg_rows =
+ * 0 / 1 / 2, at row m % seg_rows (dW of N-concatenated Q|K|V weights lands in three separate gradient slices).
+ * Replaces: linear_Q2d/K2d/V2d/d2Q (model/multihead_attention.py:70-72,89) -- Q|K|V as ONE N-concatenated problem --,
+ * fc1/fc2 with the ResidualConnection add (model/blocks.py:175-187,144), Manager.linear (model/bm_hrl_agent.py:439-440),
+ * WorkerCore.projection (model/bm_hrl_agent.py:464) and the aten mm calls of their backward. */
+typedef struct bmhrl_gemm_desc {
+    const void* A; long long lda; int a_mn;
+    const void* B; long long ldb; int b_mn;
+    int M, N, K;
+    float alpha;
+    const float* bias;
+    int act;
+    const void* gate; long long ldg; float gate_scale;
+    float drop_p; const unsigned long long* rng_state; unsigned int salt;
+    const float* resid; long long ldr;
+    float beta;
+    float* C32; long long ldc32;
+    void* C16; long long ldc16;
+    int seg_rows; float* C32_seg1; float* C32_seg2;
+} bmhrl_gemm_desc;
+int bmhrl_gemm_desc_bytes(void);   /* sizeof(bmhrl_gemm_desc): bindings check their mirror of the struct against it */
+/* 1..4 independent problems in ONE launch (tcgen05.mma kind::f16 into TMEM, TMA-staged operands, 128 x 128 / 128 x 64
+ * tiles; when the tiles alone leave most SMs idle a thread-block cluster of 2 / 4 CTAs splits K of every tile and reduces
+ * the partial accumulators through distributed shared memory: no atomics, bit-reproducible). */
+int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* problems, int n_problems, void* stream);
+/* tuning / test hook: force the tile width (0 = cost model, 64, 128), the K split (0 = cost model, 1, 2, 4) and the
+ * pipeline depth (0 = auto, 2..6). */
+int bmhrl_gemm_bf16_tuning(int force_bn, int force_split, int force_stages);
+
 /* ---- K2: residual + LayerNorm, gated mix (norm.cu) ---------------------------------------------------------- */
 /* z = x (+ resid); y = LayerNorm(z) (eps, affine).  z_out may be NULL.  ResidualConnection model/blocks.py:135-144,
  * normCA/normCV model/bm_hrl_agent.py:107-108, post-LN model/encoder.py:64-68, model/decoder.py:77-99. */
