@@ -112,3 +112,31 @@ def gemm_group(problems):
         RECORD.extend((p.M, p.N, p.K, p.a_mn, p.b_mn) for p in problems)
     arr = (GemmDesc * n)(*problems)
     LIB.call("bmhrl_gemm_bf16_group", ctypes.cast(arr, ctypes.c_void_p), n, _stream())
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# one-tile fused attention (attn16.cu)
+# ----------------------------------------------------------------------------------------------------------------
+def attn16_supported(Sq, Sk, dk):
+    return (Sq <= 128 and Sk <= 128 and dk in (64, 128, 256, 512) and
+            LIB.raw("bmhrl_attn16_smem_bytes")(1, Sq, Sk, dk) <= 220 * 1024)
+
+
+def attn16_fwd(q, k, v, mask_u8, mask_kind, causal, B, H, Sq, Sk, dk, o, lse2, drop_p=0.0, rng=None, salt=0):
+    """q (B*Sq, .), k / v (B*Sk, .) bf16 matrices (column slices of the projection output are fine) -> o (B*Sq, H*dk)
+    bf16 and lse2 (B,H,Sq) fp32, both preallocated."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v"), (o, "o")):
+        _mat16(t, n)
+    LIB.call("bmhrl_attn16_fwd", q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+             None if mask_u8 is None else mask_u8.data_ptr(), int(mask_kind), int(bool(causal)), o.data_ptr(), o.stride(0),
+             lse2.data_ptr(), B, H, Sq, Sk, dk, float(drop_p), rng.data_ptr() if drop_p > 0 else None, int(salt), _stream())
+
+
+def attn16_bwd(q, k, v, do, lse2, mask_u8, mask_kind, causal, B, H, Sq, Sk, dk, dq, dk_, dv):
+    """dq / dk_ / dv: preallocated bf16 matrices (or column slices of one N-concatenated dZ buffer)."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v"), (do, "do"), (dq, "dq"), (dk_, "dk"), (dv, "dv")):
+        _mat16(t, n)
+    LIB.call("bmhrl_attn16_bwd", q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+             do.data_ptr(), do.stride(0), lse2.data_ptr(), None if mask_u8 is None else mask_u8.data_ptr(),
+             int(mask_kind), int(bool(causal)), dq.data_ptr(), dq.stride(0), dk_.data_ptr(), dk_.stride(0), dv.data_ptr(),
+             dv.stride(0), B, H, Sq, Sk, dk, _stream())

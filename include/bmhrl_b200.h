@@ -191,6 +191,29 @@ long long bmhrl_attn_bwd_bf16_ws_bytes(int B, int H, int Sq, int Sk);
  * a pass that is switched off is returned as ZEROS (never uninitialised memory). */
 int bmhrl_attn_bwd_bf16_tuning(int passes);
 
+/* ---- K1, bf16 math mode, TRAINING path: one-tile fused attention, forward and backward (attn16.cu) ------------------- */
+/* attention() model/multihead_attention.py:7-31 and its gradients for sequences that fit one tile (Sq, Sk <= 128; the
+ * caption-side attentions always do, the encoder's do at the benchmark shapes), one CTA per (batch, head): S = Q K^T and
+ * O = P V on tcgen05 with the probabilities handed over in TMEM; nothing of size (B,H,Sq,Sk) is ever stored.
+ * Q (B*Sq, ldq), K / V (B*Sk, ld?), O (B*Sq, ldo): bf16 matrices, head h = columns [h dk, (h+1) dk) -- typically column
+ * slices of the N-concatenated Q|K|V projection output; pitches in ELEMENTS (multiples of 8).  dk in {64,128,256,512}.
+ * mask_kind / causal as bmhrl_mha_core_fwd_f32.  lse2: fp32 (B,H,Sq), base-2 log-sum-exp of the masked scaled scores
+ * (saved for backward).  Dropout (Philox, element index row*H*dk + column) is applied to the output like the reference.
+ * Returns BMHRL_ERR_UNSUPPORTED when the tiles do not fit (callers then take bmhrl_attn_fwd_bf16 / bmhrl_attn_bwd_bf16). */
+int bmhrl_attn16_fwd(const void* Q, long long ldq, const void* K, long long ldk, const void* V, long long ldv,
+                     const unsigned char* mask, int mask_kind, int causal, void* O, long long ldo, float* lse2, int B,
+                     int H, int Sq, int Sk, int dk, float drop_p, const unsigned long long* rng_state, unsigned int salt,
+                     void* stream);
+/* dQ (B*Sq, lddq), dK / dV (B*Sk, ldd?) bf16 from Q, K, V, lse2 and dO.  dO must ALREADY carry the forward's dropout mask
+ * and 1/(1-p) scale (the dX GEMM of the out-projection applies it in its epilogue: bmhrl_gemm_desc.drop_p with the same
+ * salt).  delta = rowsum(P o dP) is formed in-kernel (the whole row is resident), so neither O nor P is needed. */
+int bmhrl_attn16_bwd(const void* Q, long long ldq, const void* K, long long ldk, const void* V, long long ldv,
+                     const void* dO, long long lddo, const float* lse2, const unsigned char* mask, int mask_kind,
+                     int causal, void* dQ, long long lddq, void* dK, long long lddk, void* dV, long long lddv, int B, int H,
+                     int Sq, int Sk, int dk, void* stream);
+/* dynamic shared memory the one-tile kernels need (forward: backward = 0); above 220 KB the shape is unsupported */
+long long bmhrl_attn16_smem_bytes(int backward, int Sq, int Sk, int dk);
+
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
 int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */
 int bmhrl_log_softmax_bwd_f32(const float* dy, const float* y, float* dx, long long rows, int V, void* stream);
