@@ -244,6 +244,40 @@ TRAFFIC_SOURCE = ("profiles/r01_gemm_traffic.json (committed ncu capture of the 
                   "dram__bytes_write.sum per GEMM launch; not re-measured in this run: ncu cannot run inside a timed bench)")
 
 
+def gemm_roofline16(recorded, iters=20):
+    """bf16 math mode: re-issues every problem of the step's grouped GEMM launches (exact M, N, K and operand majors,
+    scratch operands, one problem per launch) and times the sequence with CUDA events on the launching stream."""
+    from bmhrl_b200 import ops16
+    if not recorded:
+        return 0.0, 0.0, 0
+    dev = torch.device("cuda")
+    probs, flops = [], 0.0
+    for (M, N, K, a_mn, b_mn) in recorded:
+        flops += 2.0 * M * N * K
+        A = ops16.zeros16(K, M, dev) if a_mn else ops16.zeros16(M, K, dev)
+        B = ops16.zeros16(K, N, dev) if b_mn else ops16.zeros16(N, K, dev)
+        A.normal_()
+        B.normal_()
+        probs.append(ops16.gemm_problem(A, a_mn, B, b_mn, M, N, K, C16=ops16.empty16(M, N, dev)))
+    torch.cuda.synchronize()
+
+    def run():
+        for p in probs:
+            ops16.gemm_group([p])
+    for _ in range(3):
+        run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) / 1e3 / iters
+    n = len(probs)
+    return flops / n, sec / n, n
+
+
 def gemm_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch (average over the GEMM launches of one training step),
     from the committed ncu capture profiles/r01_gemm_traffic.json (see its `command`); None when absent."""
@@ -350,9 +384,11 @@ def run_gpu(args):
     # shapes of the GEMM launches of one eager step (for the roofline section)
     eager = StepRunner(tr, args.workload, host[0], use_graph=False)
     eager.replay()
-    ops.RECORD = []
+    from bmhrl_b200 import ops16
+    ops.RECORD, ops16.RECORD = [], []
     eager.replay()
     per_step_gemms, ops.RECORD = ops.RECORD, None
+    per_step_gemms16, ops16.RECORD = ops16.RECORD, None
     del eager
     if args.scorer:
         # the REAL reward scorer in the loop: synthetic vocabulary, a 37k-caption Zipf
@@ -457,7 +493,10 @@ def run_gpu(args):
     if rank == 0:
         pk, pk_src = peaks()
         graph_launches = getattr(runner, "captured_launches", None)
-        fl, sl, ng = gemm_roofline(per_step_gemms)
+        if args.math == "bf16":
+            fl, sl, ng = gemm_roofline16(per_step_gemms16)
+        else:
+            fl, sl, ng = gemm_roofline(per_step_gemms)
         ach = fl / sl / 1e12 if sl > 0 else 0.0
         peak = pk["bf16_tflops_sustained"]
         cpu_threads = os.cpu_count() or 1
@@ -469,7 +508,7 @@ def run_gpu(args):
         line = {
             "metric": METRIC, "value": clips / sec, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "tf32" if args.math == "tf32" else "f32", "data": "synthetic",
+            "vs_baseline": None, "dtype": {"bf16": "bf16", "tf32": "tf32", "fp32": "f32"}[args.math], "data": "synthetic",
             "config": workload_config(args.workload),
             "e2e": {"value": clips / sec_e2e, "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3, "wall_ms_per_step": wall_e2e / args.steps * 1e3},
@@ -477,9 +516,12 @@ def run_gpu(args):
             "launches_per_step": graph_launches,
             "clocks": clk,
             "roofline": {"bound": "tensor",
-                         "kernel": ("projection/FFN/vocab/gradient GEMMs (gemm_tf32_tc_kernel: TMA + tcgen05.mma "
-                                    "kind::tf32, TMEM accumulators)") if args.math == "tf32" else
-                                   "projection/FFN/vocab/gradient GEMMs (gemm_simt_kernel, fp32 SIMT)",
+                         "kernel": {"bf16": "projection/FFN/vocab/gradient GEMMs (gemm_bf16_tc_kernel: grouped, TMA + "
+                                            "tcgen05.mma kind::f16 bf16 operands, 128x128/64 tiles, TMEM accumulators, "
+                                            "cluster split-K over DSMEM)",
+                                    "tf32": "projection/FFN/vocab/gradient GEMMs (gemm_tf32_tc_kernel: TMA + tcgen05.mma "
+                                            "kind::tf32, TMEM accumulators)",
+                                    "fp32": "projection/FFN/vocab/gradient GEMMs (gemm_simt_kernel, fp32 SIMT)"}[args.math],
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
                          "traffic": gemm_traffic(), "traffic_source": TRAFFIC_SOURCE, "peak_source": f"{pk_src} bf16_tflops_sustained",
                          "launches_per_step": ng, "avg_launch_us": sl * 1e6, "flops_per_launch": fl},
@@ -577,8 +619,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="warmstart", choices=["warmstart", "worker", "manager"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--math", default="tf32", choices=["tf32", "fp32"],
-                    help="tf32: tcgen05 tensor-core GEMMs (default); fp32: exact SIMT contractions")
+    ap.add_argument("--math", default="bf16", choices=["bf16", "tf32", "fp32"],
+                    help="bf16: bf16 tensor-core operands, grouped tcgen05 GEMMs + fused attention fwd/bwd (default); "
+                         "tf32: fp32 storage, tcgen05 kind::tf32 GEMMs; fp32: exact SIMT contractions")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-phases", action="store_true", help="skip the worker / manager RL-step phases (config 3)")

@@ -3,6 +3,7 @@
 // Reference: VocabularyEmbedder model/blocks.py:44-48, PositionalEncoder model/blocks.py:105-112,
 // Manager.expand_goals model/bm_hrl_agent.py:415-429, biased_kl() manager loop
 // epoch_loops/captioning_bmrl_loops.py:299-317, torch.optim.Adam scripts/train_rl_captioning_module.py:81-83.
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "../../include/bmhrl_b200.h"
 
@@ -353,6 +354,10 @@ struct AdamChunk {
 };
 constexpr int ADAM_CHUNK = 8192;
 
+// Optional weight shadows (bf16 math mode): shadow[t] != NULL makes the kernel also write the UPDATED parameter into a
+// second buffer -- bf16 (kind 0; the tensor-core operand copy of a weight matrix, (rows, shadow_cols) with row pitch
+// shadow_ld) or fp32 (kind 1; the N-concatenated bias of a fused Q|K|V projection).  Adam touches every updated weight
+// anyway, so the shadows cost their own bytes and no extra pass.
 __global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restrict__ params,
                                                          const float* const* __restrict__ grads,
                                                          float* const* __restrict__ exp_avg,
@@ -361,7 +366,11 @@ __global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restric
                                                          const int* __restrict__ chunk_tensor,
                                                          const int* __restrict__ chunk_start,
                                                          const float* __restrict__ step_ptr, float lr, float beta1,
-                                                         float beta2, float eps, float grad_scale) {
+                                                         float beta2, float eps, float grad_scale,
+                                                         void* const* __restrict__ shadow,
+                                                         const int* __restrict__ shadow_cols,
+                                                         const int* __restrict__ shadow_ld,
+                                                         const int* __restrict__ shadow_kind) {
     const int t = chunk_tensor[blockIdx.x];
     const long long s0 = chunk_start[blockIdx.x];
     const long long n = numels[t];
@@ -376,13 +385,62 @@ __global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restric
     const float inv_sqrt_bc2 = rsqrtf(bc2);
     long long end = s0 + ADAM_CHUNK;
     if (end > n) end = n;
+    void* sh = shadow ? shadow[t] : nullptr;
+    const int sk = sh ? shadow_kind[t] : 0;
+    const int scols = sh ? shadow_cols[t] : 1, sld = sh ? shadow_ld[t] : 1;
+    auto upd = [&](float pi, float gi, float& mi, float& vi) {
+        gi *= grad_scale;
+        mi = beta1 * mi + (1.f - beta1) * gi;
+        vi = beta2 * vi + (1.f - beta2) * gi * gi;
+        return pi - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+    };
+    const bool vec = ((((uintptr_t)p) | ((uintptr_t)g) | ((uintptr_t)m) | ((uintptr_t)v)) & 15u) == 0 &&
+                     (!sh || (sk == 1 ? ((uintptr_t)sh & 15u) == 0 : (((uintptr_t)sh & 7u) == 0 && scols == sld)));
+    if (vec) {
+        const long long e4 = s0 + ((end - s0) & ~3ll);
+        for (long long i = s0 + 4 * threadIdx.x; i < e4; i += 4 * 256) {
+            const float4 g4 = ld_f4(g + i), p4 = ld_f4(p + i);
+            float4 m4 = ld_f4(m + i), v4 = ld_f4(v + i), o;
+            o.x = upd(p4.x, g4.x, m4.x, v4.x);
+            o.y = upd(p4.y, g4.y, m4.y, v4.y);
+            o.z = upd(p4.z, g4.z, m4.z, v4.z);
+            o.w = upd(p4.w, g4.w, m4.w, v4.w);
+            st_f4(m + i, m4);
+            st_f4(v + i, v4);
+            st_f4(p + i, o);
+            if (sh) {
+                if (sk == 1) {
+                    st_f4(reinterpret_cast<float*>(sh) + i, o);
+                } else {
+                    uint2 w;
+                    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w.x) : "f"(o.y), "f"(o.x));
+                    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w.y) : "f"(o.w), "f"(o.z));
+                    *reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(sh) + i) = w;
+                }
+            }
+        }
+        if (threadIdx.x < (int)(end - e4)) {  // tail of the last chunk of a tensor whose numel is not a multiple of 4
+            const long long i = e4 + threadIdx.x;
+            float mi = m[i], vi = v[i];
+            const float o = upd(p[i], g[i], mi, vi);
+            m[i] = mi; v[i] = vi; p[i] = o;
+            if (sh) {
+                if (sk == 1) reinterpret_cast<float*>(sh)[i] = o;
+                else reinterpret_cast<__nv_bfloat16*>(sh)[i] = __float2bfloat16(o);
+            }
+        }
+        return;
+    }
     for (long long i = s0 + threadIdx.x; i < end; i += 256) {
-        const float gi = g[i] * grad_scale;
-        const float mi = beta1 * m[i] + (1.f - beta1) * gi;
-        const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        float mi = m[i], vi = v[i];
+        const float o = upd(p[i], g[i], mi, vi);
         m[i] = mi;
         v[i] = vi;
-        p[i] -= step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+        p[i] = o;
+        if (sh) {
+            if (sk == 1) reinterpret_cast<float*>(sh)[i] = o;
+            else reinterpret_cast<__nv_bfloat16*>(sh)[(i / scols) * sld + (i % scols)] = __float2bfloat16(o);
+        }
     }
 }
 
@@ -553,7 +611,9 @@ extern "C" int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const 
                      (act != 1 || ((ldy % 4 == 0) && aligned16(Y)));
     const int cols_per_block = vec ? 128 : 32;
     const int col_blocks = (N + cols_per_block - 1) / cols_per_block;
-    int splits = (2 * 148 + col_blocks - 1) / col_blocks;           // ~2 blocks per SM
+    // One row split whenever a bias gradient is produced: the column sums are then added in a fixed order inside one
+    // CTA and the single RED per column lands on a value no other CTA touches -> bit-reproducible bias gradients.
+    int splits = db ? 1 : (2 * 148 + col_blocks - 1) / col_blocks;  // without db: ~2 blocks per SM
     const int max_splits = (M + 7) / 8;
     if (splits > max_splits) splits = max_splits;
     const int rows_per_block = ((M + splits - 1) / splits + 7) / 8 * 8;
@@ -580,7 +640,25 @@ extern "C" int bmhrl_adam_multi_f32(float* const* params, const float* const* gr
     if (n_chunks <= 0) return BMHRL_OK;
     adam_multi_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
                                                                   chunk_tensor, chunk_start, step_counts, lr, beta1,
-                                                                  beta2, eps, grad_scale);
+                                                                  beta2, eps, grad_scale, nullptr, nullptr, nullptr, nullptr);
+    BMHRL_POST_LAUNCH("adam_multi");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_adam_multi_shadow_f32(float* const* params, const float* const* grads, float* const* exp_avg,
+                                           float* const* exp_avg_sq, const long long* numels, const int* chunk_tensor,
+                                           const int* chunk_start, int n_chunks, const float* step_counts, float lr,
+                                           float beta1, float beta2, float eps, float grad_scale, void* const* shadow,
+                                           const int* shadow_cols, const int* shadow_ld, const int* shadow_kind,
+                                           void* stream) {
+    BMHRL_CHECK_ARG(params && grads && exp_avg && exp_avg_sq && numels && chunk_tensor && chunk_start && step_counts,
+                    "bmhrl_adam_multi_shadow_f32: null pointer");
+    BMHRL_CHECK_ARG(!shadow || (shadow_cols && shadow_ld && shadow_kind), "bmhrl_adam_multi_shadow_f32: shadow tables");
+    if (n_chunks <= 0) return BMHRL_OK;
+    adam_multi_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
+                                                                  chunk_tensor, chunk_start, step_counts, lr, beta1,
+                                                                  beta2, eps, grad_scale, shadow, shadow_cols, shadow_ld,
+                                                                  shadow_kind);
     BMHRL_POST_LAUNCH("adam_multi");
     return BMHRL_OK;
 }

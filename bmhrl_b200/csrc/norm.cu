@@ -237,6 +237,79 @@ __global__ void __launch_bounds__(LN_WARPS * 32) layernorm_bwd_fused_kernel(
     }
 }
 
+// Deterministic backward in ONE launch: blocks [0, row_blocks) compute dx (one warp per row, two passes over dy / x),
+// blocks [row_blocks, row_blocks + ceil(D / 32)) each own a 32-column strip and ALL rows and produce dgamma / dbeta with a
+// fixed summation order (8 warps stride the rows, shared-memory combine).  No atomics: gradients are bit-reproducible
+// run to run.  The strips re-read dy / x from L2 (2 x rows x D x 4 B, a few MB).
+__global__ void __launch_bounds__(256) layernorm_bwd_det_kernel(
+    const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
+    const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ dres,
+    float* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int D, int vec,
+    int row_blocks, int accumulate) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if ((int)blockIdx.x < row_blocks) {
+        const int row = blockIdx.x * 8 + w;
+        if (row >= rows) return;
+        const float* dyr = dy + (long long)row * D;
+        const float* xr = x + (long long)row * D;
+        const float* dr = dres ? dres + (long long)row * D : nullptr;
+        float* dxr = dx + (long long)row * D;
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        const int D4 = vec ? (D >> 2) : 0;
+        float s1 = 0.f, s2 = 0.f;
+        for (int i = lane; i < D4; i += 32) {
+            float4 g = ld_f4(dyr + 4 * i), ww = ld_f4(gamma + 4 * i), v = ld_f4(xr + 4 * i);
+            float g0 = g.x * ww.x, g1 = g.y * ww.y, g2 = g.z * ww.z, g3 = g.w * ww.w;
+            s1 += (g0 + g1) + (g2 + g3);
+            s2 += (g0 * (v.x - mean) + g1 * (v.y - mean)) + (g2 * (v.z - mean) + g3 * (v.w - mean));
+        }
+        for (int i = 4 * D4 + lane; i < D; i += 32) {
+            float g = dyr[i] * gamma[i];
+            s1 += g;
+            s2 += g * (xr[i] - mean);
+        }
+        s1 = warp_sum(s1) / (float)D;
+        s2 = warp_sum(s2) * rstd / (float)D;  // mean(g * xhat)
+        for (int i = lane; i < D4; i += 32) {
+            float4 g = ld_f4(dyr + 4 * i), ww = ld_f4(gamma + 4 * i), v = ld_f4(xr + 4 * i);
+            float4 o;
+            o.x = rstd * (g.x * ww.x - s1 - (v.x - mean) * rstd * s2);
+            o.y = rstd * (g.y * ww.y - s1 - (v.y - mean) * rstd * s2);
+            o.z = rstd * (g.z * ww.z - s1 - (v.z - mean) * rstd * s2);
+            o.w = rstd * (g.w * ww.w - s1 - (v.w - mean) * rstd * s2);
+            if (dr) { float4 r = ld_f4(dr + 4 * i); o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
+            st_f4(dxr + 4 * i, o);
+        }
+        for (int i = 4 * D4 + lane; i < D; i += 32) {
+            float o = rstd * (dyr[i] * gamma[i] - s1 - (xr[i] - mean) * rstd * s2);
+            if (dr) o += dr[i];
+            dxr[i] = o;
+        }
+        return;
+    }
+    __shared__ float sg[8][33], sb[8][33];
+    const int c = ((int)blockIdx.x - row_blocks) * 32 + lane;
+    float ag = 0.f, ab = 0.f;
+    if (c < D) {
+        for (int r = w; r < rows; r += 8) {
+            const float d = dy[(long long)r * D + c];
+            const float xh = (x[(long long)r * D + c] - mean_in[r]) * rstd_in[r];
+            ag += d * xh;
+            ab += d;
+        }
+    }
+    sg[w][lane] = ag;
+    sb[w][lane] = ab;
+    __syncthreads();
+    if (w == 0 && c < D) {
+        float tg = 0.f, tb = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { tg += sg[i][lane]; tb += sb[i][lane]; }
+        dgamma[c] = accumulate ? dgamma[c] + tg : tg;
+        dbeta[c] = accumulate ? dbeta[c] + tb : tb;
+    }
+}
+
 // ---------------------------------------------------------------- gated mix
 __device__ __forceinline__ float gate_of(float c) {
     float cc = fminf(fmaxf(c, -2.f), 2.f);
@@ -323,47 +396,14 @@ extern "C" int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const fl
     BMHRL_CHECK_ARG(rows >= 0 && D > 0, "bmhrl_layernorm_bwd_f32: bad sizes");
     cudaStream_t st = (cudaStream_t)stream;
     const bool want_affine = dgamma && dbeta;
-    if (rows > 0 && D % 4 == 0 && D <= 1024 && aligned16(x) && aligned16(dy) && aligned16(gamma) &&
-        (!dx || aligned16(dx)) && (!dres || aligned16(dres))) {
-        if (want_affine && !accumulate_affine) {
-            if (cudaMemsetAsync(dgamma, 0, sizeof(float) * D, st) != cudaSuccess ||
-                cudaMemsetAsync(dbeta, 0, sizeof(float) * D, st) != cudaSuccess) {
-                bmhrl_set_error("bmhrl_layernorm_bwd_f32: memset failed");
-                return BMHRL_ERR_CUDA;
-            }
-        }
-        int rpb = (rows + 2 * 148 - 1) / (2 * 148);       // ~2 blocks per SM ...
-        if (rpb < 2 * LN_WARPS) rpb = 2 * LN_WARPS;       // ... but at least 2 rows per warp to amortise the REDs
-        rpb = (rpb + LN_WARPS - 1) / LN_WARPS * LN_WARPS;
-        const int blocks = (rows + rpb - 1) / rpb;
-        const size_t smem = want_affine ? sizeof(float) * LN_WARPS * 2 * D : 0;
-        float* dg = want_affine ? dgamma : nullptr;
-        float* dbp = want_affine ? dbeta : nullptr;
-        const int nv = (D / 4 + 31) / 32;
-#define BMHRL_LN_BWD(NV)                                                                                          \
-    layernorm_bwd_fused_kernel<NV><<<blocks, LN_WARPS * 32, smem, st>>>(dy, x, gamma, mean, rstd, dres, dx, dg, dbp, \
-                                                                        rows, D, rpb)
-        if (nv <= 1) BMHRL_LN_BWD(1);
-        else if (nv <= 2) BMHRL_LN_BWD(2);
-        else if (nv <= 3) BMHRL_LN_BWD(3);
-        else if (nv <= 4) BMHRL_LN_BWD(4);
-        else BMHRL_LN_BWD(8);
-#undef BMHRL_LN_BWD
-        BMHRL_POST_LAUNCH("layernorm_bwd_fused");
-        return BMHRL_OK;
-    }
-    if (dx && rows > 0) {
-        int vec = (D % 4 == 0) && aligned16(x) && aligned16(dy) && aligned16(gamma) && aligned16(dx) &&
-                  (!dres || aligned16(dres));
-        int blocks = (rows + LN_WARPS - 1) / LN_WARPS;
-        layernorm_bwd_dx_kernel<<<blocks, LN_WARPS * 32, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, rows, D, vec);
-        BMHRL_POST_LAUNCH("layernorm_bwd_dx");
-    }
-    if (dgamma && dbeta) {
-        layernorm_bwd_affine_kernel<<<(D + 31) / 32, 256, 0, st>>>(dy, x, mean, rstd, dgamma, dbeta, rows, D,
-                                                                        accumulate_affine);
-        BMHRL_POST_LAUNCH("layernorm_bwd_affine");
-    }
+    if (rows == 0 || (!dx && !want_affine)) return BMHRL_OK;
+    const int vec = (D % 4 == 0) && aligned16(x) && aligned16(dy) && aligned16(gamma) && (!dx || aligned16(dx)) &&
+                    (!dres || aligned16(dres));
+    const int row_blocks = dx ? (rows + 7) / 8 : 0;
+    const int strips = want_affine ? (D + 31) / 32 : 0;
+    layernorm_bwd_det_kernel<<<row_blocks + strips, 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, D,
+                                                                  vec, row_blocks, accumulate_affine);
+    BMHRL_POST_LAUNCH("layernorm_bwd_det");
     return BMHRL_OK;
 }
 

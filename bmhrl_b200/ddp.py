@@ -30,7 +30,8 @@ class GradSync:
                 continue
             s = opt.offsets[i]
             e = s + opt.params[i].numel()
-            if spans and spans[-1][1] == s:
+            # FusedAdam starts every slice on a 16-byte boundary: up to 3 zero padding elements between neighbours
+            if spans and 0 <= s - spans[-1][1] < 4 and (s == spans[-1][1] or s % 4 == 0):
                 spans[-1][1] = e
             else:
                 spans.append([s, e])

@@ -133,10 +133,20 @@ class ResidualConnection(nn.Module):
         self.norm = nn.LayerNorm(size)
         self.dropout = nn.Dropout(dout_p)
         self._salt = None
+        # bf16 math mode: also emit the bf16 twin of the block's output (set where that output is the key / value
+        # source of a later cross-attention, so that no separate cast kernel runs)
+        self.emit_twin = False
 
     def forward(self, x, sublayer):
-        res = ops.layer_norm(x, self.norm.weight, self.norm.bias, self.norm.eps)
         p = self.dropout.p if self.training else 0.0
+        if ops.BF16 and x.dim() == 3:
+            # one autograd node for the whole block: LayerNorm -> sublayer -> dropout -> + x, bf16 interior tensors
+            block = getattr(sublayer, "block16", None)
+            if block is not None:
+                out = block(x, self.norm, p, self.emit_twin)
+                if out is not None:
+                    return out
+        res = ops.layer_norm(x, self.norm.weight, self.norm.bias, self.norm.eps)
         fused = getattr(sublayer, "fused_residual", None)
         if fused is not None:
             return fused(res, x, p)
@@ -190,6 +200,13 @@ class PositionwiseFeedForward(nn.Module):
     def fused_residual(self, normed, x, p):
         return self.forward(normed, resid=x, resid_drop_p=p)
 
+    def block16(self, x, norm, p, emit_twin=False):
+        """bf16 math mode: x + dropout(fc2(dropout(relu(fc1(LayerNorm(x)))))) as one node (ops16._FfnBlock)."""
+        from .. import ops16
+        if self.d_model % 4 or self.d_ff % 4:
+            return None
+        return ops16.ffn_block(x, self, norm, resid=True, p_res=p, emit_twin=emit_twin)
+
 
 class AttentionSublayer:
     """The `lambda x: att(x, K, V, mask)` closures of the reference's layers (model/bm_hrl_agent.py:358-364,89-94)
@@ -204,3 +221,15 @@ class AttentionSublayer:
     def fused_residual(self, normed, x, p):
         return self.att(normed, normed if self.K is None else self.K, normed if self.V is None else self.V, self.mask,
                         self.causal, resid=x, resid_drop_p=p)
+
+    def block16(self, x, norm, p, emit_twin=False):
+        """bf16 math mode: x + dropout(attention(LayerNorm(x), K, V)) as one node (ops16._AttnBlock); None when the
+        shape has no one-tile kernel or keys and values come from different tensors (the caller then takes the
+        per-op path)."""
+        from .. import ops16
+        if self.K is not self.V or self.att.memory_kv is not None:
+            return None
+        if not ops16.attention_block_supported(self.att, x, self.K):
+            return None
+        return ops16.attention_block(x, self.K, self.mask, self.att, norm, resid=True, p_res=p, causal=self.causal,
+                                     emit_twin=emit_twin)

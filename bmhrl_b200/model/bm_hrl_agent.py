@@ -277,6 +277,10 @@ class BMEncoderLayer(nn.Module):
 
         self.res_layers_M1 = clone(ResidualConnection(d_model_M1, dout_p), 3)
         self.res_layers_M2 = clone(ResidualConnection(d_model_M2, dout_p), 3)
+        # outputs that become the key / value source of a later cross-attention (the other modality's bimodal
+        # attention; after the last layer: the caption side's eight encoder-memory attentions)
+        for r in (self.res_layers_M1[0], self.res_layers_M2[0], self.res_layers_M1[2], self.res_layers_M2[2]):
+            r.emit_twin = True
 
     def forward(self, x, masks):
         '''x (M1, M2): (B, Sm, Dm); masks (M1, M2): (B, 1, Sm) -> M1m2 (B, Sm1, Dm1), M2m1 (B, Sm2, Dm2)'''
@@ -351,7 +355,11 @@ class Manager(nn.Module):
         if self._salts is None:
             self._salts = (ops.next_salt(), ops.next_salt())
         p = self.dropout.p if self.training else 0.0
-        x = ops.linear(x, self.linear.weight, self.linear.bias, drop_p=p, salt=self._salts[0])
+        if ops.BF16 and x.shape[-1] % 4 == 0 and self.d_goal % 4 == 0:
+            from .. import ops16
+            x = ops16.linear16(x, self.linear.weight, self.linear.bias, drop_p=p, salt=self._salts[0])
+        else:
+            x = ops.linear(x, self.linear.weight, self.linear.bias, drop_p=p, salt=self._salts[0])
         noise = None
         if self.exploration:
             if self.mean_factor != 10 or self.std_factor != 5:
@@ -370,6 +378,9 @@ class WorkerCore(nn.Module):
         self.softmax = nn.Softmax(dim=-1)
 
     def forward(self, x):
+        if ops.BF16 and x.shape[-1] % 4 == 0 and self.projection.out_features % 4 == 0:
+            from .. import ops16
+            return ops.log_softmax(ops16.linear16(x, self.projection.weight, self.projection.bias))
         return ops.log_softmax(ops.linear(x, self.projection.weight, self.projection.bias))
 
 

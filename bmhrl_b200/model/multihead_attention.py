@@ -80,6 +80,11 @@ class MultiheadedAttention(nn.Module):
             q = ops.linear(Q, self.linear_Q2d.weight, self.linear_Q2d.bias)
             o = ops.mha_core(q, k, v, mask, self.H, causal=causal, drop_p=0.0, salt=s_core)
             return ops.linear(o, self.linear_d2Q.weight, self.linear_d2Q.bias, resid=resid, drop_p=0.0, salt=s_out)
+        if ops.BF16 and K is V and resid is None:
+            from .. import ops16
+            kv = None if K is Q else K
+            if ops16.attention_block_supported(self, Q, kv):
+                return ops16.attention_block(Q, kv, mask, self, None, resid=False, p_res=0.0, causal=causal)
         # the three projections are independent: concurrent branches (and so are their backward passes)
         q, k, v = ops.parallel(Q.device,
                                lambda: ops.linear(Q, self.linear_Q2d.weight, self.linear_Q2d.bias),

@@ -242,14 +242,24 @@ def next_salt():
 # ----------------------------------------------------------------------------------------------------------------
 # contractions
 # ----------------------------------------------------------------------------------------------------------------
+BF16 = False  # math mode 'bf16': the modules route their blocks through bmhrl_b200.ops16 (bf16 tensor-core operands)
+
+
 def set_math_mode(mode):
     """'fp32': exact SIMT contractions (default); 'tf32': tcgen05 tensor-core GEMMs (fp32 storage, tf32 multiplies,
-    fp32 accumulation in TMEM)."""
-    LIB.call("bmhrl_set_math_mode", {"fp32": 0, "tf32": 1}[mode])
+    fp32 accumulation in TMEM); 'bf16': the residual stream, statistics, gradients of parameters and optimiser state
+    stay fp32, every tensor that is only a tensor-core operand is bf16 (bmhrl_b200/ops16.py: grouped 128x128 tcgen05
+    GEMMs, fused one-tile attention forward + backward); whatever has no bf16 kernel (the frozen critic, the value
+    heads) runs as in 'tf32'."""
+    global BF16
+    if mode not in ("fp32", "tf32", "bf16"):
+        raise ValueError(f"unknown math mode {mode!r}")
+    LIB.call("bmhrl_set_math_mode", 0 if mode == "fp32" else 1)
+    BF16 = mode == "bf16"
 
 
 def get_math_mode():
-    return ("fp32", "tf32")[LIB.raw("bmhrl_get_math_mode")()]
+    return "bf16" if BF16 else ("fp32", "tf32")[LIB.raw("bmhrl_get_math_mode")()]
 
 
 RECORD = None  # bench.py: when a list, every GEMM launch appends its shape/stride tuple (roofline re-issue)
@@ -1062,7 +1072,9 @@ class FusedAdam:
         if dev.type != "cuda":
             raise RuntimeError("FusedAdam: parameters must live on a CUDA device (there is no CPU fallback)")
         self.lr, self.betas, self.eps, self.grad_scale = lr, betas, eps, grad_scale
-        total = sum(p.numel() for p in self.params)
+        # every tensor's slice starts on a 16-byte boundary (128-bit accesses in adam_multi_kernel); the <= 3 padding
+        # elements between slices stay zero
+        total = sum((p.numel() + 3) & ~3 for p in self.params)
         self.flat_grad = torch.zeros(total, device=dev, dtype=_F32)
         self.exp_avg = torch.zeros(total, device=dev, dtype=_F32)
         self.exp_avg_sq = torch.zeros(total, device=dev, dtype=_F32)
@@ -1081,11 +1093,13 @@ class FusedAdam:
             mp.append(self.exp_avg[off:off + n].data_ptr())
             vp.append(self.exp_avg_sq[off:off + n].data_ptr())
             ne.append(n)
-            off += n
+            off += (n + 3) & ~3
         i64 = dict(device=dev, dtype=torch.int64)
         self._pp, self._gp = torch.tensor(pp, **i64), torch.tensor(gp, **i64)
         self._mp, self._vp = torch.tensor(mp, **i64), torch.tensor(vp, **i64)
         self._ne = torch.tensor(ne, **i64)
+        self._shadow_gen = -1      # generation of the bf16 weight-shadow registry (ops16) the tables below were built for
+        self._shadow_tabs = None
         self.refresh_active()
 
     def refresh_active(self):
@@ -1141,6 +1155,40 @@ class FusedAdam:
         if n_chunks == 0:
             return
         LIB.call("bmhrl_tick", _p(self.step_counts), _p(act), n_act, None, st)
-        LIB.call("bmhrl_adam_multi_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne),
-                 _p(ct), _p(cs), n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
-                 self.eps, self.grad_scale, st)
+        sh = self._shadow_tables()
+        if sh is None:
+            LIB.call("bmhrl_adam_multi_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne),
+                     _p(ct), _p(cs), n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
+                     self.eps, self.grad_scale, st)
+        else:
+            LIB.call("bmhrl_adam_multi_shadow_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne),
+                     _p(ct), _p(cs), n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
+                     self.eps, self.grad_scale, _p(sh[0]), _p(sh[1]), _p(sh[2]), _p(sh[3]), st)
+
+    def _shadow_tables(self):
+        """Device tables of the bf16 / fp32 shadows (ops16.SHADOWS) of this optimiser's parameters: the Adam kernel
+        writes every updated weight into its shadow as well, so the tensor-core operand copies never go stale and no
+        separate conversion pass exists.  Rebuilt (eagerly, never inside a graph capture: the warm-up steps that precede
+        a capture create every shadow) when the registry has grown."""
+        from . import ops16
+        reg = ops16.SHADOWS
+        if reg.generation == 0:
+            return None
+        if reg.generation != self._shadow_gen:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("FusedAdam: weight shadows were created during a CUDA-graph capture; run the step "
+                                   "eagerly once before capturing")
+            dev = self.flat_grad.device
+            ptr, cols, ld, kind = [], [], [], []
+            for p in self.params:
+                e = reg.entry(p)
+                ptr.append(e[0] if e else 0)
+                cols.append(e[1] if e else 1)
+                ld.append(e[2] if e else 1)
+                kind.append(e[3] if e else 0)
+            self._shadow_tabs = (torch.tensor(ptr, device=dev, dtype=torch.int64),
+                                 torch.tensor(cols, device=dev, dtype=torch.int32),
+                                 torch.tensor(ld, device=dev, dtype=torch.int32),
+                                 torch.tensor(kind, device=dev, dtype=torch.int32))
+            self._shadow_gen = reg.generation
+        return self._shadow_tabs

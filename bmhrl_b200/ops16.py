@@ -140,3 +140,537 @@ def attn16_bwd(q, k, v, do, lse2, mask_u8, mask_kind, causal, B, H, Sq, Sk, dk, 
              do.data_ptr(), do.stride(0), lse2.data_ptr(), None if mask_u8 is None else mask_u8.data_ptr(),
              int(mask_kind), int(bool(causal)), dq.data_ptr(), dq.stride(0), dk_.data_ptr(), dk_.stride(0), dv.data_ptr(),
              dv.stride(0), B, H, Sq, Sk, dk, _stream())
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# bf16 twins of fp32 activations and bf16 shadows of fp32 weights
+# ----------------------------------------------------------------------------------------------------------------
+def cast16(x2d, out=None, drop_p=0.0, rng=None, salt=0, db=None, accumulate_db=False):
+    """bf16(dropout(x2d)) for a contiguous-row fp32 (rows, cols) matrix; db (fp32 (cols,)): bias gradient, fixed order."""
+    rows, cols = x2d.shape
+    if out is None:
+        out = empty16(rows, cols, x2d.device)
+    LIB.call("bmhrl_cast_bf16", x2d.data_ptr(), x2d.stride(0), out.data_ptr(), out.stride(0), rows, cols, float(drop_p),
+             rng.data_ptr() if drop_p > 0 else None, int(salt), None if db is None else db.data_ptr(),
+             1 if accumulate_db else 0, _stream())
+    return out
+
+
+def twin16(t):
+    """The bf16 (rows, D) matrix of an fp32 (..., D) activation.  Kernels that produce an activation which a later GEMM
+    consumes emit the twin in their epilogue and attach it (`attach_twin`); otherwise it is cast here, once."""
+    tw = getattr(t, "_bmhrl16", None)
+    if tw is not None and tw[1] == t._version:
+        return tw[0]
+    x = t.detach()
+    if not x.is_contiguous():
+        x = x.contiguous()
+    y = cast16(x.reshape(-1, x.shape[-1]))
+    t._bmhrl16 = (y, t._version)
+    return y
+
+
+def attach_twin(t, y16):
+    t._bmhrl16 = (y16, t._version)
+
+
+class _Shadows:
+    """bf16 operand copies of fp32 weights (and fp32 N-concatenated biases).  A group = the weights of linear layers
+    that read the same input, stacked along N (Q|K|V of a self-attention, K|V of a cross-attention): ONE GEMM.
+    Freshness: ops.FusedAdam writes the shadow of every weight it updates from inside its kernel (bmhrl_adam_multi_
+    shadow_f32), which is what keeps a captured CUDA graph self-contained; any other in-place change of a parameter
+    (load_state_dict, torch.optim.Adam, .copy_) bumps its `_version` and the group is re-cast on its next use."""
+
+    def __init__(self):
+        self.groups = {}      # tuple(id(weight)) -> dict
+        self.by_param = {}    # id(param) -> (data_ptr, cols, ld, kind) of the FIRST group that holds it
+        self.generation = 0
+
+    def entry(self, p):
+        return self.by_param.get(id(p))
+
+    def clear(self):
+        self.groups.clear()
+        self.by_param.clear()
+        self.generation += 1
+
+    def get(self, weights, biases=None):
+        key = tuple(id(w) for w in weights)
+        g = self.groups.get(key)
+        if g is None:
+            g = self._create(key, weights, biases)
+        ver = sum(w._version for w in weights) + (sum(b._version for b in biases if b is not None) if biases else 0)
+        if ver != g["ver"] or g["uncovered"]:
+            self._refresh(g, weights, biases)
+            g["ver"] = ver
+        return g["w16"], g["b32"]
+
+    def _create(self, key, weights, biases):
+        import weakref
+        dev = weights[0].device
+        K = weights[0].shape[1]
+        if any(w.dim() != 2 or w.shape[1] != K for w in weights):
+            raise RuntimeError("weight shadows: the stacked weights must share in_features")
+        n_tot = sum(w.shape[0] for w in weights)
+        w16 = empty16(n_tot, K, dev)
+        b32 = None
+        if biases is not None and any(b is not None for b in biases):
+            if len(weights) == 1:
+                b32 = biases[0]          # a single layer reads its own bias parameter
+            else:
+                b32 = torch.zeros(n_tot, device=dev, dtype=_F32)
+        g = {"w16": w16, "b32": b32, "ver": -1, "uncovered": False}
+        r0 = 0
+        for i, w in enumerate(weights):
+            n = w.shape[0]
+            if id(w) in self.by_param:
+                g["uncovered"] = True    # Adam keeps only the first shadow of a parameter fresh: re-cast this one per use
+            else:
+                self.by_param[id(w)] = (w16[r0:r0 + n].data_ptr(), K, w16.stride(0), 0)
+            if len(weights) > 1 and biases is not None and biases[i] is not None:
+                if id(biases[i]) in self.by_param:
+                    g["uncovered"] = True
+                else:
+                    self.by_param[id(biases[i])] = (b32[r0:r0 + n].data_ptr(), n, n, 1)
+            r0 += n
+        self.groups[key] = g
+        self.generation += 1
+        ids = [id(w) for w in weights] + [id(b) for b in (biases or []) if b is not None]
+
+        def _drop(reg=weakref.ref(self), key=key, ids=ids, w16ptr=w16.data_ptr()):
+            reg = reg()
+            if reg is None:
+                return
+            reg.groups.pop(key, None)
+            for i in ids:
+                reg.by_param.pop(i, None)
+            reg.generation += 1
+        weakref.finalize(weights[0], _drop)
+        return g
+
+    def _refresh(self, g, weights, biases):
+        r0 = 0
+        for i, w in enumerate(weights):
+            n = w.shape[0]
+            wd = w.detach()
+            LIB.call("bmhrl_cast_bf16", wd.data_ptr(), wd.stride(0), g["w16"][r0:r0 + n].data_ptr(), g["w16"].stride(0), n,
+                     w.shape[1], 0.0, None, 0, None, 0, _stream())
+            if len(weights) > 1 and biases is not None and biases[i] is not None:
+                g["b32"][r0:r0 + n].copy_(biases[i].detach())
+            r0 += n
+
+
+SHADOWS = _Shadows()
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# raw (non-autograd) building blocks
+# ----------------------------------------------------------------------------------------------------------------
+def ln_fwd16(x2d, gamma, beta, eps):
+    rows, D = x2d.shape
+    y = empty16(rows, D, x2d.device)
+    mean = torch.empty(rows, device=x2d.device, dtype=_F32)
+    rstd = torch.empty(rows, device=x2d.device, dtype=_F32)
+    LIB.call("bmhrl_layernorm_fwd_bf16", x2d.data_ptr(), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(), y.stride(0),
+             mean.data_ptr(), rstd.data_ptr(), rows, D, float(eps), _stream())
+    return y, mean, rstd
+
+
+def ln_bwd(dy2d, x2d, gamma, mean, rstd, dres2d, need_dx, ggrad, bgrad, need_affine):
+    """dx = LN'(dy) (+ dres); dgamma / dbeta into the flat-buffer slices (accumulating) or fresh tensors.  Deterministic."""
+    rows, D = x2d.shape
+    dx = torch.empty_like(x2d) if need_dx else None
+    acc = need_affine and ggrad is not None and bgrad is not None
+    dg = (ggrad if acc else torch.empty(D, device=x2d.device, dtype=_F32)) if need_affine else None
+    db = (bgrad if acc else torch.empty(D, device=x2d.device, dtype=_F32)) if need_affine else None
+    LIB.call("bmhrl_layernorm_bwd_f32", dy2d.data_ptr(), x2d.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+             None if dres2d is None else dres2d.data_ptr(), None if dx is None else dx.data_ptr(),
+             None if dg is None else dg.data_ptr(), None if db is None else db.data_ptr(), rows, D, 1 if acc else 0,
+             _stream())
+    return dx, (None if (acc or not need_affine) else dg), (None if (acc or not need_affine) else db)
+
+
+def colsum16(z16, outs, seg_cols=0, accumulate=False):
+    rows, cols = z16.shape
+    o = list(outs) + [None] * (3 - len(outs))
+    LIB.call("bmhrl_colsum_bf16", z16.data_ptr(), z16.stride(0), rows, cols, o[0].data_ptr(),
+             None if o[1] is None else o[1].data_ptr(), None if o[2] is None else o[2].data_ptr(), int(seg_cols),
+             1 if accumulate else 0, _stream())
+
+
+def _wgrad(dz16, x16, weights, n_each):
+    """dW (+)= dZ^T X for the stacked weights of a group, off the critical path (wgrad streams); returns the list of
+    gradient tensors autograd still has to see (None where the kernel accumulated into a FusedAdam slice)."""
+    from . import ops
+    live = [w for w in weights if w.requires_grad]
+    if not live:
+        return [None] * len(weights)
+    M = dz16.shape[0]
+    K = x16.shape[1]
+    dsts = [ops._gbuf(w) if w.requires_grad else None for w in weights]
+    outs = [None] * len(weights)
+    all_flat = all(d is not None for d in dsts) and len(live) == len(weights)
+    if all_flat:
+        prob = gemm_problem(dz16, 1, x16, 1, dz16.shape[1], K, M, C32=dsts[0], beta=1.0,
+                            seg=(n_each, dsts[1:]) if len(weights) > 1 else None)
+        if ops.CONCURRENT:
+            ops._WGRAD_KEEP.append((dz16, x16))
+            with torch.cuda.stream(ops.wgrad_stream(dz16.device, dsts[0])):
+                gemm_group([prob])
+        else:
+            gemm_group([prob])
+        return outs
+    # mixed / no flat buffer: one problem per live weight, fresh or accumulating destinations
+    probs = []
+    r0 = 0
+    for i, w in enumerate(weights):
+        n = w.shape[0]
+        if w.requires_grad:
+            if dsts[i] is not None:
+                probs.append(gemm_problem(dz16[:, r0:r0 + n], 1, x16, 1, n, K, M, C32=dsts[i], beta=1.0))
+            else:
+                outs[i] = torch.empty(n, K, device=dz16.device, dtype=_F32)
+                probs.append(gemm_problem(dz16[:, r0:r0 + n], 1, x16, 1, n, K, M, C32=outs[i]))
+        r0 += n
+    gemm_group(probs)
+    return outs
+
+
+def _bgrad16(dz16, biases, n_each):
+    """bias gradients = column sums of a bf16 dZ (deterministic); same return convention as _wgrad."""
+    from . import ops
+    outs = [None] * len(biases)
+    live = [i for i, b in enumerate(biases) if b is not None and b.requires_grad]
+    if not live:
+        return outs
+    dsts = []
+    acc = all(ops._gbuf(biases[i]) is not None for i in live) and len(live) == len(biases)
+    if acc:
+        dsts = [ops._gbuf(b) for b in biases]
+        colsum16(dz16, dsts, seg_cols=n_each if len(biases) > 1 else 0, accumulate=True)
+        return outs
+    r0 = 0
+    for i, b in enumerate(biases):
+        n = n_each
+        if b is not None and b.requires_grad:
+            g = ops._gbuf(b)
+            if g is not None:
+                colsum16(dz16[:, r0:r0 + n], [g], accumulate=True)
+            else:
+                outs[i] = torch.empty(n, device=dz16.device, dtype=_F32)
+                colsum16(dz16[:, r0:r0 + n], [outs[i]])
+        r0 += n
+    return outs
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# block-level autograd nodes: one node per ResidualConnection block, every interior tensor is bf16 and invisible to
+# autograd; the residual-stream gradient adds are fused (LayerNorm backward takes the skip gradient as `dres`)
+# ----------------------------------------------------------------------------------------------------------------
+class _AttnBlock(torch.autograd.Function):
+    """y = [x +] dropout_r( W_o dropout_a( attention( W_q n, W_k m, W_v m ) ) + b_o ),  n = LayerNorm(x) or x,
+    m = n (self-attention) or the fp32 tensor `kv` (cross-attention: the un-normed other modality / encoder memory).
+    model/blocks.py:135-144 + model/multihead_attention.py:60-92 as ONE autograd node:
+      forward  LN -> Q|K|V GEMM (one N-concatenated problem; cross: Q and K|V as two problems of one launch) ->
+               fused attention -> out-projection GEMM with bias + dropout + residual in its epilogue
+      backward cast (+ dropout mask, + db_o) -> dO GEMM (attention dropout mask in its epilogue) | dW_o -> fused attention
+               backward -> dX GEMM(s) | dW, db -> LayerNorm backward with the skip gradient folded in."""
+
+    @staticmethod
+    def forward(ctx, x, kv, mask_u8, cfg, ln_g, ln_b, Wq, bq, Wk, bk, Wv, bv, Wo, bo):
+        from . import ops
+        B, Sq, Dq = x.shape
+        M = B * Sq
+        D = Wq.shape[0]
+        H = cfg["H"]
+        dk = D // H
+        x2 = x.detach().reshape(M, Dq)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        dev = x.device
+        if ln_g is not None:
+            n16, mean, rstd = ln_fwd16(x2, ln_g.detach(), ln_b.detach(), cfg["eps"])
+        else:
+            n16, mean, rstd = twin16(x), None, None
+        if kv is None:
+            Sk, Mk = Sq, M
+            w16, b32 = SHADOWS.get([Wq, Wk, Wv], [bq, bk, bv])
+            qkv = empty16(M, 3 * D, dev)
+            gemm_group([gemm_problem(n16, 0, w16, 0, M, 3 * D, Dq, bias=b32, C16=qkv)])
+            q, k, v = qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:]
+            m16 = None
+        else:
+            Sk = kv.shape[1]
+            Mk = B * Sk
+            Dkv = kv.shape[2]
+            m16 = twin16(kv)
+            wq16, _ = SHADOWS.get([Wq], [bq])
+            wkv16, bkv32 = SHADOWS.get([Wk, Wv], [bk, bv])
+            q = empty16(M, D, dev)
+            kvp = empty16(Mk, 2 * D, dev)
+            gemm_group([gemm_problem(n16, 0, wq16, 0, M, D, Dq, bias=None if bq is None else bq.detach(), C16=q),
+                        gemm_problem(m16, 0, wkv16, 0, Mk, 2 * D, Dkv, bias=bkv32, C16=kvp)])
+            k, v = kvp[:, :D], kvp[:, D:]
+            qkv = None
+        o16 = empty16(M, D, dev)
+        lse2 = torch.empty(B, H, Sq, device=dev, dtype=_F32)
+        p_a = cfg["p_attn"]
+        attn16_fwd(q, k, v, mask_u8, cfg["mask_kind"], cfg["causal"], B, H, Sq, Sk, dk, o16, lse2, p_a, cfg["rng"],
+                   cfg["s_core"])
+        wo16, _ = SHADOWS.get([Wo], [bo])
+        out = torch.empty(B, Sq, Dq, device=dev, dtype=_F32)
+        out16 = empty16(M, Dq, dev) if cfg.get("emit_twin") else None
+        gemm_group([gemm_problem(o16, 0, wo16, 0, M, Dq, D, bias=None if bo is None else bo.detach(), drop_p=cfg["p_res"],
+                                 rng=cfg["rng"], salt=cfg["s_out"], resid=x2 if cfg["resid"] else None,
+                                 C32=out.view(M, Dq), C16=out16)])
+        if out16 is not None:
+            attach_twin(out, out16)
+        ctx.save_for_backward(x2, mean, rstd, n16, q, k, v, m16, o16, lse2, mask_u8, ln_g, Wq, Wk, Wv, Wo)
+        ctx.params = (ln_g, ln_b, Wq, bq, Wk, bk, Wv, bv, Wo, bo)
+        ctx.cfg = cfg
+        ctx.dims = (B, Sq, Sk, Dq, D, H, dk, kv is None, None if kv is None else kv.shape[2])
+        ctx.bufs = (qkv,)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import ops
+        x2, mean, rstd, n16, q, k, v, m16, o16, lse2, mask_u8, ln_g_s, *_ = ctx.saved_tensors
+        ln_g, ln_b, Wq, bq, Wk, bk, Wv, bv, Wo, bo = ctx.params
+        cfg = ctx.cfg
+        B, Sq, Sk, Dq, D, H, dk, self_att, Dkv = ctx.dims
+        M, Mk = B * Sq, B * Sk
+        dev = dy.device
+        dy2 = dy.reshape(M, Dq)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        need_x, need_kv = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        # ---- out-projection: dZ_o = dropout-mask o dy (bf16), db_o
+        need_bo = bo is not None and bo.requires_grad
+        bo_dst = ops._gbuf(bo) if need_bo else None
+        dbo = None
+        if need_bo and bo_dst is None:
+            dbo = torch.empty(Dq, device=dev, dtype=_F32)
+        dzo = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s_out"], db=(bo_dst if bo_dst is not None else dbo),
+                     accumulate_db=bo_dst is not None)
+        wo16, _ = SHADOWS.get([Wo], [bo])
+        do16 = empty16(M, D, dev)
+        gemm_group([gemm_problem(dzo, 0, wo16, 1, M, D, Dq, drop_p=cfg["p_attn"], rng=cfg["rng"], salt=cfg["s_core"], C16=do16)])
+        dWo = _wgrad(dzo, o16, [Wo], Dq)[0]
+        # ---- attention core
+        if self_att:
+            dz = empty16(M, 3 * D, dev)
+            dq, dk_, dv = dz[:, :D], dz[:, D:2 * D], dz[:, 2 * D:]
+        else:
+            dq = empty16(M, D, dev)
+            dzkv = empty16(Mk, 2 * D, dev)
+            dk_, dv = dzkv[:, :D], dzkv[:, D:]
+        attn16_bwd(q, k, v, do16, lse2, mask_u8, cfg["mask_kind"], cfg["causal"], B, H, Sq, Sk, dk, dq, dk_, dv)
+        # ---- projections
+        grads_w = {}
+        dkv = None
+        if self_att:
+            w16, _ = SHADOWS.get([Wq, Wk, Wv], [bq, bk, bv])
+            dn = torch.empty(M, Dq, device=dev, dtype=_F32) if (need_x or ln_g is not None) else None
+            if dn is not None:
+                gemm_group([gemm_problem(dz, 0, w16, 1, M, Dq, 3 * D, C32=dn)])
+            gw = _wgrad(dz, n16, [Wq, Wk, Wv], D)
+            gb = _bgrad16(dz, [bq, bk, bv], D)
+        else:
+            wq16, _ = SHADOWS.get([Wq], [bq])
+            wkv16, _ = SHADOWS.get([Wk, Wv], [bk, bv])
+            probs = []
+            dn = torch.empty(M, Dq, device=dev, dtype=_F32) if (need_x or ln_g is not None) else None
+            if dn is not None:
+                probs.append(gemm_problem(dq, 0, wq16, 1, M, Dq, D, C32=dn))
+            if need_kv:
+                dkv = torch.empty(B, Sk, Dkv, device=dev, dtype=_F32)
+                probs.append(gemm_problem(dzkv, 0, wkv16, 1, Mk, Dkv, 2 * D, C32=dkv.view(Mk, Dkv)))
+            if probs:
+                gemm_group(probs)
+            gw = _wgrad(dq, n16, [Wq], D) + _wgrad(dzkv, m16, [Wk, Wv], D)
+            gb = _bgrad16(dq, [bq], D) + _bgrad16(dzkv, [bk, bv], D)
+        # ---- LayerNorm backward with the skip gradient folded in
+        dx = dg = dbeta = None
+        if ln_g is not None:
+            need_aff = ln_g.requires_grad
+            if need_x or need_aff:
+                dx, dg, dbeta = ln_bwd(dn, x2, ln_g.detach(), mean, rstd, dy2 if cfg["resid"] else None, need_x,
+                                       ops._gbuf(ln_g), ops._gbuf(ln_b), need_aff)
+        elif need_x:
+            dx = dn + dy2 if cfg["resid"] else dn
+        if dx is not None:
+            dx = dx.view(B, Sq, Dq)
+        return (dx, dkv, None, None, dg, dbeta, gw[0], gb[0], gw[1], gb[1], gw[2], gb[2], dWo, dbo)
+
+
+class _FfnBlock(torch.autograd.Function):
+    """y = x + dropout_r( W_2 dropout_1( relu( W_1 LayerNorm(x) + b_1 ) ) + b_2 )   (model/blocks.py:135-144,175-187)."""
+
+    @staticmethod
+    def forward(ctx, x, cfg, ln_g, ln_b, W1, b1, W2, b2):
+        B, S, D = x.shape
+        M = B * S
+        F_ = W1.shape[0]
+        dev = x.device
+        x2 = x.detach().reshape(M, D)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        if ln_g is not None:
+            n16, mean, rstd = ln_fwd16(x2, ln_g.detach(), ln_b.detach(), cfg["eps"])
+        else:
+            n16, mean, rstd = twin16(x), None, None
+        w1, _ = SHADOWS.get([W1], [b1])
+        w2, _ = SHADOWS.get([W2], [b2])
+        h16 = empty16(M, F_, dev)
+        gemm_group([gemm_problem(n16, 0, w1, 0, M, F_, D, bias=b1.detach(), act=1, drop_p=cfg["p1"], rng=cfg["rng"],
+                                 salt=cfg["s1"], C16=h16)])
+        out = torch.empty(B, S, D, device=dev, dtype=_F32)
+        out16 = empty16(M, D, dev) if cfg.get("emit_twin") else None
+        gemm_group([gemm_problem(h16, 0, w2, 0, M, D, F_, bias=b2.detach(), drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"],
+                                 resid=x2 if cfg["resid"] else None, C32=out.view(M, D), C16=out16)])
+        if out16 is not None:
+            attach_twin(out, out16)
+        ctx.save_for_backward(x2, mean, rstd, n16, h16, ln_g, W1, W2)
+        ctx.params = (ln_g, ln_b, W1, b1, W2, b2)
+        ctx.cfg = cfg
+        ctx.dims = (B, S, D, F_)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import ops
+        x2, mean, rstd, n16, h16, *_ = ctx.saved_tensors
+        ln_g, ln_b, W1, b1, W2, b2 = ctx.params
+        cfg = ctx.cfg
+        B, S, D, F_ = ctx.dims
+        M = B * S
+        dev = dy.device
+        dy2 = dy.reshape(M, D)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        need_x = ctx.needs_input_grad[0]
+        need_b2 = b2.requires_grad
+        b2_dst = ops._gbuf(b2) if need_b2 else None
+        db2 = torch.empty(D, device=dev, dtype=_F32) if (need_b2 and b2_dst is None) else None
+        dz2 = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"], db=(b2_dst if b2_dst is not None else db2),
+                     accumulate_db=b2_dst is not None)
+        w1, _ = SHADOWS.get([W1], [b1])
+        w2, _ = SHADOWS.get([W2], [b2])
+        dz1 = empty16(M, F_, dev)   # dZ_1 = (dZ_2 W_2) o [h > 0] / (1 - p1): relu and dropout gates in the GEMM epilogue
+        gs = 1.0 / (1.0 - cfg["p1"]) if cfg["p1"] > 0 else 1.0
+        gemm_group([gemm_problem(dz2, 0, w2, 1, M, F_, D, gate=h16, gate_scale=gs, C16=dz1)])
+        dW2 = _wgrad(dz2, h16, [W2], D)[0]
+        dn = torch.empty(M, D, device=dev, dtype=_F32)
+        gemm_group([gemm_problem(dz1, 0, w1, 1, M, D, F_, C32=dn)])
+        dW1 = _wgrad(dz1, n16, [W1], F_)[0]
+        db1 = _bgrad16(dz1, [b1], F_)[0]
+        dx = dg = dbeta = None
+        if ln_g is not None:
+            need_aff = ln_g.requires_grad
+            if need_x or need_aff:
+                dx, dg, dbeta = ln_bwd(dn, x2, ln_g.detach(), mean, rstd, dy2 if cfg["resid"] else None, need_x,
+                                       ops._gbuf(ln_g), ops._gbuf(ln_b), need_aff)
+        elif need_x:
+            dx = dn + dy2 if cfg["resid"] else dn
+        if dx is not None:
+            dx = dx.view(B, S, D)
+        return dx, None, dg, dbeta, dW1, db1, dW2, db2
+
+
+class _Linear16(torch.autograd.Function):
+    """y = dropout(x W^T + b) for an fp32 activation x (its bf16 twin is the operand); fp32 output."""
+
+    @staticmethod
+    def forward(ctx, x, W, b, cfg):
+        K = x.shape[-1]
+        N = W.shape[0]
+        M = x.numel() // K
+        x16 = twin16(x)
+        w16, _ = SHADOWS.get([W], [b])
+        out = torch.empty(x.shape[:-1] + (N,), device=x.device, dtype=_F32)
+        out16 = empty16(M, N, x.device) if cfg.get("emit_twin") else None
+        gemm_group([gemm_problem(x16, 0, w16, 0, M, N, K, bias=None if b is None else b.detach(), drop_p=cfg["p"],
+                                 rng=cfg["rng"], salt=cfg["salt"], C32=out.view(M, N), C16=out16)])
+        if out16 is not None:
+            attach_twin(out, out16)
+        ctx.save_for_backward(x16, W)
+        ctx.params = (W, b)
+        ctx.cfg = cfg
+        ctx.dims = (M, N, K, x.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import ops
+        x16, _ = ctx.saved_tensors
+        W, b = ctx.params
+        cfg = ctx.cfg
+        M, N, K, xshape = ctx.dims
+        dev = dy.device
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        need_b = b is not None and b.requires_grad
+        b_dst = ops._gbuf(b) if need_b else None
+        db = torch.empty(N, device=dev, dtype=_F32) if (need_b and b_dst is None) else None
+        dz = cast16(dy2, drop_p=cfg["p"], rng=cfg["rng"], salt=cfg["salt"], db=(b_dst if b_dst is not None else db),
+                    accumulate_db=b_dst is not None)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            w16, _ = SHADOWS.get([W], [b])
+            dx = torch.empty(xshape, device=dev, dtype=_F32)
+            gemm_group([gemm_problem(dz, 0, w16, 1, M, K, N, C32=dx.view(M, K))])
+        dW = _wgrad(dz, x16, [W], N)[0]
+        return dx, dW, db, None
+
+
+def linear16(x, W, b=None, drop_p=0.0, salt=0, rng=None, emit_twin=False):
+    from . import ops
+    if drop_p > 0 and rng is None:
+        rng = ops.RNG.current(x.device)
+    if W.shape[0] % 4 != 0 or W.shape[1] % 4 != 0:
+        raise RuntimeError("linear16: feature sizes must be multiples of 4")
+    return _Linear16.apply(x, W, b, {"p": float(drop_p), "salt": int(salt), "rng": rng, "emit_twin": emit_twin})
+
+
+def attention_block(x, kv, mask, att, norm=None, resid=False, p_res=0.0, causal=False, emit_twin=False):
+    """The ResidualConnection + MultiheadedAttention block (or the bare attention when norm / resid are off) as one
+    autograd node.  `att`: a bmhrl_b200 MultiheadedAttention; kv: None (self-attention on the normed input) or the fp32
+    (B,Sk,Dkv) tensor both keys and values are projected from."""
+    from . import ops
+    B, Sq, _ = x.shape
+    Sk = Sq if kv is None else kv.shape[1]
+    m_u8, kind = ops._mask_args(mask, B, Sq, Sk)
+    if kind == 0:
+        causal = False
+    s_core, s_out = att._call_salts()
+    p_a = att.dropout.p if att.training else 0.0
+    rng = ops.RNG.current(x.device) if (p_a > 0 or p_res > 0) else None
+    cfg = {"H": att.H, "mask_kind": kind, "causal": bool(causal), "p_attn": float(p_a), "p_res": float(p_res), "s_core": s_core,
+           "s_out": s_out, "resid": bool(resid), "eps": norm.eps if norm is not None else 0.0, "rng": rng,
+           "emit_twin": emit_twin}
+    return _AttnBlock.apply(x, kv, m_u8, cfg, None if norm is None else norm.weight, None if norm is None else norm.bias,
+                            att.linear_Q2d.weight, att.linear_Q2d.bias, att.linear_K2d.weight, att.linear_K2d.bias,
+                            att.linear_V2d.weight, att.linear_V2d.bias, att.linear_d2Q.weight, att.linear_d2Q.bias)
+
+
+def attention_block_supported(att, x, kv):
+    D = att.d_model
+    Sq = x.shape[1]
+    Sk = Sq if kv is None else kv.shape[1]
+    dims_ok = all(d % 8 == 0 or d % 4 == 0 for d in (x.shape[-1], D)) and x.shape[-1] % 4 == 0 and \
+        (kv is None or kv.shape[-1] % 4 == 0)
+    return dims_ok and D % att.H == 0 and attn16_supported(Sq, Sk, D // att.H)
+
+
+def ffn_block(x, ff, norm=None, resid=False, p_res=0.0, emit_twin=False):
+    from . import ops
+    if ff._salts is None:
+        ff._salts = (ops.next_salt(), ops.next_salt())
+    p1 = ff.dropout.p if ff.training else 0.0
+    rng = ops.RNG.current(x.device) if (p1 > 0 or p_res > 0) else None
+    cfg = {"p1": float(p1), "p_res": float(p_res), "s1": ff._salts[0], "s2": ff._salts[1], "resid": bool(resid),
+           "eps": norm.eps if norm is not None else 0.0, "rng": rng, "emit_twin": emit_twin}
+    return _FfnBlock.apply(x, cfg, None if norm is None else norm.weight, None if norm is None else norm.bias, ff.fc1.weight,
+                           ff.fc1.bias, ff.fc2.weight, ff.fc2.bias)

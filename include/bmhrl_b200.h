@@ -214,6 +214,22 @@ int bmhrl_attn16_bwd(const void* Q, long long ldq, const void* K, long long ldk,
 /* dynamic shared memory the one-tile kernels need (forward: backward = 0); above 220 KB the shape is unsupported */
 long long bmhrl_attn16_smem_bytes(int backward, int Sq, int Sk, int dk);
 
+/* ---- bf16 math mode: HBM-bound helpers (aux16.cu); all deterministic (no floating-point atomics) ------------------- */
+/* y = bf16(LayerNorm(x)) with row pitch ldy (elements): the A operand of the projection that follows the norm
+ * (ResidualConnection model/blocks.py:135-144, normCA/normCV model/bm_hrl_agent.py:107-108); mean / rstd saved for
+ * bmhrl_layernorm_bwd_f32. */
+int bmhrl_layernorm_fwd_bf16(const float* x, const float* gamma, const float* beta, void* y, long long ldy, float* mean,
+                             float* rstd, int rows, int D, float eps, void* stream);
+/* y = bf16(dropout(x)) (Philox, element index m*cols + n; drop_p = 0: plain cast) and, when db != NULL, the bias gradient
+ * db[n] (+)= sum_m dropout(x)[m,n] in a fixed summation order: the head of every linear layer's backward (dZ from the
+ * fp32 residual-stream gradient).  y may be NULL (only db). */
+int bmhrl_cast_bf16(const float* x, long long ldx, void* y, long long ldy, int rows, int cols, float drop_p,
+                    const unsigned long long* rng_state, unsigned int salt, float* db, int accumulate_db, void* stream);
+/* Column sums of a bf16 matrix (bias gradient of a dZ a GEMM / attention epilogue emitted): column n is written to
+ * out{n / seg_cols}[n % seg_cols] (seg_cols = 0: everything to out0) -- the three bias slices of a fused Q|K|V. */
+int bmhrl_colsum_bf16(const void* z, long long ldz, int rows, int cols, float* out0, float* out1, float* out2,
+                      int seg_cols, int accumulate, void* stream);
+
 /* ---- K4 / K5: vocabulary log-softmax, KL losses, sampling (loss.cu) ----------------------------------------- */
 int bmhrl_log_softmax_fwd_f32(const float* x, float* y, long long rows, int V, void* stream); /* bm_hrl_agent.py:465 */
 int bmhrl_log_softmax_bwd_f32(const float* dy, const float* y, float* dx, long long rows, int V, void* stream);
@@ -303,6 +319,15 @@ int bmhrl_adam_multi_f32(float* const* params, const float* const* grads, float*
                          float* const* exp_avg_sq, const long long* numels, const int* chunk_tensor,
                          const int* chunk_start, int n_chunks, const float* step_counts, float lr, float beta1,
                          float beta2, float eps, float grad_scale, void* stream);
+/* Same update, and additionally every tensor t with shadow[t] != NULL gets its UPDATED values written to shadow[t]:
+ * shadow_kind[t] = 0: bf16 matrix (numel / shadow_cols[t] rows of shadow_cols[t] elements, row pitch shadow_ld[t]) -- the
+ * tensor-core operand copy of a weight in bf16 math mode; 1: fp32 flat copy (N-concatenated Q|K|V bias).  Tables are
+ * device arrays indexed like params. */
+int bmhrl_adam_multi_shadow_f32(float* const* params, const float* const* grads, float* const* exp_avg,
+                                float* const* exp_avg_sq, const long long* numels, const int* chunk_tensor,
+                                const int* chunk_start, int n_chunks, const float* step_counts, float lr, float beta1,
+                                float beta2, float eps, float grad_scale, void* const* shadow, const int* shadow_cols,
+                                const int* shadow_ld, const int* shadow_kind, void* stream);
 /* step_counts[active_tensors[i]] += 1 for i < n_active (active_tensors NULL = identity) and rng_state[1] += 1, on
  * the device; step_counts / rng_state may be NULL. */
 int bmhrl_tick(float* step_counts, const int* active_tensors, int n_active, unsigned long long* rng_state,

@@ -1,0 +1,232 @@
+"""GPU: the bf16 math mode (bmhrl_b200/ops16.py: grouped bf16 tcgen05 GEMMs, fused one-tile attention forward + backward,
+block-level autograd nodes) against the fp32 oracle and the reference's golden vectors.  Bound: the north_star's bf16
+bound 2e-2 on logits, losses and gradients; integer outputs (segment labels) exact; observed errors are printed."""
+import math
+
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import bmhrl_oracle as O
+from bmhrl_b200 import synth
+from conftest import PAD, SMOOTH, VOC, build_agent, rel
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+@pytest.fixture()
+def bf16(gpu_lib):
+    from bmhrl_b200 import ops
+    ops.set_math_mode("bf16")
+    yield ops
+    ops.set_math_mode("fp32")
+
+
+def _g(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+def _sd(mod, prefix):
+    return {prefix + k: v.detach().cpu() for k, v in mod.state_dict().items()}
+
+
+@pytest.mark.parametrize("B,Sq,Sk,dq,dkv,H,kind", [
+    (4, 30, 30, 1024, None, 4, "pad"),       # video self-attention
+    (4, 80, 80, 128, None, 4, "pad"),        # audio self-attention
+    (4, 30, 80, 1024, 128, 4, "pad"),        # video <- audio bimodal attention
+    (4, 80, 30, 128, 1024, 4, "pad"),        # audio <- video
+    (4, 20, 20, 300, None, 4, "full"),       # caption self-attention, (B,L,L) mask
+    (4, 20, 30, 300, 1024, 4, "pad"),        # caption <- video memory
+])
+def test_attention_residual_block(bf16, B, Sq, Sk, dq, dkv, H, kind):
+    from bmhrl_b200.model.blocks import AttentionSublayer, ResidualConnection
+    from bmhrl_b200.model.multihead_attention import MultiheadedAttention
+    g = _g(B + Sq + Sk + dq)
+    att = MultiheadedAttention(dq, dkv or dq, dkv or dq, H, 0.0, 1024).cuda()
+    res = ResidualConnection(dq, 0.0).cuda()
+    with torch.no_grad():
+        res.norm.weight.copy_(1 + 0.1 * torch.randn(dq, generator=g))
+        res.norm.bias.copy_(0.1 * torch.randn(dq, generator=g))
+    x = torch.randn(B, Sq, dq, generator=g)
+    kv = torch.randn(B, Sk, dkv, generator=g) if dkv else None
+    if kind == "pad":
+        lens = torch.randint(1, Sk + 1, (B,), generator=g)
+        lens[0] = Sk
+        mask = (torch.arange(Sk)[None, :] < lens[:, None])[:, None, :]
+        mask[1] = False
+    else:
+        mask = torch.tril(torch.ones(Sq, Sk, dtype=torch.bool))[None].repeat(B, 1, 1)
+        mask[0, :, Sk // 2:] = False
+    dy = torch.randn(B, Sq, dq, generator=g)
+    # oracle (fp32, CPU)
+    sd = {**_sd(att, "a."), **_sd(res.norm, "n.")}
+    xr = x.clone().requires_grad_(True)
+    kvr = kv.clone().requires_grad_(True) if dkv else None
+    pr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    n = O.layer_norm(pr, "n.", xr)
+    yr = xr + O.mha(pr, "a.", n, n if kvr is None else kvr, n if kvr is None else kvr, mask, H)
+    yr.backward(dy)
+    # device
+    xd = x.cuda().requires_grad_(True)
+    kvd = kv.cuda().requires_grad_(True) if dkv else None
+    y = res(xd, AttentionSublayer(att, kvd, kvd, mask.cuda()))
+    y.backward(dy.cuda())
+    errs = {"y": rel(y, yr), "dx": rel(xd.grad, xr.grad)}
+    if dkv:
+        errs["dkv"] = rel(kvd.grad, kvr.grad)
+    for name, p in list(att.named_parameters()) + [("norm." + k, v) for k, v in res.norm.named_parameters()]:
+        key = ("a." + name) if not name.startswith("norm.") else ("n." + name[5:])
+        if name == "linear_K2d.bias":   # softmax is shift invariant: the true gradient is 0, only noise is left
+            continue
+        errs[name] = rel(p.grad, pr[key].grad)
+    print("attention block errors", {k: f"{v:.1e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL, errs
+
+
+def test_ffn_residual_block_and_linear16(bf16):
+    from bmhrl_b200 import ops16
+    from bmhrl_b200.model.blocks import PositionwiseFeedForward, ResidualConnection
+    g = _g(5)
+    B, S, D, F_ = 4, 30, 1024, 1024
+    ff = PositionwiseFeedForward(D, F_, 0.0).cuda()
+    res = ResidualConnection(D, 0.0).cuda()
+    x = torch.randn(B, S, D, generator=g)
+    dy = torch.randn(B, S, D, generator=g)
+    sd = {**_sd(ff, "f."), **_sd(res.norm, "n.")}
+    pr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    xr = x.clone().requires_grad_(True)
+    yr = xr + O.ffn(pr, "f.", O.layer_norm(pr, "n.", xr))
+    yr.backward(dy)
+    xd = x.cuda().requires_grad_(True)
+    y = res(xd, ff)
+    y.backward(dy.cuda())
+    errs = {"y": rel(y, yr), "dx": rel(xd.grad, xr.grad)}
+    for name, p in ff.named_parameters():
+        errs[name] = rel(p.grad, pr["f." + name].grad)
+    for name, p in res.norm.named_parameters():
+        errs["norm." + name] = rel(p.grad, pr["n." + name].grad)
+    print("ffn block errors", {k: f"{v:.1e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL, errs
+    # plain linear (Manager.linear 300 -> 64, the vocabulary projection 364 -> V)
+    for (M, K, N) in [(320, 300, 64), (320, 364, 10172)]:
+        lin = nn.Linear(K, N).cuda()
+        x = torch.randn(M, K, generator=g)
+        dy = torch.randn(M, N, generator=g)
+        xr = x.clone().requires_grad_(True)
+        w, b = lin.weight.detach().cpu().requires_grad_(True), lin.bias.detach().cpu().requires_grad_(True)
+        (torch.nn.functional.linear(xr, w, b)).backward(dy)
+        xd = x.cuda().requires_grad_(True)
+        ops16.linear16(xd, lin.weight, lin.bias).backward(dy.cuda())
+        assert rel(xd.grad, xr.grad) < TOL and rel(lin.weight.grad, w.grad) < TOL and rel(lin.bias.grad, b.grad) < 1e-5
+
+
+@pytest.mark.parametrize("tag", ["small", "c16"])
+def test_agent_bf16_vs_reference_golden(bf16, golden, agent_sd, tag):
+    """Whole agent forward / backward in bf16 math mode vs the reference's fp32 outputs."""
+    from bmhrl_b200.model.masking import make_masks
+    from bmhrl_b200.loss.label_smoothing import LabelSmoothing
+    g = golden[f"agent_{tag}"]
+    c = g["cfg"]
+    model, _ = build_agent(agent_sd)
+    model.train()
+    model.teach_warmstart()
+    model.manager.exploration = False
+    b = {k: v.cuda() for k, v in synth.synthetic_batch(B=c["B"], Sv=c["Sv"], Sa=c["Sa"], L=c["L"], V=VOC, seed=c["seed"],
+                                                        ragged=c["ragged"]).items()}
+    cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+    out = model((b["rgb"] + b["flow"], b["audio"]), cin, make_masks(b, cin, "audio_video", PAD))
+    loss = torch.sum(LabelSmoothing(SMOOTH, PAD)(out[0], cy)) / (cy != PAD).sum()
+    loss.backward()
+    bf16.join_side_streams(loss.device)
+    assert torch.equal(out[4].cpu(), g["segment_labels"])
+    errs = {"pred": rel(out[0][:, :, ::101], g["pred_slice"]), "worker_feat": rel(out[1], g["worker_feat"]),
+            "manager_feat": rel(out[2], g["manager_feat"]), "goals": rel(out[3], g["goals"]), "loss": rel(loss, g["loss"])}
+    params = dict(model.named_parameters())
+    worst, wname = 0.0, ""
+    for n, gn in g["grad_norm"].items():
+        if n.endswith("linear_K2d.bias"):
+            continue
+        sl = params[n].grad.flatten()[:: max(1, params[n].grad.numel() // 64)][:64].cpu()
+        e = max(float((sl - g["grad_slice"][n]).norm()) / (gn + 1e-12), abs(float(params[n].grad.norm()) - gn) / (gn + 1e-12))
+        if e > worst:
+            worst, wname = e, n
+    errs["grads_worst"] = worst
+    print("bf16 errors", tag, {k: f"{v:.2e}" for k, v in errs.items()}, wname)
+    assert max(errs.values()) < TOL, (errs, wname)
+
+
+def _trainer(agent_sd, **kw):
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer
+    model, cfg = build_agent(agent_sd, **kw)
+    tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD)
+    tr.teach_warmstart()
+    model.manager.exploration = False
+    return model, tr
+
+
+def test_step_bf16_adam_keeps_shadows_fresh_and_is_deterministic(bf16, agent_sd):
+    """(1) after FusedAdam steps every bf16 weight shadow equals bf16(parameter) bit for bit (the Adam kernel writes
+    them); (2) the step has no floating-point atomics: two runs from the same state give bit-identical parameters;
+    (3) the CUDA-graph replay of the step equals the eager step."""
+    from bmhrl_b200 import ops16
+    from bmhrl_b200.train import StepRunner
+    b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=2, ragged=True)
+    finals = []
+    for use_graph in (False, False, True):
+        bf16.manual_seed(7)
+        model, tr = _trainer(agent_sd, dout_p=0.1)
+        run = StepRunner(tr, "warmstart", b, use_graph=use_graph, warmup=2 if use_graph else 0)
+        n0 = 2 if use_graph else 0
+        losses = [float(run.step(b)[0]) for _ in range(4 - n0)]
+        torch.cuda.synchronize()
+        finals.append((losses, {n: p.detach().clone() for n, p in model.named_parameters()}))
+        if not use_graph:
+            checked = 0
+            for n, p in model.named_parameters():
+                e = ops16.SHADOWS.entry(p)
+                if e is None or e[3] != 0:
+                    continue
+                for key, grp in ops16.SHADOWS.groups.items():
+                    if id(p) in key:
+                        r0 = sum(q.shape[0] for q in [pp for pp in model.parameters() if id(pp) in key[:key.index(id(p))]])
+                        sh = grp["w16"][r0:r0 + p.shape[0]]
+                        assert torch.equal(sh, p.detach().to(torch.bfloat16)), n
+                        checked += 1
+            assert checked > 40
+    assert finals[0][0] == finals[1][0]
+    for n in finals[0][1]:
+        assert torch.equal(finals[0][1][n], finals[1][1][n]), f"run-to-run difference in {n}"
+    worst = max(rel(finals[2][1][n], finals[0][1][n]) for n in finals[0][1])
+    assert worst < 1e-6, worst
+    assert finals[0][0][-1] < finals[0][0][0]
+
+
+def test_warmstart_step_bf16_matches_oracle_adam(bf16, agent_sd):
+    """Two warm-start steps in bf16 math mode vs oracle autograd + oracle Adam: losses within 2e-2; parameters move by
+    lr-sized steps, so they are compared through the size of the update."""
+    model, tr = _trainer(agent_sd)
+    b = synth.synthetic_batch(B=3, Sv=8, Sa=10, L=6, V=VOC, seed=31, ragged=True)
+    cin, cy = b["caption"][:, :-1], b["caption"][:, 1:]
+    params = {k: v.clone() for k, v in agent_sd.items()}
+    state, losses = {}, []
+    for _ in range(2):
+        p = {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point else v) for k, v in params.items()}
+        pred = O.agent_forward(p, b["rgb"] + b["flow"], b["audio"], cin, O.make_masks(b["rgb"], b["audio"], cin, PAD))[0]
+        loss = O.label_smoothing_kl(pred, cy, SMOOTH, PAD).sum() / (cy != PAD).sum()
+        loss.backward()
+        grads = {k: v.grad for k, v in p.items() if torch.is_tensor(v) and v.grad is not None and not k.startswith("manager.core.")}
+        params, state = O.adam_step({k: v.detach() for k, v in p.items()}, grads, state)
+        losses.append(float(loss.detach()))
+    dl = [float(tr.warmstart_step({k: v.cuda() for k, v in b.items()})) for _ in range(2)]
+    assert abs(dl[0] - losses[0]) < TOL * abs(losses[0]) and abs(dl[1] - losses[1]) < TOL * abs(losses[1])
+    moved = 0
+    for n, q in model.named_parameters():
+        if q.requires_grad and n in params and not n.endswith("linear_K2d.bias"):
+            step = (params[n] - agent_sd[n]).norm()
+            if float(step) > 0:
+                # Adam normalises the gradient: a 2e-2 gradient error moves a weight by at most ~2e-2 of its step
+                assert float((q.detach().cpu() - params[n]).norm()) < 0.25 * float(step) + 1e-7, n
+                moved += 1
+    assert moved > 50
