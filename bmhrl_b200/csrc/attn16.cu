@@ -36,7 +36,9 @@ struct A16Params {
     int B, H, Sq, Sk, dk, Sqp, Skp, nck, dvt;
     float scale;
     const unsigned char* mask; int mask_kind, causal;
-    float* lse2;                               // (B,H,Sq) log2-domain log-sum-exp of the masked scaled scores
+    float* lse2;                               // (B,H,Sq,2): row maximum m (log2 domain) and 1 / normaliser of the masked
+                                               // scaled scores.  Kept apart on purpose: a fully masked row has m = -1e9 * log2(e),
+                                               // where fp32 spacing is 128, so m + log2(l) would lose the normaliser
     // forward
     __nv_bfloat16* O; long long ldo;
     float drop_p; const unsigned long long* rng; unsigned int salt;
@@ -187,7 +189,10 @@ __global__ void __launch_bounds__(192, 1) attn16_fwd_kernel(const __grid_constan
         tmem_st_wait_b();
         tc_fence_before();
         mbar_arrive(p_ready);
-        if (row_ok && blockIdx.y == 0) p.lse2[(long long)bh * p.Sq + q] = m + log2f(l);
+        if (row_ok && blockIdx.y == 0) {
+            p.lse2[2 * ((long long)bh * p.Sq + q)] = m;
+            p.lse2[2 * ((long long)bh * p.Sq + q) + 1] = 1.f / l;
+        }
         // ---- epilogue
         mbar_wait(o_full, 0);
         tc_fence_after();
@@ -243,13 +248,14 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t qch = (uint32_t)p.Sqp * 128u, kch = (uint32_t)p.Skp * 128u;
     const uint32_t sQ = base, sG = sQ + p.nck * qch, sK = sG + p.nck * qch, sV = sK + p.nck * kch;
-    const uint32_t stats = sV + p.nck * kch + A16_SLACK;       // lse2[128], delta[128] of the queries
-    const uint32_t bars = stats + 1024;
+    const uint32_t stats = sV + p.nck * kch + A16_SLACK;       // m[128], 1/l[128], delta[128] of the queries
+    const uint32_t bars = stats + 2048;
     const uint32_t ld_full = bars, a_full = bars + 8, ds_ready = bars + 16, dq_full = bars + 24, b_full = bars + 32;
     const uint32_t pt_ready = bars + 40, dk_full = bars + 48, dk_free = bars + 56, dv_full = bars + 64;
     const uint32_t tmem_slot = bars + 72;
     float* st_lse = reinterpret_cast<float*>(smem_raw + (stats - smem_u32(smem_raw)));
-    float* st_del = st_lse + 128;
+    float* st_il = st_lse + 128;
+    float* st_del = st_lse + 256;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
@@ -350,7 +356,8 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
             uint32_t vis[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) vis[c] = c < nch ? a16_vis_row(p, b, r, row_ok, c * 32, lane) : 0u;
-            const float lse2 = row_ok ? p.lse2[(long long)bh * p.Sq + r] : INFINITY;
+            const float lse2 = row_ok ? p.lse2[2 * ((long long)bh * p.Sq + r)] : INFINITY;   // row maximum
+            const float il = row_ok ? p.lse2[2 * ((long long)bh * p.Sq + r) + 1] : 0.f;       // 1 / normaliser
             mbar_wait(a_full, 0);
             tc_fence_after();
             float delta = 0.f;
@@ -364,7 +371,7 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     const float t = ((vis[c] >> i) & 1u) ? __uint_as_float(s[i]) * sl2 : neg2;
-                    const float pr = i < cnt ? ex2_approx(t - lse2) : 0.f;
+                    const float pr = i < cnt ? ex2_approx(t - lse2) * il : 0.f;
                     delta = fmaf(pr, __uint_as_float(dp[i]), delta);
                 }
             }
@@ -379,7 +386,7 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     const bool on = ((vis[c] >> i) & 1u) != 0u && i < cnt;
-                    const float pr = ex2_approx(__uint_as_float(s[i]) * sl2 - lse2);
+                    const float pr = ex2_approx(__uint_as_float(s[i]) * sl2 - lse2) * il;
                     g[i] = on ? pr * (__uint_as_float(dp[i]) - delta) : 0.f;   // replaced scores carry no gradient
                 }
 #pragma unroll
@@ -387,6 +394,7 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
                 tmem_st_32x32_x16(tS + lane_off + c * 16, out);
             }
             st_lse[r] = lse2;
+            st_il[r] = il;
             st_del[r] = row_ok ? delta : 0.f;
             tmem_st_wait_b();
             tc_fence_before();
@@ -438,9 +446,9 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
                     if (p.mask_kind == 2)
                         on = key_ok && qi < p.Sq && p.mask[((long long)b * p.Sq + qi) * p.Sk + r] != 0;
                     if (p.causal) on = on && r <= qi;
-                    const float l2 = st_lse[qi];      // +inf for queries out of range: probability 0
+                    const float l2 = st_lse[qi];      // +inf (and 1/l = 0) for queries out of range: probability 0
                     const float t = on ? __uint_as_float(s[i]) * sl2 : neg2;
-                    const float pr = key_ok ? ex2_approx(t - l2) : 0.f;
+                    const float pr = key_ok ? ex2_approx(t - l2) * st_il[qi] : 0.f;
                     pt[i] = pr;
                     dst[i] = on ? pr * (__uint_as_float(dp[i]) - st_del[qi]) : 0.f;
                 }
@@ -520,7 +528,7 @@ using namespace bmhrl;
 
 extern "C" long long bmhrl_attn16_smem_bytes(int backward, int Sq, int Sk, int dk) {
     const long long Sqp = (Sq + 15) & ~15, Skp = (Sk + 15) & ~15, nck = dk >> 6, dvt = dk > 256 ? 256 : dk;
-    if (backward) return 2 * nck * (Sqp + Skp) * 128 + A16_SLACK + 1024 + 128 + 1024;
+    if (backward) return 2 * nck * (Sqp + Skp) * 128 + A16_SLACK + 2048 + 128 + 1024;
     return nck * (Sqp + Skp) * 128 + (dvt >> 6) * Skp * 128 + A16_SLACK + 128 + 1024;
 }
 

@@ -413,7 +413,7 @@ class _AttnBlock(torch.autograd.Function):
             k, v = kvp[:, :D], kvp[:, D:]
             qkv = None
         o16 = empty16(M, D, dev)
-        lse2 = torch.empty(B, H, Sq, device=dev, dtype=_F32)
+        lse2 = torch.empty(B, H, Sq, 2, device=dev, dtype=_F32)
         p_a = cfg["p_attn"]
         attn16_fwd(q, k, v, mask_u8, cfg["mask_kind"], cfg["causal"], B, H, Sq, Sk, dk, o16, lse2, p_a, cfg["rng"],
                    cfg["s_core"])

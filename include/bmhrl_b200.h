@@ -197,8 +197,8 @@ int bmhrl_attn_bwd_bf16_tuning(int passes);
  * O = P V on tcgen05 with the probabilities handed over in TMEM; nothing of size (B,H,Sq,Sk) is ever stored.
  * Q (B*Sq, ldq), K / V (B*Sk, ld?), O (B*Sq, ldo): bf16 matrices, head h = columns [h dk, (h+1) dk) -- typically column
  * slices of the N-concatenated Q|K|V projection output; pitches in ELEMENTS (multiples of 8).  dk in {64,128,256,512}.
- * mask_kind / causal as bmhrl_mha_core_fwd_f32.  lse2: fp32 (B,H,Sq), base-2 log-sum-exp of the masked scaled scores
- * (saved for backward).  Dropout (Philox, element index row*H*dk + column) is applied to the output like the reference.
+ * mask_kind / causal as bmhrl_mha_core_fwd_f32.  lse2: fp32 (B,H,Sq,2), per query row the maximum (base-2 domain) and the reciprocal
+ * normaliser of the masked scaled scores (saved for backward; kept apart because a fully masked row has maximum -1e9).  Dropout (Philox, element index row*H*dk + column) is applied to the output like the reference.
  * Returns BMHRL_ERR_UNSUPPORTED when the tiles do not fit (callers then take bmhrl_attn_fwd_bf16 / bmhrl_attn_bwd_bf16). */
 int bmhrl_attn16_fwd(const void* Q, long long ldq, const void* K, long long ldk, const void* V, long long ldv,
                      const unsigned char* mask, int mask_kind, int causal, void* O, long long ldo, float* lse2, int B,
@@ -332,6 +332,24 @@ int bmhrl_adam_multi_shadow_f32(float* const* params, const float* const* grads,
  * the device; step_counts / rng_state may be NULL. */
 int bmhrl_tick(float* step_counts, const int* active_tensors, int n_active, unsigned long long* rng_state,
                void* stream);
+
+/* ---- input side of the step (pipeline.cu) --------------------------------------------------------------------------- */
+/* pad_sequence + rgb + flow + padding mask in one pass over a ragged batch that arrived in ONE host->device copy:
+ * a / b (b may be NULL): the clips' frames back to back, (total_frames, D) fp32; offsets (B+1) int32 frame offsets;
+ * out (B, S, D) = a + b on the frames of clip b, pad_a + pad_b on its padding rows; mask (B, S) uint8 (may be NULL) =
+ * first component of the PADDED a != 0.  Replaces pad_sequence (captioning_datasets/captioning_dataset.py:296-299), the
+ * V = rgb + flow add (epoch_loops/captioning_bmrl_loops.py:497-499) and the feature half of make_masks
+ * (model/masking.py:18-47).  The reference pads rgb / audio with the vocabulary's pad index (1), so with pad_a = 1 the
+ * padding rows stay VISIBLE exactly as they do there; pad_a = 0 gives the length mask. */
+int bmhrl_pad_features_f32(const float* a, const float* b, const int* offsets, float* out, unsigned char* mask, int B, int S,
+                           int D, float pad_a, float pad_b, void* stream);
+/* generate_synonyms (epoch_loops/captioning_bmrl_loops.py:510-528) on the device: per row, up to and including the first
+ * end token (which becomes pad_idx and ends the row's scan): with probability p a token is replaced -- by pad_idx when
+ * u2 < 0.8, by a random word of [2, V-1] when u2 >= 0.9, by itself otherwise.  u1 / u2 (fp32) and rand_words (int64),
+ * all (B, L): explicit draws per position (reproduces the reference for a given draw table); all NULL: Philox. */
+int bmhrl_generate_synonyms(const long long* captions, long long* out, int B, int L, float p, int V, int end_idx, int pad_idx,
+                            const float* u1, const float* u2, const long long* rand_words,
+                            const unsigned long long* rng_state, unsigned int salt, void* stream);
 
 #ifdef __cplusplus
 }

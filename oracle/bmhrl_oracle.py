@@ -503,3 +503,46 @@ def greedy_decode(sd, rgb, flow, audio, max_len, start_idx, end_idx, pad_idx, H=
             trg = torch.cat([trg, nxt], dim=-1)
             done = done | (nxt == end_idx)
     return trg, torch.stack(last, dim=1)
+
+
+# --------------------------------------------------------------------------------------------------
+# input pipeline
+# --------------------------------------------------------------------------------------------------
+def crop_bounds(S, start, end, duration):
+    """captioning_datasets/load_features.py:14-31: [start_idx, end_idx) of a segment in an S-frame stack."""
+    start_idx = int(S * (start / duration))
+    end_idx = int(S * (end / duration))
+    if start_idx == end_idx:
+        if start_idx == S:
+            start_idx -= 1
+        else:
+            end_idx += 1
+    return start_idx, end_idx
+
+
+def pad_batch(stacks, pad_value):
+    """torch pad_sequence(batch_first=True, padding_value=pad_value) as used at captioning_dataset.py:296-299."""
+    S = max(s.shape[0] for s in stacks)
+    out = torch.full((len(stacks), S, stacks[0].shape[1]), float(pad_value), dtype=stacks[0].dtype)
+    for i, s in enumerate(stacks):
+        out[i, : s.shape[0]] = s
+    return out
+
+
+def generate_synonyms(caption_idx, p, vocab_size, u1, u2, rand_words, end_idx=3, pad_idx=1):
+    """epoch_loops/captioning_bmrl_loops.py:510-528 with the `random` draws laid out per position: u1[i,j] is the
+    `random.random()` compared with p at token (i,j), u2[i,j] the second draw (read only when u1 < p), rand_words[i,j]
+    the `random.randint(2, V-1)` result (read only when u2 >= 0.9)."""
+    out = caption_idx.clone()
+    for i in range(out.shape[0]):
+        for j in range(out.shape[1]):
+            w = int(caption_idx[i, j])
+            if w == end_idx:
+                out[i, j] = pad_idx
+                break
+            if float(u1[i, j]) < p:
+                if float(u2[i, j]) < 0.8:
+                    out[i, j] = pad_idx
+                elif float(u2[i, j]) >= 0.9:
+                    out[i, j] = int(rand_words[i, j])
+    return out

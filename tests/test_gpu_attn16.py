@@ -62,7 +62,7 @@ def test_attn16_forward_backward_vs_oracle(gpu_lib, B, H, Sq, Sk, dk, kind, conc
     m_u8, mk = ops._mask_args(None if mask is None else mask.cuda(), B, Sq, Sk)
     D = H * dk
     o = ops16.empty16(B * Sq, D, "cuda")
-    lse2 = torch.empty(B, H, Sq, device="cuda")
+    lse2 = torch.empty(B, H, Sq, 2, device="cuda")
     ops16.attn16_fwd(q, k, v, m_u8, mk, False, B, H, Sq, Sk, dk, o, lse2)
     ro, rdq, rdk, rdv = _oracle(q, k, v, mask, do, B, H, Sq, Sk, dk)
     assert rel(o.float(), ro) < TOL, ("o", rel(o.float(), ro))
@@ -81,7 +81,7 @@ def test_attn16_causal_and_dropout(gpu_lib):
     m_u8, mk = ops._mask_args(mask.cuda(), B, Sq, Sk)
     D = H * dk
     o = ops16.empty16(B * Sq, D, "cuda")
-    lse2 = torch.empty(B, H, Sq, device="cuda")
+    lse2 = torch.empty(B, H, Sq, 2, device="cuda")
     ops16.attn16_fwd(q, k, v, m_u8, mk, True, B, H, Sq, Sk, dk, o, lse2)   # causal (DETR decoder self-attention)
     ro, rdq, rdk, rdv = _oracle(q, k, v, mask, do, B, H, Sq, Sk, dk, causal=True)
     assert rel(o.float(), ro) < TOL
