@@ -144,7 +144,18 @@ __global__ void __launch_bounds__(256) colsum16_kernel(const __nv_bfloat16* __re
     const int n = blockIdx.x * 64 + tx * 4;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     if (n < cols) {
-        for (int m = ty; m < rows; m += 16) {
+        int m = ty;
+        for (; m + 48 < rows; m += 64) {  // four independent loads in flight per thread
+            uint2 w[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) w[u] = *reinterpret_cast<const uint2*>(z + (long long)(m + 16 * u) * ldz + n);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                a0 += __uint_as_float(w[u].x << 16); a1 += __uint_as_float(w[u].x & 0xffff0000u);
+                a2 += __uint_as_float(w[u].y << 16); a3 += __uint_as_float(w[u].y & 0xffff0000u);
+            }
+        }
+        for (; m < rows; m += 16) {
             const uint2 w = *reinterpret_cast<const uint2*>(z + (long long)m * ldz + n);
             a0 += __uint_as_float(w.x << 16); a1 += __uint_as_float(w.x & 0xffff0000u);
             a2 += __uint_as_float(w.y << 16); a3 += __uint_as_float(w.y & 0xffff0000u);

@@ -291,7 +291,23 @@ __global__ void __launch_bounds__(256) layernorm_bwd_det_kernel(
     const int c = ((int)blockIdx.x - row_blocks) * 32 + lane;
     float ag = 0.f, ab = 0.f;
     if (c < D) {
-        for (int r = w; r < rows; r += 8) {
+        int r = w;
+        for (; r + 24 < rows; r += 32) {  // four independent row loads in flight per lane (fixed order of the adds)
+            float d[4], xv[4], mu[4], rs[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                d[u] = dy[(long long)(r + 8 * u) * D + c];
+                xv[u] = x[(long long)(r + 8 * u) * D + c];
+                mu[u] = mean_in[r + 8 * u];
+                rs[u] = rstd_in[r + 8 * u];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                ag += d[u] * ((xv[u] - mu[u]) * rs[u]);
+                ab += d[u];
+            }
+        }
+        for (; r < rows; r += 8) {
             const float d = dy[(long long)r * D + c];
             const float xh = (x[(long long)r * D + c] - mean_in[r]) * rstd_in[r];
             ag += d * xh;

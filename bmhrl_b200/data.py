@@ -79,28 +79,22 @@ class FeatureLoader:
 class RaggedBatch:
     """Pinned staging of one ragged batch and its device-side expansion.
 
-    Layout of the staging buffer (bytes): [rgb frames | flow frames | audio frames | v_off (B+1) i32 | a_off (B+1) i32 |
-    captions (B, L) i64], every section 16-byte aligned.  `stage()` fills it on the host, `to_device()` issues ONE
-    cudaMemcpyAsync and the expansion kernels on the current stream and returns the padded tensors."""
+    Layout of the staging buffer (bytes, every section 16-byte aligned, packed to the batch's fill level):
+    [rgb frames | flow frames | audio frames | v_off (B+1) i32 | a_off (B+1) i32 | captions (B, L) i64].
+    `stage()` fills it on the host; `to_device()` issues ONE cudaMemcpyAsync of the used bytes and the expansion kernels
+    on the current stream and returns (or fills) the padded tensors."""
 
     def __init__(self, B, max_video_frames, max_audio_frames, L, d_video=1024, d_audio=128, device="cuda",
                  feature_pad_value=1.0, n_buffers=2):
         self.B, self.L, self.dv, self.da = B, L, d_video, d_audio
         self.max_v, self.max_a = max_video_frames, max_audio_frames
         self.pad = float(feature_pad_value)   # the reference pads rgb / audio with the vocabulary pad index (1), flow with 0
-        a16 = lambda n: (n + 15) & ~15
-        self.o_rgb = 0
-        self.o_flow = a16(self.o_rgb + 4 * B * max_video_frames * d_video)
-        self.o_aud = a16(self.o_flow + 4 * B * max_video_frames * d_video)
-        self.o_voff = a16(self.o_aud + 4 * B * max_audio_frames * d_audio)
-        self.o_aoff = a16(self.o_voff + 4 * (B + 1))
-        self.o_cap = a16(self.o_aoff + 4 * (B + 1))
-        self.nbytes = a16(self.o_cap + 8 * B * L)
+        self.nbytes = 4 * B * (2 * max_video_frames * d_video + max_audio_frames * d_audio) + 8 * (B + 1) + 8 * B * L + 6 * 16
         self.device = torch.device(device)
         self.host = [torch.empty(self.nbytes, dtype=torch.uint8).pin_memory() for _ in range(n_buffers)]
         self.dev = torch.empty(self.nbytes, dtype=torch.uint8, device=self.device)
         self.cur = 0
-        self.shape = None
+        self.layout = None
         self.h2d_bytes = 0
 
     def stage(self, clips, captions):
@@ -113,52 +107,70 @@ class RaggedBatch:
         for rgb, flow, aud in clips:
             voff.append(voff[-1] + rgb.shape[0])
             aoff.append(aoff[-1] + aud.shape[0])
+        nv, na = voff[-1], aoff[-1]
         Sv = max(voff[i + 1] - voff[i] for i in range(self.B))
         Sa = max(aoff[i + 1] - aoff[i] for i in range(self.B))
         if Sv > self.max_v or Sa > self.max_a:
             raise ValueError(f"clip longer than the staging buffer: Sv={Sv} (max {self.max_v}), Sa={Sa} (max {self.max_a})")
+        a16 = lambda n: (n + 15) & ~15
+        o_rgb = 0
+        o_flow = a16(o_rgb + 4 * nv * self.dv)
+        o_aud = a16(o_flow + 4 * nv * self.dv)
+        o_voff = a16(o_aud + 4 * na * self.da)
+        o_aoff = a16(o_voff + 4 * (self.B + 1))
+        o_cap = a16(o_aoff + 4 * (self.B + 1))
+        used = a16(o_cap + 8 * self.B * self.L)
         f = lambda off, n: buf[off:off + 4 * n].view(np.float32)
-        rgb_all = f(self.o_rgb, voff[-1] * self.dv).reshape(voff[-1], self.dv)
-        flow_all = f(self.o_flow, voff[-1] * self.dv).reshape(voff[-1], self.dv)
-        aud_all = f(self.o_aud, aoff[-1] * self.da).reshape(aoff[-1], self.da)
+        rgb_all = f(o_rgb, nv * self.dv).reshape(nv, self.dv)
+        flow_all = f(o_flow, nv * self.dv).reshape(nv, self.dv)
+        aud_all = f(o_aud, na * self.da).reshape(na, self.da)
         for i, (rgb, flow, aud) in enumerate(clips):
             rgb_all[voff[i]:voff[i + 1]] = rgb
             flow_all[voff[i]:voff[i + 1]] = flow
             aud_all[aoff[i]:aoff[i + 1]] = aud
-        buf[self.o_voff:self.o_voff + 4 * (self.B + 1)].view(np.int32)[:] = voff
-        buf[self.o_aoff:self.o_aoff + 4 * (self.B + 1)].view(np.int32)[:] = aoff
+        buf[o_voff:o_voff + 4 * (self.B + 1)].view(np.int32)[:] = voff
+        buf[o_aoff:o_aoff + 4 * (self.B + 1)].view(np.int32)[:] = aoff
         cap = captions.numpy() if torch.is_tensor(captions) else np.asarray(captions)
-        buf[self.o_cap:self.o_cap + 8 * self.B * self.L].view(np.int64).reshape(self.B, self.L)[:] = cap
-        self.shape = (Sv, Sa, voff[-1], aoff[-1])
-        # only the bytes in use travel: the three frame sections are copied up to their fill level
-        self.h2d_bytes = 4 * (2 * voff[-1] * self.dv + aoff[-1] * self.da) + 8 * (self.B + 1) + 8 * self.B * self.L
+        buf[o_cap:o_cap + 8 * self.B * self.L].view(np.int64).reshape(self.B, self.L)[:] = cap
+        self.layout = (Sv, Sa, nv, na, o_rgb, o_flow, o_aud, o_voff, o_aoff, o_cap, used)
+        self.h2d_bytes = used   # exactly what to_device() copies
         return Sv, Sa
 
-    def to_device(self, synonyms_p=0.0, vocab_size=None, end_idx=3, pad_idx=1, draws=None, salt=0, rng=None):
-        """One H2D copy + the expansion kernels.  Returns dict(V, audio, V_mask, A_mask, caption[, caption_in])."""
-        Sv, Sa, nv, na = self.shape
+    def to_device(self, out=None, synonyms_p=0.0, vocab_size=None, end_idx=3, pad_idx=1, draws=None, salt=0, rng=None):
+        """ONE H2D copy + the expansion kernels.  Returns dict(V, audio, V_mask, A_mask, caption[, caption_in]); `out`
+        (same keys, e.g. the static input buffers of a captured step) is filled in place when given."""
+        Sv, Sa, nv, na, o_rgb, o_flow, o_aud, o_voff, o_aoff, o_cap, used = self.layout
         st = torch.cuda.current_stream(self.device).cuda_stream
-        self.dev.copy_(self.host[self.cur], non_blocking=True)   # ONE cudaMemcpyAsync of the staged batch
+        self.dev[:used].copy_(self.host[self.cur][:used], non_blocking=True)   # ONE cudaMemcpyAsync of the staged batch
         B, L = self.B, self.L
         f32 = lambda off, n: self.dev[off:off + 4 * n].view(torch.float32)
-        rgb, flow = f32(self.o_rgb, nv * self.dv), f32(self.o_flow, nv * self.dv)
-        aud = f32(self.o_aud, na * self.da)
-        voff = self.dev[self.o_voff:self.o_voff + 4 * (B + 1)].view(torch.int32)
-        aoff = self.dev[self.o_aoff:self.o_aoff + 4 * (B + 1)].view(torch.int32)
-        cap = self.dev[self.o_cap:self.o_cap + 8 * B * L].view(torch.int64).view(B, L)
-        V = torch.empty(B, Sv, self.dv, device=self.device)
-        A = torch.empty(B, Sa, self.da, device=self.device)
-        vm = torch.empty(B, 1, Sv, device=self.device, dtype=torch.bool)
-        am = torch.empty(B, 1, Sa, device=self.device, dtype=torch.bool)
+        rgb, flow, aud = f32(o_rgb, nv * self.dv), f32(o_flow, nv * self.dv), f32(o_aud, na * self.da)
+        voff = self.dev[o_voff:o_voff + 4 * (B + 1)].view(torch.int32)
+        aoff = self.dev[o_aoff:o_aoff + 4 * (B + 1)].view(torch.int32)
+        cap = self.dev[o_cap:o_cap + 8 * B * L].view(torch.int64).view(B, L)
+        if out is not None:
+            V, A, vm, am = out["V"], out["audio"], out["V_mask"], out["A_mask"]
+            if V.shape != (B, Sv, self.dv) or A.shape != (B, Sa, self.da) or not (V.is_contiguous() and A.is_contiguous()):
+                raise ValueError(f"RaggedBatch.to_device: output buffers are {tuple(V.shape)} / {tuple(A.shape)}, the staged "
+                                 f"batch needs ({B},{Sv},{self.dv}) / ({B},{Sa},{self.da})")
+        else:
+            V = torch.empty(B, Sv, self.dv, device=self.device)
+            A = torch.empty(B, Sa, self.da, device=self.device)
+            vm = torch.empty(B, 1, Sv, device=self.device, dtype=torch.bool)
+            am = torch.empty(B, 1, Sa, device=self.device, dtype=torch.bool)
         LIB.call("bmhrl_pad_features_f32", rgb.data_ptr(), flow.data_ptr(), voff.data_ptr(), V.data_ptr(), vm.data_ptr(), B, Sv,
                  self.dv, self.pad, 0.0, st)
         LIB.call("bmhrl_pad_features_f32", aud.data_ptr(), None, aoff.data_ptr(), A.data_ptr(), am.data_ptr(), B, Sa, self.da,
                  self.pad, 0.0, st)
-        out = {"V": V, "audio": A, "V_mask": vm, "A_mask": am, "caption": cap}
+        if out is not None:
+            out["caption"].copy_(cap)
+            res = out
+        else:
+            res = {"V": V, "audio": A, "V_mask": vm, "A_mask": am, "caption": cap.clone()}
         if synonyms_p > 0:
-            out["caption_in"] = generate_synonyms(cap[:, :-1].contiguous(), synonyms_p, vocab_size, end_idx, pad_idx, draws,
-                                                  salt, rng)
-        return out
+            res["caption_in"] = generate_synonyms(res["caption"][:, :-1].contiguous(), synonyms_p, vocab_size, end_idx, pad_idx,
+                                                  draws, salt, rng)
+        return res
 
 
 def generate_synonyms(caption_idx, p, vocab_size, end_idx=3, pad_idx=1, draws=None, salt=0, rng=None):

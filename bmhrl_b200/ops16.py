@@ -277,16 +277,29 @@ def ln_fwd16(x2d, gamma, beta, eps):
 
 
 def ln_bwd(dy2d, x2d, gamma, mean, rstd, dres2d, need_dx, ggrad, bgrad, need_affine):
-    """dx = LN'(dy) (+ dres); dgamma / dbeta into the flat-buffer slices (accumulating) or fresh tensors.  Deterministic."""
+    """dx = LN'(dy) (+ dres); dgamma / dbeta into the flat-buffer slices (accumulating) or fresh tensors.  Deterministic.
+    When the affine gradients go straight into a FusedAdam slice nothing downstream waits for them: they are computed
+    by a second launch on a weight-gradient side stream, and the critical path only carries the dx rows."""
+    from . import ops
     rows, D = x2d.shape
     dx = torch.empty_like(x2d) if need_dx else None
     acc = need_affine and ggrad is not None and bgrad is not None
     dg = (ggrad if acc else torch.empty(D, device=x2d.device, dtype=_F32)) if need_affine else None
     db = (bgrad if acc else torch.empty(D, device=x2d.device, dtype=_F32)) if need_affine else None
-    LIB.call("bmhrl_layernorm_bwd_f32", dy2d.data_ptr(), x2d.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-             None if dres2d is None else dres2d.data_ptr(), None if dx is None else dx.data_ptr(),
-             None if dg is None else dg.data_ptr(), None if db is None else db.data_ptr(), rows, D, 1 if acc else 0,
-             _stream())
+
+    def call(dxp, dgp, dbp):
+        LIB.call("bmhrl_layernorm_bwd_f32", dy2d.data_ptr(), x2d.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                 None if dres2d is None else dres2d.data_ptr(), None if dxp is None else dxp.data_ptr(),
+                 None if dgp is None else dgp.data_ptr(), None if dbp is None else dbp.data_ptr(), rows, D, 1 if acc else 0,
+                 _stream())
+    if acc and ops.CONCURRENT:
+        ops._WGRAD_KEEP.append((dy2d, x2d, mean, rstd))
+        with torch.cuda.stream(ops.wgrad_stream(x2d.device, dg)):
+            call(None, dg, db)
+        if need_dx:
+            call(dx, None, None)
+    else:
+        call(dx, dg, db)
     return dx, (None if (acc or not need_affine) else dg), (None if (acc or not need_affine) else db)
 
 
@@ -347,7 +360,12 @@ def _bgrad16(dz16, biases, n_each):
     acc = all(ops._gbuf(biases[i]) is not None for i in live) and len(live) == len(biases)
     if acc:
         dsts = [ops._gbuf(b) for b in biases]
-        colsum16(dz16, dsts, seg_cols=n_each if len(biases) > 1 else 0, accumulate=True)
+        if ops.CONCURRENT:   # only the optimiser reads these: off the critical path
+            ops._WGRAD_KEEP.append((dz16,))
+            with torch.cuda.stream(ops.wgrad_stream(dz16.device, dsts[0])):
+                colsum16(dz16, dsts, seg_cols=n_each if len(biases) > 1 else 0, accumulate=True)
+        else:
+            colsum16(dz16, dsts, seg_cols=n_each if len(biases) > 1 else 0, accumulate=True)
         return outs
     r0 = 0
     for i, b in enumerate(biases):
@@ -446,13 +464,8 @@ class _AttnBlock(torch.autograd.Function):
             dy2 = dy2.contiguous()
         need_x, need_kv = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         # ---- out-projection: dZ_o = dropout-mask o dy (bf16), db_o
-        need_bo = bo is not None and bo.requires_grad
-        bo_dst = ops._gbuf(bo) if need_bo else None
-        dbo = None
-        if need_bo and bo_dst is None:
-            dbo = torch.empty(Dq, device=dev, dtype=_F32)
-        dzo = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s_out"], db=(bo_dst if bo_dst is not None else dbo),
-                     accumulate_db=bo_dst is not None)
+        dzo = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s_out"])
+        dbo = _bgrad16(dzo, [bo], Dq)[0]
         wo16, _ = SHADOWS.get([Wo], [bo])
         do16 = empty16(M, D, dev)
         gemm_group([gemm_problem(dzo, 0, wo16, 1, M, D, Dq, drop_p=cfg["p_attn"], rng=cfg["rng"], salt=cfg["s_core"], C16=do16)])
@@ -550,11 +563,8 @@ class _FfnBlock(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         need_x = ctx.needs_input_grad[0]
-        need_b2 = b2.requires_grad
-        b2_dst = ops._gbuf(b2) if need_b2 else None
-        db2 = torch.empty(D, device=dev, dtype=_F32) if (need_b2 and b2_dst is None) else None
-        dz2 = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"], db=(b2_dst if b2_dst is not None else db2),
-                     accumulate_db=b2_dst is not None)
+        dz2 = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"])
+        db2 = _bgrad16(dz2, [b2], D)[0]
         w1, _ = SHADOWS.get([W1], [b1])
         w2, _ = SHADOWS.get([W2], [b2])
         dz1 = empty16(M, F_, dev)   # dZ_1 = (dZ_2 W_2) o [h > 0] / (1 - p1): relu and dropout gates in the GEMM epilogue
@@ -611,11 +621,8 @@ class _Linear16(torch.autograd.Function):
         dy2 = dy.reshape(M, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        need_b = b is not None and b.requires_grad
-        b_dst = ops._gbuf(b) if need_b else None
-        db = torch.empty(N, device=dev, dtype=_F32) if (need_b and b_dst is None) else None
-        dz = cast16(dy2, drop_p=cfg["p"], rng=cfg["rng"], salt=cfg["salt"], db=(b_dst if b_dst is not None else db),
-                    accumulate_db=b_dst is not None)
+        dz = cast16(dy2, drop_p=cfg["p"], rng=cfg["rng"], salt=cfg["salt"])
+        db = _bgrad16(dz, [b], N)[0]
         dx = None
         if ctx.needs_input_grad[0]:
             w16, _ = SHADOWS.get([W], [b])

@@ -49,7 +49,10 @@ class BMHRLTrainer:
     scripts/train_rl_captioning_module.py:81-83) and the criteria (:66-67, :132)."""
 
     def __init__(self, cap_model, wv_model, mv_model, pad_idx=1, smoothing=0.7, lr=1e-4, modality="audio_video",
-                 grad_sync=None, scorer=None):
+                 grad_sync=None, scorer=None, random_synonyms=0.0, end_idx=3):
+        # feature_getter(..., random_synonyms=0.3) (captioning_bmrl_loops.py:487-528): the reference corrupts the INPUT
+        # caption tokens of every training step; 0 (default) switches it off, which is what the parity goldens assume
+        self.random_synonyms, self.end_idx = float(random_synonyms), int(end_idx)
         self.scorer = scorer  # bmhrl_b200.metrics.CiderScorer; None = the step takes batch["score"] (synthetic rewards)
         self.cap_model, self.wv_model, self.mv_model = cap_model, wv_model, mv_model
         self.pad_idx, self.modality = pad_idx, modality
@@ -100,12 +103,29 @@ class BMHRLTrainer:
 
     # ---- pieces ------------------------------------------------------------------------------------------------------
     def _inputs(self, batch):
-        """feature_getter (captioning_bmrl_loops.py:488-500) without the host-side token corruption."""
+        """feature_getter (captioning_bmrl_loops.py:488-500): input / target captions, `generate_synonyms` token
+        corruption of the input (device kernel, Philox), V = rgb + flow (fused into the positional-encoding kernel), masks.
+        A batch expanded by data.RaggedBatch.to_device already carries V and the feature masks."""
+        from .model.masking import c_mask
         cap = batch["caption"]
         cap_in, y = cap[:, :-1], cap[:, 1:]
+        if "caption_in" in batch:
+            cap_in = batch["caption_in"]
+        elif self.random_synonyms > 0:
+            from . import data
+            cap_in = data.generate_synonyms(cap_in.contiguous(), self.random_synonyms, self.cap_model.voc_size, self.end_idx,
+                                            self.pad_idx, salt=self._syn_salt())
+        if "V" in batch:
+            masks = {"V_mask": batch["V_mask"], "A_mask": batch["A_mask"], "C_mask": c_mask(cap_in, self.pad_idx)}
+            return (batch["V"], batch["audio"]), cap_in, y.contiguous(), masks
         masks = make_masks({"rgb": batch["rgb"], "flow": batch["flow"], "audio": batch["audio"]}, cap_in,
                            self.modality, self.pad_idx)
         return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y.contiguous(), masks
+
+    def _syn_salt(self):
+        if not hasattr(self, "_synsalt"):
+            self._synsalt = ops.next_salt()
+        return self._synsalt
 
     def _mark_layer_boundary(self, i, x):
         """LayerStack hook of the encoder: output (M1, M2) of layer i -> marked copies; the marker fires in backward
@@ -293,7 +313,7 @@ class StepRunner:
         self.trainer, self.kind, self.stabilize = trainer, kind, stabilize
         dev = next(trainer.cap_model.parameters()).device
         self.static = {k: torch.empty_like(v, device=dev).copy_(v) for k, v in example_batch.items()
-                       if k in ("rgb", "flow", "audio", "caption", "score")}
+                       if k in ("rgb", "flow", "audio", "caption", "score", "V", "V_mask", "A_mask")}
         self.graph = None
         self.out = None
         if use_graph:
@@ -330,6 +350,15 @@ class StepRunner:
 
     def step(self, host_batch):
         self.load(host_batch)
+        return self.replay()
+
+    def step_ragged(self, ragged, score=None):
+        """One step fed by the input pipeline: `ragged` is a data.RaggedBatch whose stage() has been called -- ONE
+        host->device copy of the packed clips + captions, the pad / rgb+flow / mask kernels straight into this runner's
+        static buffers (the runner must have been built from a batch with V / V_mask / A_mask), then the step."""
+        ragged.to_device(out=self.static)
+        if score is not None:
+            self.static["score"].copy_(score, non_blocking=True)
         return self.replay()
 
 
