@@ -429,10 +429,15 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
         // a cluster of `split` CTAs along K when the tiles alone leave most SMs idle and every problem has K to split
         while (split < 4 && tiles * split * 2 <= n_sm + n_sm / 4 && min_kb / (split * 2) >= 2 && BN / (split * 2) >= 32) split *= 2;
     }
+    static const int env_bn = getenv("BMHRL_GB_BN") ? atoi(getenv("BMHRL_GB_BN")) : 0;
+    static const int env_split = getenv("BMHRL_GB_SPLIT") ? atoi(getenv("BMHRL_GB_SPLIT")) : 0;
+    if (env_bn == 64 || env_bn == 128) BN = env_bn;
+    if (env_split == 1 || env_split == 2 || env_split == 4) split = env_split;
     if (g_gb_force_bn) BN = g_gb_force_bn;
     if (g_gb_force_split) split = g_gb_force_split;
     while (split > 1 && (BN / split < 32 || min_kb < split)) split >>= 1;
-    int nstages = g_gb_force_stages ? g_gb_force_stages : (BN == 128 ? 4 : 6);
+    static const int env_stages = getenv("BMHRL_GB_STAGES") ? atoi(getenv("BMHRL_GB_STAGES")) : 0;  // experiments
+    int nstages = g_gb_force_stages ? g_gb_force_stages : (env_stages ? env_stages : (BN == 128 ? 4 : 6));
     {
         const int kb_per_cta = (max_kb + split - 1) / split;
         if (nstages > kb_per_cta) nstages = kb_per_cta < 2 ? 2 : kb_per_cta;
