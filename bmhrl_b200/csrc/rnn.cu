@@ -285,9 +285,244 @@ __global__ void __launch_bounds__(128) segment_label_kernel(const float* __restr
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Wavefront variant for the whole critic: ALL recurrent layers in ONE cooperative launch.  Cell (layer l, step t)
+// depends on (l, t-1) and (l-1, t), so the cells with l + t = w are independent: wavefront w computes them side by
+// side and the launch needs L + n_layers - 1 grid barriers instead of n_layers * L (25 instead of 120 for the critic at
+// L = 20) -- the per-layer kernels above are latency chains (barrier + broadcast of h per step), not arithmetic.
+// A CTA is bound to one layer and a block of its hidden units; a warp computes, for one unit and 16 batch rows, the NG
+// gate pre-activations W_ih x + W_hh h (both halves here: the input half of layer l at step t exists only one
+// wavefront earlier) in exact fp32 FMAs, with the weights streamed from L2 (all six layers' 60 MB stay L2-resident).
+struct CriticWave {
+    const float* emb; int E;                       // (B, L, E) input of layer 0
+    const float* w_ih[8]; const float* w_hh[8]; const float* b_ih[8]; const float* b_hh[8];
+    int n_lstm, n_layers;
+    const float* alpha; const float* beta;         // AReLU between the LSTM and the GRU stack (device scalars)
+    float* h;                                      // (n_layers, B, L, H) hidden states of every layer
+    float* c;                                      // (n_lstm, B, H) LSTM cell states
+    unsigned* bar;
+    int B, L, H, cpl, upc;                         // CTAs per layer, hidden units per CTA
+};
+
+template <int NG>
+__device__ __forceinline__ void wave_unit(const CriticWave& p, int l, int t, int j, int b0, int nb, int Kin,
+                                          const float* xs, const float* hs, int lane) {
+    const int H = p.H;
+    const float* Wih = p.w_ih[l];
+    const float* Whh = p.w_hh[l];
+    float acc[NG][RNN_BT];
+    float gi[NG], gh[NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) { gi[g] = 0.f; gh[g] = 0.f; }
+    // ---- input half: W_ih[g*H + j, :] . x[bb, :]
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+        for (int bb = 0; bb < RNN_BT; ++bb) acc[g][bb] = 0.f;
+    for (int k4 = lane; k4 < (Kin >> 2); k4 += 32) {
+        float4 w[NG];
+#pragma unroll
+        for (int g = 0; g < NG; ++g) w[g] = __ldg(reinterpret_cast<const float4*>(Wih + ((long long)g * H + j) * Kin) + k4);
+#pragma unroll
+        for (int bb = 0; bb < RNN_BT; ++bb) {
+            const float4 xv = reinterpret_cast<const float4*>(xs + bb * Kin)[k4];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) {
+                acc[g][bb] = fmaf(w[g].x, xv.x, acc[g][bb]);
+                acc[g][bb] = fmaf(w[g].y, xv.y, acc[g][bb]);
+                acc[g][bb] = fmaf(w[g].z, xv.z, acc[g][bb]);
+                acc[g][bb] = fmaf(w[g].w, xv.w, acc[g][bb]);
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+        for (int bb = 0; bb < RNN_BT; ++bb) {
+            const float s = warp_sum(acc[g][bb]);
+            if (lane == bb) gi[g] = s;
+        }
+    // ---- recurrent half: W_hh[g*H + j, :] . h_{t-1}[bb, :]
+    if (t > 0) {
+#pragma unroll
+        for (int g = 0; g < NG; ++g)
+#pragma unroll
+            for (int bb = 0; bb < RNN_BT; ++bb) acc[g][bb] = 0.f;
+        for (int k4 = lane; k4 < (H >> 2); k4 += 32) {
+            float4 w[NG];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) w[g] = __ldg(reinterpret_cast<const float4*>(Whh + ((long long)g * H + j) * H) + k4);
+#pragma unroll
+            for (int bb = 0; bb < RNN_BT; ++bb) {
+                const float4 hv = reinterpret_cast<const float4*>(hs + bb * H)[k4];
+#pragma unroll
+                for (int g = 0; g < NG; ++g) {
+                    acc[g][bb] = fmaf(w[g].x, hv.x, acc[g][bb]);
+                    acc[g][bb] = fmaf(w[g].y, hv.y, acc[g][bb]);
+                    acc[g][bb] = fmaf(w[g].z, hv.z, acc[g][bb]);
+                    acc[g][bb] = fmaf(w[g].w, hv.w, acc[g][bb]);
+                }
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < NG; ++g)
+#pragma unroll
+            for (int bb = 0; bb < RNN_BT; ++bb) {
+                const float s = warp_sum(acc[g][bb]);
+                if (lane == bb) gh[g] = s;
+            }
+    }
+    if (lane >= nb) return;
+    const int b = b0 + lane;
+    const float* bi = p.b_ih[l];
+    const float* bh = p.b_hh[l];
+    float* hout = p.h + (((long long)l * p.B + b) * p.L + t) * H + j;
+    const float hprev = t > 0 ? hs[lane * H + j] : 0.f;
+    if (NG == 4) {
+        const float pi = (gi[0] + bi[j]) + bh[j] + gh[0];
+        const float pf = (gi[1] + bi[H + j]) + bh[H + j] + gh[1];
+        const float pg = (gi[2] + bi[2 * H + j]) + bh[2 * H + j] + gh[2];
+        const float po = (gi[NG - 1] + bi[3 * H + j]) + bh[3 * H + j] + gh[NG - 1];
+        float* cp = p.c + ((long long)l * p.B + b) * H + j;
+        const float cprev = t > 0 ? *cp : 0.f;
+        const float cn = sigmoid_exact(pf) * cprev + sigmoid_exact(pi) * tanhf(pg);
+        *cp = cn;
+        *hout = sigmoid_exact(po) * tanhf(cn);
+    } else {
+        const float r = sigmoid_exact((gi[0] + bi[j]) + gh[0] + bh[j]);
+        const float z = sigmoid_exact((gi[1] + bi[H + j]) + gh[1] + bh[H + j]);
+        const float n = tanhf((gi[2] + bi[2 * H + j]) + r * (gh[2] + bh[2 * H + j]));
+        *hout = (1.f - z) * n + z * hprev;
+    }
+}
+
+__global__ void __launch_bounds__(256) critic_wavefront_kernel(const CriticWave p) {
+    extern __shared__ float smem[];
+    const int H = p.H;
+    const int l = blockIdx.x / p.cpl, ci = blockIdx.x - l * p.cpl;
+    const int Kin = l == 0 ? p.E : H;
+    float* xs = smem;                       // [RNN_BT][Kin]
+    float* hs = smem + RNN_BT * (p.E > H ? p.E : H);   // [RNN_BT][H]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool lstm = l < p.n_lstm;
+    const bool act_in = (l == p.n_lstm) && p.alpha != nullptr;   // AReLU on the input of the first GRU layer
+    float aa = 0.f, ab = 0.f;
+    if (act_in) {
+        aa = fminf(fmaxf(p.alpha[0], 0.01f), 0.99f);
+        ab = 1.f + sigmoid_exact(p.beta[0]);
+    }
+    const int n_waves = p.L + p.n_layers - 1;
+    for (int w = 0; w < n_waves; ++w) {
+        const int t = w - l;
+        if (t >= 0 && t < p.L) {
+            for (int b0 = 0; b0 < p.B; b0 += RNN_BT) {
+                const int nb = min(RNN_BT, p.B - b0);
+                // x tile: the embedding (layer 0) or the previous layer's h at the SAME step (written one wavefront ago)
+                const int K4 = Kin >> 2;
+                for (int i = threadIdx.x; i < RNN_BT * K4; i += blockDim.x) {
+                    const int bb = i / K4, k4 = i - bb * K4;
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (bb < nb) {
+                        if (l == 0) {
+                            v = __ldg(reinterpret_cast<const float4*>(p.emb + ((long long)(b0 + bb) * p.L + t) * p.E) + k4);
+                        } else {
+                            v = __ldcg(reinterpret_cast<const float4*>(p.h + ((((long long)(l - 1) * p.B + b0 + bb) * p.L + t) * H)) + k4);
+                            if (act_in) {
+                                v.x = fmaxf(v.x, 0.f) * ab - fmaxf(-v.x, 0.f) * aa;
+                                v.y = fmaxf(v.y, 0.f) * ab - fmaxf(-v.y, 0.f) * aa;
+                                v.z = fmaxf(v.z, 0.f) * ab - fmaxf(-v.z, 0.f) * aa;
+                                v.w = fmaxf(v.w, 0.f) * ab - fmaxf(-v.w, 0.f) * aa;
+                            }
+                        }
+                    }
+                    reinterpret_cast<float4*>(xs)[i] = v;
+                }
+                if (t > 0) {
+                    const int H4 = H >> 2;
+                    for (int i = threadIdx.x; i < RNN_BT * H4; i += blockDim.x) {
+                        const int bb = i / H4, k4 = i - bb * H4;
+                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (bb < nb)
+                            v = __ldcg(reinterpret_cast<const float4*>(p.h + ((((long long)l * p.B + b0 + bb) * p.L + t - 1) * H)) + k4);
+                        reinterpret_cast<float4*>(hs)[i] = v;
+                    }
+                }
+                __syncthreads();
+                for (int u = warp; u < p.upc; u += 8) {
+                    const int j = ci * p.upc + u;
+                    if (j < H) {
+                        if (lstm) wave_unit<4>(p, l, t, j, b0, nb, Kin, xs, hs, lane);
+                        else wave_unit<3>(p, l, t, j, b0, nb, Kin, xs, hs, lane);
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        if (w + 1 < n_waves) grid_barrier(p.bar, (unsigned)(w + 1) * gridDim.x);
+    }
+}
+
 }  // namespace bmhrl
 
 using namespace bmhrl;
+
+extern "C" long long bmhrl_critic_wavefront_ws_floats(int n_layers, int n_lstm, int B, int L, int H) {
+    return (long long)n_layers * B * L * H + (long long)n_lstm * B * H + 4;
+}
+
+extern "C" int bmhrl_critic_wavefront_f32(const float* emb, int E, const float* const* w_ih, const float* const* w_hh,
+                                          const float* const* b_ih, const float* const* b_hh, int n_lstm, int n_gru,
+                                          const float* arelu_alpha, const float* arelu_beta, float* ws, int B, int L, int H,
+                                          void* stream) {
+    const int n_layers = n_lstm + n_gru;
+    BMHRL_CHECK_ARG(emb && w_ih && w_hh && b_ih && b_hh && ws, "bmhrl_critic_wavefront_f32: null pointer");
+    BMHRL_CHECK_ARG(n_layers >= 1 && n_layers <= 8 && n_lstm >= 0 && n_gru >= 0, "bmhrl_critic_wavefront_f32: 1..8 layers");
+    BMHRL_CHECK_ARG(B > 0 && L > 0 && H > 0 && E > 0 && (H & 3) == 0 && (E & 3) == 0 && aligned16(emb) && aligned16(ws),
+                    "bmhrl_critic_wavefront_f32: sizes must be multiples of 4, pointers 16-byte aligned");
+    CriticWave p{};
+    p.emb = emb; p.E = E;
+    for (int l = 0; l < n_layers; ++l) {
+        BMHRL_CHECK_ARG(w_ih[l] && w_hh[l] && b_ih[l] && b_hh[l] && aligned16(w_ih[l]) && aligned16(w_hh[l]),
+                        "bmhrl_critic_wavefront_f32: layer weights");
+        p.w_ih[l] = w_ih[l]; p.w_hh[l] = w_hh[l]; p.b_ih[l] = b_ih[l]; p.b_hh[l] = b_hh[l];
+    }
+    p.n_lstm = n_lstm; p.n_layers = n_layers; p.alpha = arelu_alpha; p.beta = arelu_beta;
+    p.h = ws;
+    p.c = ws + (long long)n_layers * B * L * H;
+    p.bar = reinterpret_cast<unsigned*>(ws + (long long)n_layers * B * L * H + (long long)n_lstm * B * H);
+    p.B = B; p.L = L; p.H = H;
+    const int n_sm = device_sm_count();
+    p.cpl = n_sm / n_layers;
+    if (p.cpl < 1) return 1;
+    p.upc = (H + p.cpl - 1) / p.cpl;
+    const size_t smem = sizeof(float) * RNN_BT * ((size_t)(E > H ? E : H) + H);
+    static DeviceOnce attr;
+    if (needs_setup(attr)) {
+        if (cudaFuncSetAttribute(critic_wavefront_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) {
+            bmhrl_set_error("critic wavefront: cannot raise the shared-memory limit");
+            return BMHRL_ERR_CUDA;
+        }
+        mark_done(attr);
+    }
+    if (smem > 200 * 1024) return 1;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, critic_wavefront_kernel, 256, smem) != cudaSuccess || per_sm < 1)
+        return 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(p.bar, 0, sizeof(unsigned), st) != cudaSuccess) {
+        bmhrl_set_error("critic wavefront: memset failed");
+        return BMHRL_ERR_CUDA;
+    }
+    void* args[] = {(void*)&p};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)critic_wavefront_kernel, dim3(p.cpl * n_layers), dim3(256), args,
+                                                smem, st);
+    if (e != cudaSuccess) {
+        bmhrl_set_error(cudaGetErrorString(e));
+        return BMHRL_ERR_CUDA;
+    }
+    bmhrl_count_launch(1);
+    return BMHRL_OK;
+}
 
 static int g_rnn_persistent = 1;
 

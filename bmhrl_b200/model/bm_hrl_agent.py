@@ -144,8 +144,14 @@ class SegmentCritic(nn.Module):
         if path is not None:  # the reference always loads; None (extension) keeps the random init
             self.load_state_dict(torch.load(path))
 
+    wavefront = True  # all six recurrent layers in one cooperative launch (ops.critic_wavefront); False: layer by layer
+
     def hidden(self, embedded_indices):
         with torch.no_grad():
+            if self.wavefront and os.environ.get("BMHRL_CRITIC_WAVEFRONT", "1") != "0":
+                h = ops.critic_wavefront(embedded_indices, self.lstm, self.gru, self.relu.alpha, self.relu.beta)
+                if h is not None:
+                    return self.relu2(h)
             h = embedded_indices
             for l in range(self.lstm.num_layers):
                 h = ops.rnn_layer("lstm", h, getattr(self.lstm, f"weight_ih_l{l}"), getattr(self.lstm, f"weight_hh_l{l}"),

@@ -1002,6 +1002,32 @@ def rnn_step(cell, gx, w_hh, b_hh, out, c, t):
              _p(out), _p(cp), _p(cn), B, L, H, int(t), _stream())
 
 
+def critic_wavefront(emb, lstm, gru, alpha, beta):
+    """All recurrent layers of the SegmentCritic (nn.LSTM stack -> AReLU -> nn.GRU stack, model/bm_hrl_agent.py:204-211)
+    in ONE cooperative launch (rnn.cu: critic_wavefront_kernel).  Returns the last layer's (B,L,H) hidden states, or
+    None when the grid cannot be co-resident (the caller then runs layer by layer)."""
+    import ctypes
+    emb = _c(emb, "embedded tokens")
+    B, L, E = emb.shape
+    H = lstm.hidden_size
+    nl, ng = lstm.num_layers, gru.num_layers
+    if gru.hidden_size != H or H % 4 or E % 4:
+        return None
+    names = [(lstm, l) for l in range(nl)] + [(gru, l) for l in range(ng)]
+    arr = lambda fmt: (ctypes.c_void_p * (nl + ng))(*[_c(getattr(m, fmt.format(l)), fmt).data_ptr() for m, l in names])
+    w_ih, w_hh, b_ih, b_hh = arr("weight_ih_l{}"), arr("weight_hh_l{}"), arr("bias_ih_l{}"), arr("bias_hh_l{}")
+    n = LIB.raw("bmhrl_critic_wavefront_ws_floats")(nl + ng, nl, B, L, H)
+    ws = torch.empty(n, device=emb.device, dtype=_F32)
+    rc = LIB.raw("bmhrl_critic_wavefront_f32")(_p(emb), E, w_ih, w_hh, b_ih, b_hh, nl, ng, _p(_c(alpha, "alpha")),
+                                               _p(_c(beta, "beta")), _p(ws), B, L, H, _stream())
+    if rc == 1:
+        return None
+    if rc != 0:
+        raise RuntimeError(f"bmhrl_critic_wavefront_f32 failed ({rc}): {LIB.raw('bmhrl_last_error')().decode()}")
+    blk = B * L * H
+    return ws[(nl + ng - 1) * blk:(nl + ng) * blk].view(B, L, H)
+
+
 def arelu(x, alpha, beta):
     x = _c(x, "x")
     y = torch.empty_like(x)

@@ -199,7 +199,7 @@ class BMHRLTrainer:
     # ---- warm-start step -------------------------------------------------------------------------------------------
     def warmstart_step(self, batch):
         """captioning_bmrl_loops.py:1148-1160.  Returns the scalar loss tensor (device)."""
-        ops.new_rng_epoch(batch["rgb"].device)
+        ops.new_rng_epoch(batch["caption"].device)
         self.cap_opt.zero_grad()
         x, cap_in, y, masks = self._inputs(batch)
         n_tokens = self._global_tokens_early(y)
@@ -288,7 +288,7 @@ class BMHRLTrainer:
         return self.rl_finish(cap_loss, value_loss, train_worker)
 
     def rl_begin(self, batch, train_worker):
-        ops.new_rng_epoch(batch["rgb"].device)
+        ops.new_rng_epoch(batch["caption"].device)
         self.cap_opt.zero_grad()
         (self.wv_opt if train_worker else self.mv_opt).zero_grad()
 

@@ -271,6 +271,18 @@ int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const floa
  * for t = 0, 1, ... gives the bits bmhrl_rnn_layer_f32 gives for the whole prefix, at the cost of one step per token. */
 int bmhrl_rnn_step_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, const float* c_prev,
                        float* c_next, int B, int L, int H, int t, void* stream);
+/* The whole recurrent part of the critic -- n_lstm nn.LSTM layers, AReLU (may be NULL: none), n_gru nn.GRU layers
+ * (model/bm_hrl_agent.py:192-193,204-211) -- in ONE cooperative launch: cells (layer, step) with layer + step = w are
+ * independent and are computed side by side, L + n_layers - 1 grid barriers instead of n_layers * L.  Input AND
+ * recurrent halves of the gate pre-activations in exact fp32 FMAs, weights streamed from L2.  w_ih / w_hh / b_ih / b_hh:
+ * HOST arrays of n_lstm + n_gru device pointers (nn.LSTM / nn.GRU parameter layout, layer 0 has E input features).
+ * ws: bmhrl_critic_wavefront_ws_floats() floats; the hidden states of layer l are ws[l*B*L*H ...] as (B, L, H): the last
+ * layer's block is the output.  Returns 1 (nothing launched) when the grid cannot be co-resident. */
+long long bmhrl_critic_wavefront_ws_floats(int n_layers, int n_lstm, int B, int L, int H);
+int bmhrl_critic_wavefront_f32(const float* emb, int E, const float* const* w_ih, const float* const* w_hh,
+                               const float* const* b_ih, const float* const* b_hh, int n_lstm, int n_gru,
+                               const float* arelu_alpha, const float* arelu_beta, float* ws, int B, int L, int H,
+                               void* stream);
 /* AReLU model/bm_hrl_agent.py:13-23 (alpha, beta: device scalars). */
 int bmhrl_arelu_f32(const float* x, const float* alpha, const float* beta, float* y, long long n, void* stream);
 /* scores[row] = x[row,:] . w + b; labels[row] = sigmoid(score) > threshold (model/bm_hrl_agent.py:213,638-640). */

@@ -422,3 +422,29 @@ def test_errors_are_loud(gpu_lib):
                      torch.randn(2, 3, 10, device="cuda"), None, 4)
     with pytest.raises(RuntimeError):
         ops.layer_norm(torch.randn(4, 8, device="cuda").double(), torch.ones(8, device="cuda"), torch.zeros(8, device="cuda"))
+
+
+@pytest.mark.parametrize("B,L", [(3, 7), (16, 20), (17, 5), (1, 1)])
+def test_critic_wavefront_equals_layer_by_layer(gpu_lib, agent_sd, B, L):
+    """ops.critic_wavefront (all recurrent layers of the SegmentCritic in one cooperative launch, L + 5 grid barriers)
+    against the layer-by-layer kernels and the fp32 oracle: hidden states to 1e-5, segment labels exact."""
+    from types import SimpleNamespace as NS
+    from bmhrl_b200 import ops
+    from bmhrl_b200.model.bm_hrl_agent import SegmentCritic
+    g = _g(31 + B)
+    crit = SegmentCritic(NS(d_model_caps=300, rl_critic_path=None))
+    csd = {k[len("critic."):]: v for k, v in agent_sd.items() if k.startswith("critic.")}
+    crit.load_state_dict(csd)
+    crit = crit.cuda()
+    x = (torch.randn(B, L, 300, generator=g) * math.sqrt(300) * 0.3)
+    hw = ops.critic_wavefront(x.cuda(), crit.lstm, crit.gru, crit.relu.alpha, crit.relu.beta)
+    assert hw is not None
+    ref = _critic_last_gru(crit, x.cuda())
+    assert rel(hw, ref) < 1e-5
+    crit.wavefront = True
+    s1, l1 = crit.scores_and_labels(x.cuda(), 0.25)
+    crit.wavefront = False
+    s0, l0 = crit.scores_and_labels(x.cuda(), 0.25)
+    assert torch.equal(l1, l0) and rel(s1, s0) < 1e-5
+    so = O.segment_critic({"critic." + k: v for k, v in csd.items()}, x)
+    assert torch.equal(l1.cpu(), O.segment_labels_from_scores(so, 0.25).to(l1.dtype).cpu().reshape(l1.shape))
