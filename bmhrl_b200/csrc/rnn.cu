@@ -7,6 +7,7 @@
 // part is one fused kernel per time step: h_{t-1} W_hh^T, the gate non-linearities and the state update.  One
 // warp owns one hidden unit (its 4 / 3 gate rows of W_hh, read once, coalesced) for up to 16 batch rows whose
 // h_{t-1} sits in shared memory.
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/bmhrl_b200.h"
 
@@ -542,6 +543,10 @@ static int launch_rnn_persistent_t(const float* gx, const float* W_hh, const flo
     }
     // smallest units-per-block whose grid is co-resident (1 CTA per SM is assumed; smaller smem only helps)
     int upb = (H + n_sm - 1) / n_sm;
+    // BMHRL_RNN_UPB: at least that many hidden units per CTA -> fewer, fatter CTAs (a step is a latency chain, not
+    // arithmetic: the layer then leaves the other SMs to the kernels that run beside the frozen critic)
+    static const int env_upb = getenv("BMHRL_RNN_UPB") ? atoi(getenv("BMHRL_RNN_UPB")) : 0;
+    if (env_upb > upb) upb = env_upb;
     for (; upb <= 16; ++upb) {
         const size_t smem = sizeof(float) * ((size_t)upb * NG * H + (size_t)RNN_BT * H);
         if (smem > 220 * 1024) return 1;

@@ -148,7 +148,7 @@ class SegmentCritic(nn.Module):
 
     def hidden(self, embedded_indices):
         with torch.no_grad():
-            if self.wavefront and os.environ.get("BMHRL_CRITIC_WAVEFRONT", "1") != "0":
+            if self.wavefront and os.environ.get("BMHRL_CRITIC_WAVEFRONT", "0") != "0":
                 h = ops.critic_wavefront(embedded_indices, self.lstm, self.gru, self.relu.alpha, self.relu.beta)
                 if h is not None:
                     return self.relu2(h)

@@ -441,9 +441,12 @@ def test_critic_wavefront_equals_layer_by_layer(gpu_lib, agent_sd, B, L):
     assert hw is not None
     ref = _critic_last_gru(crit, x.cuda())
     assert rel(hw, ref) < 1e-5
-    crit.wavefront = True
-    s1, l1 = crit.scores_and_labels(x.cuda(), 0.25)
-    crit.wavefront = False
+    import os
+    os.environ["BMHRL_CRITIC_WAVEFRONT"] = "1"
+    try:
+        s1, l1 = crit.scores_and_labels(x.cuda(), 0.25)
+    finally:
+        os.environ["BMHRL_CRITIC_WAVEFRONT"] = "0"
     s0, l0 = crit.scores_and_labels(x.cuda(), 0.25)
     assert torch.equal(l1, l0) and rel(s1, s0) < 1e-5
     so = O.segment_critic({"critic." + k: v for k, v in csd.items()}, x)
