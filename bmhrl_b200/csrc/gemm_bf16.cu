@@ -49,6 +49,10 @@ struct alignas(64) GbProblem {
     int vec32, vec16, vecr, vecg;  // 128-bit access allowed on C32 rows / 64-bit on C16 / resid / gate
     float alpha, beta, gate_scale, drop_p;
     unsigned int salt;
+    // MODE 1 / 2 (vocabulary projection fused with the log-softmax / KL statistics, see the end of this file)
+    const long long* v_trg; const long long* v_tok; const float* v_q; float* v_part;
+    const float* v_stats; const float* v_dstat;
+    int v_pad, v_smode;
 };
 
 struct GbParams {
@@ -65,7 +69,7 @@ __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
     return r;
 }
 
-template <int BN>
+template <int BN, int MODE>
 __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant__ GbParams P) {
     constexpr int B_BYTES = BN * 128;
     constexpr int STAGE_BYTES = GB_A_BYTES + B_BYTES;
@@ -199,7 +203,106 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
         __syncwarp();
         cluster_sync_all();  // release / acquire: all partial slices have landed
     }
-    if (warp >= 2) {
+    if (MODE == 1 && warp >= 2) {
+        // ---- vocabulary statistics of row m over this CTA's BN columns (no output tile is written):
+        //   max, sum exp(v - max), sum v, v[target], v[pad], and the sampling arg-max (key, index, logit)
+        const int trg = m < p.M ? (int)p.v_trg[m] : -1;
+        float mx = -INFINITY, sv = 0.f, lt = 0.f, lp = 0.f, bk = -INFINITY, bl = 0.f;
+        int bi = 0x7fffffff;
+#pragma unroll 1
+        for (int cc = 0; cc < BN; cc += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
+            tmem_ld_wait();
+            const int nb = n0 + cc;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = nb + j;
+                if (n < p.N && m < p.M) {
+                    const float v = __uint_as_float(r[j]) + (p.bias ? p.bias[n] : 0.f);
+                    mx = fmaxf(mx, v);
+                    sv += v;
+                    if (n == trg) lt = v;
+                    if (n == p.v_pad) lp = v;
+                    float key = v;
+                    if (p.v_smode == 1) {
+                        key = v - logf(p.v_q[(long long)m * p.N + n]);
+                    } else if (p.v_smode == 2) {
+                        const float u = u32_to_unit(philox_u32(p.rng, p.salt, (unsigned long long)m * p.N + n));
+                        key = v - logf(-logf(1.f - u));
+                    }
+                    if (key > bk) { bk = key; bi = n; bl = v; }   // ascending n: the first maximum wins
+                }
+            }
+        }
+        float se = 0.f;
+#pragma unroll 1
+        for (int cc = 0; cc < BN; cc += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
+            tmem_ld_wait();
+            const int nb = n0 + cc;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int n = nb + j;
+                if (n < p.N && m < p.M) se += __expf(__uint_as_float(r[j]) + (p.bias ? p.bias[n] : 0.f) - mx);
+            }
+        }
+        if (m < p.M) {
+            float* o = p.v_part + ((long long)m * p.tiles_n + tn) * 8;
+            st_f4(o, make_float4(mx, se, sv, lt));
+            st_f4(o + 4, make_float4(lp, bk, __int_as_float(bi), bl));
+        }
+        tc_fence_before();
+    }
+    if (MODE == 2 && warp >= 2) {
+        // ---- d logits from the gradients of the row statistics {lse, sum v, v[target], v[pad], v[token]}:
+        //   dv(n) = dlse * exp(v(n) - lse) + dsum + [n == target] dlt + [n == pad] dlp + [n == token] dls   -> bf16
+        float lse = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f, g4 = 0.f;
+        int trg = -1, tok = -1;
+        if (m < p.M) {
+            lse = p.v_stats[(long long)m * 5];
+            const float* g = p.v_dstat + (long long)m * 5;
+            g0 = g[0]; g1 = g[1]; g2 = g[2]; g3 = g[3]; g4 = g[4];
+            trg = (int)p.v_trg[m];
+            tok = p.v_tok ? (int)p.v_tok[m] : -1;
+        }
+#pragma unroll 1
+        for (int cc = 0; cc < BN; cc += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
+            tmem_ld_wait();
+            const int nb = n0 + cc;
+            if (m < p.M && nb < p.N) {
+                __nv_bfloat16* hrow = p.C16 + (long long)m * p.ldc16 + nb;
+#pragma unroll
+                for (int j4 = 0; j4 < 32; j4 += 4) {
+                    const int n = nb + j4;
+                    if (n >= p.N) break;
+                    float v[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int nn = n + j;
+                        const float lg = __uint_as_float(r[j4 + j]) + ((p.bias && nn < p.N) ? p.bias[nn] : 0.f);
+                        float d = g0 * __expf(lg - lse) + g1;
+                        if (nn == trg) d += g2;
+                        if (nn == p.v_pad) d += g3;
+                        if (nn == tok) d += g4;
+                        v[j] = d;
+                    }
+                    if (n + 3 < p.N && p.vec16) {
+                        *reinterpret_cast<uint2*>(hrow + j4) = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < p.N) hrow[j4 + j] = __float2bfloat16(v[j]);
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    if (MODE == 0 && warp >= 2) {
         const float ks = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
         // destination row of the fp32 output (optionally one of up to three row segments)
         float* c32row = nullptr;
@@ -338,13 +441,13 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
 // ---------------------------------------------------------------------------------------------- host side
 static int g_gb_force_bn = 0, g_gb_force_split = 0, g_gb_force_stages = 0;
 
-template <int BN>
+template <int BN, int MODE = 0>
 static int launch_gb(const GbParams& P, int total_tiles, int split, cudaStream_t st) {
     const int stage_bytes = GB_A_BYTES + BN * 128;
     const int smem = P.nstages * stage_bytes + 1024 + 8 * (2 * P.nstages + 2) + (P.cluster > 1 ? GB_BM * BN * 4 : 0);
     static DeviceOnce attr;
     if (needs_setup(attr)) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tc_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (e != cudaSuccess) {
             bmhrl_set_error(cudaGetErrorString(e));
             return BMHRL_ERR_CUDA;
@@ -365,7 +468,7 @@ static int launch_gb(const GbParams& P, int total_tiles, int split, cudaStream_t
         cfg.attrs = at;
         cfg.numAttrs = 1;
     }
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bf16_tc_kernel<BN>, P);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bf16_tc_kernel<BN, MODE>, P);
     if (e != cudaSuccess) {
         bmhrl_set_error(cudaGetErrorString(e));
         return BMHRL_ERR_CUDA;
@@ -487,4 +590,114 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
     cudaStream_t st = (cudaStream_t)stream;
     if (BN == 128) return launch_gb<128>(P, tile_start, split, st);
     return launch_gb<64>(P, tile_start, split, st);
+}
+
+
+// ================================================================================================================
+// K4: vocabulary projection fused with log-softmax and the KL losses (north_star kernel 3).
+// Reference: WorkerCore model/bm_hrl_agent.py:463-466 (Linear 364 -> V + LogSoftmax), LabelSmoothing
+// loss/label_smoothing.py:12-32, BiasedKL loss/biased_kl.py:22-53, biased_kl() sampling
+// epoch_loops/captioning_bmrl_loops.py:273-285.  The (B*L, V) logits / log-probabilities are never written:
+//   forward   the GEMM tiles stay in TMEM; the epilogue reduces each row of a tile to {max, sum exp, sum v, v[target],
+//             v[pad], sampling arg-max}; vocab_finalize_kernel merges the V/128 partials of a row into the sufficient
+//             statistics {lse, sum v, v[target], v[pad], v[token]} and the sampled / arg-max token.  Both KL losses are
+//             closed forms of these five numbers (their target distribution takes at most four distinct values per row).
+//   backward  the GEMM is recomputed and the epilogue turns the five statistic gradients into d logits (bf16), the
+//             operand of the dX / dW GEMMs.
+__global__ void vocab_finalize_kernel(const float* __restrict__ part, int tiles, float* __restrict__ stats,
+                                      long long* __restrict__ tok, int M) {
+    const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (m >= M) return;
+    const float* pr = part + (long long)m * tiles * 8;
+    float mx = -INFINITY;
+    for (int t = lane; t < tiles; t += 32) mx = fmaxf(mx, pr[t * 8]);
+    mx = warp_max(mx);
+    float se = 0.f, sv = 0.f, lt = 0.f, lp = 0.f, bk = -INFINITY, bl = 0.f;
+    int bi = 0x7fffffff;
+    for (int t = lane; t < tiles; t += 32) {
+        const float4 a = ld_f4(pr + t * 8), b = ld_f4(pr + t * 8 + 4);
+        se += a.y * __expf(a.x - mx);
+        sv += a.z;
+        lt += a.w;
+        lp += b.x;
+        const int i = __float_as_int(b.z);
+        if (b.y > bk || (b.y == bk && i < bi)) { bk = b.y; bi = i; bl = b.w; }
+    }
+    se = warp_sum(se); sv = warp_sum(sv); lt = warp_sum(lt); lp = warp_sum(lp);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ok = __shfl_xor_sync(0xffffffffu, bk, o), ol = __shfl_xor_sync(0xffffffffu, bl, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ok > bk || (ok == bk && oi < bi)) { bk = ok; bi = oi; bl = ol; }
+    }
+    if (lane == 0) {
+        float* o = stats + (long long)m * 5;
+        o[0] = mx + logf(se); o[1] = sv; o[2] = lt; o[3] = lp; o[4] = bl;
+        if (tok) tok[m] = bi;
+    }
+}
+
+static int vocab_problem(GbParams& P, const void* x16, long long ldx, const void* w16, long long ldw, const float* bias, int M,
+                         int V, int K) {
+    if (get_encode_fn() == nullptr) {
+        bmhrl_set_error("vocab: cuTensorMapEncodeTiled unavailable");
+        return BMHRL_ERR_CUDA;
+    }
+    P.n = 1; P.cluster = 1;
+    const int num_kb = (K + GB_BK - 1) / GB_BK;
+    P.nstages = num_kb < 4 ? (num_kb < 2 ? 2 : num_kb) : 4;
+    GbProblem& q = P.p[0];
+    const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    if (!encode_2d(&q.tmA, BF, 2, x16, K, M, ldx, GB_BK, GB_BM) || !encode_2d(&q.tmB, BF, 2, w16, K, V, ldw, GB_BK, 128)) {
+        bmhrl_set_error("vocab: cuTensorMapEncodeTiled failed");
+        return BMHRL_ERR_CUDA;
+    }
+    q.bias = bias; q.M = M; q.N = V; q.K = K; q.num_kb = num_kb; q.kb_per_split = num_kb;
+    q.tiles_n = (V + 127) / 128; q.tile_start = 0; q.alpha = 1.f;
+    return BMHRL_OK;
+}
+
+extern "C" long long bmhrl_vocab_stats_ws_floats(int M, int V) { return (long long)M * ((V + 127) / 128) * 8; }
+
+extern "C" int bmhrl_vocab_stats_bf16(const void* x16, long long ldx, const void* w16, long long ldw, const float* bias, int M,
+                                      int V, int K, const long long* target, int pad_idx, int sample_mode,
+                                      const float* exp_noise, const unsigned long long* rng_state, unsigned int salt,
+                                      float* part_ws, float* stats, long long* tokens, void* stream) {
+    BMHRL_CHECK_ARG(gb_operand_ok(x16, ldx) && gb_operand_ok(w16, ldw) && target && part_ws && stats && M > 0 && V > 2 && K > 0,
+                    "bmhrl_vocab_stats_bf16: bad arguments");
+    BMHRL_CHECK_ARG(sample_mode >= 0 && sample_mode <= 2 && (sample_mode != 1 || exp_noise) && (sample_mode != 2 || rng_state),
+                    "bmhrl_vocab_stats_bf16: sample_mode 0 arg-max, 1 explicit Exp(1) noise, 2 Philox");
+    BMHRL_CHECK_ARG(aligned16(part_ws), "bmhrl_vocab_stats_bf16: workspace alignment");
+    GbParams P{};
+    int rc = vocab_problem(P, x16, ldx, w16, ldw, bias, M, V, K);
+    if (rc != BMHRL_OK) return rc;
+    GbProblem& q = P.p[0];
+    q.v_trg = target; q.v_q = exp_noise; q.v_part = part_ws; q.v_pad = pad_idx; q.v_smode = sample_mode;
+    q.rng = rng_state; q.salt = salt;
+    const int tiles = ((M + GB_BM - 1) / GB_BM) * q.tiles_n;
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = launch_gb<128, 1>(P, tiles, 1, st);
+    if (rc != BMHRL_OK) return rc;
+    vocab_finalize_kernel<<<(M + 7) / 8, 256, 0, st>>>(part_ws, q.tiles_n, stats, tokens, M);
+    BMHRL_POST_LAUNCH("vocab_finalize");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_vocab_dlogits_bf16(const void* x16, long long ldx, const void* w16, long long ldw, const float* bias, int M,
+                                        int V, int K, const long long* target, const long long* tokens, int pad_idx,
+                                        const float* stats, const float* dstats, void* dlogits16, long long lddl,
+                                        void* stream) {
+    BMHRL_CHECK_ARG(gb_operand_ok(x16, ldx) && gb_operand_ok(w16, ldw) && target && stats && dstats && dlogits16 && M > 0 &&
+                        V > 2 && K > 0 && lddl >= V && (lddl & 7) == 0,
+                    "bmhrl_vocab_dlogits_bf16: bad arguments");
+    GbParams P{};
+    int rc = vocab_problem(P, x16, ldx, w16, ldw, bias, M, V, K);
+    if (rc != BMHRL_OK) return rc;
+    GbProblem& q = P.p[0];
+    q.v_trg = target; q.v_tok = tokens; q.v_pad = pad_idx; q.v_stats = stats; q.v_dstat = dstats;
+    q.C16 = (__nv_bfloat16*)dlogits16; q.ldc16 = lddl;
+    q.vec16 = ((uintptr_t)dlogits16 & 7u) == 0 && (lddl & 3) == 0;
+    const int tiles = ((M + GB_BM - 1) / GB_BM) * q.tiles_n;
+    return launch_gb<128, 2>(P, tiles, 1, (cudaStream_t)stream);
 }

@@ -151,6 +151,98 @@ __global__ void __launch_bounds__(ROW_THREADS) kl_bwd_kernel(int mode, const flo
     }
 }
 
+// ------------------------------------------------------------------ KL row sums from the vocabulary statistics
+// The fused vocabulary kernel (gemm_bf16.cu, MODE 1) leaves five numbers per row: lse, S = sum_v logit, and the logits
+// of the target, pad and sampled-token columns.  The target distribution of both KL losses is constant (b = u + add)
+// outside at most three "special" columns, so with p_c = logit_c - lse and sum_v p_v = S - V lse
+//   row = sum_{c special} [xlogy(d_c) - d_c p_c] + (V - n) xlogy(b) - b (sum_v p_v - sum_{c special} p_c).
+// One thread per row; the same case analysis as kl_target() above (pad column first, then target, then the ADDED sampled
+// mass; zeroed pad rows; the reference's flat-row-0 quirk).
+struct KlSpec {
+    bool pad_row;
+    int n;             // number of special columns (1..3)
+    float d[3], pc[3]; // their target mass (incl. add) and log-probability
+    int which[3];      // statistic index of the column's logit: 2 target, 3 pad, 4 token
+    float b, add;
+    int sigma;         // special-column slot that received the sampled mass (-1: none / merged with the target)
+    int tslot;         // slot of the ground-truth column (-1 when it coincides with the pad column)
+};
+
+__device__ __forceinline__ KlSpec kl_spec(const KlRow& r, const float* st) {
+    KlSpec k;
+    const float lse = st[0];
+    k.pad_row = r.pad_row;
+    k.add = r.add;
+    k.b = r.u + r.add;
+    k.n = 0;
+    k.sigma = -1;
+    k.tslot = -1;
+    // pad column
+    k.d[0] = r.add; k.pc[0] = st[3] - lse; k.which[0] = 3; k.n = 1;
+    if (r.trg != r.pad_idx) {  // ground-truth column (when the target IS the pad column the scatter was overwritten by 0)
+        k.d[1] = r.t_trg + r.add; k.pc[1] = st[2] - lse; k.which[1] = 2; k.tslot = 1; k.n = 2;
+    }
+    if (r.mode == 1) {
+        if (r.samp == r.pad_idx) { k.d[0] += r.t_samp; k.sigma = 0; }
+        else if (r.samp == r.trg) { k.d[k.tslot] += r.t_samp; k.sigma = -1; }   // (1-eps)(1-a) + a(1-eps): constant in a
+        else { k.d[k.n] = r.u + r.t_samp + r.add; k.pc[k.n] = st[4] - lse; k.which[k.n] = 4; k.sigma = k.n; ++k.n; }
+    }
+    return k;
+}
+
+__global__ void kl_stats_fwd_kernel(int mode, const float* __restrict__ stats, const long long* __restrict__ trg,
+                                    const long long* __restrict__ samp, const float* __restrict__ offset,
+                                    float* __restrict__ rowsum, long long rows, int V, float smoothing, int pad_idx) {
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    const KlRow r = make_row(mode, trg, samp, offset, row, rows, V, smoothing, pad_idx);
+    const float* st = stats + row * 5;
+    const float sum_p = st[1] - (float)V * st[0];
+    if (r.pad_row) {
+        rowsum[row] = (float)V * xlogy(r.add) - r.add * sum_p;
+        return;
+    }
+    const KlSpec k = kl_spec(r, st);
+    float acc = 0.f, ps = 0.f;
+    for (int i = 0; i < k.n; ++i) { acc += xlogy(k.d[i]) - k.d[i] * k.pc[i]; ps += k.pc[i]; }
+    rowsum[row] = acc + (float)(V - k.n) * xlogy(k.b) - k.b * (sum_p - ps);
+}
+
+// dstats (rows,5) = drow * d row / d {lse, S, logit_t, logit_pad, logit_tok};  doffset (mode 1) = drow * d row / d a
+__global__ void kl_stats_bwd_kernel(int mode, const float* __restrict__ stats, const long long* __restrict__ trg,
+                                    const long long* __restrict__ samp, const float* __restrict__ offset,
+                                    const float* __restrict__ drow, float* __restrict__ dstats,
+                                    float* __restrict__ doffset, long long rows, int V, float smoothing, int pad_idx) {
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    const KlRow r = make_row(mode, trg, samp, offset, row, rows, V, smoothing, pad_idx);
+    const float* st = stats + row * 5;
+    const float g = drow[row];
+    float ds[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    float da = 0.f;
+    if (r.pad_row) {
+        ds[0] = r.add * (float)V;
+        ds[1] = -r.add;
+    } else {
+        const KlSpec k = kl_spec(r, st);
+        float mass = k.b * (float)(V - k.n);
+        ds[1] = -k.b;
+        for (int i = 0; i < k.n; ++i) {
+            mass += k.d[i];
+            ds[k.which[i]] += k.b - k.d[i];
+        }
+        ds[0] = mass;  // d row / d lse = total target mass
+        if (mode == 1 && k.sigma >= 0) {
+            const float dsig = logf(k.d[k.sigma]) + 1.f - k.pc[k.sigma];
+            const float dt = k.tslot >= 0 ? logf(k.d[k.tslot]) + 1.f - k.pc[k.tslot] : 0.f;
+            da = (1.f - smoothing) * (dsig - dt);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 5; ++i) dstats[row * 5 + i] = g * ds[i];
+    if (doffset) doffset[row] = g * da;
+}
+
 // ------------------------------------------------------------------ sampling (K5)
 // mode 0: argmax over exp(pred)                      (manager, captioning_bmrl_loops.py:283)
 // mode 1: argmax((exp(pred)/sum) / q) with explicit q (worker; q ~ Exp(1) supplied by the caller -- the exact
@@ -320,5 +412,32 @@ extern "C" int bmhrl_reinforce_gather_bwd_f32(const float* probs, const long lon
     reinforce_gather_bwd_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, (cudaStream_t)stream>>>(probs, action, g,
                                                                                                   dprobs, rows, V, eps);
     BMHRL_POST_LAUNCH("reinforce_gather_bwd");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_kl_stats_fwd_f32(int mode, const float* stats, const long long* trg, const long long* biased_trg,
+                                      const float* biased_offset, float* rowsum, long long rows, int V, float smoothing,
+                                      int pad_idx, void* stream) {
+    BMHRL_CHECK_ARG(mode == 0 || mode == 1, "bmhrl_kl_stats_fwd_f32: mode must be 0 (label smoothing) or 1 (biased KL)");
+    BMHRL_CHECK_ARG(stats && trg && rowsum && V > 2 && rows >= 0, "bmhrl_kl_stats_fwd_f32: bad arguments");
+    BMHRL_CHECK_ARG(mode == 0 || (biased_trg && biased_offset), "bmhrl_kl_stats_fwd_f32: biased KL needs trg/offset");
+    if (rows == 0) return BMHRL_OK;
+    kl_stats_fwd_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, (cudaStream_t)stream>>>(mode, stats, trg, biased_trg,
+                                                                                          biased_offset, rowsum, rows, V,
+                                                                                          smoothing, pad_idx);
+    BMHRL_POST_LAUNCH("kl_stats_fwd");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_kl_stats_bwd_f32(int mode, const float* stats, const long long* trg, const long long* biased_trg,
+                                      const float* biased_offset, const float* drow, float* dstats, float* doffset,
+                                      long long rows, int V, float smoothing, int pad_idx, void* stream) {
+    BMHRL_CHECK_ARG(mode == 0 || mode == 1, "bmhrl_kl_stats_bwd_f32: mode");
+    BMHRL_CHECK_ARG(stats && trg && drow && dstats && V > 2 && rows >= 0, "bmhrl_kl_stats_bwd_f32: bad arguments");
+    BMHRL_CHECK_ARG(mode == 0 || (biased_trg && biased_offset), "bmhrl_kl_stats_bwd_f32: biased KL needs trg/offset");
+    if (rows == 0) return BMHRL_OK;
+    kl_stats_bwd_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        mode, stats, trg, biased_trg, biased_offset, drow, dstats, doffset, rows, V, smoothing, pad_idx);
+    BMHRL_POST_LAUNCH("kl_stats_bwd");
     return BMHRL_OK;
 }

@@ -404,10 +404,17 @@ class Worker(nn.Module):
         self.logsoftmax = nn.LogSoftmax(dim=-1)
         self.softmax = nn.Softmax(dim=-1)
 
+    # trainer-only switch (bf16 math mode): hand back the 364-d features + projection (ops16.VocabHead) instead of the
+    # (B,L,V) log-probabilities, so that the losses are evaluated by the fused vocabulary kernel without the logits
+    fused_vocab = False
+
     def forward(self, x, goal, mask):
         goal_completion = self.goal_attention(goal, x, x, mask)
         if not self.core.__class__ == torch.nn.Identity:
             x = ops.concat_last(x, goal_completion)
+            if self.fused_vocab and ops.BF16 and isinstance(self.core, WorkerCore) and x.shape[-1] % 4 == 0:
+                from .. import ops16
+                return ops16.VocabHead(x, self.core.projection)
             return self.core(x)
         return goal_completion
 

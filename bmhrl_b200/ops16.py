@@ -681,3 +681,120 @@ def ffn_block(x, ff, norm=None, resid=False, p_res=0.0, emit_twin=False):
            "eps": norm.eps if norm is not None else 0.0, "rng": rng, "emit_twin": emit_twin}
     return _FfnBlock.apply(x, cfg, None if norm is None else norm.weight, None if norm is None else norm.bias, ff.fc1.weight,
                            ff.fc1.bias, ff.fc2.weight, ff.fc2.bias)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# K4 fused: vocabulary projection + log-softmax + KL-loss statistics (gemm_bf16.cu, MODE 1 / 2)
+# ----------------------------------------------------------------------------------------------------------------
+class _VocabStats(torch.autograd.Function):
+    """(M,K) features -> the five per-row statistics {lse, sum logit, logit[target], logit[pad], logit[token]} of the
+    vocabulary logits x W^T + b and the sampled / arg-max token, without the (M,V) logits ever reaching memory.
+    Backward: d logits (bf16) from the five statistic gradients (recomputing GEMM), then the ordinary dX / dW GEMMs."""
+
+    @staticmethod
+    def forward(ctx, x, W, b, trg, pad_idx, smode, noise, rng, salt):
+        K = x.shape[-1]
+        V = W.shape[0]
+        M = x.numel() // K
+        x16 = twin16(x)
+        w16, _ = SHADOWS.get([W], [b])
+        trg = trg.reshape(-1).contiguous()
+        dev = x.device
+        part = torch.empty(LIB.raw("bmhrl_vocab_stats_ws_floats")(M, V), device=dev, dtype=_F32)
+        stats = torch.empty(M, 5, device=dev, dtype=_F32)
+        tok = torch.empty(M, device=dev, dtype=torch.int64)
+        if smode == 1:
+            noise = noise.reshape(M, V).contiguous()
+        LIB.call("bmhrl_vocab_stats_bf16", x16.data_ptr(), x16.stride(0), w16.data_ptr(), w16.stride(0),
+                 None if b is None else b.data_ptr(), M, V, K, trg.data_ptr(), int(pad_idx), int(smode),
+                 noise.data_ptr() if smode == 1 else None, rng.data_ptr() if smode == 2 else None, int(salt), part.data_ptr(),
+                 stats.data_ptr(), tok.data_ptr(), _stream())
+        ctx.save_for_backward(x16, stats, trg, tok)
+        ctx.params = (W, b)
+        ctx.cfg = (M, V, K, int(pad_idx), x.shape)
+        ctx.mark_non_differentiable(tok)
+        return stats, tok
+
+    @staticmethod
+    def backward(ctx, dstats, _dtok):
+        x16, stats, trg, tok = ctx.saved_tensors
+        W, b = ctx.params
+        M, V, K, pad_idx, xshape = ctx.cfg
+        dev = dstats.device
+        dstats = dstats.contiguous()
+        w16, _ = SHADOWS.get([W], [b])
+        dl = empty16(M, V, dev)
+        LIB.call("bmhrl_vocab_dlogits_bf16", x16.data_ptr(), x16.stride(0), w16.data_ptr(), w16.stride(0),
+                 None if b is None else b.data_ptr(), M, V, K, trg.data_ptr(), tok.data_ptr(), pad_idx, stats.data_ptr(),
+                 dstats.data_ptr(), dl.data_ptr(), dl.stride(0), _stream())
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(xshape, device=dev, dtype=_F32)
+            gemm_group([gemm_problem(dl, 0, w16, 1, M, K, V, C32=dx.view(M, K))])
+        dW = _wgrad(dl, x16, [W], V)[0]
+        db = _bgrad16(dl, [b], V)[0] if b is not None else None
+        return dx, dW, db, None, None, None, None, None, None
+
+
+def vocab_stats(x, W, b, trg, pad_idx, mode="argmax", exp_noise=None, salt=0, rng=None):
+    """stats (M,5) fp32 (differentiable in x, W, b) and tokens (M,) int64; see bmhrl_vocab_stats_bf16."""
+    from . import ops
+    m = {"argmax": 0, "noise": 1, "philox": 2}[mode]
+    if m == 2 and rng is None:
+        rng = ops.RNG.current(x.device)
+    return _VocabStats.apply(x, W, b, trg, pad_idx, m, exp_noise, rng, salt)
+
+
+class _KlStats(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, stats, trg, samp, offset, mode, smoothing, pad_idx, V):
+        stats = stats.contiguous()
+        rows = stats.shape[0]
+        trg = trg.reshape(-1).contiguous()
+        if mode == 1:
+            samp = samp.reshape(-1).contiguous()
+            offset = offset.reshape(-1).contiguous()
+        rs = torch.empty(rows, device=stats.device, dtype=_F32)
+        LIB.call("bmhrl_kl_stats_fwd_f32", mode, stats.data_ptr(), trg.data_ptr(), samp.data_ptr() if mode == 1 else None,
+                 offset.data_ptr() if mode == 1 else None, rs.data_ptr(), rows, V, smoothing, pad_idx, _stream())
+        ctx.save_for_backward(stats, trg, samp if mode == 1 else None, offset if mode == 1 else None)
+        ctx.cfg = (mode, smoothing, pad_idx, V, rows)
+        return rs
+
+    @staticmethod
+    def backward(ctx, g):
+        stats, trg, samp, offset = ctx.saved_tensors
+        mode, smoothing, pad_idx, V, rows = ctx.cfg
+        g = g.contiguous()
+        ds = torch.empty(rows, 5, device=g.device, dtype=_F32)
+        doff = torch.empty(rows, device=g.device, dtype=_F32) if (mode == 1 and ctx.needs_input_grad[3]) else None
+        LIB.call("bmhrl_kl_stats_bwd_f32", mode, stats.data_ptr(), trg.data_ptr(), samp.data_ptr() if mode == 1 else None,
+                 offset.data_ptr() if mode == 1 else None, g.data_ptr(), ds.data_ptr(), None if doff is None else doff.data_ptr(),
+                 rows, V, smoothing, pad_idx, _stream())
+        return ds, None, None, doff, None, None, None, None
+
+
+def kl_rowsum_from_stats(stats, trg, smoothing, pad_idx, V, biased_trg=None, biased_offset=None):
+    """Row sums of the LabelSmoothing (biased_trg None; loss/label_smoothing.py:12-32) or BiasedKL
+    (loss/biased_kl.py:22-53) divergence, sum_v [xlogy(d_v) - d_v log p_v], in closed form from the five statistics
+    (loss.cu: kl_stats_fwd / bwd kernels).  Differentiable in stats and biased_offset."""
+    if biased_trg is None:
+        return _KlStats.apply(stats, trg, None, None, 0, float(smoothing), int(pad_idx), int(V))
+    return _KlStats.apply(stats, trg, biased_trg, biased_offset.reshape(-1), 1, float(smoothing), int(pad_idx), int(V))
+
+
+class VocabHead:
+    """What BMHrlAgent returns in place of the (B,L,V) log-probability tensor when `fused_vocab` is on (the trainer's
+    bf16 path): the 364-d features and the projection, from which the losses are evaluated without the logits."""
+
+    def __init__(self, x, proj):
+        self.x, self.proj = x, proj
+        self.shape = tuple(x.shape[:-1]) + (proj.out_features,)
+
+    def stats(self, trg, pad_idx, mode="argmax", exp_noise=None, salt=0):
+        st, tok = vocab_stats(self.x, self.proj.weight, self.proj.bias, trg, pad_idx, mode, exp_noise, salt)
+        return st, tok.view(self.x.shape[:-1])
+
+    def log_probs(self):
+        from . import ops
+        return ops.log_softmax(linear16(self.x, self.proj.weight, self.proj.bias))

@@ -14,7 +14,7 @@ synchronise or allocate, dropout/sampling counters and Adam step counts advance 
 """
 import torch
 
-from . import ops
+from . import ops, ops16
 from .loss.biased_kl import BiasedKL
 from .loss.label_smoothing import LabelSmoothing
 from .model.masking import make_masks
@@ -63,6 +63,8 @@ class BMHRLTrainer:
         self.mv_opt = ops.FusedAdam(mv_model.parameters(), lr=lr)
         self.grad_sync = grad_sync  # data-parallel hook: callable(optimizer) all-reducing optimizer.flat_grad
         self.loss_factor = 4.0 / 20.0  # captioning_bmrl_loops.py:831-833
+        # bf16 math mode: vocabulary projection + log-softmax + KL loss as the fused kernel pair (no (B*L,V) tensors)
+        self.fuse_vocab = True
         # Overlap of the gradient all-reduce (and of Adam) with backward.  Autograd runs ready nodes in reverse creation
         # order, so when a marker placed on the output of a module fires in backward, the backward kernels of everything
         # created after it have been enqueued.  Stage 0 = everything after the encoder (fusion stacks, heads), fired by
@@ -128,6 +130,18 @@ class BMHRLTrainer:
         if not hasattr(self, "_synsalt"):
             self._synsalt = ops.next_salt()
         return self._synsalt
+
+    def _forward(self, x, cap_in, masks):
+        """cap_model(x, cap_in, masks) with the worker handing back its vocabulary head un-evaluated (bf16 math mode)."""
+        w = getattr(self.cap_model, "worker", None)
+        fuse = self.fuse_vocab and ops.BF16 and w is not None
+        if fuse:
+            w.fused_vocab = True
+        try:
+            return self.cap_model(x, cap_in, masks)
+        finally:
+            if fuse:
+                w.fused_vocab = False
 
     def _mark_layer_boundary(self, i, x):
         """LayerStack hook of the encoder: output (M1, M2) of layer i -> marked copies; the marker fires in backward
@@ -209,9 +223,14 @@ class BMHRLTrainer:
         self.cap_opt.zero_grad()
         x, cap_in, y, masks = self._inputs(batch)
         n_tokens = self._global_tokens_early(y)
-        pred = self.cap_model(x, cap_in, masks)[0]
+        pred = self._forward(x, cap_in, masks)[0]
         n_tokens = n_tokens()
-        loss = self.ls.row_sums(pred, y).sum() / n_tokens
+        if isinstance(pred, ops16.VocabHead):
+            stats, _ = pred.stats(y, self.pad_idx)
+            rows = ops16.kl_rowsum_from_stats(stats, y, self.ls.smoothing, self.pad_idx, pred.shape[-1])
+        else:
+            rows = self.ls.row_sums(pred, y)
+        loss = rows.sum() / n_tokens
         loss.backward()
         ops.join_side_streams(loss.device)
         self._sync_and_step(self.cap_opt)
@@ -223,42 +242,51 @@ class BMHRLTrainer:
         reward scorer needs.  Returns the state `rl_tail` continues from."""
         x, cap_in, y, masks = self._inputs(batch)
         n_tokens = self._global_tokens_early(y)
-        pred, worker_feat, manager_feat, goal_feat, seg = self.cap_model(x, cap_in, masks)
+        pred, worker_feat, manager_feat, goal_feat, seg = self._forward(x, cap_in, masks)
         loss_mask = y != self.pad_idx
         n_tokens = n_tokens()
         if train_worker:
             ev = self.wv_model((worker_feat.detach(), goal_feat.detach())).squeeze(-1)
             mode = "noise" if exp_noise is not None else "philox"
-            tok, sp = ops.sample_tokens(pred, mode, exp_noise, salt=self._sample_salt())
         else:
             ev = self.mv_model(manager_feat.detach()).squeeze(-1)
-            tok, sp = ops.sample_tokens(pred, "argmax")
+            mode = "argmax"
+        stats = None
+        if isinstance(pred, ops16.VocabHead):  # sampling inside the fused vocabulary kernel, p(token) from the statistics
+            stats, tok = pred.stats(y, self.pad_idx, mode, exp_noise, salt=self._sample_salt())
+            sp = torch.exp(stats[:, 4] - stats[:, 0]).view(tok.shape)
+        else:
+            tok, sp = ops.sample_tokens(pred, mode, exp_noise, salt=self._sample_salt())
         return {"pred": pred, "y": y, "loss_mask": loss_mask, "n_tokens": n_tokens, "ev": ev, "seg": seg, "tok": tok,
-                "sp": sp}
+                "sp": sp, "stats": stats}
 
     def rl_tail(self, st, score, seg, train_worker, stabilize=False):
         """Second half (biased_kl() :287-334, value function :873-875) given the (B, L) scores and the segment labels
         the scorer left behind.  Returns (cap_loss, value_loss, tokens, score, divergence row sums)."""
         pred, y, loss_mask, n_tokens, ev, tok, sp = (st[k] for k in ("pred", "y", "loss_mask", "n_tokens", "ev", "tok",
                                                                       "sp"))
-        score = score.to(pred.dtype)
-        lm = loss_mask.to(pred.dtype)
+        fdt = torch.float32
+        score = score.to(fdt)
+        lm = loss_mask.to(fdt)
         expected = ev.detach()
         if train_worker:
             norm = lm.sum(-1, keepdim=True)
         else:
-            segf = seg.to(pred.dtype)
+            segf = seg.to(fdt)
             norm = segf.sum(-1, keepdim=True)
             score = score * segf
             sp, expected = ops.segment_scan(sp, expected, seg)
         if stabilize:
             score = (score - expected) * lm
         amplitude = torch.clamp(score * sp * norm, 0, 1)
-        div = self.bkl.row_sums(pred, y, tok, amplitude)
+        if st.get("stats") is not None:
+            div = ops16.kl_rowsum_from_stats(st["stats"], y, self.bkl.ls, self.pad_idx, pred.shape[-1], tok, amplitude)
+        else:
+            div = self.bkl.row_sums(pred, y, tok, amplitude)
         cap_loss = div.sum() / (n_tokens * self.loss_factor)
         # value function :873-875; the reference's host loop wrote the segment sums INTO the value output (aliasing)
         ev_used = ev if train_worker else ev + (expected - ev).detach()
-        vmask = lm if train_worker else seg.to(pred.dtype)
+        vmask = lm if train_worker else seg.to(fdt)
         value_loss = (((ev_used - score.detach()) ** 2) * vmask).mean()
         return cap_loss, value_loss, tok, score.detach(), div.detach()
 
@@ -414,7 +442,7 @@ class ScoredStepRunner:
             self.seg_out = self.st["seg"]
         torch.cuda.synchronize(dev)
         B, L = self.tok_out.shape
-        self.score_buf = torch.zeros(B, L, device=dev, dtype=self.st["pred"].dtype)
+        self.score_buf = torch.zeros(B, L, device=dev, dtype=torch.float32)
         self.seg_buf = torch.zeros_like(self.seg_out)   # filled by the host part of every replay
         self.graph_b = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph_b, pool=self.graph_a.pool()):

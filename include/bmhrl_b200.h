@@ -191,6 +191,27 @@ long long bmhrl_attn_bwd_bf16_ws_bytes(int B, int H, int Sq, int Sk);
  * a pass that is switched off is returned as ZEROS (never uninitialised memory). */
 int bmhrl_attn_bwd_bf16_tuning(int passes);
 
+/* ---- K4 fused: vocabulary projection + log-softmax + KL-loss statistics, bf16 operands (gemm_bf16.cu) ---------------- */
+/* WorkerCore (model/bm_hrl_agent.py:463-466: Linear 364 -> V, LogSoftmax) together with what LabelSmoothing
+ * (loss/label_smoothing.py:12-32), BiasedKL (loss/biased_kl.py:22-53) and the token sampling of biased_kl()
+ * (epoch_loops/captioning_bmrl_loops.py:273-285) read from its output -- WITHOUT materialising the (M, V) logits or
+ * log-probabilities: the logits tile lives in TMEM, the GEMM epilogue reduces it per row, a tiny second kernel merges
+ * the V/128 partials.  stats (M,5) fp32 = {lse, sum_v logit, logit[target], logit[pad_idx], logit[token]}; tokens (M)
+ * int64 (may be NULL) = arg-max of logit (sample_mode 0), of logit - log(exp_noise) (1: explicit Exp(1) draws (M,V),
+ * the arithmetic of Categorical.sample) or of logit - log(q), q Philox Exp(1) (2).  Both KL losses are closed forms of
+ * the five statistics (bmhrl_b200/ops16.py: kl_rowsum_from_stats).  part_ws: bmhrl_vocab_stats_ws_floats() floats. */
+long long bmhrl_vocab_stats_ws_floats(int M, int V);
+int bmhrl_vocab_stats_bf16(const void* x16, long long ldx, const void* w16, long long ldw, const float* bias, int M, int V,
+                           int K, const long long* target, int pad_idx, int sample_mode, const float* exp_noise,
+                           const unsigned long long* rng_state, unsigned int salt, float* part_ws, float* stats,
+                           long long* tokens, void* stream);
+/* Backward: recomputes the logits tile by tile and writes d logits (M, V) bf16 (row pitch lddl) from the gradients of the
+ * five statistics, dstats (M,5):  dl(n) = dstats[0] exp(logit(n) - lse) + dstats[1] + [n == target] dstats[2] +
+ * [n == pad_idx] dstats[3] + [n == token] dstats[4].  dX / dW follow as ordinary bmhrl_gemm_bf16_group problems. */
+int bmhrl_vocab_dlogits_bf16(const void* x16, long long ldx, const void* w16, long long ldw, const float* bias, int M, int V,
+                             int K, const long long* target, const long long* tokens, int pad_idx, const float* stats,
+                             const float* dstats, void* dlogits16, long long lddl, void* stream);
+
 /* ---- K1, bf16 math mode, TRAINING path: one-tile fused attention, forward and backward (attn16.cu) ------------------- */
 /* attention() model/multihead_attention.py:7-31 and its gradients for sequences that fit one tile (Sq, Sk <= 128; the
  * caption-side attentions always do, the encoder's do at the benchmark shapes), one CTA per (batch, head): S = Q K^T and
@@ -242,6 +263,15 @@ int bmhrl_kl_loss_fwd_f32(int mode, const float* pred, const long long* trg, con
 int bmhrl_kl_loss_bwd_f32(int mode, const float* pred, const long long* trg, const long long* biased_trg,
                           const float* biased_offset, const float* dout, const float* drow, float* dpred,
                           float* doffset, long long rows, int V, float smoothing, int pad_idx, void* stream);
+/* The same two losses as ROW SUMS, in closed form from the five per-row statistics of bmhrl_vocab_stats_bf16 (the target
+ * distribution is constant outside the pad, ground-truth and sampled-token columns): rowsum (rows); backward gives dstats
+ * (rows,5) and, for mode 1, doffset (rows; may be NULL). */
+int bmhrl_kl_stats_fwd_f32(int mode, const float* stats, const long long* trg, const long long* biased_trg,
+                           const float* biased_offset, float* rowsum, long long rows, int V, float smoothing, int pad_idx,
+                           void* stream);
+int bmhrl_kl_stats_bwd_f32(int mode, const float* stats, const long long* trg, const long long* biased_trg,
+                           const float* biased_offset, const float* drow, float* dstats, float* doffset, long long rows,
+                           int V, float smoothing, int pad_idx, void* stream);
 /* biased_kl() epoch_loops/captioning_bmrl_loops.py:273-285.  mode 0 argmax, 1 Categorical sample with explicit
  * Exp(1) noise (rows,V), 2 Categorical sample with in-kernel Philox noise.  probs[row] = exp(pred[row, token]). */
 int bmhrl_sample_rows_f32(int mode, const float* pred, const float* exp_noise, long long* tokens, float* probs,

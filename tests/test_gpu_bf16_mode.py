@@ -260,3 +260,124 @@ def test_warmstart_step_bf16_matches_oracle_adam(bf16, agent_sd):
                 assert float((q.detach().cpu() - params[n]).norm()) < 0.25 * float(step) + 1e-7, n
                 moved += 1
     assert moved > 50
+
+
+def test_fused_vocab_stats_and_kl_vs_oracle(bf16):
+    """K4 fused: vocabulary projection + log-softmax + KL losses without the (M,V) logits.  Statistics and tokens against
+    fp32 torch on the same bf16-rounded operands; LabelSmoothing / BiasedKL row sums and ALL gradients (features,
+    projection weight / bias, biased offset) against the oracle's element-wise divergence on log_softmax of those logits;
+    covers pad rows, sampled == target, sampled == pad and the reference's flat-row-0 quirk."""
+    from bmhrl_b200 import ops16
+    g = _g(13)
+    M, K, V = 41, 364, 10172
+    lin = nn.Linear(K, V).cuda()
+    x = torch.randn(M, K, generator=g)
+    xb = x.to(torch.bfloat16).float()
+    wb = lin.weight.detach().cpu().to(torch.bfloat16).float()
+    bias = lin.bias.detach().cpu()
+    for case in ("plain", "row0_quirk"):
+        trg = torch.randint(2, V, (M,), generator=g)
+        if case == "plain":
+            trg[5] = PAD; trg[17] = PAD; trg[0] = PAD
+        else:
+            trg[0] = PAD                      # the ONLY pad target is flat row 0: the reference zeroes nothing
+        logits = xb @ wb.t() + bias
+        # ---- statistics + arg-max / noisy arg-max tokens
+        st, tok = ops16.vocab_stats(x.cuda(), lin.weight, lin.bias, trg.cuda(), PAD, "argmax")
+        ref = torch.stack([torch.logsumexp(logits, -1), logits.sum(-1), logits.gather(1, trg[:, None])[:, 0], logits[:, PAD],
+                           logits.max(-1).values], -1)
+        assert rel(st, ref) < 1e-5
+        assert torch.equal(tok.cpu(), logits.argmax(-1))
+        q = torch.empty(M, V).exponential_(1, generator=g)
+        st2, tok2 = ops16.vocab_stats(x.cuda(), lin.weight, lin.bias, trg.cuda(), PAD, "noise", q.cuda())
+        key = logits - q.log()
+        assert float((tok2.cpu() == key.argmax(-1)).float().mean()) > 0.95
+        flipped = tok2.cpu() != key.argmax(-1)
+        if flipped.any():   # only exact near-ties may differ
+            a = key.gather(1, tok2.cpu()[:, None])[:, 0][flipped]
+            assert float((key.max(-1).values[flipped] - a).abs().max()) < 1e-3
+        # ---- losses: label smoothing and biased KL with awkward sampled tokens
+        samp = torch.randint(0, V, (M,), generator=g)
+        samp[3] = trg[3]
+        samp[4] = PAD
+        samp[0] = 7
+        off = torch.rand(M, generator=g)
+        w = torch.randn(M, generator=g)
+        for mode in ("ls", "bkl"):
+            xr = xb.clone().requires_grad_(True)
+            wr = wb.clone().requires_grad_(True)
+            br = bias.clone().requires_grad_(True)
+            offr = off.clone().requires_grad_(True)
+            lp = torch.log_softmax(xr @ wr.t() + br, -1)
+            if mode == "ls":
+                rows_r = O.label_smoothing_kl(lp[None], trg[None], SMOOTH, PAD).sum(-1)
+            else:
+                rows_r = O.biased_kl_divergence(lp[None], trg[None], samp[None], offr[None], SMOOTH, PAD).sum(-1)
+            (rows_r * w).sum().backward()
+            xd = x.cuda().requires_grad_(True)
+            offd = off.cuda().requires_grad_(True)
+            lin.zero_grad()
+            if mode == "ls":
+                std, _ = ops16.vocab_stats(xd, lin.weight, lin.bias, trg.cuda(), PAD, "argmax")
+                rows = ops16.kl_rowsum_from_stats(std, trg.cuda(), SMOOTH, PAD, V)
+            else:
+                # the token the statistics carry must be the sampled one: feed it through the noise channel
+                qq = torch.ones(M, V)
+                qq[torch.arange(M), samp] = 1e-30
+                std, tk = ops16.vocab_stats(xd, lin.weight, lin.bias, trg.cuda(), PAD, "noise", qq.cuda())
+                assert torch.equal(tk.cpu(), samp)
+                rows = ops16.kl_rowsum_from_stats(std, trg.cuda(), SMOOTH, PAD, V, samp.cuda(), offd)
+            (rows * w.cuda()).sum().backward()
+            bf16.join_side_streams("cuda")
+            errs = {"rows": rel(rows, rows_r), "dx": rel(xd.grad, xr.grad), "dW": rel(lin.weight.grad, wr.grad),
+                    "db": rel(lin.bias.grad, br.grad)}
+            if mode == "bkl":
+                errs["doffset"] = rel(offd.grad, offr.grad)
+            print("fused vocab", case, mode, {k: f"{v:.1e}" for k, v in errs.items()})
+            assert errs["rows"] < 1e-4 and max(errs.values()) < TOL, (case, mode, errs)
+
+
+@pytest.mark.parametrize("kind", ["warmstart", "worker", "manager"])
+def test_trainer_fused_vocab_equals_materialised(bf16, agent_sd, golden, kind):
+    """The trainer's fused vocabulary path (no (B*L,V) tensor) against its materialising path in the same math mode:
+    same losses, same tokens, same gradients."""
+    res = []
+    b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=2, ragged=True)
+    b = {k: v.cuda() for k, v in b.items()}
+    for fuse in (False, True):
+        bf16.manual_seed(3)
+        bf16.RNG.salt = 7000
+        model, tr = _trainer(agent_sd)
+        tr.fuse_vocab = fuse
+        if kind == "warmstart":
+            tr.cap_opt.zero_grad()
+            loss = None
+            x, cap_in, y, masks = tr._inputs(b)
+            pred = tr._forward(x, cap_in, masks)[0]
+            from bmhrl_b200 import ops16
+            if fuse:
+                assert isinstance(pred, ops16.VocabHead)
+                st, _ = pred.stats(y, PAD)
+                loss = ops16.kl_rowsum_from_stats(st, y, SMOOTH, PAD, VOC).sum() / (y != PAD).sum()
+            else:
+                loss = tr.ls.row_sums(pred, y).sum() / (y != PAD).sum()
+            loss.backward()
+            tok = None
+        else:
+            (tr.teach_worker if kind == "worker" else tr.teach_manager)()
+            model.manager.exploration = False
+            tr.cap_opt.zero_grad()
+            torch.manual_seed(5)
+            q = torch.empty(4, 7, VOC).exponential_(1).cuda() if kind == "worker" else None
+            loss, vloss, tok, _, _ = tr.rl_losses(b, kind == "worker", False, q)
+            loss.backward()
+        bf16.join_side_streams("cuda")
+        torch.cuda.synchronize()
+        res.append((float(loss), tok, {n: p.grad.detach().clone() for n, p in model.named_parameters() if p.grad is not None}))
+    assert abs(res[0][0] - res[1][0]) < 2e-3 * abs(res[0][0]), (res[0][0], res[1][0])
+    if res[0][1] is not None:
+        assert float((res[0][1] == res[1][1]).float().mean()) > 0.9
+    if res[0][1] is None or torch.equal(res[0][1], res[1][1]):
+        worst = max(rel(res[1][2][n], res[0][2][n]) for n in res[0][2] if not n.endswith("linear_K2d.bias")
+                    and not n.endswith("a_v_constant"))
+        assert worst < 1e-2, worst

@@ -40,18 +40,13 @@ def main():
     torch.cuda.synchronize()
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-        for _ in range(3):
-            runner.replay()
+        runner.replay()   # exactly ONE replay inside the profiled region: every kernel event belongs to it
         torch.cuda.synchronize()
     path = os.path.join(ROOT, "gpurun_out", "trace.json")
     prof.export_chrome_trace(path)
     ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") == "kernel"]
     ev.sort(key=lambda e: e["ts"])
-    # split into replays: find the adam kernel ends
-    ends = [i for i, e in enumerate(ev) if "adam_multi" in e["name"]]
-    lo = ends[-2] + 1 if len(ends) >= 2 else 0
-    hi = ends[-1] + 1
-    step = ev[lo:hi]
+    step = ev
     t0 = step[0]["ts"]
     t1 = max(e["ts"] + e["dur"] for e in step)
     print(f"# one graph replay, workload {workload}: {len(step)} kernels, span {t1 - t0:.1f} us")
