@@ -524,9 +524,12 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
         max_n = g.N > max_n ? g.N : max_n;
     }
     const int n_sm = device_sm_count();
-    int BN = 128, split = 1;
-    if (max_n <= 64) BN = 64;
-    else if (t128 < n_sm / 2 && t64 <= 2 * n_sm && min_kb <= 4) BN = 64;  // short K: nothing to split, use narrow tiles
+    // Tile width.  Measured inside the training step (profiles/r02_gemm_tile_experiments.txt): these GEMMs are latency
+    // chains per CTA (TMA round trip per stage), several of them run side by side on different streams, and what
+    // counts is how many CTAs -- bytes in flight -- an SM can hold: 128 x 64 tiles with a 3-deep ring (72 KB, three CTAs
+    // per SM next to a co-resident kernel) beat 128 x 128 / 4 stages (132 KB, one CTA per SM) by 12 % of the step.  Only
+    // when 128-wide tiles alone fill the machine twice over (large M x N: operand-bandwidth bound) are they worth it.
+    int BN = (t128 >= 2ll * n_sm) ? 128 : 64, split = 1;
     {
         const long long tiles = BN == 128 ? t128 : t64;
         // a cluster of `split` CTAs along K when the tiles alone leave most SMs idle and every problem has K to split
@@ -540,7 +543,7 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
     if (g_gb_force_split) split = g_gb_force_split;
     while (split > 1 && (BN / split < 32 || min_kb < split)) split >>= 1;
     static const int env_stages = getenv("BMHRL_GB_STAGES") ? atoi(getenv("BMHRL_GB_STAGES")) : 0;  // experiments
-    int nstages = g_gb_force_stages ? g_gb_force_stages : (env_stages ? env_stages : (BN == 128 ? 4 : 6));
+    int nstages = g_gb_force_stages ? g_gb_force_stages : (env_stages ? env_stages : (BN == 128 ? 4 : 3));
     {
         const int kb_per_cta = (max_kb + split - 1) / split;
         if (nstages > kb_per_cta) nstages = kb_per_cta < 2 ? 2 : kb_per_cta;

@@ -144,7 +144,11 @@ def test_rl_step_golden_reduced_precision(gpu_lib, golden, agent_sd, tag, mode):
         tr.cap_opt.zero_grad()
         (tr.wv_opt if train_worker else tr.mv_opt).zero_grad()
         st = tr.rl_forward(_dev(b), train_worker, q)
-        pred, tok = st["pred"].detach(), st["tok"]
+        pred, tok = st["pred"], st["tok"]
+        if not torch.is_tensor(pred):   # bf16 mode: the fused vocabulary head; materialise only for the margin report
+            with torch.no_grad():
+                pred = pred.log_probs()
+        pred = pred.detach()
         gold_tok = g["tokens"].cuda()
         flips = (tok != gold_tok)
         n_flip, n_pos = int(flips.sum()), tok.numel()

@@ -13,7 +13,10 @@ sd = synth.fill_state_dict(g["agent_shapes"], seed=1234)
 b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=2, ragged=True)
 ops.set_math_mode(os.environ.get("BMHRL_MATH", "bf16"))
 res = {}
-for name, use_graph, overlap in (("eager/off", False, False), ("eager/on", False, True), ("graph/off", True, False), ("graph/on", True, True)):
+CASES = (("eager/off", False, False, True), ("eager/serial", False, False, False), ("graph/on", True, True, True),
+         ("graph/on#2", True, True, True), ("graph/serial", True, False, False), ("graph/off", True, False, True))
+for name, use_graph, overlap, conc in CASES:
+    ops.CONCURRENT = conc
     ops.manual_seed(7)
     ops.RNG.salt = 5000
     model, cfg = build_agent(sd, dout_p=0.1)
