@@ -77,9 +77,15 @@ def cpu_step_fn(workload, threads):
             return not k.startswith(frozen_m)
         return True
 
+    cin0 = cin
+
     def step():
         p = {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point and trainable(k) else v)
              for k, v in state["params"].items()}
+        # feature_getter(random_synonyms=0.3): the reference corrupts the input tokens of every step (Python loop)
+        cin = O.generate_synonyms(cin0, 0.3, VOC, torch.rand(cin0.shape), torch.rand(cin0.shape),
+                                  torch.randint(2, VOC, cin0.shape))
+        masks = O.make_masks(b["rgb"], b["audio"], cin, PAD)
         pred, wf, mf, gf, seg = O.agent_forward(p, b["rgb"] + b["flow"], b["audio"], cin, masks)
         if workload == "warmstart":
             loss = O.label_smoothing_kl(pred, cy, SMOOTH, PAD).sum() / (cy != PAD).sum()
@@ -364,7 +370,8 @@ def run_gpu(args):
     wv.load_state_dict(synth.fill_state_dict(vshapes, seed=77))
     mv.load_state_dict(synth.fill_state_dict(vshapes, seed=78))
     sync = GradSync() if world > 1 else None
-    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync)
+    # random_synonyms 0.3: the reference's feature_getter corrupts the input tokens of every training step
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync, random_synonyms=0.3)
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[args.workload]()
     ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode(args.math)
@@ -409,7 +416,8 @@ def run_gpu(args):
                      else BleuScorer(NS(itos=itos), "cpu", 0.9, 0.9))
         runner = ScoredStepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
     else:
-        runner = StepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
+        runner = StepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3,
+                            pipeline_critic=not args.no_pipeline)
 
     def barrier():
         if world > 1:
@@ -431,15 +439,21 @@ def run_gpu(args):
     barrier()
     sec = e0.elapsed_time(e1) / 1e3
     # ---- end-to-end timing through the public step API with host buffers
+    def estep(r, i):
+        # the public step API: this batch from pinned host memory (+ the captions of the batch that follows, which a
+        # prefetching loader has at hand, for the pipelined frozen critic)
+        if getattr(r, "pipeline_critic", False):
+            return r.step(host[i % n_host], host[(i + 1) % n_host])
+        return r.step(host[i % n_host])
     for i in range(args.warmup):
-        float(runner.step(host[i % n_host])[0])
+        float(estep(runner, i)[0])
     barrier()
     t0 = time.perf_counter()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = 0.0
     for i in range(args.steps):
-        last = float(runner.step(host[i % n_host])[0])  # D2H read of the step's loss (synchronises)
+        last = float(estep(runner, i)[0])  # D2H read of the step's loss (synchronises)
     e3.record()
     barrier()
     sec_e2e = max(e2.elapsed_time(e3) / 1e3, 0.0)
@@ -457,7 +471,7 @@ def run_gpu(args):
         main_runner = runner
         for ph in ("worker", "manager"):
             {"worker": tr.teach_worker, "manager": tr.teach_manager}[ph]()
-            r2 = StepRunner(tr, ph, host[0], use_graph=not args.no_graph, warmup=3)
+            r2 = StepRunner(tr, ph, host[0], use_graph=not args.no_graph, warmup=3, pipeline_critic=not args.no_pipeline)
             for _ in range(args.warmup):
                 r2.replay()
             barrier()
@@ -469,11 +483,11 @@ def run_gpu(args):
             barrier()
             psec = p0.elapsed_time(p1) / 1e3
             for i in range(args.warmup):
-                float(r2.step(host[i % n_host])[0])
+                float(estep(r2, i)[0])
             barrier()
             p0.record()
             for i in range(args.steps):
-                float(r2.step(host[i % n_host])[0])
+                float(estep(r2, i)[0])
             p1.record()
             barrier()
             psec_e2e = p0.elapsed_time(p1) / 1e3
@@ -624,6 +638,8 @@ def main():
                          "tf32: fp32 storage, tcgen05 kind::tf32 GEMMs; fp32: exact SIMT contractions")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="evaluate the frozen critic inside the step instead of one step ahead on a side stream")
     ap.add_argument("--no-phases", action="store_true", help="skip the worker / manager RL-step phases (config 3)")
     ap.add_argument("--no-eager", action="store_true", help="skip the eager module-swap measurement")
     ap.add_argument("--scorer", default=None, choices=["cider", "bleu"],

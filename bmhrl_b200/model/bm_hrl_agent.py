@@ -557,9 +557,29 @@ class BMHrlAgent(nn.Module):
             return Va, Av
         return ops.grad_marker(Va, cb), ops.grad_marker(Av, cb)
 
+    # Trainer hook: segment labels of THIS batch computed ahead of time (the critic is frozen and sees only the caption
+    # tokens, so train.StepRunner evaluates it for the NEXT batch underneath the current step's backward); None = run
+    # the critic here, like the reference
+    precomputed_segment_labels = None
+
+    def segment_labels_of(self, trg):
+        """Segment labels (B,L) int32 of a token tensor: emb_C + frozen critic + threshold (:630-640), nothing else."""
+        with torch.no_grad():
+            return self.critic.scores_and_labels(self.emb_C(trg), self.critic_score_threshhold)[1]
+
     def predict_with_features(self, C, V, A, mask):
         """:637-651.  The frozen critic (depends only on the caption embedding) and the worker fusion stack
         (independent of the manager one, model/bm_hrl_agent.py:646-647) are forked onto side streams."""
+        if self.precomputed_segment_labels is not None:
+            segment_labels = self.precomputed_segment_labels
+            C = self.pos_enc_C(C)
+            Va, Av = self.bm_enc((V, A), mask)
+            Va, Av = self._mark_encoder_outputs(Va, Av)
+            worker_feat, manager_feat = ops.parallel(C.device, lambda: self.bm_worker_fus((C, (Av, Va)), mask),
+                                                     lambda: self.bm_manager_fus((C, (Av, Va)), mask))
+            goals = self.manager(manager_feat, segment_labels)
+            pred = self.worker(worker_feat, goals, mask["C_mask"])
+            return pred, worker_feat, manager_feat, goals, segment_labels
         if not (self.concurrent_branches and ops.CONCURRENT):
             _, segment_labels = self.critic.scores_and_labels(C, self.critic_score_threshhold)
             C = self.pos_enc_C(C)

@@ -156,6 +156,9 @@ class BMHRLTrainer:
         stream, behind everything enqueued so far on this stream and on the side streams."""
         if not self.overlap_grad_sync or stage in self._fired or stage >= len(self._stages):
             return
+        import os
+        if not (int(os.environ.get("BMHRL_EARLY_STAGES", "255")) >> stage) & 1:   # experiment switch
+            return
         if not any(self.cap_opt.params[i].requires_grad for i in self._stages[stage]):
             return   # nothing of this stage is trained in the current phase
         self._fired.append(stage)
@@ -220,11 +223,12 @@ class BMHRLTrainer:
     def warmstart_step(self, batch):
         """captioning_bmrl_loops.py:1148-1160.  Returns the scalar loss tensor (device)."""
         ops.new_rng_epoch(batch["caption"].device)
-        self.cap_opt.zero_grad()
+        zero_done = self._zero_grads_beside_forward([self.cap_opt])
         x, cap_in, y, masks = self._inputs(batch)
         n_tokens = self._global_tokens_early(y)
         pred = self._forward(x, cap_in, masks)[0]
         n_tokens = n_tokens()
+        zero_done()
         if isinstance(pred, ops16.VocabHead):
             stats, _ = pred.stats(y, self.pad_idx)
             rows = ops16.kl_rowsum_from_stats(stats, y, self.ls.smoothing, self.pad_idx, pred.shape[-1])
@@ -321,13 +325,31 @@ class BMHRLTrainer:
         cap_loss, value_loss, _, _, _ = self.rl_losses(batch, train_worker, stabilize, exp_noise)
         return self.rl_finish(cap_loss, value_loss, train_worker)
 
+    def _zero_grads_beside_forward(self, opts):
+        """The flat gradient buffers (188 MB for the agent) are first touched by backward: their memset runs on a side
+        stream next to the forward pass instead of in front of it.  Returns the join to call before backward."""
+        dev = opts[0].flat_grad.device
+        if not ops.CONCURRENT:
+            for o in opts:
+                o.zero_grad()
+            return lambda: None
+        cur = torch.cuda.current_stream(dev)
+        zs = ops.side_stream(dev, 13)
+        zs.wait_stream(cur)
+        with torch.cuda.stream(zs):
+            for o in opts:
+                o.zero_grad()
+        return lambda: torch.cuda.current_stream(dev).wait_stream(zs)
+
     def rl_begin(self, batch, train_worker):
         ops.new_rng_epoch(batch["caption"].device)
-        self.cap_opt.zero_grad()
-        (self.wv_opt if train_worker else self.mv_opt).zero_grad()
+        self._zero_join = self._zero_grads_beside_forward([self.cap_opt, self.wv_opt if train_worker else self.mv_opt])
 
     def rl_finish(self, cap_loss, value_loss, train_worker):
         vopt = self.wv_opt if train_worker else self.mv_opt
+        if getattr(self, "_zero_join", None) is not None:
+            self._zero_join()
+            self._zero_join = None
         cap_loss.backward()
         ops.join_side_streams(cap_loss.device)
         self._sync_and_step(self.cap_opt)
@@ -343,13 +365,28 @@ class StepRunner:
     `step(host_batch)` copies the pinned host batch into the static device buffers (H2D), replays the graph and
     returns the device loss tensors; `replay()` re-runs the step on whatever the buffers hold."""
 
-    def __init__(self, trainer, kind, example_batch, stabilize=False, use_graph=True, warmup=3):
+    def __init__(self, trainer, kind, example_batch, stabilize=False, use_graph=True, warmup=3, pipeline_critic=False):
+        """pipeline_critic: the frozen SegmentCritic depends on nothing but the caption tokens, and at B = 16 its six
+        recurrent layers are the longest dependency chain of the forward pass.  With this switch a step evaluates the
+        critic (and the `generate_synonyms` corruption it sees) for the NEXT batch on a side stream, underneath its own
+        forward / backward, and uses the labels the previous step left behind: same arithmetic, off the critical path.
+        `step(batch, next_batch)` then needs the next batch's captions (a data loader has them: it prefetches)."""
         self.trainer, self.kind, self.stabilize = trainer, kind, stabilize
         dev = next(trainer.cap_model.parameters()).device
         self.static = {k: torch.empty_like(v, device=dev).copy_(v) for k, v in example_batch.items()
                        if k in ("rgb", "flow", "audio", "caption", "score", "V", "V_mask", "A_mask")}
         self.graph = None
         self.out = None
+        self.pipeline_critic = bool(pipeline_critic) and hasattr(trainer.cap_model, "segment_labels_of")
+        if self.pipeline_critic:
+            self.static["caption_next"] = self.static["caption"].clone()
+            with torch.no_grad():
+                self.cap_in_cur = self._corrupt(self.static["caption"]).clone()
+                self.labels_cur = trainer.cap_model.segment_labels_of(self.cap_in_cur).clone()
+            self.cap_in_next = self.cap_in_cur.clone()
+            self.labels_next = self.labels_cur.clone()
+            torch.cuda.synchronize(dev)
+        self._need_prime = False
         if use_graph:
             side = ops.warmup_stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))
@@ -364,16 +401,54 @@ class StepRunner:
             with torch.cuda.graph(self.graph):
                 self.out = self._eager()
             self.captured_launches = launch_count() - n0  # kernels of libbmhrl_b200 inside one graph replay
+        self._need_prime = self.pipeline_critic
+
+    def _corrupt(self, caption):
+        """Input tokens the model (and the critic) see: caption[:, :-1] after the reference's generate_synonyms."""
+        t = self.trainer
+        cap_in = caption[:, :-1].contiguous()
+        if t.random_synonyms > 0:
+            from . import data
+            cap_in = data.generate_synonyms(cap_in, t.random_synonyms, t.cap_model.voc_size, t.end_idx, t.pad_idx,
+                                            salt=t._syn_salt())
+        return cap_in
 
     def _eager(self):
         t = self.trainer
-        if self.kind == "warmstart":
-            return (t.warmstart_step(self.static),)
-        return t.rl_step(self.static, self.kind == "worker", self.stabilize)
+        if not self.pipeline_critic:
+            if self.kind == "warmstart":
+                return (t.warmstart_step(self.static),)
+            return t.rl_step(self.static, self.kind == "worker", self.stabilize)
+        dev = self.static["caption"].device
+        cur = torch.cuda.current_stream(dev)
+        side = ops.side_stream(dev, 12)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side), torch.no_grad():   # the NEXT batch's corruption + critic, beside this step
+            nxt = self._corrupt(self.static["caption_next"])
+            self.cap_in_next.copy_(nxt)
+            self.labels_next.copy_(t.cap_model.segment_labels_of(self.cap_in_next))
+        batch = {k: v for k, v in self.static.items() if k != "caption_next"}
+        batch["caption_in"] = self.cap_in_cur
+        t.cap_model.precomputed_segment_labels = self.labels_cur
+        try:
+            if self.kind == "warmstart":
+                out = (t.warmstart_step(batch),)
+            else:
+                out = t.rl_step(batch, self.kind == "worker", self.stabilize)
+        finally:
+            t.cap_model.precomputed_segment_labels = None
+        cur.wait_stream(side)
+        self.cap_in_cur.copy_(self.cap_in_next)
+        self.labels_cur.copy_(self.labels_next)
+        return out
 
-    def load(self, host_batch, non_blocking=True):
+    def load(self, host_batch, non_blocking=True, next_host_batch=None):
         for k, buf in self.static.items():
-            buf.copy_(host_batch[k], non_blocking=non_blocking)
+            if k == "caption_next":
+                src = (next_host_batch if next_host_batch is not None else host_batch)["caption"]
+                buf.copy_(src, non_blocking=non_blocking)
+            else:
+                buf.copy_(host_batch[k], non_blocking=non_blocking)
 
     def replay(self):
         if self.graph is not None:
@@ -382,9 +457,21 @@ class StepRunner:
             self.out = self._eager()
         return self.out
 
-    def step(self, host_batch):
-        self.load(host_batch)
+    def step(self, host_batch, next_host_batch=None):
+        """One step on `host_batch`.  With pipeline_critic the captions of the batch that FOLLOWS must come along
+        (`next_host_batch`; None = the same batch again): this step labels them for the next one."""
+        self.load(host_batch, next_host_batch=next_host_batch)
+        if self.pipeline_critic and self._need_prime:
+            self.prime()
         return self.replay()
+
+    def prime(self):
+        """(Re)labels the batch that sits in the static buffers: needed once, before the first step of a stream of
+        batches (afterwards every step labels its successor)."""
+        with torch.no_grad():
+            self.cap_in_cur.copy_(self._corrupt(self.static["caption"]))
+            self.labels_cur.copy_(self.trainer.cap_model.segment_labels_of(self.cap_in_cur))
+        self._need_prime = False
 
     def step_ragged(self, ragged, score=None):
         """One step fed by the input pipeline: `ragged` is a data.RaggedBatch whose stage() has been called -- ONE

@@ -550,3 +550,32 @@ def test_scored_step_two_graphs_equals_eager(gpu_lib, golden, agent_sd, kind):
     for a, c in zip(l_graph, l_eager):
         assert abs(a[0] - c[0]) <= 1e-4 * abs(c[0]) + 1e-7 and abs(a[1] - c[1]) <= 1e-4 * abs(c[1]) + 1e-7, (l_graph, l_eager)
     assert rel(p_graph, p_eager) < 1e-5
+
+
+@pytest.mark.parametrize("kind", ["warmstart", "worker"])
+def test_pipelined_critic_equals_inline(gpu_lib, agent_sd, kind):
+    """StepRunner(pipeline_critic=True) evaluates the frozen critic for the NEXT batch beside the current step and uses
+    the labels the previous step left behind: over a stream of DIFFERENT batches it must train exactly like the inline
+    critic (same losses, same parameters), captured as a graph."""
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, StepRunner
+    batches = [synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=40 + i, ragged=True) for i in range(4)]
+    res = []
+    for pipe in (False, True):
+        model, cfg = build_agent(agent_sd)
+        tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD)
+        (tr.teach_warmstart if kind == "warmstart" else tr.teach_worker)()
+        model.manager.exploration = False
+        from bmhrl_b200 import ops
+        ops.manual_seed(3)
+        ops.RNG.salt = 9000
+        run = StepRunner(tr, kind, batches[0], use_graph=True, warmup=2, pipeline_critic=pipe)
+        losses = []
+        for i, b in enumerate(batches):
+            nxt = batches[i + 1] if i + 1 < len(batches) else None
+            losses.append(float(run.step(b, nxt)[0]) if pipe else float(run.step(b)[0]))
+        torch.cuda.synchronize()
+        res.append((losses, model.worker.core.projection.weight.detach().clone()))
+    for a, c in zip(*[r[0] for r in res]):
+        assert abs(a - c) <= 1e-6 * abs(c), res
+    assert rel(res[1][1], res[0][1]) < 1e-6

@@ -13,9 +13,11 @@ sd = synth.fill_state_dict(g["agent_shapes"], seed=1234)
 b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=2, ragged=True)
 ops.set_math_mode(os.environ.get("BMHRL_MATH", "bf16"))
 res = {}
-CASES = (("eager/off", False, False, True), ("eager/serial", False, False, False), ("graph/on", True, True, True),
-         ("graph/on#2", True, True, True), ("graph/serial", True, False, False), ("graph/off", True, False, True))
-for name, use_graph, overlap, conc in CASES:
+CASES = (("eager/off", False, False, True, 255), ("graph/off", True, False, True, 255), ("graph/on", True, True, True, 255),
+         ("graph/on#2", True, True, True, 255), ("graph/stage0", True, True, True, 1), ("graph/stage0#2", True, True, True, 1),
+         ("graph/stage1", True, True, True, 2), ("graph/stage1#2", True, True, True, 2))
+for name, use_graph, overlap, conc, stages in CASES:
+    os.environ["BMHRL_EARLY_STAGES"] = str(stages)
     ops.CONCURRENT = conc
     ops.manual_seed(7)
     ops.RNG.salt = 5000

@@ -1,0 +1,6 @@
+O=gpurun_out/r2exp6; mkdir -p $O
+(make -C bmhrl_b200/csrc -j16 > $O/make.log 2>&1 || (tail -20 $O/make.log; exit 1)) && echo "build ok"
+timeout 300 python tools/diag_overlap.py > $O/diag_overlap.txt 2>&1; echo "diag exit $?"; grep -v "^     " $O/diag_overlap.txt | tail -12
+timeout 900 python -m pytest tests -m gpu -q > $O/pytest.log 2>&1; echo "pytest exit $?"; tail -8 $O/pytest.log | cut -c1-250; grep -n "fused vocab\|bf16 errors" $O/pytest.log | cut -c1-400
+B="python bench.py --steps 20 --warmup 5 --no-cpu --no-phases --no-eager"
+for cfg in "" "--no-pipeline"; do echo "== bench $cfg"; timeout 300 $B $cfg 2> $O/err.log | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['ms_per_step'], d['launches_per_step'], d['e2e']['ms_per_step'])"; tail -3 $O/err.log; done
