@@ -34,6 +34,7 @@ constexpr int A16_SLACK = 16 * 1024;  // an M = 128 A operand reads 128 rows of 
 
 struct A16Params {
     int B, H, Sq, Sk, dk, Sqp, Skp, nck, dvt;
+    int t_p, t_a, t_cols, two_acc;             // backward TMEM map: dP region, accumulator region, columns allocated
     float scale;
     const unsigned char* mask; int mask_kind, causal;
     float* lse2;                               // (B,H,Sq,2): row maximum m (log2 domain) and 1 / normaliser of the masked
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
     const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
     const int dv0 = blockIdx.y * p.dvt;
     const int col0 = h * p.dk;
-    const bool two_acc = p.dvt <= 128;  // dK and dV accumulators side by side
+    const bool two_acc = p.two_acc != 0;  // dK and dV accumulators side by side
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
@@ -279,13 +280,13 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
         mbar_init(dv_full, 1);
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    if (warp == 1) tmem_alloc(tmem_slot, p.t_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
-    const uint32_t tS = tmem_base, tP = tmem_base + 128, tA = tmem_base + 256;
+    const uint32_t tS = tmem_base, tP = tmem_base + p.t_p, tA = tmem_base + p.t_a;
 
     if (warp == 0) {
         if (elect_one()) {
@@ -340,7 +341,7 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
                 mbar_wait(dk_free, 0);                // dK drained from the shared accumulator columns
                 tc_fence_after();
             }
-            row_mma(two_acc ? tA + 128 : tA, tS, sG, qch, p.Sqp >> 4);   // dV = P^T dO
+            row_mma(two_acc ? tA + p.dvt : tA, tS, sG, qch, p.Sqp >> 4);   // dV = P^T dO
             tc_commit(dv_full);
         }
     } else {
@@ -490,14 +491,14 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
             mbar_arrive(dk_free);
             mbar_wait(dv_full, 0);
             tc_fence_after();
-            drain(two_acc ? tA + 128 : tA, p.dV, p.lddv, 1.f);
+            drain(two_acc ? tA + p.dvt : tA, p.dV, p.lddv, 1.f);
             tc_fence_before();
         }
     }
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        tmem_dealloc(tmem_base, p.t_cols);
     }
 }
 
@@ -513,11 +514,27 @@ static int a16_geometry(A16Params& p, int B, int H, int Sq, int Sk, int dk, cons
         bmhrl_set_error("attn16: d_k must be 64, 128, 256 or 512");
         return BMHRL_ERR_UNSUPPORTED;
     }
-    (void)who;
     p.B = B; p.H = H; p.Sq = Sq; p.Sk = Sk; p.dk = dk;
     p.Sqp = (Sq + 15) & ~15; p.Skp = (Sk + 15) & ~15;
     p.nck = dk >> 6;
-    p.dvt = dk > 256 ? 256 : dk;
+    // Tensor memory is the resource these kernels share with the GEMM CTAs that run beside them (512 columns per SM, an
+    // allocation blocks until it fits): slices of the head dimension are chosen so that a CTA needs 256 columns, never
+    // the whole SM -- more, smaller CTAs that co-reside with GEMM tiles instead of serialising against them.
+    const bool bwd = who[0] == 'b';
+    if (!bwd) {
+        p.dvt = dk > 128 ? 128 : dk;                       // S (128) + O slice (128)
+        p.t_cols = 128 + p.dvt <= 256 ? 256 : 512;
+    } else {
+        const int cs = ((p.Sqp > p.Skp ? p.Sqp : p.Skp) + 31) & ~31;   // S / S^T and dP / dP^T regions
+        p.t_p = cs;
+        p.t_a = 2 * cs;
+        p.two_acc = 0;
+        if (cs <= 64) p.dvt = dk > 128 ? 128 : dk;         // 2 x 64 + 128 = 256
+        else if (cs <= 96) p.dvt = 64;                     // 2 x 96 + 64 = 256
+        else p.dvt = dk > 256 ? 256 : dk;                  // 2 x 128 + 256 = 512: the whole SM
+        const int need = 2 * cs + p.dvt;
+        p.t_cols = need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
+    }
     p.scale = 1.0f / sqrtf((float)dk);
     return BMHRL_OK;
 }
@@ -527,7 +544,7 @@ static int a16_geometry(A16Params& p, int B, int H, int Sq, int Sk, int dk, cons
 using namespace bmhrl;
 
 extern "C" long long bmhrl_attn16_smem_bytes(int backward, int Sq, int Sk, int dk) {
-    const long long Sqp = (Sq + 15) & ~15, Skp = (Sk + 15) & ~15, nck = dk >> 6, dvt = dk > 256 ? 256 : dk;
+    const long long Sqp = (Sq + 15) & ~15, Skp = (Sk + 15) & ~15, nck = dk >> 6, dvt = dk > 128 ? 128 : dk;
     if (backward) return 2 * nck * (Sqp + Skp) * 128 + A16_SLACK + 2048 + 128 + 1024;
     return nck * (Sqp + Skp) * 128 + (dvt >> 6) * Skp * 128 + A16_SLACK + 128 + 1024;
 }
@@ -568,9 +585,7 @@ extern "C" int bmhrl_attn16_fwd(const void* Q, long long ldq, const void* K, lon
         }
         mark_done(attr);
     }
-    const int need = 128 + p.dvt;
-    const int tmem_cols = need <= 256 ? 256 : 512;
-    attn16_fwd_kernel<<<dim3(B * H, dk / p.dvt), 192, (size_t)smem, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p, tmem_cols);
+    attn16_fwd_kernel<<<dim3(B * H, dk / p.dvt), 192, (size_t)smem, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p, p.t_cols);
     BMHRL_POST_LAUNCH("attn16_fwd");
     return BMHRL_OK;
 }

@@ -207,45 +207,72 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
         // ---- vocabulary statistics of row m over this CTA's BN columns (no output tile is written):
         //   max, sum exp(v - max), sum v, v[target], v[pad], and the sampling arg-max (key, index, logit)
         const int trg = m < p.M ? (int)p.v_trg[m] : -1;
-        float mx = -INFINITY, sv = 0.f, lt = 0.f, lp = 0.f, bk = -INFINITY, bl = 0.f;
+        float mx = -INFINITY, se = 0.f, sv = 0.f, lt = 0.f, lp = 0.f, bk = -INFINITY, bl = 0.f;
         int bi = 0x7fffffff;
+        const bool row_ok = m < p.M;
+        const bool bias_vec = p.bias && aligned16(p.bias);
 #pragma unroll 1
-        for (int cc = 0; cc < BN; cc += 32) {
+        for (int cc = 0; cc < BN; cc += 32) {   // ONE pass: online max / sum-exp per 32-column chunk
             uint32_t r[32];
             tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
             tmem_ld_wait();
             const int nb = n0 + cc;
+            if (nb >= p.N) break;
+            float v[32];
+            const bool full = nb + 31 < p.N;
+            if (full && bias_vec) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int n = nb + j;
-                if (n < p.N && m < p.M) {
-                    const float v = __uint_as_float(r[j]) + (p.bias ? p.bias[n] : 0.f);
-                    mx = fmaxf(mx, v);
-                    sv += v;
-                    if (n == trg) lt = v;
-                    if (n == p.v_pad) lp = v;
-                    float key = v;
-                    if (p.v_smode == 1) {
-                        key = v - logf(p.v_q[(long long)m * p.N + n]);
-                    } else if (p.v_smode == 2) {
-                        const float u = u32_to_unit(philox_u32(p.rng, p.salt, (unsigned long long)m * p.N + n));
-                        key = v - logf(-logf(1.f - u));
-                    }
-                    if (key > bk) { bk = key; bi = n; bl = v; }   // ascending n: the first maximum wins
+                for (int j4 = 0; j4 < 32; j4 += 4) {
+                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + j4));
+                    v[j4] = __uint_as_float(r[j4]) + b4.x; v[j4 + 1] = __uint_as_float(r[j4 + 1]) + b4.y;
+                    v[j4 + 2] = __uint_as_float(r[j4 + 2]) + b4.z; v[j4 + 3] = __uint_as_float(r[j4 + 3]) + b4.w;
                 }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    v[j] = nb + j < p.N ? __uint_as_float(r[j]) + (p.bias ? p.bias[nb + j] : 0.f) : -INFINITY;
             }
-        }
-        float se = 0.f;
-#pragma unroll 1
-        for (int cc = 0; cc < BN; cc += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
-            tmem_ld_wait();
-            const int nb = n0 + cc;
+            float cm = v[0];
+#pragma unroll
+            for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
+            const float nm = fmaxf(mx, cm);
+            float cs = 0.f, csum = 0.f;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-                const int n = nb + j;
-                if (n < p.N && m < p.M) se += __expf(__uint_as_float(r[j]) + (p.bias ? p.bias[n] : 0.f) - mx);
+                const bool in = full || nb + j < p.N;
+                cs += in ? __expf(v[j] - nm) : 0.f;
+                csum += in ? v[j] : 0.f;
+            }
+            se = se * __expf(mx - nm) + cs;
+            mx = nm;
+            sv += csum;
+            if (trg >= nb && trg < nb + 32) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) lt = (nb + j == trg) ? v[j] : lt;
+            }
+            if (p.v_pad >= nb && p.v_pad < nb + 32) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) lp = (nb + j == p.v_pad) ? v[j] : lp;
+            }
+            if (p.v_smode == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (v[j] > bk) { bk = v[j]; bi = nb + j; bl = v[j]; }   // ascending n: the first maximum wins
+            } else if (row_ok) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int n = nb + j;
+                    if (n < p.N) {
+                        float key;
+                        if (p.v_smode == 1) {
+                            key = v[j] - __logf(p.v_q[(long long)m * p.N + n]);
+                        } else {
+                            const float u = u32_to_unit(philox_u32(p.rng, p.salt, (unsigned long long)m * p.N + n));
+                            key = v[j] - __logf(-__logf(1.f - u));
+                        }
+                        if (key > bk) { bk = key; bi = n; bl = v[j]; }
+                    }
+                }
             }
         }
         if (m < p.M) {

@@ -213,7 +213,11 @@ class _GradMarker(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, callback):
         ctx.callback = callback
-        return x.view_as(x)
+        y = x.view_as(x)
+        tw = getattr(x, "_bmhrl16", None)   # bf16 twin emitted by the producing kernel (ops16): same data, keep it
+        if tw is not None:
+            y._bmhrl16 = tw
+        return y
 
     @staticmethod
     def backward(ctx, g):

@@ -161,17 +161,24 @@ def twin16(t):
     consumes emit the twin in their epilogue and attach it (`attach_twin`); otherwise it is cast here, once."""
     tw = getattr(t, "_bmhrl16", None)
     if tw is not None and tw[1] == t._version:
+        if tw[2] is not None:
+            # cast lazily by ANOTHER consumer, possibly on another stream (the worker / manager fusion stacks share the
+            # encoder memory): order this stream behind that cast
+            torch.cuda.current_stream(t.device).wait_event(tw[2])
         return tw[0]
     x = t.detach()
     if not x.is_contiguous():
         x = x.contiguous()
     y = cast16(x.reshape(-1, x.shape[-1]))
-    t._bmhrl16 = (y, t._version)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(t.device))
+    t._bmhrl16 = (y, t._version, ev)
     return y
 
 
 def attach_twin(t, y16):
-    t._bmhrl16 = (y16, t._version)
+    """y16 was written by the SAME kernel as t: whoever is ordered behind t is ordered behind y16 (no event needed)."""
+    t._bmhrl16 = (y16, t._version, None)
 
 
 class _Shadows:

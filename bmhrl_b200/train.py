@@ -524,6 +524,9 @@ class ScoredStepRunner:
         with torch.cuda.graph(self.graph_a):
             trainer.rl_begin(self.static, self.train_worker)
             self.st = trainer.rl_forward(self.static, self.train_worker)
+            if getattr(trainer, "_zero_join", None) is not None:   # the gradient memset belongs to THIS graph
+                trainer._zero_join()
+                trainer._zero_join = None
             ops.join_side_streams(dev)
             self.tok_out = self.st["tok"]
             self.seg_out = self.st["seg"]
