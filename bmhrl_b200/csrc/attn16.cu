@@ -529,9 +529,9 @@ static int a16_geometry(A16Params& p, int B, int H, int Sq, int Sk, int dk, cons
         p.t_p = cs;
         p.t_a = 2 * cs;
         p.two_acc = 0;
-        if (cs <= 64) p.dvt = dk > 128 ? 128 : dk;         // 2 x 64 + 128 = 256
-        else if (cs <= 96) p.dvt = 64;                     // 2 x 96 + 64 = 256
-        else p.dvt = dk > 256 ? 256 : dk;                  // 2 x 128 + 256 = 512: the whole SM
+        // cs <= 64: 2 x 64 + 128 = 256 columns.  Longer sequences need all 512 (2 x 128 + 128); 64-wide slices would fit
+        // 256 but make four CTAs per (b, h) recompute S and dP -- measured slower (27 vs 21 us at Sq = Sk = 80)
+        p.dvt = dk > 128 ? 128 : dk;
         const int need = 2 * cs + p.dvt;
         p.t_cols = need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
     }

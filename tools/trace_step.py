@@ -30,11 +30,11 @@ def main():
     tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7)
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[workload]()
     ops.manual_seed(1234, dev)
-    ops.set_math_mode(os.environ.get("BMHRL_MATH", "tf32"))
+    ops.set_math_mode(os.environ.get("BMHRL_MATH", "bf16"))
     if os.environ.get("BMHRL_CONCURRENT") is not None:
         ops.CONCURRENT = bool(int(os.environ["BMHRL_CONCURRENT"]))
     b = synth.synthetic_batch(V=bench.VOC, seed=1234, **bench.SHAPE)
-    runner = StepRunner(tr, workload, b, use_graph=True, warmup=3)
+    runner = StepRunner(tr, workload, b, use_graph=True, warmup=3, pipeline_critic=os.environ.get("BMHRL_PIPELINE", "1") != "0")
     for _ in range(5):
         runner.replay()
     torch.cuda.synchronize()
