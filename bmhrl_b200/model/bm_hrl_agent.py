@@ -288,6 +288,11 @@ class BMEncoderLayer(nn.Module):
         for r in (self.res_layers_M1[0], self.res_layers_M2[0], self.res_layers_M1[2], self.res_layers_M2[2]):
             r.emit_twin = True
 
+    # optional callable((M1, M2)) -> (M1, M2) applied between the self-attention blocks and the bimodal blocks: both
+    # tensors feed BOTH bimodal blocks, so when either one's gradient is complete the bimodal and FFN blocks of this
+    # layer have finished their backward (their gradients can be reduced / stepped while the self-attention runs)
+    mid_hook = None
+
     def forward(self, x, masks):
         '''x (M1, M2): (B, Sm, Dm); masks (M1, M2): (B, 1, Sm) -> M1m2 (B, Sm1, Dm1), M2m1 (B, Sm2, Dm2)'''
         M1, M2 = x
@@ -299,6 +304,8 @@ class BMEncoderLayer(nn.Module):
         M1, M2 = ops.parallel(
             dev, lambda: self.res_layers_M1[0](M1, AttentionSublayer(self.self_att_M1, None, None, M1_mask)),
             lambda: self.res_layers_M2[0](M2, AttentionSublayer(self.self_att_M2, None, None, M2_mask)))
+        if self.mid_hook is not None:   # data-parallel trainer: marks the end (in backward) of the bimodal + FFN blocks
+            M1, M2 = self.mid_hook((M1, M2))
         # 2. bimodal attention (queries are normed, keys / values are the un-normed other modality), then
         # 3. position-wise feed forward of the same modality
         M1m2, M2m1 = ops.parallel(

@@ -74,10 +74,20 @@ class BMHRLTrainer:
         ids = {id(p): n for n, p in cap_model.named_parameters()}
         pnames = [ids[id(p)] for p in self.cap_opt.params]
         n_enc = len(cap_model.bm_enc.encoder.layers) if hasattr(cap_model, "bm_enc") else 0
+        # stage 0: everything behind the encoder.  Then, per encoder layer from the last to the first, TWO stages: the
+        # bimodal-attention + FFN blocks (complete when the marker between them and the self-attention blocks fires) and
+        # the self-attention blocks (complete at the layer boundary).  What is left for the tail after the final join is
+        # the self-attention of encoder layer 0 only (4.7 M of the 47 M parameters).
         self._stages = [frozenset(i for i, n in enumerate(pnames) if not n.startswith("bm_enc."))]
-        for k in range(1, n_enc):
-            pre = f"bm_enc.encoder.layers.{n_enc - k}."
-            self._stages.append(frozenset(i for i, n in enumerate(pnames) if n.startswith(pre)))
+        self._stage_of_mid, self._stage_of_boundary = {}, {}
+        is_self = lambda n: (".self_att_" in n) or (".res_layers_M1.0." in n) or (".res_layers_M2.0." in n)
+        for k in range(n_enc - 1, -1, -1):
+            pre = f"bm_enc.encoder.layers.{k}."
+            self._stage_of_mid[k] = len(self._stages)
+            self._stages.append(frozenset(i for i, n in enumerate(pnames) if n.startswith(pre) and not is_self(n)))
+            if k > 0:
+                self._stage_of_boundary[k] = len(self._stages)
+                self._stages.append(frozenset(i for i, n in enumerate(pnames) if n.startswith(pre) and is_self(n)))
         self._fired = []          # stages already handed to the communication stream in this backward
         self._comm_stream = None
         self.overlap_grad_sync = True
@@ -86,6 +96,8 @@ class BMHRLTrainer:
         if n_enc > 0:
             cap_model.grad_ready_callback = lambda: self._early_sync(0)
             cap_model.bm_enc.encoder.layer_boundary_hook = self._mark_layer_boundary
+            for k, layer in enumerate(cap_model.bm_enc.encoder.layers):
+                layer.mid_hook = (lambda x, k=k: self._mark_mid(k, x))
 
     # ---- phase switching (captioning_bmrl_loops.py:809-820, :1144) ------------------------------------------------
     def teach_warmstart(self):
@@ -145,9 +157,14 @@ class BMHRLTrainer:
 
     def _mark_layer_boundary(self, i, x):
         """LayerStack hook of the encoder: output (M1, M2) of layer i -> marked copies; the marker fires in backward
-        when layer i+1 is done, i.e. stage n_enc - (i+1)."""
-        n_enc = len(self.cap_model.bm_enc.encoder.layers)
-        stage = n_enc - (i + 1)
+        when layer i+1 (its self-attention blocks last) is done."""
+        stage = self._stage_of_boundary[i + 1]
+        cb = lambda: self._early_sync(stage)
+        return tuple(ops.grad_marker(t, cb) for t in x)
+
+    def _mark_mid(self, k, x):
+        """BMEncoderLayer.mid_hook of layer k: fires in backward when the bimodal + FFN blocks of layer k are done."""
+        stage = self._stage_of_mid[k]
         cb = lambda: self._early_sync(stage)
         return tuple(ops.grad_marker(t, cb) for t in x)
 

@@ -418,10 +418,14 @@ def test_overlapped_grad_sync_reduces_every_gradient_once(gpu_lib, agent_sd, kin
         assert torch.equal(cnt[~pad], act[~pad]), "a gradient element was reduced twice or not at all"
         assert not pad.any() or float(cnt[pad].max()) <= 1
         cap_calls = [l for l in sync.log if l[0] is not None]
-        if overlap:  # post-encoder stage, encoder layer 1 (both on the communication stream), then the rest
-            assert len(cap_calls) == 3 and cap_calls[0][1] == cap_calls[1][1] != cap_calls[2][1]
-            assert cap_calls[0][0] == len(tr._stages[0]) and cap_calls[1][0] == len(tr._stages[1])
-            assert cap_calls[2][0] == len(tr.cap_opt.params) - len(tr._stages[0]) - len(tr._stages[1])
+        if overlap:  # post-encoder stage, then per encoder layer its bimodal + FFN blocks and its self-attention blocks
+            # (all on the communication stream), then the rest (self-attention of layer 0) after the join
+            ns = len(tr._stages)
+            assert ns == 4 and len(cap_calls) == ns + 1
+            assert all(c[1] == cap_calls[0][1] for c in cap_calls[:ns]) and cap_calls[ns][1] != cap_calls[0][1]
+            for k in range(ns):
+                assert cap_calls[k][0] == len(tr._stages[k])
+            assert cap_calls[ns][0] == len(tr.cap_opt.params) - sum(len(st) for st in tr._stages)
         else:
             assert not cap_calls
         for _ in range(2):
