@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "../../include/bmhrl_b200.h"
 #include <atomic>
+#include <stdlib.h>
 #include <string.h>
 
 static thread_local char g_err[512] = "";
@@ -16,6 +17,25 @@ extern "C" const char* bmhrl_last_error(void) { return g_err; }
 extern "C" long long bmhrl_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 extern "C" void bmhrl_reset_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
 extern "C" int bmhrl_abi_version(void) { return BMHRL_ABI_VERSION; }
+
+// Programmatic dependent launch of the chain kernels (common.cuh): -1 = not decided yet (BMHRL_PDL, default on)
+static std::atomic<int> g_pdl{-1};
+namespace bmhrl {
+int pdl_enabled() {
+    int v = g_pdl.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char* e = getenv("BMHRL_PDL");
+        v = e ? (atoi(e) != 0) : 1;
+        g_pdl.store(v, std::memory_order_relaxed);
+    }
+    return v;
+}
+}  // namespace bmhrl
+extern "C" int bmhrl_set_pdl(int on) {
+    g_pdl.store(on ? 1 : 0, std::memory_order_relaxed);
+    return BMHRL_OK;
+}
+extern "C" int bmhrl_get_pdl(void) { return bmhrl::pdl_enabled(); }
 
 // A new non-blocking stream on the current device with a handle no other stream shares (see the header).  Never
 // destroyed: the host layer keeps its side streams for the life of the process.

@@ -111,6 +111,8 @@ __global__ void __launch_bounds__(192, 1) attn16_fwd_kernel(const __grid_constan
 
     if (warp == 0) {
         if (elect_one()) {
+            griddep_wait();                 // Q / K / V are the previous kernel's output
+            griddep_launch_dependents();
             mbar_arrive_expect_tx(qk_full, p.nck * (qch + kch));
             for (int c = 0; c < p.nck; ++c) {
                 tma_load_4d(sQ + c * qch, &tmQ, qk_full, col0 + c * 64, 0, 0, b);
@@ -141,6 +143,7 @@ __global__ void __launch_bounds__(192, 1) attn16_fwd_kernel(const __grid_constan
             tc_commit(o_full);
         }
     } else {
+        griddep_wait();                     // the mask may be a tensor an earlier kernel of the stream wrote
         const int qt = warp & 3;
         const int q = qt * 32 + lane;
         const bool row_ok = q < p.Sq;
@@ -290,6 +293,8 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
 
     if (warp == 0) {
         if (elect_one()) {
+            griddep_wait();                 // dO is the previous kernel's output
+            griddep_launch_dependents();
             mbar_arrive_expect_tx(ld_full, 2 * p.nck * (qch + kch));
             for (int c = 0; c < p.nck; ++c) {
                 tma_load_4d(sQ + c * qch, &tmQ, ld_full, col0 + c * 64, 0, 0, b);
@@ -345,6 +350,7 @@ __global__ void __launch_bounds__(192, 1) attn16_bwd_kernel(const __grid_constan
             tc_commit(dv_full);
         }
     } else {
+        griddep_wait();
         const int qt = warp & 3;
         const int r = qt * 32 + lane;             // phase A: query row; phase B: key row
         const uint32_t lane_off = (uint32_t)(qt * 32) << 16;
@@ -585,8 +591,8 @@ extern "C" int bmhrl_attn16_fwd(const void* Q, long long ldq, const void* K, lon
         }
         mark_done(attr);
     }
-    attn16_fwd_kernel<<<dim3(B * H, dk / p.dvt), 192, (size_t)smem, (cudaStream_t)stream>>>(tmQ, tmK, tmV, p, p.t_cols);
-    BMHRL_POST_LAUNCH("attn16_fwd");
+    BMHRL_LAUNCH_PDL("attn16_fwd", attn16_fwd_kernel, dim3(B * H, dk / p.dvt), dim3(192), (size_t)smem, (cudaStream_t)stream,
+                     tmQ, tmK, tmV, p, p.t_cols);
     return BMHRL_OK;
 }
 
@@ -629,7 +635,7 @@ extern "C" int bmhrl_attn16_bwd(const void* Q, long long ldq, const void* K, lon
         }
         mark_done(attr);
     }
-    attn16_bwd_kernel<<<dim3(B * H, dk / p.dvt), 192, (size_t)smem, (cudaStream_t)stream>>>(tmQ, tmK, tmV, tmG, p);
-    BMHRL_POST_LAUNCH("attn16_bwd");
+    BMHRL_LAUNCH_PDL("attn16_bwd", attn16_bwd_kernel, dim3(B * H, dk / p.dvt), dim3(192), (size_t)smem, (cudaStream_t)stream,
+                     tmQ, tmK, tmV, tmG, p);
     return BMHRL_OK;
 }

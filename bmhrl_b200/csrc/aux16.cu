@@ -25,6 +25,8 @@ __global__ void __launch_bounds__(LN16_WARPS * 32) layernorm_fwd16_kernel(
     const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
     __nv_bfloat16* __restrict__ y, long long ldy, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
     int D, float eps, int vec) {
+    griddep_wait();
+    griddep_launch_dependents();
     const int row = blockIdx.x * LN16_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= rows) return;
@@ -79,6 +81,8 @@ __global__ void __launch_bounds__(LN16_WARPS * 32) layernorm_fwd16_kernel(
 __global__ void cast16_kernel(const float* __restrict__ x, long long ldx, __nv_bfloat16* __restrict__ y, long long ldy,
                               int rows, int cols, float drop_p, const unsigned long long* __restrict__ rng,
                               unsigned int salt) {
+    griddep_wait();
+    griddep_launch_dependents();
     const int c4 = cols >> 2;
     const long long n4 = (long long)rows * c4;
     const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
@@ -139,6 +143,8 @@ __global__ void __launch_bounds__(256) cast16_colsum_kernel(const float* __restr
 __global__ void __launch_bounds__(256) colsum16_kernel(const __nv_bfloat16* __restrict__ z, long long ldz, int rows, int cols,
                                                        float* __restrict__ o0, float* __restrict__ o1,
                                                        float* __restrict__ o2, int seg_cols, int accumulate) {
+    griddep_wait();
+    griddep_launch_dependents();
     __shared__ float red[16][64 + 1];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const int n = blockIdx.x * 64 + tx * 4;
@@ -204,9 +210,9 @@ extern "C" int bmhrl_layernorm_fwd_bf16(const float* x, const float* gamma, cons
     if (rows == 0) return BMHRL_OK;
     const int vec = (D % 4 == 0) && D <= 1024 && aligned16(x) && aligned16(gamma) && aligned16(beta) &&
                     (((uintptr_t)y) & 7u) == 0 && (ldy & 3) == 0;
-    layernorm_fwd16_kernel<<<(rows + LN16_WARPS - 1) / LN16_WARPS, LN16_WARPS * 32, 0, (cudaStream_t)stream>>>(
-        x, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, rows, D, eps, vec);
-    BMHRL_POST_LAUNCH("layernorm_fwd16");
+    BMHRL_LAUNCH_PDL("layernorm_fwd16", layernorm_fwd16_kernel, dim3((rows + LN16_WARPS - 1) / LN16_WARPS),
+                     dim3(LN16_WARPS * 32), 0, (cudaStream_t)stream, x, gamma, beta, (__nv_bfloat16*)y, ldy, mean, rstd, rows, D,
+                     eps, vec);
     return BMHRL_OK;
 }
 
@@ -229,9 +235,8 @@ extern "C" int bmhrl_cast_bf16(const float* x, long long ldx, void* y, long long
                                                               salt, db, accumulate_db);
         BMHRL_POST_LAUNCH("cast16_colsum");
     } else {
-        cast16_kernel<<<grid1d((long long)rows * (cols / 4), 256, 148 * 4), 256, 0, st>>>(x, ldx, (__nv_bfloat16*)y, ldy, rows,
-                                                                                        cols, drop_p, rng_state, salt);
-        BMHRL_POST_LAUNCH("cast16");
+        BMHRL_LAUNCH_PDL("cast16", cast16_kernel, dim3(grid1d((long long)rows * (cols / 4), 256, 148 * 4)), dim3(256), 0, st, x,
+                         ldx, (__nv_bfloat16*)y, ldy, rows, cols, drop_p, rng_state, salt);
     }
     return BMHRL_OK;
 }
@@ -242,8 +247,7 @@ extern "C" int bmhrl_colsum_bf16(const void* z, long long ldz, int rows, int col
     BMHRL_CHECK_ARG((cols % 4 == 0) && (ldz % 4 == 0) && ((((uintptr_t)z) & 7u) == 0), "bmhrl_colsum_bf16: cols / pitch % 4");
     BMHRL_CHECK_ARG(seg_cols == 0 || (seg_cols > 0 && cols <= 3 * seg_cols && (cols <= seg_cols || out1) &&
                                       (cols <= 2 * seg_cols || out2)), "bmhrl_colsum_bf16: segments");
-    colsum16_kernel<<<(cols + 63) / 64, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)z, ldz, rows, cols, out0, out1,
-                                                                        out2, seg_cols, accumulate);
-    BMHRL_POST_LAUNCH("colsum16");
+    BMHRL_LAUNCH_PDL("colsum16", colsum16_kernel, dim3((cols + 63) / 64), dim3(256), 0, (cudaStream_t)stream,
+                     (const __nv_bfloat16*)z, ldz, rows, cols, out0, out1, out2, seg_cols, accumulate);
     return BMHRL_OK;
 }

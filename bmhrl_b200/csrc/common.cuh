@@ -64,6 +64,46 @@ inline int device_sm_count() {
     return v;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch (PDL)
+// The kernels of a residual block form a dependency chain on one stream (LayerNorm -> projection GEMM -> attention ->
+// out-projection GEMM -> ...), each a few microseconds long.  Launched with the programmatic-stream-serialisation
+// attribute, the NEXT kernel's CTAs become resident as soon as every CTA of the current one has passed its own
+// `griddep_wait()` + `griddep_launch_dependents()`: its prologue (barrier init, TMEM allocation, tensor-map fetch) and
+// the TMA loads of operands that no earlier launch of the stream produces (weights) overlap the current kernel's body.
+// Rules every kernel launched through launch_pdl() follows: (1) no memory a predecessor may have written is read
+// before griddep_wait(); (2) launch_dependents is issued only AFTER the own wait, so a dependent never runs ahead of its
+// predecessor's predecessors.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+int pdl_enabled();   // api.cu: bmhrl_set_pdl(), BMHRL_PDL environment variable
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    if (pdl_enabled()) {
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+    }
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define BMHRL_LAUNCH_PDL(name, ...)                                \
+    do {                                                           \
+        cudaError_t _e = launch_pdl(__VA_ARGS__);                  \
+        if (_e != cudaSuccess) {                                   \
+            bmhrl_set_error(cudaGetErrorString(_e));               \
+            return BMHRL_ERR_CUDA;                                 \
+        }                                                          \
+        bmhrl_count_launch(1);                                     \
+    } while (0)
+
 constexpr float kNegFill = -1e9f;  // reference replaces masked scores by -1e9 (model/multihead_attention.py:21-22)
 
 // ---------------------------------------------------------------- Philox4x32-10 (counter based RNG)

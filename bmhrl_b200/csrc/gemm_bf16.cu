@@ -44,7 +44,7 @@ struct alignas(64) GbProblem {
     const unsigned long long* rng;
     long long ldc32, ldc16, ldr, ldg;
     int M, N, K, num_kb, kb_per_split;
-    int a_mn, b_mn, act, seg_rows;
+    int a_mn, b_mn, act, seg_rows, b_static;
     int tiles_n, tile_start;   // tiles of this problem are blockIdx.x in [tile_start, tile_start + tiles_m * tiles_n)
     int vec32, vec16, vecr, vecg;  // 128-bit access allowed on C32 rows / 64-bit on C16 / resid / gate
     float alpha, beta, gate_scale, drop_p;
@@ -118,12 +118,8 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
 
     if (warp == 0) {
         if (elect_one()) {  // ===== TMA producer
-            int s = 0;
-            uint32_t ph = 0;
-            for (int kb = kb0; kb < kb1; ++kb) {
-                mbar_wait(empty_bar(s), ph ^ 1u);
-                mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
-                const uint32_t sA = base + s * STAGE_BYTES, sB = sA + GB_A_BYTES;
+            auto load_a = [&](int s, int kb) {
+                const uint32_t sA = base + s * STAGE_BYTES;
                 const int k = kb * GB_BK;
                 if (!p.a_mn) {
                     tma_load_2d(sA, &p.tmA, full_bar(s), k, m0);            // box {64 k, 128 m}
@@ -132,6 +128,10 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
                     for (int c = 0; c < GB_BM / 64; ++c)                    // box {64 m, 64 k} per 128-byte MN chunk
                         tma_load_2d(sA + c * 8192, &p.tmA, full_bar(s), m0 + c * 64, k);
                 }
+            };
+            auto load_b = [&](int s, int kb) {
+                const uint32_t sB = base + s * STAGE_BYTES + GB_A_BYTES;
+                const int k = kb * GB_BK;
                 if (!p.b_mn) {
                     tma_load_2d(sB, &p.tmB, full_bar(s), k, n0);            // box {64 k, BN n}
                 } else {
@@ -139,6 +139,27 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
                     for (int c = 0; c < BN / 64; ++c)
                         tma_load_2d(sB + c * 8192, &p.tmB, full_bar(s), n0 + c * 64, k);
                 }
+            };
+            // the first ring-full of stages: a static B (weights) is requested BEFORE the grid dependency is resolved --
+            // under programmatic dependent launch these loads run while the previous kernel of the stream is finishing
+            const int npre = min(STAGES, kb1 - kb0);
+            for (int i = 0; i < npre; ++i) {
+                mbar_arrive_expect_tx(full_bar(i), STAGE_BYTES);
+                if (p.b_static) load_b(i, kb0 + i);
+            }
+            griddep_wait();
+            griddep_launch_dependents();
+            for (int i = 0; i < npre; ++i) {
+                if (!p.b_static) load_b(i, kb0 + i);
+                load_a(i, kb0 + i);
+            }
+            int s = npre == STAGES ? 0 : npre;
+            uint32_t ph = npre == STAGES ? 1u : 0u;
+            for (int kb = kb0 + npre; kb < kb1; ++kb) {
+                mbar_wait(empty_bar(s), ph ^ 1u);
+                mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
+                load_a(s, kb);
+                load_b(s, kb);
                 if (++s == STAGES) { s = 0; ph ^= 1u; }
             }
         }
@@ -170,6 +191,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
     const int row = q * 32 + lane;
     const int m = m0 + row;
     const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    if (warp >= 2) griddep_wait();   // the epilogue reads bias / residual / gate / C: nothing before the dependency resolves
     const int csz = P.cluster > 1 ? P.cluster : 1;
     const int W = BN / csz;  // columns of the tile this CTA finishes (cluster mode)
     const uint32_t rank = P.cluster > 1 ? cluster_ctarank() : 0u;
@@ -486,14 +508,23 @@ static int launch_gb(const GbParams& P, int total_tiles, int split, cudaStream_t
     cfg.blockDim = dim3(192);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
+    int na = 0;
     if (P.cluster > 1) {
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = 1;
-        at[0].val.clusterDim.y = 1;
-        at[0].val.clusterDim.z = P.cluster;
+        at[na].id = cudaLaunchAttributeClusterDimension;
+        at[na].val.clusterDim.x = 1;
+        at[na].val.clusterDim.y = 1;
+        at[na].val.clusterDim.z = P.cluster;
+        ++na;
+    }
+    if (pdl_enabled()) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (na) {
         cfg.attrs = at;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = na;
     }
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bf16_tc_kernel<BN, MODE>, P);
     if (e != cudaSuccess) {
@@ -607,6 +638,7 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
         q.num_kb = (g.K + GB_BK - 1) / GB_BK;
         q.kb_per_split = (q.num_kb + split - 1) / split;
         q.a_mn = g.a_mn ? 1 : 0; q.b_mn = g.b_mn ? 1 : 0; q.act = g.act; q.seg_rows = g.seg_rows;
+        q.b_static = g.b_static ? 1 : 0;
         q.tiles_n = (g.N + BN - 1) / BN;
         q.tile_start = tile_start;
         tile_start += ((g.M + GB_BM - 1) / GB_BM) * q.tiles_n;
@@ -636,6 +668,8 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
 //             operand of the dX / dW GEMMs.
 __global__ void vocab_finalize_kernel(const float* __restrict__ part, int tiles, float* __restrict__ stats,
                                       long long* __restrict__ tok, int M) {
+    griddep_wait();
+    griddep_launch_dependents();
     const int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (m >= M) return;
@@ -684,6 +718,7 @@ static int vocab_problem(GbParams& P, const void* x16, long long ldx, const void
         return BMHRL_ERR_CUDA;
     }
     q.bias = bias; q.M = M; q.N = V; q.K = K; q.num_kb = num_kb; q.kb_per_split = num_kb;
+    q.b_static = 1;   // the projection weight shadow
     q.tiles_n = (V + 127) / 128; q.tile_start = 0; q.alpha = 1.f;
     return BMHRL_OK;
 }
@@ -709,8 +744,8 @@ extern "C" int bmhrl_vocab_stats_bf16(const void* x16, long long ldx, const void
     cudaStream_t st = (cudaStream_t)stream;
     rc = launch_gb<128, 1>(P, tiles, 1, st);
     if (rc != BMHRL_OK) return rc;
-    vocab_finalize_kernel<<<(M + 7) / 8, 256, 0, st>>>(part_ws, q.tiles_n, stats, tokens, M);
-    BMHRL_POST_LAUNCH("vocab_finalize");
+    BMHRL_LAUNCH_PDL("vocab_finalize", vocab_finalize_kernel, dim3((M + 7) / 8), dim3(256), 0, st, (const float*)part_ws,
+                     q.tiles_n, stats, tokens, M);
     return BMHRL_OK;
 }
 

@@ -246,6 +246,8 @@ __global__ void __launch_bounds__(256) layernorm_bwd_det_kernel(
     const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ dres,
     float* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int D, int vec,
     int row_blocks, int accumulate) {
+    griddep_wait();
+    griddep_launch_dependents();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     if ((int)blockIdx.x < row_blocks) {
         const int row = blockIdx.x * 8 + w;
@@ -417,9 +419,8 @@ extern "C" int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const fl
                     (!dres || aligned16(dres));
     const int row_blocks = dx ? (rows + 7) / 8 : 0;
     const int strips = want_affine ? (D + 31) / 32 : 0;
-    layernorm_bwd_det_kernel<<<row_blocks + strips, 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, D,
-                                                                  vec, row_blocks, accumulate_affine);
-    BMHRL_POST_LAUNCH("layernorm_bwd_det");
+    BMHRL_LAUNCH_PDL("layernorm_bwd_det", layernorm_bwd_det_kernel, dim3(row_blocks + strips), dim3(256), 0, st, dy, x, gamma,
+                     mean, rstd, dres, dx, dgamma, dbeta, rows, D, vec, row_blocks, accumulate_affine);
     return BMHRL_OK;
 }
 

@@ -26,7 +26,8 @@ class GemmDesc(ctypes.Structure):
                 ("resid", ctypes.c_void_p), ("ldr", ctypes.c_longlong), ("beta", ctypes.c_float),
                 ("C32", ctypes.c_void_p), ("ldc32", ctypes.c_longlong),
                 ("C16", ctypes.c_void_p), ("ldc16", ctypes.c_longlong),
-                ("seg_rows", ctypes.c_int), ("C32_seg1", ctypes.c_void_p), ("C32_seg2", ctypes.c_void_p)]
+                ("seg_rows", ctypes.c_int), ("C32_seg1", ctypes.c_void_p), ("C32_seg2", ctypes.c_void_p),
+                ("b_static", ctypes.c_int)]
 
 
 _DESC_CHECKED = [False]
@@ -67,7 +68,7 @@ def _f32mat(t, name, rows, cols):
 
 
 def gemm_problem(A, a_mn, B, b_mn, M, N, K, *, alpha=1.0, bias=None, act=0, gate=None, gate_scale=1.0, drop_p=0.0,
-                 rng=None, salt=0, resid=None, beta=0.0, C32=None, C16=None, seg=None):
+                 rng=None, salt=0, resid=None, beta=0.0, C32=None, C16=None, seg=None, b_static=False):
     """One `bmhrl_gemm_desc`.  A / B: bf16 matrices as stored (see the header for the two majors); C32 (fp32, 2-D,
     contiguous rows) / C16 (bf16 matrix) outputs; seg = (rows_per_segment, [seg1, seg2]) splits C32 by rows."""
     _mat16(A, "A")
@@ -97,6 +98,10 @@ def gemm_problem(A, a_mn, B, b_mn, M, N, K, *, alpha=1.0, bias=None, act=0, gate
         d.seg_rows = int(rows)
         d.C32_seg1 = others[0].data_ptr()
         d.C32_seg2 = others[1].data_ptr() if len(others) > 1 else None
+    if b_static and getattr(B, "_bmhrl_refreshed", False):
+        b_static = False              # re-cast on this stream a moment ago: this first use must wait for that kernel
+        B._bmhrl_refreshed = False
+    d.b_static = 1 if b_static else 0   # B is a weight shadow: may be fetched before the grid dependency resolves (PDL)
     d._keep = (A, B, bias, gate, rng, resid, C32, C16, seg)  # operands stay alive until the call returns
     return d
 
@@ -256,6 +261,7 @@ class _Shadows:
         return g
 
     def _refresh(self, g, weights, biases):
+        g["w16"]._bmhrl_refreshed = True   # see gemm_problem: no early (pre-dependency) fetch of a shadow just re-cast
         r0 = 0
         for i, w in enumerate(weights):
             n = w.shape[0]
@@ -421,7 +427,7 @@ class _AttnBlock(torch.autograd.Function):
             Sk, Mk = Sq, M
             w16, b32 = SHADOWS.get([Wq, Wk, Wv], [bq, bk, bv])
             qkv = empty16(M, 3 * D, dev)
-            gemm_group([gemm_problem(n16, 0, w16, 0, M, 3 * D, Dq, bias=b32, C16=qkv)])
+            gemm_group([gemm_problem(n16, 0, w16, 0, M, 3 * D, Dq, b_static=True, bias=b32, C16=qkv)])
             q, k, v = qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:]
             m16 = None
         else:
@@ -433,8 +439,8 @@ class _AttnBlock(torch.autograd.Function):
             wkv16, bkv32 = SHADOWS.get([Wk, Wv], [bk, bv])
             q = empty16(M, D, dev)
             kvp = empty16(Mk, 2 * D, dev)
-            gemm_group([gemm_problem(n16, 0, wq16, 0, M, D, Dq, bias=None if bq is None else bq.detach(), C16=q),
-                        gemm_problem(m16, 0, wkv16, 0, Mk, 2 * D, Dkv, bias=bkv32, C16=kvp)])
+            gemm_group([gemm_problem(n16, 0, wq16, 0, M, D, Dq, b_static=True, bias=None if bq is None else bq.detach(), C16=q),
+                        gemm_problem(m16, 0, wkv16, 0, Mk, 2 * D, Dkv, b_static=True, bias=bkv32, C16=kvp)])
             k, v = kvp[:, :D], kvp[:, D:]
             qkv = None
         o16 = empty16(M, D, dev)
@@ -445,7 +451,7 @@ class _AttnBlock(torch.autograd.Function):
         wo16, _ = SHADOWS.get([Wo], [bo])
         out = torch.empty(B, Sq, Dq, device=dev, dtype=_F32)
         out16 = empty16(M, Dq, dev) if cfg.get("emit_twin") else None
-        gemm_group([gemm_problem(o16, 0, wo16, 0, M, Dq, D, bias=None if bo is None else bo.detach(), drop_p=cfg["p_res"],
+        gemm_group([gemm_problem(o16, 0, wo16, 0, M, Dq, D, b_static=True, bias=None if bo is None else bo.detach(), drop_p=cfg["p_res"],
                                  rng=cfg["rng"], salt=cfg["s_out"], resid=x2 if cfg["resid"] else None,
                                  C32=out.view(M, Dq), C16=out16)])
         if out16 is not None:
@@ -475,7 +481,7 @@ class _AttnBlock(torch.autograd.Function):
         dbo = _bgrad16(dzo, [bo], Dq)[0]
         wo16, _ = SHADOWS.get([Wo], [bo])
         do16 = empty16(M, D, dev)
-        gemm_group([gemm_problem(dzo, 0, wo16, 1, M, D, Dq, drop_p=cfg["p_attn"], rng=cfg["rng"], salt=cfg["s_core"], C16=do16)])
+        gemm_group([gemm_problem(dzo, 0, wo16, 1, M, D, Dq, b_static=True, drop_p=cfg["p_attn"], rng=cfg["rng"], salt=cfg["s_core"], C16=do16)])
         dWo = _wgrad(dzo, o16, [Wo], Dq)[0]
         # ---- attention core
         if self_att:
@@ -493,7 +499,7 @@ class _AttnBlock(torch.autograd.Function):
             w16, _ = SHADOWS.get([Wq, Wk, Wv], [bq, bk, bv])
             dn = torch.empty(M, Dq, device=dev, dtype=_F32) if (need_x or ln_g is not None) else None
             if dn is not None:
-                gemm_group([gemm_problem(dz, 0, w16, 1, M, Dq, 3 * D, C32=dn)])
+                gemm_group([gemm_problem(dz, 0, w16, 1, M, Dq, 3 * D, b_static=True, C32=dn)])
             gw = _wgrad(dz, n16, [Wq, Wk, Wv], D)
             gb = _bgrad16(dz, [bq, bk, bv], D)
         else:
@@ -502,10 +508,10 @@ class _AttnBlock(torch.autograd.Function):
             probs = []
             dn = torch.empty(M, Dq, device=dev, dtype=_F32) if (need_x or ln_g is not None) else None
             if dn is not None:
-                probs.append(gemm_problem(dq, 0, wq16, 1, M, Dq, D, C32=dn))
+                probs.append(gemm_problem(dq, 0, wq16, 1, M, Dq, D, b_static=True, C32=dn))
             if need_kv:
                 dkv = torch.empty(B, Sk, Dkv, device=dev, dtype=_F32)
-                probs.append(gemm_problem(dzkv, 0, wkv16, 1, Mk, Dkv, 2 * D, C32=dkv.view(Mk, Dkv)))
+                probs.append(gemm_problem(dzkv, 0, wkv16, 1, Mk, Dkv, 2 * D, b_static=True, C32=dkv.view(Mk, Dkv)))
             if probs:
                 gemm_group(probs)
             gw = _wgrad(dq, n16, [Wq], D) + _wgrad(dzkv, m16, [Wk, Wv], D)
@@ -543,11 +549,11 @@ class _FfnBlock(torch.autograd.Function):
         w1, _ = SHADOWS.get([W1], [b1])
         w2, _ = SHADOWS.get([W2], [b2])
         h16 = empty16(M, F_, dev)
-        gemm_group([gemm_problem(n16, 0, w1, 0, M, F_, D, bias=b1.detach(), act=1, drop_p=cfg["p1"], rng=cfg["rng"],
+        gemm_group([gemm_problem(n16, 0, w1, 0, M, F_, D, b_static=True, bias=b1.detach(), act=1, drop_p=cfg["p1"], rng=cfg["rng"],
                                  salt=cfg["s1"], C16=h16)])
         out = torch.empty(B, S, D, device=dev, dtype=_F32)
         out16 = empty16(M, D, dev) if cfg.get("emit_twin") else None
-        gemm_group([gemm_problem(h16, 0, w2, 0, M, D, F_, bias=b2.detach(), drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"],
+        gemm_group([gemm_problem(h16, 0, w2, 0, M, D, F_, b_static=True, bias=b2.detach(), drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"],
                                  resid=x2 if cfg["resid"] else None, C32=out.view(M, D), C16=out16)])
         if out16 is not None:
             attach_twin(out, out16)
@@ -576,10 +582,10 @@ class _FfnBlock(torch.autograd.Function):
         w2, _ = SHADOWS.get([W2], [b2])
         dz1 = empty16(M, F_, dev)   # dZ_1 = (dZ_2 W_2) o [h > 0] / (1 - p1): relu and dropout gates in the GEMM epilogue
         gs = 1.0 / (1.0 - cfg["p1"]) if cfg["p1"] > 0 else 1.0
-        gemm_group([gemm_problem(dz2, 0, w2, 1, M, F_, D, gate=h16, gate_scale=gs, C16=dz1)])
+        gemm_group([gemm_problem(dz2, 0, w2, 1, M, F_, D, b_static=True, gate=h16, gate_scale=gs, C16=dz1)])
         dW2 = _wgrad(dz2, h16, [W2], D)[0]
         dn = torch.empty(M, D, device=dev, dtype=_F32)
-        gemm_group([gemm_problem(dz1, 0, w1, 1, M, D, F_, C32=dn)])
+        gemm_group([gemm_problem(dz1, 0, w1, 1, M, D, F_, b_static=True, C32=dn)])
         dW1 = _wgrad(dz1, n16, [W1], F_)[0]
         db1 = _bgrad16(dz1, [b1], F_)[0]
         dx = dg = dbeta = None
@@ -607,7 +613,7 @@ class _Linear16(torch.autograd.Function):
         w16, _ = SHADOWS.get([W], [b])
         out = torch.empty(x.shape[:-1] + (N,), device=x.device, dtype=_F32)
         out16 = empty16(M, N, x.device) if cfg.get("emit_twin") else None
-        gemm_group([gemm_problem(x16, 0, w16, 0, M, N, K, bias=None if b is None else b.detach(), drop_p=cfg["p"],
+        gemm_group([gemm_problem(x16, 0, w16, 0, M, N, K, b_static=True, bias=None if b is None else b.detach(), drop_p=cfg["p"],
                                  rng=cfg["rng"], salt=cfg["salt"], C32=out.view(M, N), C16=out16)])
         if out16 is not None:
             attach_twin(out, out16)
@@ -634,7 +640,7 @@ class _Linear16(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             w16, _ = SHADOWS.get([W], [b])
             dx = torch.empty(xshape, device=dev, dtype=_F32)
-            gemm_group([gemm_problem(dz, 0, w16, 1, M, K, N, C32=dx.view(M, K))])
+            gemm_group([gemm_problem(dz, 0, w16, 1, M, K, N, b_static=True, C32=dx.view(M, K))])
         dW = _wgrad(dz, x16, [W], N)[0]
         return dx, dW, db, None
 
@@ -737,7 +743,7 @@ class _VocabStats(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty(xshape, device=dev, dtype=_F32)
-            gemm_group([gemm_problem(dl, 0, w16, 1, M, K, V, C32=dx.view(M, K))])
+            gemm_group([gemm_problem(dl, 0, w16, 1, M, K, V, b_static=True, C32=dx.view(M, K))])
         dW = _wgrad(dl, x16, [W], V)[0]
         db = _bgrad16(dl, [b], V)[0] if b is not None else None
         return dx, dW, db, None, None, None, None, None, None

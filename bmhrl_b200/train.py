@@ -478,7 +478,9 @@ class StepRunner:
         """One step on `host_batch`.  With pipeline_critic the captions of the batch that FOLLOWS must come along
         (`next_host_batch`; None = the same batch again): this step labels them for the next one."""
         self.load(host_batch, next_host_batch=next_host_batch)
-        if self.pipeline_critic and self._need_prime:
+        if self.pipeline_critic and (self._need_prime or next_host_batch is None):
+            # first step of a stream, or no look-ahead given: label THIS batch now (the step then labels whatever
+            # caption_next holds -- this batch again -- for a possible repeat)
             self.prime()
         return self.replay()
 
@@ -490,13 +492,21 @@ class StepRunner:
             self.labels_cur.copy_(self.trainer.cap_model.segment_labels_of(self.cap_in_cur))
         self._need_prime = False
 
-    def step_ragged(self, ragged, score=None):
+    def step_ragged(self, ragged, score=None, next_caption=None):
         """One step fed by the input pipeline: `ragged` is a data.RaggedBatch whose stage() has been called -- ONE
         host->device copy of the packed clips + captions, the pad / rgb+flow / mask kernels straight into this runner's
         static buffers (the runner must have been built from a batch with V / V_mask / A_mask), then the step."""
         ragged.to_device(out=self.static)
         if score is not None:
             self.static["score"].copy_(score, non_blocking=True)
+        if self.pipeline_critic:
+            if next_caption is not None:
+                self.static["caption_next"].copy_(next_caption, non_blocking=True)
+                if self._need_prime:
+                    self.prime()
+            else:   # no look-ahead available: label this batch now (correct, just not pipelined)
+                self.static["caption_next"].copy_(self.static["caption"])
+                self.prime()
         return self.replay()
 
 

@@ -38,6 +38,13 @@ void bmhrl_reset_launch_count(void);
  * the caching allocator relies on while a CUDA graph is being captured (a block freed by one branch was re-used by an
  * unordered branch).  Replaces nothing in the reference (its nn.DataParallel threads share the default stream). */
 int bmhrl_stream_create(void** stream);
+/* Programmatic dependent launch of the chain kernels of the bf16 math mode (GEMM, one-tile attention, LayerNorm, cast,
+ * column sums): with it, the next kernel of a stream becomes resident and runs its prologue -- and the TMA loads of
+ * operands no earlier launch produces (weights: bmhrl_gemm_desc.b_static) -- while the current one is still running;
+ * every such kernel executes griddepcontrol.wait before it touches anything a predecessor wrote.  1 (default; the
+ * environment variable BMHRL_PDL=0 sets the initial value) / 0. */
+int bmhrl_set_pdl(int on);
+int bmhrl_get_pdl(void);
 
 /* ---- math mode ------------------------------------------------------------------------------------------------ */
 /* 0 (default): every contraction in exact fp32 on the SIMT pipes (parity bound 1e-3, in practice ~1e-6).
@@ -107,6 +114,8 @@ typedef struct bmhrl_gemm_desc {
     float* C32; long long ldc32;
     void* C16; long long ldc16;
     int seg_rows; float* C32_seg1; float* C32_seg2;
+    int b_static;   /* != 0: B is not written by any earlier launch of the stream since the last full dependency (a weight
+                       shadow inside one training step): its tiles may be fetched before griddepcontrol.wait */
 } bmhrl_gemm_desc;
 int bmhrl_gemm_desc_bytes(void);   /* sizeof(bmhrl_gemm_desc): bindings check their mirror of the struct against it */
 /* 1..4 independent problems in ONE launch (tcgen05.mma kind::f16 into TMEM, TMA-staged operands, 128 x 128 / 128 x 64

@@ -1,5 +1,4 @@
-"""Summarises an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel totals of ONE training step
-(the launches between two consecutive adam_multi_kernel launches).  usage: summarize_launches.py launches.csv [title]"""
+"""Summarises an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel totals of ONE training step.  usage: summarize_launches.py launches.csv [title]"""
 import collections
 import csv
 import re
@@ -13,8 +12,12 @@ for x in csv.DictReader(lines):
         u = x["Metric Unit"]
         v = v / 1e3 if u == "ns" else (v * 1e3 if u == "ms" else v)
         rows.append((x["Kernel Name"], v))
-idx = [i for i, (n, v) in enumerate(rows) if "adam_multi" in n]
-step = rows[idx[-2] + 1:idx[-1] + 1]
+# one training step = the launches between two consecutive embed_posenc_kernel launches (exactly one per forward pass;
+# the staged optimiser launches adam_multi_kernel several times per step, so it no longer marks a boundary)
+idx = [i for i, (n, v) in enumerate(rows) if "embed_posenc" in n]
+if len(idx) < 2:
+    idx = [i for i, (n, v) in enumerate(rows) if "adam_multi" in n]
+step = rows[idx[-2]:idx[-1]]
 tot = sum(v for _, v in step)
 print("#", " ".join(sys.argv[2:]))
 print("# per-launch times are cold-cache + serialised (ncu replay): compare SHARES, not absolutes")
