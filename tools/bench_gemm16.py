@@ -59,10 +59,12 @@ def main():
         with torch.no_grad():
             rec["tf32_fwd_us"] = timed(lambda i: ops.linear(x32, w32[i % ncopy]), iters)
         rec["bf16_fwd_us"] = timed(lambda i: ops16.gemm_group([ops16.gemm_problem(x16, 0, w16[i % ncopy], 0, M, N, K, C16=c16)]), iters)
+        rec["bf16_fwd_hotW_us"] = timed(lambda i: ops16.gemm_group([ops16.gemm_problem(x16, 0, w16[0], 0, M, N, K, C16=c16)]), iters)
+        rec["bf16_dx_hotW_us"] = timed(lambda i: ops16.gemm_group([ops16.gemm_problem(dz16, 0, w16[0], 1, M, K, N, C32=dx)]), iters)
         rec["bf16_fwd32_us"] = timed(lambda i: ops16.gemm_group([ops16.gemm_problem(x16, 0, w16[i % ncopy], 0, M, N, K, C32=c32)]), iters)
         rec["bf16_dx_us"] = timed(lambda i: ops16.gemm_group([ops16.gemm_problem(dz16, 0, w16[i % ncopy], 1, M, K, N, C32=dx)]), iters)
         rec["bf16_dw_us"] = timed(lambda i: ops16.gemm_group([ops16.gemm_problem(dz16, 1, x16, 1, N, K, M, C32=dw, beta=1.0)]), iters)
-        for bn, sp in ((128, 1), (128, 2), (128, 4), (64, 1), (64, 2)):
+        for bn, sp in ((128, 1), (64, 1), (64, 2)):
             LIB.call("bmhrl_gemm_bf16_tuning", bn, sp, 0)
             rec[f"bf16_fwd_bn{bn}_s{sp}_us"] = timed(
                 lambda i: ops16.gemm_group([ops16.gemm_problem(x16, 0, w16[i % ncopy], 0, M, N, K, C16=c16)]), iters)

@@ -35,9 +35,22 @@ def main():
         ops.CONCURRENT = bool(int(os.environ["BMHRL_CONCURRENT"]))
     b = synth.synthetic_batch(V=bench.VOC, seed=1234, **bench.SHAPE)
     runner = StepRunner(tr, workload, b, use_graph=True, warmup=3, pipeline_critic=os.environ.get("BMHRL_PIPELINE", "1") != "0")
+    if os.environ.get("BMHRL_DIAG_NO_CRITIC"):   # diagnosis only: what the step costs with the critic taken out altogether
+        lab = runner.labels_cur.clone()
+        model.segment_labels_of = lambda trg: lab
+        runner = StepRunner(tr, workload, b, use_graph=True, warmup=3, pipeline_critic=True)
     for _ in range(5):
         runner.replay()
     torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 40
+    e0.record()
+    for _ in range(reps):
+        runner.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"# back-to-back replays without the profiler: {e0.elapsed_time(e1) / reps * 1e3:.1f} us per step "
+          f"(CUDA_DEVICE_MAX_CONNECTIONS={os.environ.get('CUDA_DEVICE_MAX_CONNECTIONS', 'default')})")
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         runner.replay()   # exactly ONE replay inside the profiled region: every kernel event belongs to it
