@@ -58,7 +58,22 @@ struct alignas(64) GbProblem {
 struct GbParams {
     GbProblem p[GB_MAXP];
     int n, cluster, nstages;
+    unsigned long long* trace;   // diagnosis (bmhrl_gemm_bf16_trace): CTA 0 stamps clock64() at its hand-over points; else NULL
 };
+
+// slots: 0 entry, 1 set-up done, 2 producer past the grid dependency, 3 first ring requested, 4 first stage landed,
+// 5 last MMA committed, 6 accumulator visible to the epilogue, 7 epilogue stores issued, 8 exit, 9 globaltimer at entry,
+// 10 globaltimer at exit, 11 first accumulator chunk in registers, 12 first pass staged, 13 first pass stored, 16 + i: stage of k-block i landed (i < 48)
+__device__ __forceinline__ void gb_stamp(const GbParams& P, int slot) {
+    if (P.trace && blockIdx.x == 0 && blockIdx.z == 0) P.trace[slot] = (unsigned long long)clock64();
+}
+__device__ __forceinline__ void gb_stamp_ns(const GbParams& P, int slot) {
+    if (P.trace && blockIdx.x == 0 && blockIdx.z == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        P.trace[slot] = t;
+    }
+}
 
 __device__ __forceinline__ uint2 ld_bf16x4(const __nv_bfloat16* p) { return *reinterpret_cast<const uint2*>(p); }
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
@@ -70,7 +85,7 @@ __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
 }
 
 template <int BN, int MODE>
-__global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant__ GbParams P) {
+__global__ void __launch_bounds__(192, (BN == 64 ? 3 : 1)) gemm_bf16_tc_kernel(const __grid_constant__ GbParams P) {
     constexpr int B_BYTES = BN * 128;
     constexpr int STAGE_BYTES = GB_A_BYTES + B_BYTES;
     constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
@@ -90,17 +105,31 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
 #pragma unroll
     for (int i = 1; i < GB_MAXP; ++i)
         if (i < P.n && (int)blockIdx.x >= P.p[i].tile_start) pi = i;
-    const GbProblem& p = P.p[pi];
-    const int t = blockIdx.x - p.tile_start;
-    const int tm = t / p.tiles_n, tn = t - tm * p.tiles_n;
+    const GbProblem& p = P.p[pi];   // a DYNAMICALLY indexed parameter slot: every p.x is an indexed constant load (slow,
+                                    // and serial when it feeds a branch); what the hot paths need is copied into
+                                    // registers below through a switch, i.e. with static indices
+    int c_tile_start = 0, c_tiles_n = 1, c_kb_per_split = 0, c_num_kb = 0, c_a_mn = 0, c_b_mn = 0, c_b_static = 0;
+    const CUtensorMap* c_tmA = nullptr;
+    const CUtensorMap* c_tmB = nullptr;
+#define GB_COMMON(i)                                                                                       \
+    case i:                                                                                                \
+        c_tile_start = P.p[i].tile_start; c_tiles_n = P.p[i].tiles_n; c_kb_per_split = P.p[i].kb_per_split; \
+        c_num_kb = P.p[i].num_kb; c_a_mn = P.p[i].a_mn; c_b_mn = P.p[i].b_mn; c_b_static = P.p[i].b_static; \
+        c_tmA = &P.p[i].tmA; c_tmB = &P.p[i].tmB;                                                           \
+        break;
+    switch (pi) { GB_COMMON(0) GB_COMMON(1) GB_COMMON(2) GB_COMMON(3) }
+#undef GB_COMMON
+    const int t = blockIdx.x - c_tile_start;
+    const int tm = t / c_tiles_n, tn = t - tm * c_tiles_n;
     const int m0 = tm * GB_BM, n0 = tn * BN;
-    const int kb0 = blockIdx.z * p.kb_per_split;
-    const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+    const int kb0 = blockIdx.z * c_kb_per_split;
+    const int kb1 = min(c_num_kb, kb0 + c_kb_per_split);
     const bool has_k = kb1 > kb0;   // a split without k-blocks contributes zeros (cluster mode only)
 
+    if (threadIdx.x == 0) { gb_stamp(P, 0); gb_stamp_ns(P, 9); }
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&p.tmA);
-        tma_prefetch_desc(&p.tmB);
+        tma_prefetch_desc(c_tmA);
+        tma_prefetch_desc(c_tmB);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full_bar(s), 1);
             mbar_init(empty_bar(s), 1);
@@ -115,29 +144,31 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
     if (P.cluster > 1) cluster_sync_all();  // every CTA of the cluster is running before anyone writes into its smem
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    if (threadIdx.x == 0) gb_stamp(P, 1);
 
     if (warp == 0) {
         if (elect_one()) {  // ===== TMA producer
+            const int a_mn = c_a_mn, b_mn = c_b_mn, b_static = c_b_static;
             auto load_a = [&](int s, int kb) {
                 const uint32_t sA = base + s * STAGE_BYTES;
                 const int k = kb * GB_BK;
-                if (!p.a_mn) {
-                    tma_load_2d(sA, &p.tmA, full_bar(s), k, m0);            // box {64 k, 128 m}
+                if (!a_mn) {
+                    tma_load_2d(sA, c_tmA, full_bar(s), k, m0);            // box {64 k, 128 m}
                 } else {
 #pragma unroll
                     for (int c = 0; c < GB_BM / 64; ++c)                    // box {64 m, 64 k} per 128-byte MN chunk
-                        tma_load_2d(sA + c * 8192, &p.tmA, full_bar(s), m0 + c * 64, k);
+                        tma_load_2d(sA + c * 8192, c_tmA, full_bar(s), m0 + c * 64, k);
                 }
             };
             auto load_b = [&](int s, int kb) {
                 const uint32_t sB = base + s * STAGE_BYTES + GB_A_BYTES;
                 const int k = kb * GB_BK;
-                if (!p.b_mn) {
-                    tma_load_2d(sB, &p.tmB, full_bar(s), k, n0);            // box {64 k, BN n}
+                if (!b_mn) {
+                    tma_load_2d(sB, c_tmB, full_bar(s), k, n0);            // box {64 k, BN n}
                 } else {
 #pragma unroll
                     for (int c = 0; c < BN / 64; ++c)
-                        tma_load_2d(sB + c * 8192, &p.tmB, full_bar(s), n0 + c * 64, k);
+                        tma_load_2d(sB + c * 8192, c_tmB, full_bar(s), n0 + c * 64, k);
                 }
             };
             // the first ring-full of stages: a static B (weights) is requested BEFORE the grid dependency is resolved --
@@ -145,14 +176,16 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
             const int npre = min(STAGES, kb1 - kb0);
             for (int i = 0; i < npre; ++i) {
                 mbar_arrive_expect_tx(full_bar(i), STAGE_BYTES);
-                if (p.b_static) load_b(i, kb0 + i);
+                if (b_static) load_b(i, kb0 + i);
             }
             griddep_wait();
             griddep_launch_dependents();
+            gb_stamp(P, 2);
             for (int i = 0; i < npre; ++i) {
-                if (!p.b_static) load_b(i, kb0 + i);
+                if (!b_static) load_b(i, kb0 + i);
                 load_a(i, kb0 + i);
             }
+            gb_stamp(P, 3);
             int s = npre == STAGES ? 0 : npre;
             uint32_t ph = npre == STAGES ? 1u : 0u;
             for (int kb = kb0 + npre; kb < kb1; ++kb) {
@@ -165,16 +198,20 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
         }
     } else if (warp == 1) {
         if (elect_one()) {  // ===== MMA issuer
-            const uint32_t idesc = make_idesc(1, GB_BM, BN, p.a_mn, p.b_mn);
-            const uint64_t ad0 = p.a_mn ? make_smem_desc(base, 8192, 1024) : make_smem_desc(base, 16, 1024);
-            const uint64_t bd0 = p.b_mn ? make_smem_desc(base + GB_A_BYTES, 8192, 1024)
+            const uint32_t idesc = make_idesc(1, GB_BM, BN, c_a_mn, c_b_mn);
+            const uint64_t ad0 = c_a_mn ? make_smem_desc(base, 8192, 1024) : make_smem_desc(base, 16, 1024);
+            const uint64_t bd0 = c_b_mn ? make_smem_desc(base + GB_A_BYTES, 8192, 1024)
                                         : make_smem_desc(base + GB_A_BYTES, 16, 1024);
-            const uint32_t a_step = p.a_mn ? 2048u : 32u, b_step = p.b_mn ? 2048u : 32u;
+            const uint32_t a_step = c_a_mn ? 2048u : 32u, b_step = c_b_mn ? 2048u : 32u;
             int s = 0;
             uint32_t ph = 0;
             for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(full_bar(s), ph);
                 tc_fence_after();
+                if (P.trace) {
+                    if (kb == kb0) gb_stamp(P, 4);
+                    if (kb - kb0 < 48) gb_stamp(P, 16 + kb - kb0);
+                }
                 const uint64_t ad = desc_advance(ad0, s * STAGE_BYTES), bd = desc_advance(bd0, s * STAGE_BYTES);
 #pragma unroll
                 for (int k = 0; k < GB_BK / 16; ++k)  // UMMA_K = 16 for bf16 (32 bytes of K)
@@ -184,6 +221,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
                 if (++s == STAGES) { s = 0; ph ^= 1u; }
             }
             tc_commit(tmem_full_bar);  // accumulator complete (arrives at once when nothing was issued)
+            gb_stamp(P, 5);
         }
     }
     // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4, thread = output row
@@ -191,6 +229,34 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
     const int row = q * 32 + lane;
     const int m = m0 + row;
     const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    // every field of the problem that the epilogue loops touch, in registers BEFORE the wait for the accumulator (left as
+    // p.x inside the loop bodies they formed a serial chain of ~20 indexed constant loads and branches per 4 output
+    // columns: 4-6 us per tile, longer than the main loop -- measured with bmhrl_gemm_bf16_trace)
+    int e_M = 0, e_N = 0, e_act = 0, e_seg_rows = 0, e_v_pad = 0, e_vec32 = 0, e_vec16 = 0, e_vecr = 0, e_vecg = 0;
+    float e_alpha = 1.f, e_beta = 0.f, e_gate_scale = 1.f, e_drop_p = 0.f;
+    unsigned int e_salt = 0;
+    const float* e_bias = nullptr;
+    const float* e_resid = nullptr;
+    const __nv_bfloat16* e_gate = nullptr;
+    const unsigned long long* e_rng = nullptr;
+    float* e_C32 = nullptr;
+    float* e_seg1 = nullptr;
+    float* e_seg2 = nullptr;
+    __nv_bfloat16* e_C16 = nullptr;
+    long long e_ldc32 = 0, e_ldc16 = 0, e_ldr = 0, e_ldg = 0;
+#define GB_EPI(i)                                                                                                       \
+    case i:                                                                                                             \
+        e_M = P.p[i].M; e_N = P.p[i].N; e_act = P.p[i].act; e_seg_rows = P.p[i].seg_rows; e_v_pad = P.p[i].v_pad;       \
+        e_vec32 = P.p[i].vec32; e_vec16 = P.p[i].vec16; e_vecr = P.p[i].vecr; e_vecg = P.p[i].vecg;                     \
+        e_alpha = P.p[i].alpha; e_beta = P.p[i].beta; e_gate_scale = P.p[i].gate_scale; e_drop_p = P.p[i].drop_p;       \
+        e_salt = P.p[i].salt; e_bias = P.p[i].bias; e_resid = P.p[i].resid; e_gate = P.p[i].gate; e_rng = P.p[i].rng;   \
+        e_C32 = P.p[i].C32; e_seg1 = P.p[i].seg1; e_seg2 = P.p[i].seg2; e_C16 = P.p[i].C16;                             \
+        e_ldc32 = P.p[i].ldc32; e_ldc16 = P.p[i].ldc16; e_ldr = P.p[i].ldr; e_ldg = P.p[i].ldg;                         \
+        break;
+    if (warp >= 2) {
+        switch (pi) { GB_EPI(0) GB_EPI(1) GB_EPI(2) GB_EPI(3) }
+    }
+#undef GB_EPI
     if (warp >= 2) griddep_wait();   // the epilogue reads bias / residual / gate / C: nothing before the dependency resolves
     const int csz = P.cluster > 1 ? P.cluster : 1;
     const int W = BN / csz;  // columns of the tile this CTA finishes (cluster mode)
@@ -198,6 +264,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
     if (warp >= 2) {
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
+        if (threadIdx.x == 64) gb_stamp(P, 6);
         if (P.cluster > 1) {
             // reduce-scatter, send side: slice r of my partial accumulator goes to CTA r's receive buffer, slot `rank`
             for (uint32_t r = 0; r < (uint32_t)csz; ++r) {
@@ -226,33 +293,37 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
         cluster_sync_all();  // release / acquire: all partial slices have landed
     }
     if (MODE == 1 && warp >= 2) {
+        const int s_tiles_n = c_tiles_n, s_v_smode = p.v_smode;
+        const float* const s_v_q = p.v_q;
+        float* const s_v_part = p.v_part;
+        const long long* const s_v_trg = p.v_trg;
         // ---- vocabulary statistics of row m over this CTA's BN columns (no output tile is written):
         //   max, sum exp(v - max), sum v, v[target], v[pad], and the sampling arg-max (key, index, logit)
-        const int trg = m < p.M ? (int)p.v_trg[m] : -1;
+        const int trg = m < e_M ? (int)s_v_trg[m] : -1;
         float mx = -INFINITY, se = 0.f, sv = 0.f, lt = 0.f, lp = 0.f, bk = -INFINITY, bl = 0.f;
         int bi = 0x7fffffff;
-        const bool row_ok = m < p.M;
-        const bool bias_vec = p.bias && aligned16(p.bias);
+        const bool row_ok = m < e_M;
+        const bool bias_vec = e_bias && aligned16(e_bias);
 #pragma unroll 1
         for (int cc = 0; cc < BN; cc += 32) {   // ONE pass: online max / sum-exp per 32-column chunk
             uint32_t r[32];
             tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
             tmem_ld_wait();
             const int nb = n0 + cc;
-            if (nb >= p.N) break;
+            if (nb >= e_N) break;
             float v[32];
-            const bool full = nb + 31 < p.N;
+            const bool full = nb + 31 < e_N;
             if (full && bias_vec) {
 #pragma unroll
                 for (int j4 = 0; j4 < 32; j4 += 4) {
-                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + j4));
+                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(e_bias + nb + j4));
                     v[j4] = __uint_as_float(r[j4]) + b4.x; v[j4 + 1] = __uint_as_float(r[j4 + 1]) + b4.y;
                     v[j4 + 2] = __uint_as_float(r[j4 + 2]) + b4.z; v[j4 + 3] = __uint_as_float(r[j4 + 3]) + b4.w;
                 }
             } else {
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                    v[j] = nb + j < p.N ? __uint_as_float(r[j]) + (p.bias ? p.bias[nb + j] : 0.f) : -INFINITY;
+                    v[j] = nb + j < e_N ? __uint_as_float(r[j]) + (e_bias ? e_bias[nb + j] : 0.f) : -INFINITY;
             }
             float cm = v[0];
 #pragma unroll
@@ -261,7 +332,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
             float cs = 0.f, csum = 0.f;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-                const bool in = full || nb + j < p.N;
+                const bool in = full || nb + j < e_N;
                 cs += in ? __expf(v[j] - nm) : 0.f;
                 csum += in ? v[j] : 0.f;
             }
@@ -272,11 +343,11 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
 #pragma unroll
                 for (int j = 0; j < 32; ++j) lt = (nb + j == trg) ? v[j] : lt;
             }
-            if (p.v_pad >= nb && p.v_pad < nb + 32) {
+            if (e_v_pad >= nb && e_v_pad < nb + 32) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) lp = (nb + j == p.v_pad) ? v[j] : lp;
+                for (int j = 0; j < 32; ++j) lp = (nb + j == e_v_pad) ? v[j] : lp;
             }
-            if (p.v_smode == 0) {
+            if (s_v_smode == 0) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
                     if (v[j] > bk) { bk = v[j]; bi = nb + j; bl = v[j]; }   // ascending n: the first maximum wins
@@ -284,12 +355,12 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int n = nb + j;
-                    if (n < p.N) {
+                    if (n < e_N) {
                         float key;
-                        if (p.v_smode == 1) {
-                            key = v[j] - __logf(p.v_q[(long long)m * p.N + n]);
+                        if (s_v_smode == 1) {
+                            key = v[j] - __logf(s_v_q[(long long)m * e_N + n]);
                         } else {
-                            const float u = u32_to_unit(philox_u32(p.rng, p.salt, (unsigned long long)m * p.N + n));
+                            const float u = u32_to_unit(philox_u32(e_rng, e_salt, (unsigned long long)m * e_N + n));
                             key = v[j] - __logf(-__logf(1.f - u));
                         }
                         if (key > bk) { bk = key; bi = n; bl = v[j]; }
@@ -297,198 +368,326 @@ __global__ void __launch_bounds__(192) gemm_bf16_tc_kernel(const __grid_constant
                 }
             }
         }
-        if (m < p.M) {
-            float* o = p.v_part + ((long long)m * p.tiles_n + tn) * 8;
+        if (m < e_M) {
+            float* o = s_v_part + ((long long)m * s_tiles_n + tn) * 8;
             st_f4(o, make_float4(mx, se, sv, lt));
             st_f4(o + 4, make_float4(lp, bk, __int_as_float(bi), bl));
         }
         tc_fence_before();
     }
-    if (MODE == 2 && warp >= 2) {
-        // ---- d logits from the gradients of the row statistics {lse, sum v, v[target], v[pad], v[token]}:
-        //   dv(n) = dlse * exp(v(n) - lse) + dsum + [n == target] dlt + [n == pad] dlp + [n == token] dls   -> bf16
-        float lse = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f, g4 = 0.f;
-        int trg = -1, tok = -1;
-        if (m < p.M) {
-            lse = p.v_stats[(long long)m * 5];
-            const float* g = p.v_dstat + (long long)m * 5;
-            g0 = g[0]; g1 = g[1]; g2 = g[2]; g3 = g[3]; g4 = g[4];
-            trg = (int)p.v_trg[m];
-            tok = p.v_tok ? (int)p.v_tok[m] : -1;
+    // ---- MODE 0 / 2 epilogue in two phases through shared memory.  Phase A (thread = accumulator row = TMEM lane) moves
+    // raw accumulators into a warp-private staging tile; phase B re-reads it with the lanes running ALONG a row, so that
+    // every global load (bias, gate, residual, C) and store (C32, C16) of a warp covers whole 128-byte lines.  The
+    // row-per-thread form wrote 8..16 bytes into 32 different lines per instruction and cost 4-5 us per tile (measured
+    // with bmhrl_gemm_bf16_trace: longer than the 16 k-blocks of the main loop).  The staging tile lives in the operand
+    // ring: by the time the accumulator barrier fires every TMA load has landed and every MMA has read its operands.
+    constexpr int STG_COLS = 64, STG_LD = STG_COLS + 4;          // +4 floats: conflict-free 128-bit row-strided stores
+    constexpr int STG_WARP_FLOATS = 32 * STG_LD + 32 * 8;        // + 8 floats of per-row state (MODE 2)
+    float* stg = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + (size_t)q * STG_WARP_FLOATS;
+    if ((MODE == 0 || MODE == 2) && warp >= 2) {
+        const float ks = e_drop_p > 0.f ? 1.f / (1.f - e_drop_p) : 1.f;
+        if (MODE == 2) {   // per-row statistics / gradients of the row statistics: one row per thread, read in phase B
+            float* rs = stg + 32 * STG_LD + lane * 8;
+            float lse = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f, g4 = 0.f;
+            int trg = -1, tok = -1;
+            if (m < e_M) {
+                lse = p.v_stats[(long long)m * 5];
+                const float* g = p.v_dstat + (long long)m * 5;
+                g0 = g[0]; g1 = g[1]; g2 = g[2]; g3 = g[3]; g4 = g[4];
+                trg = (int)p.v_trg[m];
+                tok = p.v_tok ? (int)p.v_tok[m] : -1;
+            }
+            rs[0] = lse; rs[1] = g0; rs[2] = g1; rs[3] = g2; rs[4] = g3; rs[5] = g4;
+            rs[6] = __int_as_float(trg); rs[7] = __int_as_float(tok);
         }
 #pragma unroll 1
-        for (int cc = 0; cc < BN; cc += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32(lane_taddr + (uint32_t)cc, r);
-            tmem_ld_wait();
-            const int nb = n0 + cc;
-            if (m < p.M && nb < p.N) {
-                __nv_bfloat16* hrow = p.C16 + (long long)m * p.ldc16 + nb;
+        for (int p0 = 0; p0 < W; p0 += STG_COLS) {
+            const int ncols = min(STG_COLS, W - p0);
+            // ---- phase A
+#pragma unroll 1
+            for (int cc = 0; cc < ncols; cc += 32) {
+                const int c0 = (int)rank * W + p0 + cc;
+                uint32_t r[32];
+                if (has_k) {
+                    tmem_ld_32x32(lane_taddr + (uint32_t)c0, r);
+                    tmem_ld_wait();
+                } else {
 #pragma unroll
-                for (int j4 = 0; j4 < 32; j4 += 4) {
-                    const int n = nb + j4;
-                    if (n >= p.N) break;
-                    float v[4];
+                    for (int i = 0; i < 32; ++i) r[i] = 0u;
+                }
+                if (threadIdx.x == 64 && p0 == 0 && cc == 0) gb_stamp(P, 11);
+                if (P.cluster > 1) {
+                    for (uint32_t src = 0; src < (uint32_t)csz; ++src) {
+                        if (src == rank) continue;
+                        const uint32_t sb = recv + (src * (uint32_t)(W / 4)) * (GB_BM * 16u);
+#pragma unroll
+                        for (int i4 = 0; i4 < 8; ++i4) {
+                            float4 tt = ld_shared_v4(sb + ((uint32_t)((p0 + cc) / 4 + i4) * GB_BM + row) * 16u);
+                            r[4 * i4] = __float_as_uint(__uint_as_float(r[4 * i4]) + tt.x);
+                            r[4 * i4 + 1] = __float_as_uint(__uint_as_float(r[4 * i4 + 1]) + tt.y);
+                            r[4 * i4 + 2] = __float_as_uint(__uint_as_float(r[4 * i4 + 2]) + tt.z);
+                            r[4 * i4 + 3] = __float_as_uint(__uint_as_float(r[4 * i4 + 3]) + tt.w);
+                        }
+                    }
+                }
+                float* srow = stg + lane * STG_LD + cc;
+#pragma unroll
+                for (int i4 = 0; i4 < 8; ++i4)
+                    *reinterpret_cast<float4*>(srow + 4 * i4) =
+                        make_float4(__uint_as_float(r[4 * i4]), __uint_as_float(r[4 * i4 + 1]), __uint_as_float(r[4 * i4 + 2]),
+                                    __uint_as_float(r[4 * i4 + 3]));
+            }
+            __syncwarp();
+            if (threadIdx.x == 64 && p0 == 0) gb_stamp(P, 12);
+            // ---- phase B: lane -> (row rr of this warp's 32, 4 consecutive columns)
+            const int sh = ncols == 64 ? 4 : 3;   // float4 per staged row: 16 or 8
+            // Fast form (every vector access legal: N % 4 == 0, aligned rows): FOUR items per trip, each optional step of
+            // the epilogue applied to all four before the next one -- the tests on the problem's options are uniform and
+            // now cost one branch per four items, and the four items are independent instruction streams.  One warp per
+            // scheduler running the per-item form below is a serial chain of ~60 dependent instructions per item
+            // (2.2 us per 128 x 64 tile, measured).
+            const bool fast = MODE == 0 && (e_N & 3) == 0 && (!e_C32 || e_vec32) && (!e_C16 || e_vec16) &&
+                              (!e_resid || e_vecr) && (!e_gate || e_vecg) && (!e_bias || aligned16(e_bias));
+            if (fast) {
+                const int cmask = (1 << sh) - 1;
+#pragma unroll 1
+                for (int it0 = 0; it0 < (1 << sh); it0 += 4) {
+                    float4 v[4];
+                    int mm[4], nn[4];
+                    bool ok[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int idx = (it0 + i) * 32 + lane;
+                        const int rr = idx >> sh, c4 = idx & cmask;
+                        mm[i] = m0 + q * 32 + rr;
+                        nn[i] = n0 + (int)rank * W + p0 + c4 * 4;
+                        ok[i] = mm[i] < e_M && nn[i] < e_N;
+                        const float4 a4 = *reinterpret_cast<const float4*>(stg + rr * STG_LD + c4 * 4);
+                        v[i] = make_float4(a4.x * e_alpha, a4.y * e_alpha, a4.z * e_alpha, a4.w * e_alpha);
+                    }
+                    if (e_bias) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[i]) {
+                                const float4 b4 = __ldg(reinterpret_cast<const float4*>(e_bias + nn[i]));
+                                v[i].x += b4.x; v[i].y += b4.y; v[i].z += b4.z; v[i].w += b4.w;
+                            }
+                    }
+                    if (e_act == 1) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            v[i].x = fmaxf(v[i].x, 0.f); v[i].y = fmaxf(v[i].y, 0.f);
+                            v[i].z = fmaxf(v[i].z, 0.f); v[i].w = fmaxf(v[i].w, 0.f);
+                        }
+                    }
+                    if (e_gate) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[i]) {
+                                const uint2 g = ld_bf16x4(e_gate + (long long)mm[i] * e_ldg + nn[i]);
+                                v[i].x = bf16_lo(g.x) > 0.f ? v[i].x * e_gate_scale : 0.f;
+                                v[i].y = bf16_hi(g.x) > 0.f ? v[i].y * e_gate_scale : 0.f;
+                                v[i].z = bf16_lo(g.y) > 0.f ? v[i].z * e_gate_scale : 0.f;
+                                v[i].w = bf16_hi(g.y) > 0.f ? v[i].w * e_gate_scale : 0.f;
+                            }
+                    }
+                    if (e_drop_p > 0.f) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[i]) {   // N % 4 == 0 and nn % 4 == 0: the 4 elements share one Philox block
+                                const unsigned long long e0 = (unsigned long long)mm[i] * e_N + nn[i];
+                                const Philox4 rb = philox_block(e_rng, e_salt, e0 >> 2);
+                                v[i].x = u32_to_unit(rb.x) >= e_drop_p ? v[i].x * ks : 0.f;
+                                v[i].y = u32_to_unit(rb.y) >= e_drop_p ? v[i].y * ks : 0.f;
+                                v[i].z = u32_to_unit(rb.z) >= e_drop_p ? v[i].z * ks : 0.f;
+                                v[i].w = u32_to_unit(rb.w) >= e_drop_p ? v[i].w * ks : 0.f;
+                            }
+                    }
+                    if (e_resid) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[i]) {
+                                const float4 tt = ld_f4(e_resid + (long long)mm[i] * e_ldr + nn[i]);
+                                v[i].x += tt.x; v[i].y += tt.y; v[i].z += tt.z; v[i].w += tt.w;
+                            }
+                    }
+                    if (e_C32) {
+                        float* crow[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            if (e_seg_rows > 0) {
+                                const int sgi = mm[i] / e_seg_rows;
+                                float* b = sgi == 0 ? e_C32 : (sgi == 1 ? e_seg1 : e_seg2);
+                                crow[i] = b + (long long)(mm[i] - sgi * e_seg_rows) * e_ldc32 + nn[i];
+                            } else {
+                                crow[i] = e_C32 + (long long)mm[i] * e_ldc32 + nn[i];
+                            }
+                        }
+                        if (e_beta != 0.f) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                if (ok[i]) {
+                                    const float4 tt = ld_f4(crow[i]);
+                                    v[i].x += e_beta * tt.x; v[i].y += e_beta * tt.y;
+                                    v[i].z += e_beta * tt.z; v[i].w += e_beta * tt.w;
+                                }
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[i]) st_f4(crow[i], v[i]);
+                    }
+                    if (e_C16) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[i])
+                                *reinterpret_cast<uint2*>(e_C16 + (long long)mm[i] * e_ldc16 + nn[i]) =
+                                    make_uint2(pack2_bf16(v[i].x, v[i].y), pack2_bf16(v[i].z, v[i].w));
+                    }
+                }
+            } else
+#pragma unroll 1
+            for (int idx = lane; idx < (32 << sh); idx += 32) {
+                const int rr = idx >> sh, c4 = idx - (rr << sh);
+                const int mm = m0 + q * 32 + rr;
+                const int n = n0 + (int)rank * W + p0 + c4 * 4;
+                if (mm >= e_M || n >= e_N) continue;
+                const bool full = n + 3 < e_N;
+                const float4 a4 = *reinterpret_cast<const float4*>(stg + rr * STG_LD + c4 * 4);
+                float v[4] = {a4.x, a4.y, a4.z, a4.w};
+                if (MODE == 2) {
+                    // d logits from the gradients of the row statistics {lse, sum v, v[target], v[pad], v[token]}:
+                    //   dv(n) = dlse * exp(v(n) - lse) + dsum + [n == target] dlt + [n == pad] dlp + [n == token] dls
+                    const float* rs = stg + 32 * STG_LD + rr * 8;
+                    const float lse = rs[0], g0 = rs[1], g1 = rs[2], g2 = rs[3], g3 = rs[4], g4 = rs[5];
+                    const int trg = __float_as_int(rs[6]), tok = __float_as_int(rs[7]);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int nn = n + j;
-                        const float lg = __uint_as_float(r[j4 + j]) + ((p.bias && nn < p.N) ? p.bias[nn] : 0.f);
+                        const float lg = v[j] + ((e_bias && nn < e_N) ? e_bias[nn] : 0.f);
                         float d = g0 * __expf(lg - lse) + g1;
                         if (nn == trg) d += g2;
-                        if (nn == p.v_pad) d += g3;
+                        if (nn == e_v_pad) d += g3;
                         if (nn == tok) d += g4;
                         v[j] = d;
                     }
-                    if (n + 3 < p.N && p.vec16) {
-                        *reinterpret_cast<uint2*>(hrow + j4) = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
+                    __nv_bfloat16* hrow = e_C16 + (long long)mm * e_ldc16 + n;
+                    if (full && e_vec16) {
+                        *reinterpret_cast<uint2*>(hrow) = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
                     } else {
 #pragma unroll
                         for (int j = 0; j < 4; ++j)
-                            if (n + j < p.N) hrow[j4 + j] = __float2bfloat16(v[j]);
+                            if (n + j < e_N) hrow[j] = __float2bfloat16(v[j]);
                     }
+                    continue;
                 }
-            }
-        }
-        tc_fence_before();
-    }
-    if (MODE == 0 && warp >= 2) {
-        const float ks = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
-        // destination row of the fp32 output (optionally one of up to three row segments)
-        float* c32row = nullptr;
-        if (p.C32 && m < p.M) {
-            if (p.seg_rows > 0) {
-                const int sgi = m / p.seg_rows;
-                float* b = sgi == 0 ? p.C32 : (sgi == 1 ? p.seg1 : p.seg2);
-                c32row = b + (long long)(m - sgi * p.seg_rows) * p.ldc32;
-            } else {
-                c32row = p.C32 + (long long)m * p.ldc32;
-            }
-        }
-#pragma unroll 1
-        for (int cc = 0; cc < W; cc += 32) {
-            const int c0 = (int)rank * W + cc;
-            uint32_t r[32];
-            if (has_k) {
-                tmem_ld_32x32(lane_taddr + (uint32_t)c0, r);
-                tmem_ld_wait();
-            } else {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) r[i] = 0u;
-            }
-            if (P.cluster > 1) {
-                for (uint32_t src = 0; src < (uint32_t)csz; ++src) {
-                    if (src == rank) continue;
-                    const uint32_t sb = recv + (src * (uint32_t)(W / 4)) * (GB_BM * 16u);
-#pragma unroll
-                    for (int i4 = 0; i4 < 8; ++i4) {
-                        float4 tt = ld_shared_v4(sb + ((uint32_t)(cc / 4 + i4) * GB_BM + row) * 16u);
-                        r[4 * i4] = __float_as_uint(__uint_as_float(r[4 * i4]) + tt.x);
-                        r[4 * i4 + 1] = __float_as_uint(__uint_as_float(r[4 * i4 + 1]) + tt.y);
-                        r[4 * i4 + 2] = __float_as_uint(__uint_as_float(r[4 * i4 + 2]) + tt.z);
-                        r[4 * i4 + 3] = __float_as_uint(__uint_as_float(r[4 * i4 + 3]) + tt.w);
-                    }
-                }
-            }
-            const int nb = n0 + c0;
-            if (m < p.M && nb < p.N) {
-                const float* rrow = p.resid ? p.resid + (long long)m * p.ldr + nb : nullptr;
-                const __nv_bfloat16* grow = p.gate ? p.gate + (long long)m * p.ldg + nb : nullptr;
-                float* crow = c32row ? c32row + nb : nullptr;
-                __nv_bfloat16* hrow = p.C16 ? p.C16 + (long long)m * p.ldc16 + nb : nullptr;
-#pragma unroll
-                for (int j4 = 0; j4 < 32; j4 += 4) {
-                    const int n = nb + j4;
-                    if (n >= p.N) break;
-                    const bool full = n + 3 < p.N;
-                    float v[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) v[j] = p.alpha * __uint_as_float(r[j4 + j]);
-                    if (p.bias) {
+                for (int j = 0; j < 4; ++j) v[j] *= e_alpha;
+                if (e_bias) {
+                    if (full && aligned16(e_bias + n)) {
+                        const float4 b4 = __ldg(reinterpret_cast<const float4*>(e_bias + n));
+                        v[0] += b4.x; v[1] += b4.y; v[2] += b4.z; v[3] += b4.w;
+                    } else {
 #pragma unroll
                         for (int j = 0; j < 4; ++j)
-                            if (n + j < p.N) v[j] += p.bias[n + j];
+                            if (n + j < e_N) v[j] += e_bias[n + j];
                     }
-                    if (p.act == 1) {
+                }
+                if (e_act == 1) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) v[j] = fmaxf(v[j], 0.f);
+                    for (int j = 0; j < 4; ++j) v[j] = fmaxf(v[j], 0.f);
+                }
+                if (e_gate) {
+                    const __nv_bfloat16* grow = e_gate + (long long)mm * e_ldg + n;
+                    if (full && e_vecg) {
+                        const uint2 g = ld_bf16x4(grow);
+                        v[0] = bf16_lo(g.x) > 0.f ? v[0] * e_gate_scale : 0.f;
+                        v[1] = bf16_hi(g.x) > 0.f ? v[1] * e_gate_scale : 0.f;
+                        v[2] = bf16_lo(g.y) > 0.f ? v[2] * e_gate_scale : 0.f;
+                        v[3] = bf16_hi(g.y) > 0.f ? v[3] * e_gate_scale : 0.f;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < e_N) v[j] = __bfloat162float(grow[j]) > 0.f ? v[j] * e_gate_scale : 0.f;
                     }
-                    if (grow) {
-                        if (full && p.vecg) {
-                            const uint2 g = ld_bf16x4(grow + j4);
-                            v[0] = bf16_lo(g.x) > 0.f ? v[0] * p.gate_scale : 0.f;
-                            v[1] = bf16_hi(g.x) > 0.f ? v[1] * p.gate_scale : 0.f;
-                            v[2] = bf16_lo(g.y) > 0.f ? v[2] * p.gate_scale : 0.f;
-                            v[3] = bf16_hi(g.y) > 0.f ? v[3] * p.gate_scale : 0.f;
-                        } else {
+                }
+                if (e_drop_p > 0.f) {
+                    const unsigned long long e0 = (unsigned long long)mm * e_N + n;
+                    if ((e0 & 3ull) == 0) {  // the 4 elements share one Philox block
+                        const Philox4 rb = philox_block(e_rng, e_salt, e0 >> 2);
+                        v[0] = u32_to_unit(rb.x) >= e_drop_p ? v[0] * ks : 0.f;
+                        v[1] = u32_to_unit(rb.y) >= e_drop_p ? v[1] * ks : 0.f;
+                        v[2] = u32_to_unit(rb.z) >= e_drop_p ? v[2] * ks : 0.f;
+                        v[3] = u32_to_unit(rb.w) >= e_drop_p ? v[3] * ks : 0.f;
+                    } else {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (n + j < p.N)
-                                    v[j] = __bfloat162float(grow[j4 + j]) > 0.f ? v[j] * p.gate_scale : 0.f;
+                        for (int j = 0; j < 4; ++j)
+                            v[j] = u32_to_unit(philox_u32(e_rng, e_salt, e0 + j)) >= e_drop_p ? v[j] * ks : 0.f;
+                    }
+                }
+                if (e_resid) {
+                    const float* rrow = e_resid + (long long)mm * e_ldr + n;
+                    if (full && e_vecr) {
+                        const float4 tt = ld_f4(rrow);
+                        v[0] += tt.x; v[1] += tt.y; v[2] += tt.z; v[3] += tt.w;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < e_N) v[j] += rrow[j];
+                    }
+                }
+                if (e_C32) {
+                    // destination row of the fp32 output (optionally one of up to three row segments)
+                    float* crow;
+                    if (e_seg_rows > 0) {
+                        const int sgi = mm / e_seg_rows;
+                        float* b = sgi == 0 ? e_C32 : (sgi == 1 ? e_seg1 : e_seg2);
+                        crow = b + (long long)(mm - sgi * e_seg_rows) * e_ldc32 + n;
+                    } else {
+                        crow = e_C32 + (long long)mm * e_ldc32 + n;
+                    }
+                    if (full && e_vec32) {
+                        if (e_beta != 0.f) {
+                            const float4 tt = ld_f4(crow);
+                            v[0] += e_beta * tt.x; v[1] += e_beta * tt.y; v[2] += e_beta * tt.z; v[3] += e_beta * tt.w;
                         }
-                    }
-                    if (p.drop_p > 0.f) {
-                        const unsigned long long e0 = (unsigned long long)m * p.N + n;
-                        if ((e0 & 3ull) == 0) {  // the 4 elements share one Philox block
-                            const Philox4 rb = philox_block(p.rng, p.salt, e0 >> 2);
-                            v[0] = u32_to_unit(rb.x) >= p.drop_p ? v[0] * ks : 0.f;
-                            v[1] = u32_to_unit(rb.y) >= p.drop_p ? v[1] * ks : 0.f;
-                            v[2] = u32_to_unit(rb.z) >= p.drop_p ? v[2] * ks : 0.f;
-                            v[3] = u32_to_unit(rb.w) >= p.drop_p ? v[3] * ks : 0.f;
-                        } else {
+                        st_f4(crow, make_float4(v[0], v[1], v[2], v[3]));
+                    } else {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                v[j] = u32_to_unit(philox_u32(p.rng, p.salt, e0 + j)) >= p.drop_p ? v[j] * ks : 0.f;
-                        }
-                    }
-                    if (rrow) {
-                        if (full && p.vecr) {
-                            const float4 tt = ld_f4(rrow + j4);
-                            v[0] += tt.x; v[1] += tt.y; v[2] += tt.z; v[3] += tt.w;
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (n + j < p.N) v[j] += rrow[j4 + j];
-                        }
-                    }
-                    if (crow) {
-                        if (full && p.vec32) {
-                            if (p.beta != 0.f) {
-                                const float4 tt = ld_f4(crow + j4);
-                                v[0] += p.beta * tt.x; v[1] += p.beta * tt.y; v[2] += p.beta * tt.z; v[3] += p.beta * tt.w;
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < e_N) {
+                                if (e_beta != 0.f) v[j] += e_beta * crow[j];
+                                crow[j] = v[j];
                             }
-                            st_f4(crow + j4, make_float4(v[0], v[1], v[2], v[3]));
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (n + j < p.N) {
-                                    if (p.beta != 0.f) v[j] += p.beta * crow[j4 + j];
-                                    crow[j4 + j] = v[j];
-                                }
-                        }
                     }
-                    if (hrow) {
-                        if (full && p.vec16) {
-                            *reinterpret_cast<uint2*>(hrow + j4) = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
-                        } else {
+                }
+                if (e_C16) {
+                    __nv_bfloat16* hrow = e_C16 + (long long)mm * e_ldc16 + n;
+                    if (full && e_vec16) {
+                        *reinterpret_cast<uint2*>(hrow) = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
+                    } else {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (n + j < p.N) hrow[j4 + j] = __float2bfloat16(v[j]);
-                        }
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < e_N) hrow[j] = __float2bfloat16(v[j]);
                     }
                 }
             }
+            __syncwarp();   // the next pass overwrites the staging tile
+            if (threadIdx.x == 64 && p0 == 0) gb_stamp(P, 13);
         }
         tc_fence_before();
+        if (threadIdx.x == 64) gb_stamp(P, 7);
     }
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
+    if (threadIdx.x == 32) { gb_stamp(P, 8); gb_stamp_ns(P, 10); }
 }
 
 // ---------------------------------------------------------------------------------------------- host side
 static int g_gb_force_bn = 0, g_gb_force_split = 0, g_gb_force_stages = 0;
+static unsigned long long* g_gb_trace = nullptr;
 
 template <int BN, int MODE = 0>
 static int launch_gb(const GbParams& P, int total_tiles, int split, cudaStream_t st) {
@@ -554,6 +753,11 @@ extern "C" int bmhrl_gemm_bf16_tuning(int force_bn, int force_split, int force_s
     return BMHRL_OK;
 }
 
+extern "C" int bmhrl_gemm_bf16_trace(unsigned long long* device_slots) {
+    g_gb_trace = device_slots;
+    return BMHRL_OK;
+}
+
 extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stream) {
     BMHRL_CHECK_ARG(d && n >= 1 && n <= GB_MAXP, "bmhrl_gemm_bf16_group: 1..4 problems per launch");
     if (get_encode_fn() == nullptr) {
@@ -612,6 +816,7 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
     P.n = n;
     P.cluster = split;
     P.nstages = nstages;
+    P.trace = g_gb_trace;
     int tile_start = 0;
     const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     for (int i = 0; i < n; ++i) {
@@ -708,7 +913,7 @@ static int vocab_problem(GbParams& P, const void* x16, long long ldx, const void
         bmhrl_set_error("vocab: cuTensorMapEncodeTiled unavailable");
         return BMHRL_ERR_CUDA;
     }
-    P.n = 1; P.cluster = 1;
+    P.n = 1; P.cluster = 1; P.trace = nullptr;
     const int num_kb = (K + GB_BK - 1) / GB_BK;
     P.nstages = num_kb < 4 ? (num_kb < 2 ? 2 : num_kb) : 4;
     GbProblem& q = P.p[0];

@@ -256,6 +256,186 @@ __global__ void __launch_bounds__(512) rnn_layer_persistent_kernel(const float* 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Exchange variant of the persistent layer: no grid barrier.  A time step of the barrier kernel above is a chain of
+// L2 round trips (atomic arrive, poll, then the h broadcast) -- ~9 us at B = 16, H = 600.  Here every h value travels
+// as ONE 64-bit word {fp32 bits, tag = t + 1} (single-copy atomic, so the tag vouches for the value next to it): the
+// producer stores it, the consumers poll the words themselves; data and "ready" arrive in the same round trip and a slow
+// CTA only delays the words it owes.  X is double-buffered by step parity (a CTA can only produce step t + 1 after it
+// has consumed ALL of step t - 1 ... so nobody still reads the buffer that step t + 1 overwrites) and zeroed by the
+// host side before the launch (tags start at 1).  The grid is still launched cooperatively: consumers spin on words
+// owed by other CTAs, so all of them must be resident.
+// A warp owns one hidden unit x RNN2_RB batch rows (2 warps per unit instead of 1: half the serial FMA chain); the
+// per-lane partial sums run over k = lane, lane + 32, ... exactly like rnn_step_kernel, and the 32 (gate, row) totals of
+// a warp are reduced by a TRANSPOSED butterfly -- same pairs, same order (xor 16, 8, 4, 2, 1) as warp_sum, so the
+// results are bit-identical to the other two variants, with 31 shuffles instead of 160.
+constexpr int RNN2_RB = 8;
+constexpr int RNN2_NGRP = RNN_BT / RNN2_RB;
+
+__device__ __forceinline__ void st_tagged(unsigned long long* p, float v, unsigned tag) {
+    const unsigned long long w = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ void ld_tagged2(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
+    // .cg: served by L2 (the point of coherence), never by this SM's L1 -- and, measured, several times the throughput of
+    // ld.relaxed.gpu for a 77 KB tile (each 64-bit word is still read whole: value and tag cannot be torn apart)
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+
+// hs[bb][k] = value part of X[b0 + bb][k] once its tag equals `tag`, rows bb < nb (H even: two words per 128-bit load;
+// one load per row in flight per thread, all rows at once)
+__device__ __forceinline__ void load_h_tagged(float* hs, const unsigned long long* X, int b0, int nb, int H, unsigned tag) {
+    const int H2 = H >> 1;
+    for (int k2 = threadIdx.x; k2 < H2; k2 += blockDim.x) {
+        unsigned long long qa[RNN_BT], qb[RNN_BT];
+        unsigned pending = nb >= RNN_BT ? 0xffffu : ((1u << nb) - 1u);
+        unsigned spins = 0;
+        while (pending) {
+#pragma unroll
+            for (int bb = 0; bb < RNN_BT; ++bb)
+                if (pending >> bb & 1u) ld_tagged2(X + (long long)(b0 + bb) * H + 2 * k2, qa[bb], qb[bb]);
+#pragma unroll
+            for (int bb = 0; bb < RNN_BT; ++bb)
+                if ((pending >> bb & 1u) && (unsigned)(qa[bb] >> 32) == tag && (unsigned)(qb[bb] >> 32) == tag) {
+                    *reinterpret_cast<float2*>(hs + bb * H + 2 * k2) =
+                        make_float2(__uint_as_float((unsigned)qa[bb]), __uint_as_float((unsigned)qb[bb]));
+                    pending &= ~(1u << bb);
+                }
+            if (pending && ++spins > (1u << 24)) __trap();  // a scheduling bug must fault, never hang the GPU
+        }
+    }
+}
+
+constexpr int RNN2_KI = 19;        // k-slots per lane: the W_hh row of a (unit, gate) lives in registers, H <= 32 * 19 = 608
+constexpr int RNN2_MAXT = 320;     // 5 units x 2 row groups x 32 lanes
+
+template <int NG>
+__global__ void __launch_bounds__(RNN2_MAXT) rnn_layer_exchange_kernel(const float* __restrict__ gx,    // (B,L,NG*H)
+                                                                 const float* __restrict__ W_hh,  // (NG*H,H)
+                                                                 const float* __restrict__ b_hh,  // (NG*H)
+                                                                 float* out,                      // (B,L,H)
+                                                                 float* c,                        // (B,H) LSTM
+                                                                 unsigned long long* X,           // (2,B,H) tagged h
+                                                                 int B, int L, int H, int upb,
+                                                                 unsigned long long* trace) {
+    extern __shared__ float smem[];
+    float* hs = smem;                                 // [2][RNN_BT][H]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int u = warp / RNN2_NGRP, grp = warp - u * RNN2_NGRP;
+    const int j = blockIdx.x * upb + u;
+    const bool unit_ok = u < upb && j < H;
+    // the NG rows of W_hh of this warp's unit stay in REGISTERS for all L steps, lane l holding k = l, l + 32, ...: the
+    // dot products then read only h from shared memory (with W there too the loop was bound by LDS bandwidth: 12 loads
+    // per 32 FMAs)
+    float wreg[NG][RNN2_KI];
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+        for (int i = 0; i < RNN2_KI; ++i) {
+            const int k = lane + 32 * i;
+            wreg[g][i] = (unit_ok && k < H) ? __ldg(W_hh + ((long long)g * H + j) * H + k) : 0.f;
+        }
+    for (int i = threadIdx.x; i < 2 * RNN_BT * H; i += blockDim.x) hs[i] = 0.f;
+    float bh[NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) bh[g] = unit_ok ? b_hh[g * H + j] : 0.f;
+    const int r_mine = grp * RNN2_RB + (lane & (RNN2_RB - 1));   // the row whose gates this lane finishes (lanes < RNN2_RB)
+    __syncthreads();
+    for (int t = 0; t < L; ++t) {
+        float* hcur = hs + (size_t)(t & 1) * RNN_BT * H;   // h_{t-1} of the current row group
+        const unsigned long long* Xprev = X + (size_t)((t + 1) & 1) * B * H;
+        unsigned long long* Xnext = X + (size_t)(t & 1) * B * H;
+        for (int b0 = 0; b0 < B; b0 += RNN_BT) {
+            const int nb = min(RNN_BT, B - b0);
+            const bool mine_ok = unit_ok && lane < RNN2_RB && r_mine < nb;
+            const int b = b0 + r_mine;
+            // this step's input contributions and cell state do not depend on h: request them before polling for h
+            float gxv[NG], cprev = 0.f;
+#pragma unroll
+            for (int g = 0; g < NG; ++g)
+                gxv[g] = mine_ok ? __ldg(gx + ((long long)b * L + t) * (NG * H) + g * H + j) : 0.f;
+            if (NG == 4 && mine_ok && t > 0) cprev = c[(long long)b * H + j];
+            const bool stamp = trace && blockIdx.x == 0 && threadIdx.x == 0 && t < 60 && b0 == 0;
+            if (stamp) trace[t * 8 + 0] = clock64();
+            if (t > 0) {
+                // a hint, not a guard: thread i watches ONE word of producer CTA i (its last unit, the last row of the
+                // group) so that the CTA polls ~1 KB per round trip instead of hammering L2 with the whole h tile; the
+                // tags checked by load_h_tagged are what makes the values safe to use
+                for (int pc = threadIdx.x; pc < (int)gridDim.x; pc += blockDim.x) {
+                    const unsigned long long* w = Xprev + (long long)(b0 + nb - 1) * H + min(pc * upb + upb - 1, H - 1);
+                    unsigned long long q;
+                    unsigned spins = 0;
+                    do {
+                        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(q) : "l"(w) : "memory");
+                        if (++spins > (1u << 24)) __trap();
+                    } while ((unsigned)(q >> 32) != (unsigned)t);
+                }
+                __syncthreads();
+                if (stamp) trace[t * 8 + 1] = clock64();
+                load_h_tagged(hcur, Xprev, b0, nb, H, (unsigned)t);
+            }
+            if (stamp) trace[t * 8 + 2] = clock64();
+            __syncthreads();
+            if (stamp) trace[t * 8 + 3] = clock64();
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            if (t > 0 && unit_ok) {
+                const float* hg = hcur + (size_t)grp * RNN2_RB * H;
+#pragma unroll
+                for (int i = 0; i < RNN2_KI; ++i) {
+                    const int k = lane + 32 * i;
+                    if (k < H) {
+#pragma unroll
+                        for (int r = 0; r < RNN2_RB; ++r) {
+                            const float hv = hg[r * H + k];
+#pragma unroll
+                            for (int g = 0; g < NG; ++g) v[g * RNN2_RB + r] = fmaf(wreg[g][i], hv, v[g * RNN2_RB + r]);
+                        }
+                    }
+                }
+            }
+            if (stamp) trace[t * 8 + 4] = clock64();
+            // transposed butterfly: afterwards lane l holds the warp-wide total of value l = gate * RNN2_RB + row
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const bool up = (lane & o) != 0;
+#pragma unroll
+                for (int i = 0; i < o; ++i) {
+                    const float keep = up ? v[i + o] : v[i];
+                    const float send = up ? v[i] : v[i + o];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+                }
+            }
+            float mine[NG];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) mine[g] = __shfl_sync(0xffffffffu, v[0], g * RNN2_RB + (lane & (RNN2_RB - 1)));
+            if (mine_ok) {
+                const float hprev = t > 0 ? hcur[r_mine * H + j] : 0.f;
+                float hnew;
+                if (NG == 4) {
+                    float pi = gxv[0] + bh[0] + mine[0];
+                    float pf = gxv[1] + bh[1] + mine[1];
+                    float pg = gxv[2] + bh[2] + mine[2];
+                    float po = gxv[NG - 1] + bh[NG - 1] + mine[NG - 1];
+                    float cn = sigmoid_exact(pf) * cprev + sigmoid_exact(pi) * tanhf(pg);
+                    c[(long long)b * H + j] = cn;
+                    hnew = sigmoid_exact(po) * tanhf(cn);
+                } else {
+                    float r = sigmoid_exact(gxv[0] + mine[0] + bh[0]);
+                    float z = sigmoid_exact(gxv[1] + mine[1] + bh[1]);
+                    float n = tanhf(gxv[2] + r * (mine[2] + bh[2]));
+                    hnew = (1.f - z) * n + z * hprev;
+                }
+                if (t + 1 < L) st_tagged(Xnext + (long long)b * H + j, hnew, (unsigned)(t + 1));
+                out[((long long)b * L + t) * H + j] = hnew;
+            }
+            if (stamp) trace[t * 8 + 5] = clock64();
+            if (B > RNN_BT) __syncthreads();   // several row groups share the h tile of this step
+        }
+    }
+}
+
 // AReLU (model/bm_hrl_agent.py:13-23): relu(x) * (1 + sigmoid(beta)) - relu(-x) * clamp(alpha, 0.01, 0.99)
 __global__ void arelu_kernel(const float* __restrict__ x, const float* __restrict__ alpha_p,
                              const float* __restrict__ beta_p, float* __restrict__ y, long long n) {
@@ -526,6 +706,7 @@ extern "C" int bmhrl_critic_wavefront_f32(const float* emb, int E, const float* 
 }
 
 static int g_rnn_persistent = 1;
+static int g_rnn_min_upb = 0;   // bmhrl_rnn_set_units_per_cta
 
 // Returns BMHRL_OK / error, or 1 when the shape cannot run as one co-resident grid.
 template <int NG>
@@ -546,7 +727,8 @@ static int launch_rnn_persistent_t(const float* gx, const float* W_hh, const flo
     // BMHRL_RNN_UPB: at least that many hidden units per CTA -> fewer, fatter CTAs (a step is a latency chain, not
     // arithmetic: the layer then leaves the other SMs to the kernels that run beside the frozen critic)
     static const int env_upb = getenv("BMHRL_RNN_UPB") ? atoi(getenv("BMHRL_RNN_UPB")) : 0;
-    if (env_upb > upb) upb = env_upb;
+    const int want_upb = env_upb > 0 ? env_upb : g_rnn_min_upb;
+    if (want_upb > upb) upb = want_upb > 16 ? 16 : want_upb;
     for (; upb <= 16; ++upb) {
         const size_t smem = sizeof(float) * ((size_t)upb * NG * H + (size_t)RNN_BT * H);
         if (smem > 220 * 1024) return 1;
@@ -579,13 +761,87 @@ static int launch_rnn_persistent_t(const float* gx, const float* W_hh, const flo
     return 1;
 }
 
+// offset (in floats) of the tagged exchange buffer inside the workspace: behind the cell state and the barrier words
+static inline long long rnn_ws_x_offset(int B, int H) { return (((long long)B * H + 32) + 3) & ~3LL; }
+static unsigned long long* g_rnn_trace = nullptr;   // diagnosis: bmhrl_rnn_trace
+static int g_rnn_exchange = -1;   // -1: environment BMHRL_RNN_EXCHANGE (default on), 0 / 1: forced by bmhrl_rnn_set_exchange
+
+// Returns BMHRL_OK / error, or 1 when the shape cannot run as one co-resident grid of the exchange kernel.
+template <int NG>
+static int launch_rnn_exchange_t(const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B, int L,
+                                 int H, cudaStream_t st) {
+    if ((H & 1) || H > 32 * RNN2_KI || !aligned16(ws)) return 1;
+    const int n_sm = device_sm_count();
+    static DeviceOnce attr;
+    if (needs_setup(attr)) {
+        if (cudaFuncSetAttribute(rnn_layer_exchange_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024) !=
+            cudaSuccess) {
+            bmhrl_set_error("rnn exchange: cannot raise the shared-memory limit");
+            return BMHRL_ERR_CUDA;
+        }
+        mark_done(attr);
+    }
+    int upb = (H + n_sm - 1) / n_sm;
+    static const int env_upb = getenv("BMHRL_RNN_UPB") ? atoi(getenv("BMHRL_RNN_UPB")) : 0;
+    if (env_upb > upb) upb = env_upb;
+    for (; upb * RNN2_NGRP * 32 <= RNN2_MAXT; ++upb) {
+        const size_t smem = sizeof(float) * (2 * (size_t)RNN_BT * H);
+        if (smem > 220 * 1024) return 1;
+        const int threads = upb * RNN2_NGRP * 32 < 128 ? 128 : upb * RNN2_NGRP * 32;
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rnn_layer_exchange_kernel<NG>, threads, smem) !=
+            cudaSuccess) {
+            bmhrl_set_error("rnn exchange: occupancy query failed");
+            return BMHRL_ERR_CUDA;
+        }
+        const int grid = (H + upb - 1) / upb;
+        if (per_sm * n_sm < grid) continue;
+        float* c = ws;
+        unsigned long long* X = reinterpret_cast<unsigned long long*>(ws + rnn_ws_x_offset(B, H));
+        if (cudaMemsetAsync(X, 0, sizeof(unsigned long long) * 2 * (size_t)B * H, st) != cudaSuccess) {
+            bmhrl_set_error("rnn exchange: memset failed");
+            return BMHRL_ERR_CUDA;
+        }
+        unsigned long long* trace = g_rnn_trace;
+        void* args[] = {(void*)&gx, (void*)&W_hh, (void*)&b_hh, (void*)&out, (void*)&c, (void*)&X,
+                        (void*)&B,  (void*)&L,    (void*)&H,    (void*)&upb, (void*)&trace};
+        cudaError_t e = cudaLaunchCooperativeKernel((const void*)rnn_layer_exchange_kernel<NG>, dim3(grid), dim3(threads),
+                                                    args, smem, st);
+        if (e != cudaSuccess) {
+            bmhrl_set_error(cudaGetErrorString(e));
+            return BMHRL_ERR_CUDA;
+        }
+        bmhrl_count_launch(1);
+        return BMHRL_OK;
+    }
+    return 1;
+}
+
 static int launch_rnn_persistent(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws,
                                  int B, int L, int H, cudaStream_t st) {
+    static const int env_x = getenv("BMHRL_RNN_EXCHANGE") ? atoi(getenv("BMHRL_RNN_EXCHANGE")) : 0;
+    if (g_rnn_exchange < 0 ? env_x != 0 : g_rnn_exchange != 0) {
+        const int rc = cell == 0 ? launch_rnn_exchange_t<4>(gx, W_hh, b_hh, out, ws, B, L, H, st)
+                                 : launch_rnn_exchange_t<3>(gx, W_hh, b_hh, out, ws, B, L, H, st);
+        if (rc != 1) return rc;   // 1: not this shape -> the barrier kernel
+    }
     return cell == 0 ? launch_rnn_persistent_t<4>(gx, W_hh, b_hh, out, ws, B, L, H, st)
                      : launch_rnn_persistent_t<3>(gx, W_hh, b_hh, out, ws, B, L, H, st);
 }
 
-extern "C" long long bmhrl_rnn_ws_floats(int B, int H) { return (long long)B * H + 32; }
+extern "C" long long bmhrl_rnn_ws_floats(int B, int H) { return rnn_ws_x_offset(B, H) + 4LL * B * H; }
+extern "C" int bmhrl_rnn_set_units_per_cta(int units) {
+    g_rnn_min_upb = units > 0 ? units : 0;
+    return BMHRL_OK;
+}
+extern "C" int bmhrl_rnn_trace(unsigned long long* device_slots) {
+    g_rnn_trace = device_slots;
+    return BMHRL_OK;
+}
+extern "C" int bmhrl_rnn_set_exchange(int mode) {
+    g_rnn_exchange = mode < 0 ? -1 : (mode ? 1 : 0);
+    return BMHRL_OK;
+}
 extern "C" int bmhrl_rnn_set_persistent(int on) {
     g_rnn_persistent = on ? 1 : 0;
     return BMHRL_OK;

@@ -12,6 +12,8 @@ loss like the reference does; that variant has a host round trip and is not grap
 Every step can be captured into ONE CUDA graph (`StepRunner.capture`): the library's entry points never
 synchronise or allocate, dropout/sampling counters and Adam step counts advance on the device.  No CPU fallback.
 """
+import os
+
 import torch
 
 from . import ops, ops16
@@ -173,7 +175,6 @@ class BMHRLTrainer:
         stream, behind everything enqueued so far on this stream and on the side streams."""
         if not self.overlap_grad_sync or stage in self._fired or stage >= len(self._stages):
             return
-        import os
         if not (int(os.environ.get("BMHRL_EARLY_STAGES", "255")) >> stage) & 1:   # experiment switch
             return
         if not any(self.cap_opt.params[i].requires_grad for i in self._stages[stage]):
@@ -395,6 +396,7 @@ class StepRunner:
         self.graph = None
         self.out = None
         self.pipeline_critic = bool(pipeline_critic) and hasattr(trainer.cap_model, "segment_labels_of")
+        self.critic_units_per_cta = int(os.environ.get("BMHRL_CRITIC_UPB", "16"))
         if self.pipeline_critic:
             self.static["caption_next"] = self.static["caption"].clone()
             with torch.no_grad():
@@ -440,7 +442,8 @@ class StepRunner:
         cur = torch.cuda.current_stream(dev)
         side = ops.side_stream(dev, 12)
         side.wait_stream(cur)
-        with torch.cuda.stream(side), torch.no_grad():   # the NEXT batch's corruption + critic, beside this step
+        with torch.cuda.stream(side), torch.no_grad(), ops.rnn_units_per_cta(self.critic_units_per_cta):
+            # the NEXT batch's corruption + critic, beside this step, confined to a quarter of the SMs
             nxt = self._corrupt(self.static["caption_next"])
             self.cap_in_next.copy_(nxt)
             self.labels_next.copy_(t.cap_model.segment_labels_of(self.cap_in_next))

@@ -125,6 +125,9 @@ int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* problems, int n_problems, void*
 /* tuning / test hook: force the tile width (0 = cost model, 64, 128), the K split (0 = cost model, 1, 2, 4) and the
  * pipeline depth (0 = auto, 2..6). */
 int bmhrl_gemm_bf16_tuning(int force_bn, int force_split, int force_stages);
+/* diagnosis hook: with a device buffer of 64 slots set, CTA 0 of every following bmhrl_gemm_bf16_group launch stamps
+ * clock64() at its hand-over points (slot map: csrc/gemm_bf16.cu, gb_stamp); NULL switches it off (the default). */
+int bmhrl_gemm_bf16_trace(unsigned long long* device_slots);
 
 /* ---- K2: residual + LayerNorm, gated mix (norm.cu) ---------------------------------------------------------- */
 /* z = x (+ resid); y = LayerNorm(z) (eps, affine).  z_out may be NULL.  ResidualConnection model/blocks.py:135-144,
@@ -296,11 +299,21 @@ int bmhrl_reinforce_gather_bwd_f32(const float* probs, const long long* action, 
 /* ---- frozen SegmentCritic recurrences, forward only (rnn.cu) ------------------------------------------------- */
 /* One nn.LSTM (cell 0, gates i,f,g,o) or nn.GRU (cell 1, gates r,z,n) layer, batch_first, zero initial state
  * (model/bm_hrl_agent.py:192-193,206,209).  gx (B,L,NG*H) = x W_ih^T + b_ih for all steps (bmhrl_linear_fwd_f32);
- * out (B,L,H); ws: bmhrl_rnn_ws_floats(B,H) floats (cell state + the grid-barrier counter).  One cooperative launch
- * per layer: W_hh stays resident in shared memory across all L steps (falls back to one launch per step when the
- * layer does not fit one co-resident grid, or after bmhrl_rnn_set_persistent(0); both give identical bits). */
+ * out (B,L,H); ws: bmhrl_rnn_ws_floats(B,H) floats, 16-byte aligned (cell state, the grid-barrier counter and the
+ * tagged h exchange buffer).  One cooperative launch per layer: W_hh stays resident in shared memory across all L
+ * steps, one grid barrier per step (or, after bmhrl_rnn_set_exchange(1) and for even H <= 608: h_t travels between
+ * the CTAs as 64-bit {value, step tag} words that the consumers poll, no barrier).  Falls back to one launch per step
+ * when the layer does not fit one co-resident grid, or after bmhrl_rnn_set_persistent(0).  All variants give identical
+ * bits.  bmhrl_rnn_set_units_per_cta(n): at least n hidden units per CTA (0 = as few as fill the GPU): a layer that
+ * runs BESIDE other work (the frozen critic of the next batch under the current step) is a latency chain, and
+ * n = 16 confines it to H / 16 SMs at nearly the same duration. */
 long long bmhrl_rnn_ws_floats(int B, int H);
 int bmhrl_rnn_set_persistent(int on);
+int bmhrl_rnn_set_units_per_cta(int units);
+int bmhrl_rnn_set_exchange(int mode);   /* 1 / 0: force the exchange / the barrier kernel; -1: BMHRL_RNN_EXCHANGE (default 0) */
+/* diagnosis hook: CTA 0 of the exchange kernel stamps clock64() per time step into 8 slots per step (step start, hint
+ * seen, h tile loaded, barrier passed, dot products done, gates stored; 60 steps -> 480 slots); NULL = off (default). */
+int bmhrl_rnn_trace(unsigned long long* device_slots);
 int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B,
                         int L, int H, void* stream);
 /* ONE time step t of the same layer on caller-kept buffers laid out for L steps: reads h_{t-1} from out[:, t-1, :] and

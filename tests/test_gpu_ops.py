@@ -424,6 +424,43 @@ def test_errors_are_loud(gpu_lib):
         ops.layer_norm(torch.randn(4, 8, device="cuda").double(), torch.ones(8, device="cuda"), torch.zeros(8, device="cuda"))
 
 
+@pytest.mark.parametrize("cell", ["lstm", "gru"])
+def test_rnn_layer_variants_bit_identical(gpu_lib, cell):
+    """The three forms of one recurrent layer -- tagged-exchange persistent kernel (default), grid-barrier persistent
+    kernel, one launch per step -- give the same bits; repeated launches on a recycled workspace (stale tags of the
+    previous call in the exchange buffer) included, and batches of more than one 16-row group."""
+    from bmhrl_b200 import ops
+    from bmhrl_b200._lib import LIB
+    g = _g(77)
+    NG = 4 if cell == "lstm" else 3
+    for H, E in ((600, 300), (64, 40)):
+        w_ih = (torch.randn(NG * H, E, generator=g) / math.sqrt(E)).cuda()
+        w_hh = (torch.randn(NG * H, H, generator=g) / math.sqrt(H)).cuda()
+        b_ih = (torch.randn(NG * H, generator=g) * 0.1).cuda()
+        b_hh = (torch.randn(NG * H, generator=g) * 0.1).cuda()
+        for B, L in ((16, 20), (3, 7), (35, 4), (1, 1), (16, 2)):
+            x = torch.randn(B, L, E, generator=g).cuda()
+            outs = {}
+            try:
+                for name, (persistent, exchange) in {"exchange": (1, 1), "barrier": (1, 0), "steps": (0, 0)}.items():
+                    LIB.call("bmhrl_rnn_set_persistent", persistent)
+                    LIB.call("bmhrl_rnn_set_exchange", exchange)
+                    outs[name] = [ops.rnn_layer(cell, x, w_ih, w_hh, b_ih, b_hh).clone() for _ in range(3)]
+            finally:
+                LIB.call("bmhrl_rnn_set_persistent", 1)
+                LIB.call("bmhrl_rnn_set_exchange", -1)
+            torch.cuda.synchronize()
+            for name, o in outs.items():
+                assert torch.isfinite(o[0]).all()
+                assert torch.equal(o[0], o[1]) and torch.equal(o[0], o[2]), (name, H, B, L)
+                assert torch.equal(o[0], outs["steps"][0]), (name, H, B, L)
+            ref = getattr(torch.nn, cell.upper())(E, H, batch_first=True)   # CPU fp32 (no TF32 in the way)
+            with torch.no_grad():
+                ref.weight_ih_l0.copy_(w_ih); ref.weight_hh_l0.copy_(w_hh); ref.bias_ih_l0.copy_(b_ih); ref.bias_hh_l0.copy_(b_hh)
+                want = ref(x.cpu())[0]
+            assert rel(outs["exchange"][0], want) < 1e-4
+
+
 @pytest.mark.parametrize("B,L", [(3, 7), (16, 20), (17, 5), (1, 1)])
 def test_critic_wavefront_equals_layer_by_layer(gpu_lib, agent_sd, B, L):
     """ops.critic_wavefront (all recurrent layers of the SegmentCritic in one cooperative launch, L + 5 grid barriers)
