@@ -14,7 +14,7 @@ import torch.distributed as dist
 
 
 class GradSync:
-    def __init__(self, group=None, bucket_bytes=32 << 20, value_fn_mean=True):
+    def __init__(self, group=None, bucket_bytes=128 << 20, value_fn_mean=True):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.bucket_elems = max(1, bucket_bytes // 4)

@@ -92,6 +92,7 @@ class BMHRLTrainer:
                 self._stages.append(frozenset(i for i, n in enumerate(pnames) if n.startswith(pre) and is_self(n)))
         self._fired = []          # stages already handed to the communication stream in this backward
         self._comm_stream = None
+        self._adam_stream = None
         self.overlap_grad_sync = True
         # also on ONE GPU: the Adam update of a finished stage (1.3 GB of optimiser traffic per step in total) then runs
         # under the rest of backward instead of after it
@@ -186,9 +187,19 @@ class BMHRLTrainer:
         comm = self._comm_stream
         comm.wait_stream(torch.cuda.current_stream(dev))
         ops.wait_dirty_side_streams(comm)
+        if self.grad_sync is None:
+            with torch.cuda.stream(comm):
+                self.cap_opt.step(only=self._stages[stage])
+            return
+        # data parallel: the all-reduces of successive stages queue on the communication stream, the Adam updates on a
+        # stream of their own behind an event each -- the all-reduce of stage k + 1 (NVLink-bound) then runs beside the
+        # Adam update of stage k (HBM-bound) instead of behind it
+        if self._adam_stream is None:
+            self._adam_stream = torch.cuda.Stream(device=dev)
         with torch.cuda.stream(comm):
-            if self.grad_sync is not None:
-                self.grad_sync(self.cap_opt, only=self._stages[stage])
+            self.grad_sync(self.cap_opt, only=self._stages[stage])
+        self._adam_stream.wait_stream(comm)
+        with torch.cuda.stream(self._adam_stream):
             self.cap_opt.step(only=self._stages[stage])
 
     def _sync_and_step(self, opt, mean=False):
@@ -201,6 +212,8 @@ class BMHRLTrainer:
                 self.grad_sync(opt, mean=mean, only=rest)
             opt.step(only=rest)
             torch.cuda.current_stream(opt.flat_grad.device).wait_stream(self._comm_stream)
+            if self._adam_stream is not None:
+                torch.cuda.current_stream(opt.flat_grad.device).wait_stream(self._adam_stream)
             return
         if self.grad_sync is not None:
             self.grad_sync(opt, mean=mean)

@@ -17,7 +17,17 @@ def main():
     from bmhrl_b200 import ops, synth, _lib
     from bmhrl_b200.model.bm_hrl_agent import BMHrlAgent, BMManagerValueFunction, BMWorkerValueFunction
     from bmhrl_b200.train import BMHRLTrainer, StepRunner
-    dev = torch.device("cuda", 0)
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    sync = None
+    if world > 1:   # under torchrun: the data-parallel step (rank 0 prints its own timeline, NCCL kernels included)
+        import torch.distributed as dist
+        from bmhrl_b200.ddp import GradSync
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        sync = GradSync(bucket_bytes=int(os.environ.get("BMHRL_BUCKET_MB", "128")) << 20)
     shapes, vshapes = bench.agent_shapes()
     sd = synth.fill_state_dict(shapes, seed=1234)
     cfg = bench.cfg_ns("cuda")
@@ -27,13 +37,13 @@ def main():
     model.load_state_dict(sd)
     model = model.to(dev)
     wv, mv = BMWorkerValueFunction(cfg), BMManagerValueFunction(cfg)
-    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7)
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7, grad_sync=sync)
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[workload]()
-    ops.manual_seed(1234, dev)
+    ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode(os.environ.get("BMHRL_MATH", "bf16"))
     if os.environ.get("BMHRL_CONCURRENT") is not None:
         ops.CONCURRENT = bool(int(os.environ["BMHRL_CONCURRENT"]))
-    b = synth.synthetic_batch(V=bench.VOC, seed=1234, **bench.SHAPE)
+    b = synth.synthetic_batch(V=bench.VOC, seed=1234 + rank, **bench.SHAPE)
     runner = StepRunner(tr, workload, b, use_graph=True, warmup=3, pipeline_critic=os.environ.get("BMHRL_PIPELINE", "1") != "0")
     if os.environ.get("BMHRL_DIAG_NO_CRITIC"):   # diagnosis only: what the step costs with the critic taken out altogether
         lab = runner.labels_cur.clone()
@@ -49,12 +59,23 @@ def main():
         runner.replay()
     e1.record()
     torch.cuda.synchronize()
-    print(f"# back-to-back replays without the profiler: {e0.elapsed_time(e1) / reps * 1e3:.1f} us per step "
-          f"(CUDA_DEVICE_MAX_CONNECTIONS={os.environ.get('CUDA_DEVICE_MAX_CONNECTIONS', 'default')})")
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    if rank == 0:
+        print(f"# world size {world}")
+    if rank == 0:
+        print(f"# back-to-back replays without the profiler: {e0.elapsed_time(e1) / reps * 1e3:.1f} us per step "
+              f"(CUDA_DEVICE_MAX_CONNECTIONS={os.environ.get('CUDA_DEVICE_MAX_CONNECTIONS', 'default')})")
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         runner.replay()   # exactly ONE replay inside the profiled region: every kernel event belongs to it
         torch.cuda.synchronize()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        if rank != 0:
+            os._exit(0)
     path = os.path.join(ROOT, "gpurun_out", "trace.json")
     prof.export_chrome_trace(path)
     ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") == "kernel"]
@@ -95,6 +116,9 @@ def main():
         for e in step:
             print(f"{e['ts'] - t0:9.1f} {e['dur']:7.1f} {e['args'].get('stream')} {e['name'].split('(')[0][:60]}")
     os.remove(path)
+    if world > 1:
+        sys.stdout.flush()
+        os._exit(0)   # tearing the communicator down with the captured graph alive hangs
 
 
 if __name__ == "__main__":
