@@ -370,8 +370,15 @@ def run_gpu(args):
     wv.load_state_dict(synth.fill_state_dict(vshapes, seed=77))
     mv.load_state_dict(synth.fill_state_dict(vshapes, seed=78))
     sync = GradSync() if world > 1 else None
+    # data parallel: --dp peer (default) = gradient sum + Adam + parameter broadcast as one kernel over NVLink peer memory
+    # (bmhrl_b200/peer.py, csrc/peer.cu); --dp nccl = bucketed NCCL all-reduce + the same Adam on every rank (ddp.GradSync)
+    peer = None
+    if world > 1 and args.dp == "peer":
+        from bmhrl_b200.peer import PeerGroup
+        peer = PeerGroup(dev)
     # random_synonyms 0.3: the reference's feature_getter corrupts the input tokens of every training step
-    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync, random_synonyms=0.3)
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync, random_synonyms=0.3,
+                      peer=peer)
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[args.workload]()
     ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode(args.math)
@@ -523,7 +530,12 @@ def run_gpu(args):
             "metric": METRIC, "value": clips / sec, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": {"bf16": "bf16", "tf32": "tf32", "fp32": "f32"}[args.math], "data": "synthetic",
-            "config": workload_config(args.workload),
+            "config": dict(workload_config(args.workload),
+                           parallelism=("single GPU" if world == 1 else
+                                        f"dp{world}, one process per GPU, " +
+                                        ("gradient sum + Adam + parameter broadcast fused in one kernel over NVLink peer "
+                                         "memory (CUDA IPC), Adam state sharded" if peer is not None else
+                                         "NCCL all-reduce of the flat gradient buffer overlapped with backward, replicated Adam"))),
             "e2e": {"value": clips / sec_e2e, "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3, "wall_ms_per_step": wall_e2e / args.steps * 1e3},
             "gpu_launches": graph_launches * (2 * args.steps + args.warmup) if graph_launches else launches_eager,
@@ -636,6 +648,9 @@ def main():
     ap.add_argument("--math", default="bf16", choices=["bf16", "tf32", "fp32"],
                     help="bf16: bf16 tensor-core operands, grouped tcgen05 GEMMs + fused attention fwd/bwd (default); "
                          "tf32: fp32 storage, tcgen05 kind::tf32 GEMMs; fp32: exact SIMT contractions")
+    ap.add_argument("--dp", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: peer = gradient sum + Adam + parameter broadcast in one kernel over NVLink peer memory "
+                         "(default); nccl = bucketed all-reduce + replicated Adam")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-pipeline", action="store_true",

@@ -152,6 +152,18 @@ __device__ __forceinline__ bool dropout_keep(const unsigned long long* rng_state
 }
 
 // ---------------------------------------------------------------- reductions
+// One Adam update (torch.optim.Adam, no weight decay / amsgrad) with every rounding spelled out: adam_multi_kernel
+// (misc.cu) and adam_peer_kernel (peer.cu) must give the same bits for the same inputs whatever loop the compiler finds
+// the expression in (left to the contraction heuristics the two differed by one ulp in a tail element).
+__device__ __forceinline__ float adam_update(float pi, float gi, float& mi, float& vi, float beta1, float beta2, float eps,
+                                             float grad_scale, float step_size, float inv_sqrt_bc2) {
+    gi = __fmul_rn(gi, grad_scale);
+    mi = __fmaf_rn(beta1, mi, __fmul_rn(1.f - beta1, gi));
+    vi = __fmaf_rn(beta2, vi, __fmul_rn(__fmul_rn(1.f - beta2, gi), gi));
+    const float denom = __fadd_rn(__fmul_rn(sqrtf(vi), inv_sqrt_bc2), eps);
+    return __fsub_rn(pi, __fdiv_rn(__fmul_rn(step_size, mi), denom));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -389,10 +389,7 @@ __global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restric
     const int sk = sh ? shadow_kind[t] : 0;
     const int scols = sh ? shadow_cols[t] : 1, sld = sh ? shadow_ld[t] : 1;
     auto upd = [&](float pi, float gi, float& mi, float& vi) {
-        gi *= grad_scale;
-        mi = beta1 * mi + (1.f - beta1) * gi;
-        vi = beta2 * vi + (1.f - beta2) * gi * gi;
-        return pi - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+        return adam_update(pi, gi, mi, vi, beta1, beta2, eps, grad_scale, step_size, inv_sqrt_bc2);
     };
     const bool vec = ((((uintptr_t)p) | ((uintptr_t)g) | ((uintptr_t)m) | ((uintptr_t)v)) & 15u) == 0 &&
                      (!sh || (sk == 1 ? ((uintptr_t)sh & 15u) == 0 : (((uintptr_t)sh & 7u) == 0 && scols == sld)));

@@ -1112,8 +1112,12 @@ class FusedAdam:
     Phase switching (BMHrlAgent.teach_worker / teach_manager flip requires_grad): call `refresh_active()` afterwards;
     frozen tensors are then skipped exactly like torch skips parameters whose grad is None."""
 
-    def __init__(self, params, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
+    def __init__(self, params, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0, peer=None):
+        """peer: a peer.PeerGroup (not yet shared) -- the flat gradient buffer and the parameters themselves (re-pointed
+        at slices of one flat buffer, values kept) are then carved from its IPC-shareable arenas, which is what
+        `step_peer` (gradient sum over the ranks + Adam + parameter broadcast in one kernel) works on."""
         self.params = list(params)
+        self.peer = peer
         if not self.params:
             raise RuntimeError("FusedAdam: no parameters")
         dev = self.params[0].device
@@ -1123,7 +1127,20 @@ class FusedAdam:
         # every tensor's slice starts on a 16-byte boundary (128-bit accesses in adam_multi_kernel); the <= 3 padding
         # elements between slices stay zero
         total = sum((p.numel() + 3) & ~3 for p in self.params)
-        self.flat_grad = torch.zeros(total, device=dev, dtype=_F32)
+        self.flat_param = None
+        if peer is not None:
+            self.flat_grad = peer.arena(peer.GRAD, total * 4 + 4096).take(total, _F32)
+            self.flat_param = peer.arena(peer.PARAM, total * 4 + 4096).take(total, _F32)
+            off = 0
+            with torch.no_grad():
+                for p in self.params:   # the parameters move into the shared flat buffer (same values, same objects)
+                    n = p.numel()
+                    fp = self.flat_param[off:off + n].view_as(p)
+                    fp.copy_(p.data)
+                    p.data = fp
+                    off += (n + 3) & ~3
+        else:
+            self.flat_grad = torch.zeros(total, device=dev, dtype=_F32)
         self.exp_avg = torch.zeros(total, device=dev, dtype=_F32)
         self.exp_avg_sq = torch.zeros(total, device=dev, dtype=_F32)
         self.step_counts = torch.zeros(len(self.params), device=dev, dtype=_F32)
@@ -1170,6 +1187,7 @@ class FusedAdam:
         self._cs = torch.tensor(cs, device=dev, dtype=torch.int32)
         self.n_chunks = len(ct)
         self._subsets = {}  # frozenset of parameter indices -> (act, ct, cs, n_act, n_chunks) device tables
+        self._peer_subsets = {}
 
     def _subset_tables(self, only):
         """Chunk tables of the active parameters whose index is in `only` (built on first use: call once eagerly
@@ -1212,6 +1230,66 @@ class FusedAdam:
             LIB.call("bmhrl_adam_multi_shadow_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne),
                      _p(ct), _p(cs), n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1],
                      self.eps, self.grad_scale, _p(sh[0]), _p(sh[1]), _p(sh[2]), _p(sh[3]), st)
+
+    def _peer_tables(self, only):
+        """Chunk tables of the chunks THIS rank owns among the active parameters (in `only`): every N-th chunk."""
+        key = None if only is None else (only if isinstance(only, frozenset) else frozenset(only))
+        t = self._peer_subsets.get(key)
+        if t is None:
+            dev = self.flat_grad.device
+            act = [i for i in self.active if key is None or i in key]
+            # the owner of a chunk holds its Adam moments, so ownership must not depend on which subset a step updates:
+            # owner = (index of the chunk among ALL chunks of ALL parameters) mod N
+            if not hasattr(self, "_chunk_base"):
+                self._chunk_base, k = [], 0
+                for p in self.params:
+                    self._chunk_base.append(k)
+                    k += (p.numel() + self.chunk - 1) // self.chunk
+            ct, cs = [], []
+            for i in act:
+                for s in range(0, self.params[i].numel(), self.chunk):
+                    if (self._chunk_base[i] + s // self.chunk) % self.peer.world == self.peer.rank:
+                        ct.append(i)
+                        cs.append(s)
+            i32 = dict(device=dev, dtype=torch.int32)
+            t = (torch.tensor(act, **i32), torch.tensor(ct, **i32), torch.tensor(cs, **i32), len(act), len(ct))
+            self._peer_subsets[key] = t
+        return t
+
+    def step_peer(self, slot, only=None):
+        """Data-parallel step over NVLink peer memory (csrc/peer.cu): cross-GPU signal "my gradients of these parameters
+        are final", wait for everyone's, then for the chunks this rank owns: gradient sum over all ranks (peer loads),
+        Adam, new parameter and bf16 shadow stored into every rank's buffers.  Stream-ordered, CUDA-graph capturable.
+        The caller ends the step with `peer.barrier(end_slot)` before any rank touches gradients or parameters again."""
+        if self._peer_tables(only)[3] == 0:
+            return
+        self.peer.signal(slot)
+        self.step_peer_finish(slot, only)
+
+    def step_peer_finish(self, slot, only=None):
+        """step_peer behind an already issued `peer.signal(slot)` (a single-process simulation of several ranks must
+        issue every rank's signal before any rank's wait: a kernel that is launched for the first time is loaded lazily,
+        which waits for running kernels -- such as another simulated rank's spinning wait)."""
+        peer = self.peer
+        st = _stream()
+        act, ct, cs, n_act, n_chunks = self._peer_tables(only)
+        if n_act == 0:
+            return
+        peer.wait(slot)
+        LIB.call("bmhrl_tick", _p(self.step_counts), _p(act), n_act, None, st)
+        if n_chunks == 0:
+            return
+        sh = self._shadow_tables()
+        from . import ops16
+        if sh is not None and ops16.SHADOWS.arena is None:
+            raise RuntimeError("FusedAdam.step_peer: the weight shadows must live in the peer group's shadow arena "
+                               "(ops16.SHADOWS.arena) so that every rank's copy can be written")
+        go, po = peer.arena(peer.GRAD).offsets(), peer.arena(peer.PARAM).offsets()
+        so = peer.arena(peer.SHADOW).offsets() if sh is not None else None
+        LIB.call("bmhrl_adam_peer_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne), _p(ct), _p(cs),
+                 n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1], self.eps, self.grad_scale,
+                 None if sh is None else _p(sh[0]), None if sh is None else _p(sh[1]), None if sh is None else _p(sh[2]),
+                 None if sh is None else _p(sh[3]), go, po, so, peer.world, st)
 
     def _shadow_tables(self):
         """Device tables of the bf16 / fp32 shadows (ops16.SHADOWS) of this optimiser's parameters: the Adam kernel

@@ -197,6 +197,9 @@ class _Shadows:
         self.groups = {}      # tuple(id(weight)) -> dict
         self.by_param = {}    # id(param) -> (data_ptr, cols, ld, kind) of the FIRST group that holds it
         self.generation = 0
+        # peer.Arena the shadows are carved from (data parallel over peer memory: FusedAdam.step_peer stores the
+        # updated shadows into every rank's arena, so all ranks must create them in the same order); None: torch memory
+        self.arena = None
 
     def entry(self, p):
         return self.by_param.get(id(p))
@@ -224,11 +227,18 @@ class _Shadows:
         if any(w.dim() != 2 or w.shape[1] != K for w in weights):
             raise RuntimeError("weight shadows: the stacked weights must share in_features")
         n_tot = sum(w.shape[0] for w in weights)
-        w16 = empty16(n_tot, K, dev)
+        if self.arena is not None:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("weight shadows (peer arena) must exist before a CUDA-graph capture: run the step eagerly once")
+            w16 = self.arena.take(n_tot * pad8(K), _BF16).view(n_tot, pad8(K))[:, :K]
+        else:
+            w16 = empty16(n_tot, K, dev)
         b32 = None
         if biases is not None and any(b is not None for b in biases):
             if len(weights) == 1:
                 b32 = biases[0]          # a single layer reads its own bias parameter
+            elif self.arena is not None:
+                b32 = self.arena.take(n_tot, _F32)
             else:
                 b32 = torch.zeros(n_tot, device=dev, dtype=_F32)
         g = {"w16": w16, "b32": b32, "ver": -1, "uncovered": False}

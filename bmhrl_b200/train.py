@@ -51,7 +51,7 @@ class BMHRLTrainer:
     scripts/train_rl_captioning_module.py:81-83) and the criteria (:66-67, :132)."""
 
     def __init__(self, cap_model, wv_model, mv_model, pad_idx=1, smoothing=0.7, lr=1e-4, modality="audio_video",
-                 grad_sync=None, scorer=None, random_synonyms=0.0, end_idx=3):
+                 grad_sync=None, scorer=None, random_synonyms=0.0, end_idx=3, peer=None):
         # feature_getter(..., random_synonyms=0.3) (captioning_bmrl_loops.py:487-528): the reference corrupts the INPUT
         # caption tokens of every training step; 0 (default) switches it off, which is what the parity goldens assume
         self.random_synonyms, self.end_idx = float(random_synonyms), int(end_idx)
@@ -60,7 +60,15 @@ class BMHRLTrainer:
         self.pad_idx, self.modality = pad_idx, modality
         self.ls = LabelSmoothing(smoothing, pad_idx)
         self.bkl = BiasedKL(smoothing, pad_idx)
-        self.cap_opt = ops.FusedAdam(used_parameters(cap_model), lr=lr)
+        # peer: a peer.PeerGroup -- the agent's gradients are then summed over the ranks, Adam-stepped and the parameters
+        # broadcast by ONE kernel over NVLink peer memory (ops.FusedAdam.step_peer) instead of NCCL all-reduce + a
+        # replicated Adam; grad_sync still carries the scalar loss normaliser and the (tiny) value functions
+        self.peer = peer
+        self.cap_opt = ops.FusedAdam(used_parameters(cap_model), lr=lr, peer=peer)
+        if peer is not None:
+            n_el = self.cap_opt.flat_grad.numel()
+            ops16.SHADOWS.arena = peer.arena(peer.SHADOW, int(2 * n_el * 1.15) + (32 << 20))
+            peer.share()
         self.wv_opt = ops.FusedAdam(wv_model.parameters(), lr=lr)
         self.mv_opt = ops.FusedAdam(mv_model.parameters(), lr=lr)
         self.grad_sync = grad_sync  # data-parallel hook: callable(optimizer) all-reducing optimizer.flat_grad
@@ -187,6 +195,10 @@ class BMHRLTrainer:
         comm = self._comm_stream
         comm.wait_stream(torch.cuda.current_stream(dev))
         ops.wait_dirty_side_streams(comm)
+        if self.peer is not None:
+            with torch.cuda.stream(comm):
+                self.cap_opt.step_peer(stage, only=self._stages[stage])
+            return
         if self.grad_sync is None:
             with torch.cuda.stream(comm):
                 self.cap_opt.step(only=self._stages[stage])
@@ -204,6 +216,20 @@ class BMHRLTrainer:
 
     def _sync_and_step(self, opt, mean=False):
         """All-reduce (data parallel) + Adam of whatever has not been handled from a backward marker."""
+        if opt is self.cap_opt and self.peer is not None:
+            # peer-memory data parallel: what no backward marker has handled yet, then the end-of-step barrier (nobody
+            # zeroes gradients or reads parameters of the next step while a peer still reads / writes this step's)
+            cur = torch.cuda.current_stream(opt.flat_grad.device)
+            rest = None
+            if self._fired:
+                done = frozenset().union(*(self._stages[k] for k in self._fired))
+                rest = frozenset(range(len(opt.params))) - done
+                self._fired = []
+            opt.step_peer(len(self._stages), only=rest)
+            if self._comm_stream is not None:
+                cur.wait_stream(self._comm_stream)
+            self.peer.barrier(self.peer.n_slots - 1)
+            return
         if opt is self.cap_opt and self._fired:
             done = frozenset().union(*(self._stages[k] for k in self._fired))
             rest = frozenset(range(len(opt.params))) - done

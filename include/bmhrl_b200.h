@@ -397,6 +397,40 @@ int bmhrl_adam_multi_shadow_f32(float* const* params, const float* const* grads,
 int bmhrl_tick(float* step_counts, const int* active_tensors, int n_active, unsigned long long* rng_state,
                void* stream);
 
+/* ---- data parallel over NVLink peer memory (peer.cu): gradient sum + Adam + parameter broadcast in ONE kernel ----
+ * Replaces nn.DataParallel's gradient reduction + torch.optim.Adam on every replica
+ * (scripts/train_rl_captioning_module.py:81-83,97-99) when there is one process per GPU on one NVLink / NVSwitch node.
+ * Set-up (host, once): every rank allocates its arenas with bmhrl_peer_alloc (cudaMalloc, zeroed), publishes their IPC
+ * handles (bmhrl_peer_get_handle, 64 bytes each, exchanged by the caller, e.g. torch.distributed.all_gather_object) and
+ * maps the other ranks' arenas with bmhrl_peer_open_handle.  All ranks lay their arenas out identically, so a peer's
+ * copy of a local address is that address + (peer arena base - local arena base): the *_off_bytes arrays below hold
+ * that difference per rank (0 for the caller's own rank), at most bmhrl_peer_max_ranks() entries. */
+int bmhrl_peer_max_ranks(void);
+int bmhrl_peer_slots(void);
+long long bmhrl_peer_flag_bytes(void);     /* size of the flag table bmhrl_peer_signal / _wait work on (zero-initialised) */
+int bmhrl_peer_alloc(long long bytes, void** out_ptr);
+int bmhrl_peer_free(void* ptr);
+int bmhrl_peer_handle_bytes(void);
+int bmhrl_peer_get_handle(const void* ptr, unsigned char* handle);
+int bmhrl_peer_open_handle(const unsigned char* handle, void** out_ptr);
+int bmhrl_peer_close_handle(void* ptr);
+/* Cross-GPU ordering, stream-ordered and CUDA-graph capturable.  signal: "everything enqueued before this on `stream` is
+ * done on my GPU" -> the slot's (only growing) count is stored into every rank's flag table.  wait: blocks `stream` (one
+ * warp spinning, never the consumer grid) until every rank's count of the slot has reached the count this rank's own
+ * last signal of that slot sent: call signal before wait, once each per step and slot, on every rank. */
+int bmhrl_peer_signal(unsigned long long* flags, const long long* flag_off_bytes, int n_ranks, int rank, int slot,
+                      void* stream);
+int bmhrl_peer_wait(const unsigned long long* flags, int n_ranks, int slot, void* stream);
+/* bmhrl_adam_multi_shadow_f32 on the chunks THIS rank owns (the caller lists them; chunk = bmhrl_adam_chunk_elems()
+ * elements): gradient = sum over ranks 0 .. n_ranks-1 of that rank's flat gradient (peer loads, fixed order), Adam on the
+ * local moments, new parameter (+ its bf16 / fp32 shadow) stored into every rank's parameter (shadow) arena. */
+int bmhrl_adam_peer_f32(float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
+                        const long long* numels, const int* chunk_tensor, const int* chunk_start, int n_chunks,
+                        const float* step_counts, float lr, float beta1, float beta2, float eps, float grad_scale,
+                        void* const* shadow, const int* shadow_cols, const int* shadow_ld, const int* shadow_kind,
+                        const long long* grad_off_bytes, const long long* param_off_bytes, const long long* shadow_off_bytes,
+                        int n_ranks, void* stream);
+
 /* ---- input side of the step (pipeline.cu) --------------------------------------------------------------------------- */
 /* pad_sequence + rgb + flow + padding mask in one pass over a ragged batch that arrived in ONE host->device copy:
  * a / b (b may be NULL): the clips' frames back to back, (total_frames, D) fp32; offsets (B+1) int32 frame offsets;
