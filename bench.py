@@ -246,7 +246,7 @@ def gemm_roofline(recorded, iters=20):
     return flops / n, sec / n, n
 
 
-TRAFFIC_SOURCE = ("profiles/r01_gemm_traffic.json (committed ncu capture of the same command, dram__bytes_read.sum + "
+TRAFFIC_SOURCE = ("profiles/r02_gemm_traffic.json (committed ncu capture of the same command, dram__bytes_read.sum + "
                   "dram__bytes_write.sum per GEMM launch; not re-measured in this run: ncu cannot run inside a timed bench)")
 
 
@@ -286,9 +286,10 @@ def gemm_roofline16(recorded, iters=20):
 
 def gemm_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch (average over the GEMM launches of one training step),
-    from the committed ncu capture profiles/r01_gemm_traffic.json (see its `command`); None when absent."""
+    from the committed ncu capture profiles/r02_gemm_traffic.json (see its `command`; written by
+    profiles/gemm_traffic_from_launches.py from the launch list of the same command); None when absent."""
     try:
-        return json.load(open(os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")))["avg_dram_bytes_per_launch"]
+        return json.load(open(os.path.join(ROOT, "profiles", "r02_gemm_traffic.json")))["avg_dram_bytes_per_launch"]
     except Exception:
         return None
 
@@ -372,13 +373,22 @@ def run_gpu(args):
     sync = GradSync() if world > 1 else None
     # data parallel: --dp peer (default) = gradient sum + Adam + parameter broadcast as one kernel over NVLink peer memory
     # (bmhrl_b200/peer.py, csrc/peer.cu); --dp nccl = bucketed NCCL all-reduce + the same Adam on every rank (ddp.GradSync)
-    peer = None
+    peer, tr = None, None
     if world > 1 and args.dp == "peer":
         from bmhrl_b200.peer import PeerGroup
-        peer = PeerGroup(dev)
-    # random_synonyms 0.3: the reference's feature_getter corrupts the input tokens of every training step
-    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync, random_synonyms=0.3,
-                      peer=peer)
+        try:
+            peer = PeerGroup(dev)
+            # random_synonyms 0.3: the reference's feature_getter corrupts the input tokens of every training step
+            tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync,
+                              random_synonyms=0.3, peer=peer)
+        except RuntimeError as e:   # raised on EVERY rank (PeerGroup.share agrees on the outcome): no CUDA IPC here
+            if rank == 0:
+                print(f"bench.py: peer-memory data parallel unavailable ({e}); using --dp nccl", file=sys.stderr)
+            from bmhrl_b200 import ops16
+            ops16.SHADOWS.arena = None
+            peer, tr = None, None
+    if tr is None:
+        tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync, random_synonyms=0.3)
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[args.workload]()
     ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode(args.math)

@@ -113,23 +113,33 @@ class PeerGroup:
             dist.all_gather_object(everyone, mine, group=self.group)
         else:
             everyone = [mine]
-        for n in names:
-            bases = []
-            for r in range(self.world):
-                if r == self.rank:
-                    bases.append(self.arenas[n].base)
-                    continue
-                h, nb = everyone[r][n]
-                if nb != self.arenas[n].nbytes:
-                    raise RuntimeError(f"peer arena {n!r}: rank {r} allocated {nb} bytes, this rank {self.arenas[n].nbytes}")
-                out = ctypes.c_void_p()
-                with torch.cuda.device(self.device):
-                    LIB.call("bmhrl_peer_open_handle", ctypes.create_string_buffer(h, hb), ctypes.byref(out))
-                bases.append(int(out.value))
-            self.arenas[n].peer_bases = bases
-        self._shared = True
+        err = None
+        try:
+            for n in names:
+                bases = []
+                for r in range(self.world):
+                    if r == self.rank:
+                        bases.append(self.arenas[n].base)
+                        continue
+                    h, nb = everyone[r][n]
+                    if nb != self.arenas[n].nbytes:
+                        raise RuntimeError(f"peer arena {n!r}: rank {r} allocated {nb} bytes, this rank {self.arenas[n].nbytes}")
+                    out = ctypes.c_void_p()
+                    with torch.cuda.device(self.device):
+                        LIB.call("bmhrl_peer_open_handle", ctypes.create_string_buffer(h, hb), ctypes.byref(out))
+                    bases.append(int(out.value))
+                self.arenas[n].peer_bases = bases
+        except Exception as e:   # noqa: BLE001 -- every rank must learn about it, or the others wait forever
+            err = e
         if self.world > 1:
-            dist.barrier(group=self.group)
+            ok = torch.tensor([0 if err is not None else 1], device=self.device, dtype=torch.int32)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            if int(ok) == 0:
+                raise RuntimeError(f"PeerGroup.share: mapping the peers' arenas failed on at least one rank "
+                                   f"(this rank: {err!r}); CUDA IPC / peer access between all GPUs of the node is required")
+        elif err is not None:
+            raise err
+        self._shared = True
 
     @classmethod
     def simulate(cls, device, world):
