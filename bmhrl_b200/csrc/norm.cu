@@ -2,6 +2,7 @@
 // Reference: ResidualConnection model/blocks.py:128-144 (nn.LayerNorm eps 1e-5, biased variance),
 // BMFusionLayer tail model/bm_hrl_agent.py:103-114.  HBM-bound: one warp per row, 128-bit accesses,
 // two-pass mean/variance like ATen (re-reads hit L1).
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "../../include/bmhrl_b200.h"
 
@@ -245,10 +246,12 @@ __global__ void __launch_bounds__(256) layernorm_bwd_det_kernel(
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
     const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ dres,
     float* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int D, int vec,
-    int row_blocks, int accumulate) {
+    int row_blocks, int accumulate, __nv_bfloat16* __restrict__ dx16, long long ld16, float drop_p,
+    const unsigned long long* __restrict__ rng, unsigned int salt) {
     griddep_wait();
     griddep_launch_dependents();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const float ks = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
     if ((int)blockIdx.x < row_blocks) {
         const int row = blockIdx.x * 8 + w;
         if (row >= rows) return;
@@ -281,6 +284,19 @@ __global__ void __launch_bounds__(256) layernorm_bwd_det_kernel(
             o.w = rstd * (g.w * ww.w - s1 - (v.w - mean) * rstd * s2);
             if (dr) { float4 r = ld_f4(dr + 4 * i); o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
             st_f4(dxr + 4 * i, o);
+            if (dx16) {   // bf16(dropout-mask o dx): what the backward of the block that PRODUCED x starts from (cast16_kernel)
+                if (drop_p > 0.f) {
+                    const Philox4 rb = philox_block(rng, salt, ((unsigned long long)row * D + 4 * i) >> 2);
+                    o.x = u32_to_unit(rb.x) >= drop_p ? o.x * ks : 0.f;
+                    o.y = u32_to_unit(rb.y) >= drop_p ? o.y * ks : 0.f;
+                    o.z = u32_to_unit(rb.z) >= drop_p ? o.z * ks : 0.f;
+                    o.w = u32_to_unit(rb.w) >= drop_p ? o.w * ks : 0.f;
+                }
+                uint2 pk;
+                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(pk.x) : "f"(o.y), "f"(o.x));
+                asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(pk.y) : "f"(o.w), "f"(o.z));
+                *reinterpret_cast<uint2*>(dx16 + (long long)row * ld16 + 4 * i) = pk;
+            }
         }
         for (int i = 4 * D4 + lane; i < D; i += 32) {
             float o = rstd * (dyr[i] * gamma[i] - s1 - (xr[i] - mean) * rstd * s2);
@@ -420,7 +436,26 @@ extern "C" int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const fl
     const int row_blocks = dx ? (rows + 7) / 8 : 0;
     const int strips = want_affine ? (D + 31) / 32 : 0;
     BMHRL_LAUNCH_PDL("layernorm_bwd_det", layernorm_bwd_det_kernel, dim3(row_blocks + strips), dim3(256), 0, st, dy, x, gamma,
-                     mean, rstd, dres, dx, dgamma, dbeta, rows, D, vec, row_blocks, accumulate_affine);
+                     mean, rstd, dres, dx, dgamma, dbeta, rows, D, vec, row_blocks, accumulate_affine,
+                     (__nv_bfloat16*)nullptr, 0ll, 0.f, (const unsigned long long*)nullptr, 0u);
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_layernorm_bwd_twin_f32(const float* dy, const float* x, const float* gamma, const float* mean,
+                                            const float* rstd, const float* dres, float* dx, void* dx16, long long lddx16,
+                                            float drop_p, const unsigned long long* rng_state, unsigned int salt, int rows,
+                                            int D, void* stream) {
+    BMHRL_CHECK_ARG(dy && x && gamma && mean && rstd && dx && dx16, "bmhrl_layernorm_bwd_twin_f32: null pointer");
+    BMHRL_CHECK_ARG(rows >= 0 && D > 0 && D % 4 == 0 && lddx16 >= D && lddx16 % 4 == 0, "bmhrl_layernorm_bwd_twin_f32: D and the bf16 pitch must be multiples of 4");
+    BMHRL_CHECK_ARG(aligned16(x) && aligned16(dy) && aligned16(gamma) && aligned16(dx) && (!dres || aligned16(dres)) &&
+                        ((uintptr_t)dx16 & 7u) == 0, "bmhrl_layernorm_bwd_twin_f32: alignment");
+    BMHRL_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || rng_state), "bmhrl_layernorm_bwd_twin_f32: dropout");
+    if (rows == 0) return BMHRL_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int row_blocks = (rows + 7) / 8;
+    BMHRL_LAUNCH_PDL("layernorm_bwd_det", layernorm_bwd_det_kernel, dim3(row_blocks), dim3(256), 0, st, dy, x, gamma, mean, rstd,
+                     dres, dx, (float*)nullptr, (float*)nullptr, rows, D, 1, row_blocks, 0, (__nv_bfloat16*)dx16, lddx16,
+                     drop_p, rng_state, salt);
     return BMHRL_OK;
 }
 

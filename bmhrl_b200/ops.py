@@ -217,6 +217,9 @@ class _GradMarker(torch.autograd.Function):
         tw = getattr(x, "_bmhrl16", None)   # bf16 twin emitted by the producing kernel (ops16): same data, keep it
         if tw is not None:
             y._bmhrl16 = tw
+        hint = getattr(x, "_bmhrl_bwd_cast", None)   # ops16.hint_backward_cast: an identity keeps it valid
+        if hint is not None:
+            y._bmhrl_bwd_cast = hint
         return y
 
     @staticmethod

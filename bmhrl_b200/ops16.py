@@ -299,7 +299,7 @@ def ln_fwd16(x2d, gamma, beta, eps):
     return y, mean, rstd
 
 
-def ln_bwd(dy2d, x2d, gamma, mean, rstd, dres2d, need_dx, ggrad, bgrad, need_affine):
+def ln_bwd(dy2d, x2d, gamma, mean, rstd, dres2d, need_dx, ggrad, bgrad, need_affine, twin=None):
     """dx = LN'(dy) (+ dres); dgamma / dbeta into the flat-buffer slices (accumulating) or fresh tensors.  Deterministic.
     When the affine gradients go straight into a FusedAdam slice nothing downstream waits for them: they are computed
     by a second launch on a weight-gradient side stream, and the critical path only carries the dx rows."""
@@ -315,15 +315,55 @@ def ln_bwd(dy2d, x2d, gamma, mean, rstd, dres2d, need_dx, ggrad, bgrad, need_aff
                  None if dres2d is None else dres2d.data_ptr(), None if dxp is None else dxp.data_ptr(),
                  None if dgp is None else dgp.data_ptr(), None if dbp is None else dbp.data_ptr(), rows, D, 1 if acc else 0,
                  _stream())
+    dx16 = None
+    if twin is not None and need_dx and D % 4 == 0:
+        # the dx rows by the variant that also writes bf16(dropout(dx)) for the producer of x (see hint_backward_cast)
+        p, rng, salt = twin
+        dx16 = empty16(rows, D, x2d.device)
+        ops._WGRAD_KEEP.append(dx16)   # read by another node, possibly on another stream: alive until the step ends
+
+        def call_dx():
+            LIB.call("bmhrl_layernorm_bwd_twin_f32", dy2d.data_ptr(), x2d.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
+                     rstd.data_ptr(), None if dres2d is None else dres2d.data_ptr(), dx.data_ptr(), dx16.data_ptr(),
+                     dx16.stride(0), float(p), rng.data_ptr() if p > 0 else None, int(salt), rows, D, _stream())
+    else:
+        def call_dx():
+            call(dx, None, None)
     if acc and ops.CONCURRENT:
         ops._WGRAD_KEEP.append((dy2d, x2d, mean, rstd))
         with torch.cuda.stream(ops.wgrad_stream(x2d.device, dg)):
             call(None, dg, db)
         if need_dx:
-            call(dx, None, None)
+            call_dx()
+    elif dx16 is not None:
+        if need_affine:
+            call(None, dg, db)
+        call_dx()
     else:
         call(dx, dg, db)
+    if dx16 is not None:
+        dx._bmhrl16m_pending = (dx16, float(twin[0]), int(twin[2]))
     return dx, (None if (acc or not need_affine) else dg), (None if (acc or not need_affine) else db)
+
+
+def hint_backward_cast(out, drop_p, rng, salt):
+    """Marks a block's fp32 output: the block's backward will start from bf16(dropout-mask o d_out) with these dropout
+    parameters.  A block that consumes `out` as its residual-stream input reads the hint and makes its LayerNorm backward
+    emit that matrix next to dx (`grad16_of` finds it) -- one launch fewer at the head of every block's backward."""
+    out._bmhrl_bwd_cast = (float(drop_p), rng, int(salt))
+
+
+def grad16_of(dy, rows, cols, drop_p, salt):
+    """The masked bf16 copy of the incoming gradient `dy`, if the node that produced dy emitted one for exactly these
+    dropout parameters.  The attribute travels with the tensor object through autograd as long as the gradient has a single
+    producer (a summed gradient is a new tensor without it); the version check rejects an in-place accumulation."""
+    tw = getattr(dy, "_bmhrl16m", None)
+    if tw is None:
+        return None
+    t16, p, sl, ver = tw
+    if p == float(drop_p) and sl == int(salt) and ver == dy._version and tuple(t16.shape) == (rows, cols):
+        return t16
+    return None
 
 
 def colsum16(z16, outs, seg_cols=0, accumulate=False):
@@ -408,6 +448,15 @@ def _bgrad16(dz16, biases, n_each):
 # block-level autograd nodes: one node per ResidualConnection block, every interior tensor is bf16 and invisible to
 # autograd; the residual-stream gradient adds are fused (LayerNorm backward takes the skip gradient as `dres`)
 # ----------------------------------------------------------------------------------------------------------------
+def _finish_dx(dx2d, shape):
+    """The (B, S, D) gradient a block returns; a masked bf16 copy emitted by ln_bwd moves onto the returned object."""
+    out = dx2d.view(shape)
+    pend = getattr(dx2d, "_bmhrl16m_pending", None)
+    if pend is not None:
+        out._bmhrl16m = (pend[0], pend[1], pend[2], out._version)
+    return out
+
+
 class _AttnBlock(torch.autograd.Function):
     """y = [x +] dropout_r( W_o dropout_a( attention( W_q n, W_k m, W_v m ) ) + b_o ),  n = LayerNorm(x) or x,
     m = n (self-attention) or the fp32 tensor `kv` (cross-attention: the un-normed other modality / encoder memory).
@@ -466,6 +515,8 @@ class _AttnBlock(torch.autograd.Function):
                                  C32=out.view(M, Dq), C16=out16)])
         if out16 is not None:
             attach_twin(out, out16)
+        hint_backward_cast(out, cfg["p_res"], cfg["rng"], cfg["s_out"])
+        ctx.in_hint = getattr(x, "_bmhrl_bwd_cast", None) if ln_g is not None else None
         ctx.save_for_backward(x2, mean, rstd, n16, q, k, v, m16, o16, lse2, mask_u8, ln_g, Wq, Wk, Wv, Wo)
         ctx.params = (ln_g, ln_b, Wq, bq, Wk, bk, Wv, bv, Wo, bo)
         ctx.cfg = cfg
@@ -487,7 +538,9 @@ class _AttnBlock(torch.autograd.Function):
             dy2 = dy2.contiguous()
         need_x, need_kv = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         # ---- out-projection: dZ_o = dropout-mask o dy (bf16), db_o
-        dzo = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s_out"])
+        dzo = grad16_of(dy, M, Dq, cfg["p_res"], cfg["s_out"])
+        if dzo is None:
+            dzo = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s_out"])
         dbo = _bgrad16(dzo, [bo], Dq)[0]
         wo16, _ = SHADOWS.get([Wo], [bo])
         do16 = empty16(M, D, dev)
@@ -532,11 +585,11 @@ class _AttnBlock(torch.autograd.Function):
             need_aff = ln_g.requires_grad
             if need_x or need_aff:
                 dx, dg, dbeta = ln_bwd(dn, x2, ln_g.detach(), mean, rstd, dy2 if cfg["resid"] else None, need_x,
-                                       ops._gbuf(ln_g), ops._gbuf(ln_b), need_aff)
+                                       ops._gbuf(ln_g), ops._gbuf(ln_b), need_aff, twin=ctx.in_hint)
         elif need_x:
             dx = dn + dy2 if cfg["resid"] else dn
         if dx is not None:
-            dx = dx.view(B, Sq, Dq)
+            dx = _finish_dx(dx, (B, Sq, Dq))
         return (dx, dkv, None, None, dg, dbeta, gw[0], gb[0], gw[1], gb[1], gw[2], gb[2], dWo, dbo)
 
 
@@ -567,6 +620,8 @@ class _FfnBlock(torch.autograd.Function):
                                  resid=x2 if cfg["resid"] else None, C32=out.view(M, D), C16=out16)])
         if out16 is not None:
             attach_twin(out, out16)
+        hint_backward_cast(out, cfg["p_res"], cfg["rng"], cfg["s2"])
+        ctx.in_hint = getattr(x, "_bmhrl_bwd_cast", None) if ln_g is not None else None
         ctx.save_for_backward(x2, mean, rstd, n16, h16, ln_g, W1, W2)
         ctx.params = (ln_g, ln_b, W1, b1, W2, b2)
         ctx.cfg = cfg
@@ -586,7 +641,9 @@ class _FfnBlock(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         need_x = ctx.needs_input_grad[0]
-        dz2 = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"])
+        dz2 = grad16_of(dy, M, D, cfg["p_res"], cfg["s2"])
+        if dz2 is None:
+            dz2 = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"])
         db2 = _bgrad16(dz2, [b2], D)[0]
         w1, _ = SHADOWS.get([W1], [b1])
         w2, _ = SHADOWS.get([W2], [b2])
@@ -603,11 +660,11 @@ class _FfnBlock(torch.autograd.Function):
             need_aff = ln_g.requires_grad
             if need_x or need_aff:
                 dx, dg, dbeta = ln_bwd(dn, x2, ln_g.detach(), mean, rstd, dy2 if cfg["resid"] else None, need_x,
-                                       ops._gbuf(ln_g), ops._gbuf(ln_b), need_aff)
+                                       ops._gbuf(ln_g), ops._gbuf(ln_b), need_aff, twin=ctx.in_hint)
         elif need_x:
             dx = dn + dy2 if cfg["resid"] else dn
         if dx is not None:
-            dx = dx.view(B, S, D)
+            dx = _finish_dx(dx, (B, S, D))
         return dx, None, dg, dbeta, dW1, db1, dW2, db2
 
 

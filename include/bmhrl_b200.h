@@ -138,6 +138,12 @@ int bmhrl_layernorm_fwd_f32(const float* x, const float* resid, const float* gam
 int bmhrl_layernorm_bwd_f32(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                             const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int D,
                             int accumulate_affine, void* stream);
+/* The dx rows of the same backward, plus dx16 = bf16(dropout(dx)) (Philox, element index row*D + col, like
+ * bmhrl_cast_bf16): in bf16 math mode the backward of the block that produced x starts from exactly that matrix, so the
+ * separate mask + cast launch at the head of every block's backward disappears.  D % 4 == 0. */
+int bmhrl_layernorm_bwd_twin_f32(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                                 const float* dres, float* dx, void* dx16, long long lddx16, float drop_p,
+                                 const unsigned long long* rng_state, unsigned int salt, int rows, int D, void* stream);
 /* out = s*v + (1-s)*a, s = sigmoid(clamp(*gate_param,-2,2)); model/bm_hrl_agent.py:111-114. */
 int bmhrl_gated_mix_fwd_f32(const float* v, const float* a, const float* gate_param, float* out, long long n,
                             void* stream);

@@ -233,6 +233,41 @@ def test_step_bf16_adam_keeps_shadows_fresh_and_is_deterministic(bf16, agent_sd)
     assert finals[0][0][-1] < finals[0][0][0]
 
 
+def test_backward_gradient_twin_equals_separate_cast(bf16, agent_sd, monkeypatch):
+    """A block's LayerNorm backward emits bf16(dropout-mask o dx) for the block that produced its input
+    (ops16.hint_backward_cast / grad16_of): same parameters after two steps, bit for bit, as with the separate mask + cast
+    launch at the head of every block's backward -- and the emitted copy is really used where a block's output has a single
+    consumer (6 of the 25 block heads of this model per step: the FFN <- bimodal-attention and the layer-to-layer hand-overs
+    of the encoder; everywhere else the gradient is a sum over several consumers and the cast stays)."""
+    from bmhrl_b200 import ops16
+    from bmhrl_b200.train import StepRunner
+    b = synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=3, ragged=True)
+    finals, taken = [], []
+    real = ops16.grad16_of
+    for fused in (True, False):
+        hits = [0, 0]
+
+        def spy(dy, rows, cols, drop_p, salt, fused=fused, hits=hits):
+            t = real(dy, rows, cols, drop_p, salt) if fused else None
+            hits[0 if t is not None else 1] += 1
+            return t
+        monkeypatch.setattr(ops16, "grad16_of", spy)
+        bf16.manual_seed(11)
+        bf16.RNG.salt = 7000
+        model, tr = _trainer(agent_sd, dout_p=0.1)
+        run = StepRunner(tr, "warmstart", b, use_graph=False)
+        losses = [float(run.step(b)[0]) for _ in range(2)]
+        torch.cuda.synchronize()
+        finals.append((losses, {n: p.detach().clone() for n, p in model.named_parameters()}))
+        taken.append(hits)
+    monkeypatch.setattr(ops16, "grad16_of", real)
+    print("blocks that started from an emitted gradient copy / from a cast:", taken)
+    assert taken[0][0] >= 10 and taken[1][0] == 0
+    assert finals[0][0] == finals[1][0]
+    for n in finals[0][1]:
+        assert torch.equal(finals[0][1][n], finals[1][1][n]), n
+
+
 def test_warmstart_step_bf16_matches_oracle_adam(bf16, agent_sd):
     """Two warm-start steps in bf16 math mode vs oracle autograd + oracle Adam: losses within 2e-2; parameters move by
     lr-sized steps, so they are compared through the size of the update."""
