@@ -807,6 +807,11 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
     static const int env_stages = getenv("BMHRL_GB_STAGES") ? atoi(getenv("BMHRL_GB_STAGES")) : 0;  // experiments
     int nstages = g_gb_force_stages ? g_gb_force_stages : (env_stages ? env_stages : (BN == 128 ? 4 : 3));
     {
+        // a launch with at most one CTA per SM cannot hide the TMA round trip behind other CTAs of its own: deeper ring
+        // (experiment switch BMHRL_GB_DEEP = ring depth for such launches, 0 = off)
+        static const int env_deep = getenv("BMHRL_GB_DEEP") ? atoi(getenv("BMHRL_GB_DEEP")) : 0;
+        const long long ctas = (BN == 128 ? t128 : t64) * split;
+        if (env_deep > nstages && !g_gb_force_stages && !env_stages && ctas <= n_sm) nstages = env_deep > 6 ? 6 : env_deep;
         const int kb_per_cta = (max_kb + split - 1) / split;
         if (nstages > kb_per_cta) nstages = kb_per_cta < 2 ? 2 : kb_per_cta;
         if (split > 1 && nstages > 3) nstages = 3;  // room for the DSMEM receive buffer beside a co-resident kernel
