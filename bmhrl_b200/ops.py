@@ -1168,6 +1168,7 @@ class FusedAdam:
         self._ne = torch.tensor(ne, **i64)
         self._shadow_gen = -1      # generation of the bf16 weight-shadow registry (ops16) the tables below were built for
         self._shadow_tabs = None
+        self._shadow_ptrs = []
         self.refresh_active()
 
     def refresh_active(self):
@@ -1283,10 +1284,15 @@ class FusedAdam:
         if n_chunks == 0:
             return
         sh = self._shadow_tables()
-        from . import ops16
-        if sh is not None and ops16.SHADOWS.arena is None:
-            raise RuntimeError("FusedAdam.step_peer: the weight shadows must live in the peer group's shadow arena "
-                               "(ops16.SHADOWS.arena) so that every rank's copy can be written")
+        if sh is not None:
+            ptrs = [p for p in self._shadow_ptrs if p]
+            if not ptrs:
+                sh = None   # the registry holds shadows, but none of THIS optimiser's parameters
+            else:
+                arena = peer.arenas.get(peer.SHADOW)
+                if arena is None or not all(arena.contains(p) for p in ptrs):
+                    raise RuntimeError("FusedAdam.step_peer: the weight shadows must live in the peer group's shadow arena "
+                                       "(ops16.SHADOWS.arena) so that every rank's copy can be written")
         go, po = peer.arena(peer.GRAD).offsets(), peer.arena(peer.PARAM).offsets()
         so = peer.arena(peer.SHADOW).offsets() if sh is not None else None
         LIB.call("bmhrl_adam_peer_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne), _p(ct), _p(cs),
@@ -1315,6 +1321,7 @@ class FusedAdam:
                 cols.append(e[1] if e else 1)
                 ld.append(e[2] if e else 1)
                 kind.append(e[3] if e else 0)
+            self._shadow_ptrs = list(ptr)
             self._shadow_tabs = (torch.tensor(ptr, device=dev, dtype=torch.int64),
                                  torch.tensor(cols, device=dev, dtype=torch.int32),
                                  torch.tensor(ld, device=dev, dtype=torch.int32),

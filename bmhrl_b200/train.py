@@ -445,6 +445,8 @@ class StepRunner:
             self.labels_next = self.labels_cur.clone()
             torch.cuda.synchronize(dev)
         self._need_prime = False
+        self.prefetch_inputs = True   # step(batch, next_batch): copy the next batch's inputs under this step (see load)
+        self._staged = None
         if use_graph:
             side = ops.warmup_stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))
@@ -502,12 +504,43 @@ class StepRunner:
         return out
 
     def load(self, host_batch, non_blocking=True, next_host_batch=None):
-        for k, buf in self.static.items():
-            if k == "caption_next":
-                src = (next_host_batch if next_host_batch is not None else host_batch)["caption"]
-                buf.copy_(src, non_blocking=non_blocking)
-            else:
-                buf.copy_(host_batch[k], non_blocking=non_blocking)
+        """Inputs of this step into the static buffers.  When the step is given its successor (`next_host_batch`), that
+        batch's host->device copy is issued on a copy stream into a staging set NOW, so it runs under this step's kernels;
+        the next `load` of that same batch object is then a device-to-device copy (a few microseconds) instead of 4.6 MB
+        over the host link in front of the graph.  The caller must not overwrite the pinned buffers of a batch it has
+        handed over as `next_host_batch` before the step that consumes it has been issued (the usual non_blocking rule)."""
+        dev = self.static["caption"].device
+        cur = torch.cuda.current_stream(dev)
+        st = getattr(self, "_staged", None)
+        if st is not None and st["src"] is host_batch:
+            cur.wait_event(st["ready"])
+            for k, buf in self.static.items():
+                if k != "caption_next":
+                    buf.copy_(st["bufs"][k], non_blocking=True)
+            st["free"] = torch.cuda.Event()
+            st["free"].record(cur)
+        else:
+            for k, buf in self.static.items():
+                if k != "caption_next":
+                    buf.copy_(host_batch[k], non_blocking=non_blocking)
+        if "caption_next" in self.static:
+            src = (next_host_batch if next_host_batch is not None else host_batch)["caption"]
+            self.static["caption_next"].copy_(src, non_blocking=non_blocking)
+        if next_host_batch is not None and non_blocking and self.prefetch_inputs:
+            if st is None:
+                st = self._staged = {"bufs": {k: torch.empty_like(v) for k, v in self.static.items() if k != "caption_next"},
+                                     "stream": torch.cuda.Stream(device=dev), "free": None}
+            cs = st["stream"]
+            if st["free"] is not None:
+                cs.wait_event(st["free"])      # the previous device-to-device copy out of the staging set is done
+            with torch.cuda.stream(cs):
+                for k, buf in st["bufs"].items():
+                    buf.copy_(next_host_batch[k], non_blocking=True)
+                st["ready"] = torch.cuda.Event()
+                st["ready"].record(cs)
+            st["src"] = next_host_batch
+        elif st is not None:
+            st["src"] = None
 
     def replay(self):
         if self.graph is not None:
