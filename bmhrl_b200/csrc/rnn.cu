@@ -8,6 +8,7 @@
 // warp owns one hidden unit (its 4 / 3 gate rows of W_hh, read once, coalesced) for up to 16 batch rows whose
 // h_{t-1} sits in shared memory.
 #include <stdlib.h>
+#include <atomic>
 #include "common.cuh"
 #include "../../include/bmhrl_b200.h"
 
@@ -903,6 +904,52 @@ extern "C" int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh,
         BMHRL_POST_LAUNCH("rnn_step");
     }
     return BMHRL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// bmhrl_rnn_layer_noalloc_f32: the same layer for callers that cannot allocate device memory (CUDA-graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  The workspace of bmhrl_rnn_layer_f32 (LSTM cell state, the grid-
+// barrier counter, the tagged exchange buffer) lives in ONE file-scope device array of a fixed, modest size that every
+// GPU which loads the library holds until exit.  No counterpart in the reference.
+// In host code `g_rnn_noalloc_scratch` is only a stand-in for the symbol, NOT a device address: the address
+// comes from cudaGetSymbolAddress, once per device, with that device current.  All calls share the array and it keeps
+// the last call's contents: the launcher clears what must start at zero (barrier counter / exchange tags, stream-ordered
+// memsets), the cell state is written before it is read (t = 0 reads no state).  Two calls that overlap on the GPU
+// (different streams, or concurrent graph branches) RACE on it -- serialise them.
+constexpr long long RNN_NOALLOC_MAX_FLOATS = 256 * 1024;   // 1 MB per GPU; B = 16, H = 600 needs 48 032 floats
+static __device__ __align__(256) float g_rnn_noalloc_scratch[RNN_NOALLOC_MAX_FLOATS];
+
+static int rnn_noalloc_scratch_ptr(float** out) {
+    static std::atomic<float*> ptr[kMaxDevices];
+    const int slot = current_device_slot();
+    float* p = ptr[slot].load(std::memory_order_acquire);
+    if (!p) {
+        void* q = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&q, g_rnn_noalloc_scratch);   // the current device's copy of the array
+        if (e != cudaSuccess || !q) {
+            bmhrl_set_error(e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned a null address");
+            return BMHRL_ERR_CUDA;
+        }
+        p = static_cast<float*>(q);
+        ptr[slot].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return BMHRL_OK;
+}
+
+extern "C" long long bmhrl_rnn_noalloc_max_floats(void) { return RNN_NOALLOC_MAX_FLOATS; }
+
+extern "C" int bmhrl_rnn_layer_noalloc_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out,
+                                           int B, int L, int H, void* stream) {
+    BMHRL_CHECK_ARG(B >= 0 && L >= 0 && H > 0, "bmhrl_rnn_layer_noalloc_f32: bad sizes");
+    if (bmhrl_rnn_ws_floats(B, H) > RNN_NOALLOC_MAX_FLOATS) {
+        bmhrl_set_error("bmhrl_rnn_layer_noalloc_f32: B x H needs more than the built-in scratch (bmhrl_rnn_ws_floats(B, H) > "
+                        "bmhrl_rnn_noalloc_max_floats() = 262144 floats): use bmhrl_rnn_layer_f32 with a caller workspace");
+        return BMHRL_ERR_ARG;
+    }
+    float* ws = nullptr;
+    if (int rc = rnn_noalloc_scratch_ptr(&ws)) return rc;
+    return bmhrl_rnn_layer_f32(cell, gx, W_hh, b_hh, out, ws, B, L, H, stream);
 }
 
 extern "C" int bmhrl_arelu_f32(const float* x, const float* alpha, const float* beta, float* y, long long n,

@@ -322,6 +322,16 @@ int bmhrl_rnn_set_exchange(int mode);   /* 1 / 0: force the exchange / the barri
 int bmhrl_rnn_trace(unsigned long long* device_slots);
 int bmhrl_rnn_layer_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, float* ws, int B,
                         int L, int H, void* stream);
+/* The same layer without any allocation by the caller or the library: the workspace is a file-scope device array of
+ * bmhrl_rnn_noalloc_max_floats() = 262 144 floats (1 MB, held by every GPU that loads the library until exit).  No
+ * counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA-graph capture, serving loops).  Shapes with bmhrl_rnn_ws_floats(B, H) above the maximum return BMHRL_ERR_ARG.
+ * Calls no cudaMalloc / cudaFree.  All calls share the array (it keeps the last call's contents; what must start at zero
+ * is cleared per call, stream-ordered): calls that overlap on the GPU race -- serialise them.  Same bits as
+ * bmhrl_rnn_layer_f32. */
+long long bmhrl_rnn_noalloc_max_floats(void);
+int bmhrl_rnn_layer_noalloc_f32(int cell, const float* gx, const float* W_hh, const float* b_hh, float* out, int B, int L,
+                                int H, void* stream);
 /* ONE time step t of the same layer on caller-kept buffers laid out for L steps: reads h_{t-1} from out[:, t-1, :] and
  * the LSTM cell state from c_prev (B,H) (both taken as zero at t == 0), gx[:, t, :]; writes out[:, t, :] and the new
  * cell state to c_next (B,H; may be c_prev; GRU: both null).  Distinct c_prev / c_next make the step repeatable.
