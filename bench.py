@@ -380,7 +380,8 @@ def run_gpu(args):
             peer = PeerGroup(dev)
             # random_synonyms 0.3: the reference's feature_getter corrupts the input tokens of every training step
             tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=PAD, smoothing=SMOOTH, grad_sync=sync,
-                              random_synonyms=0.3, peer=peer)
+                              random_synonyms=0.3, peer=peer,
+                              owner_only_master=(args.math == "bf16" and not args.replicate_masters))
         except RuntimeError as e:   # raised on EVERY rank (PeerGroup.share agrees on the outcome): no CUDA IPC here
             if rank == 0:
                 print(f"bench.py: peer-memory data parallel unavailable ({e}); using --dp nccl", file=sys.stderr)
@@ -544,7 +545,9 @@ def run_gpu(args):
                            parallelism=("single GPU" if world == 1 else
                                         f"dp{world}, one process per GPU, " +
                                         ("gradient sum + Adam + parameter broadcast fused in one kernel over NVLink peer "
-                                         "memory (CUDA IPC), Adam state sharded" if peer is not None else
+                                         "memory (CUDA IPC), Adam state sharded" +
+                                         (", fp32 masters of GEMM weights on their owner only (bf16 shadows broadcast)"
+                                          if tr.cap_opt.owner_only_master else "") if peer is not None else
                                          "NCCL all-reduce of the flat gradient buffer overlapped with backward, replicated Adam"))),
             "e2e": {"value": clips / sec_e2e, "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3, "wall_ms_per_step": wall_e2e / args.steps * 1e3},
@@ -661,6 +664,9 @@ def main():
     ap.add_argument("--dp", default="peer", choices=["peer", "nccl"],
                     help="N > 1: peer = gradient sum + Adam + parameter broadcast in one kernel over NVLink peer memory "
                          "(default); nccl = bucketed all-reduce + replicated Adam")
+    ap.add_argument("--replicate-masters", action="store_true",
+                    help="--dp peer: also broadcast the fp32 master of GEMM weights every step (default in bf16 mode: the "
+                         "owner of a chunk keeps it, replicas compute with the broadcast bf16 shadow)")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-pipeline", action="store_true",

@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
                                                         float eps, float grad_scale, void* const* __restrict__ shadow,
                                                         const int* __restrict__ shadow_cols, const int* __restrict__ shadow_ld,
                                                         const int* __restrict__ shadow_kind, PeerOff og, PeerOff op, PeerOff os,
-                                                        int n_ranks) {
+                                                        int n_ranks, int owner_only_master) {
     const int t = chunk_tensor[blockIdx.x];
     const long long s0 = chunk_start[blockIdx.x];
     const long long n = numels[t];
@@ -102,6 +102,11 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
     auto upd = [&](float pi, float gi, float& mi, float& vi) {
         return adam_update(pi, gi, mi, vi, beta1, beta2, eps, grad_scale, step_size, inv_sqrt_bc2);
     };
+    // owner_only_master: a weight that has a bf16 tensor-core shadow is READ through that shadow only (bf16 math mode), so
+    // its fp32 master is needed where its Adam moments are -- on the owner.  Not broadcasting it removes 4 of the 6 bytes a
+    // GEMM weight element sends to every peer.  The replicas' fp32 copies of such weights then go stale until
+    // bmhrl_peer_bcast_params_f32 (checkpoints, math-mode switches).
+    const bool bcast_master = !(owner_only_master && sh && sk == 0);
     const bool vec = ((((uintptr_t)p) | ((uintptr_t)g) | ((uintptr_t)m) | ((uintptr_t)v)) & 15u) == 0 &&
                      (!sh || (sk == 1 ? ((uintptr_t)sh & 15u) == 0
                                       : (((uintptr_t)sh & 7u) == 0 && (scols == sld || ((scols & 3) == 0 && (sld & 3) == 0)))));
@@ -129,10 +134,11 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
                 asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w.x) : "f"(o.y), "f"(o.x));
                 asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w.y) : "f"(o.w), "f"(o.z));
             }
+            if (!bcast_master) st_f4(p + i, o);
 #pragma unroll
             for (int r = 0; r < PEER_MAX; ++r)
                 if (r < n_ranks) {
-                    *reinterpret_cast<float4*>(reinterpret_cast<char*>(p + i) + op.b[r]) = o;
+                    if (bcast_master) *reinterpret_cast<float4*>(reinterpret_cast<char*>(p + i) + op.b[r]) = o;
                     if (sh) {
                         if (sk == 1)
                             *reinterpret_cast<float4*>(reinterpret_cast<char*>(reinterpret_cast<float*>(sh) + i) + os.b[r]) = o;
@@ -152,8 +158,9 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
         const float o = upd(p[i], gi, mi, vi);
         m[i] = mi;
         v[i] = vi;
+        if (!bcast_master) p[i] = o;
         for (int r = 0; r < n_ranks; ++r) {
-            *reinterpret_cast<float*>(reinterpret_cast<char*>(p + i) + op.b[r]) = o;
+            if (bcast_master) *reinterpret_cast<float*>(reinterpret_cast<char*>(p + i) + op.b[r]) = o;
             if (sh) {
                 if (sk == 1) {
                     *reinterpret_cast<float*>(reinterpret_cast<char*>(reinterpret_cast<float*>(sh) + i) + os.b[r]) = o;
@@ -164,6 +171,24 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
                 }
             }
         }
+    }
+}
+
+// The owner's fp32 values of the listed chunks into every rank's parameter arena (after steps with owner_only_master).
+__global__ void __launch_bounds__(256) peer_bcast_params_kernel(float* const* __restrict__ params,
+                                                                const long long* __restrict__ numels,
+                                                                const int* __restrict__ chunk_tensor,
+                                                                const int* __restrict__ chunk_start, PeerOff op, int n_ranks) {
+    const int t = chunk_tensor[blockIdx.x];
+    const long long s0 = chunk_start[blockIdx.x];
+    const long long n = numels[t];
+    const float* p = params[t];
+    long long end = s0 + ADAM_PEER_CHUNK;
+    if (end > n) end = n;
+    for (long long i = s0 + threadIdx.x; i < end; i += 256) {
+        const float o = p[i];
+        for (int r = 0; r < n_ranks; ++r)
+            if (op.b[r] != 0) *reinterpret_cast<float*>(reinterpret_cast<char*>(const_cast<float*>(p) + i) + op.b[r]) = o;
     }
 }
 
@@ -258,7 +283,7 @@ extern "C" int bmhrl_adam_peer_f32(float* const* params, const float* const* gra
                                    float beta2, float eps, float grad_scale, void* const* shadow, const int* shadow_cols,
                                    const int* shadow_ld, const int* shadow_kind, const long long* grad_off_bytes,
                                    const long long* param_off_bytes, const long long* shadow_off_bytes, int n_ranks,
-                                   void* stream) {
+                                   int owner_only_master, void* stream) {
     BMHRL_CHECK_ARG(params && grads && exp_avg && exp_avg_sq && numels && chunk_tensor && chunk_start && step_counts,
                     "bmhrl_adam_peer_f32: null pointer");
     BMHRL_CHECK_ARG(!shadow || (shadow_cols && shadow_ld && shadow_kind && shadow_off_bytes), "bmhrl_adam_peer_f32: shadow tables");
@@ -271,7 +296,20 @@ extern "C" int bmhrl_adam_peer_f32(float* const* params, const float* const* gra
     adam_peer_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels, chunk_tensor,
                                                                  chunk_start, step_counts, lr, beta1, beta2, eps, grad_scale,
                                                                  shadow, shadow_cols, shadow_ld, shadow_kind, og, op, os,
-                                                                 n_ranks);
+                                                                 n_ranks, owner_only_master ? 1 : 0);
     BMHRL_POST_LAUNCH("adam_peer");
+    return BMHRL_OK;
+}
+
+extern "C" int bmhrl_peer_bcast_params_f32(float* const* params, const long long* numels, const int* chunk_tensor,
+                                           const int* chunk_start, int n_chunks, const long long* param_off_bytes, int n_ranks,
+                                           void* stream) {
+    BMHRL_CHECK_ARG(params && numels && chunk_tensor && chunk_start && param_off_bytes && n_ranks >= 1 && n_ranks <= PEER_MAX,
+                    "bmhrl_peer_bcast_params_f32: bad arguments");
+    if (n_chunks <= 0) return BMHRL_OK;
+    PeerOff op;
+    fill_off(op, param_off_bytes, n_ranks);
+    peer_bcast_params_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, numels, chunk_tensor, chunk_start, op, n_ranks);
+    BMHRL_POST_LAUNCH("peer_bcast_params");
     return BMHRL_OK;
 }

@@ -1121,6 +1121,10 @@ class FusedAdam:
         `step_peer` (gradient sum over the ranks + Adam + parameter broadcast in one kernel) works on."""
         self.params = list(params)
         self.peer = peer
+        # step_peer: keep the fp32 master of weights that have a bf16 shadow on the owning rank only (bf16 math mode reads
+        # such weights through the shadow); `gather_params()` completes every rank's fp32 copies again
+        self.owner_only_master = False
+        self._masters_stale = False
         if not self.params:
             raise RuntimeError("FusedAdam: no parameters")
         dev = self.params[0].device
@@ -1293,12 +1297,39 @@ class FusedAdam:
                 if arena is None or not all(arena.contains(p) for p in ptrs):
                     raise RuntimeError("FusedAdam.step_peer: the weight shadows must live in the peer group's shadow arena "
                                        "(ops16.SHADOWS.arena) so that every rank's copy can be written")
+        if self.owner_only_master and sh is not None:
+            from . import ops16
+            if not BF16:
+                raise RuntimeError("FusedAdam.step_peer(owner_only_master): only in bf16 math mode (other modes read the fp32 "
+                                   "weights, which then exist on their owner only)")
+            if any(g["uncovered"] for g in ops16.SHADOWS.groups.values()):
+                raise RuntimeError("FusedAdam.step_peer(owner_only_master): a weight sits in two shadow groups (the second "
+                                   "is re-cast from the fp32 master on every use): keep the masters replicated")
         go, po = peer.arena(peer.GRAD).offsets(), peer.arena(peer.PARAM).offsets()
         so = peer.arena(peer.SHADOW).offsets() if sh is not None else None
         LIB.call("bmhrl_adam_peer_f32", _p(self._pp), _p(self._gp), _p(self._mp), _p(self._vp), _p(self._ne), _p(ct), _p(cs),
                  n_chunks, _p(self.step_counts), self.lr, self.betas[0], self.betas[1], self.eps, self.grad_scale,
                  None if sh is None else _p(sh[0]), None if sh is None else _p(sh[1]), None if sh is None else _p(sh[2]),
-                 None if sh is None else _p(sh[3]), go, po, so, peer.world, st)
+                 None if sh is None else _p(sh[3]), go, po, so, peer.world,
+                 1 if (self.owner_only_master and sh is not None) else 0, st)
+        if self.owner_only_master and sh is not None:
+            self._masters_stale = True
+
+    def gather_params(self):
+        """After steps with `owner_only_master`: every owner pushes the fp32 values of its chunks to all ranks, so that
+        every rank's parameters are complete again (state_dict / checkpoints, leaving bf16 math mode).  Collective over
+        the peer group: every rank calls it; returns when all ranks' pushes have landed."""
+        if self.peer is None or not getattr(self, "_masters_stale", False):
+            return
+        peer = self.peer
+        st = _stream()
+        act, ct, cs, n_act, n_chunks = self._peer_tables(None)
+        peer.barrier(peer.n_slots - 2)      # nobody is still inside a step
+        LIB.call("bmhrl_peer_bcast_params_f32", _p(self._pp), _p(self._ne), _p(ct), _p(cs), n_chunks,
+                 peer.arena(peer.PARAM).offsets(), peer.world, st)
+        peer.barrier(peer.n_slots - 2)
+        torch.cuda.current_stream().synchronize()
+        self._masters_stale = False
 
     def _shadow_tables(self):
         """Device tables of the bf16 / fp32 shadows (ops16.SHADOWS) of this optimiser's parameters: the Adam kernel

@@ -51,7 +51,7 @@ class BMHRLTrainer:
     scripts/train_rl_captioning_module.py:81-83) and the criteria (:66-67, :132)."""
 
     def __init__(self, cap_model, wv_model, mv_model, pad_idx=1, smoothing=0.7, lr=1e-4, modality="audio_video",
-                 grad_sync=None, scorer=None, random_synonyms=0.0, end_idx=3, peer=None):
+                 grad_sync=None, scorer=None, random_synonyms=0.0, end_idx=3, peer=None, owner_only_master=False):
         # feature_getter(..., random_synonyms=0.3) (captioning_bmrl_loops.py:487-528): the reference corrupts the INPUT
         # caption tokens of every training step; 0 (default) switches it off, which is what the parity goldens assume
         self.random_synonyms, self.end_idx = float(random_synonyms), int(end_idx)
@@ -65,6 +65,10 @@ class BMHRLTrainer:
         # replicated Adam; grad_sync still carries the scalar loss normaliser and the (tiny) value functions
         self.peer = peer
         self.cap_opt = ops.FusedAdam(used_parameters(cap_model), lr=lr, peer=peer)
+        # owner_only_master (peer mode, bf16 math mode only): fp32 masters of GEMM weights stay on the rank that owns their
+        # Adam state; the replicas compute with the broadcast bf16 shadows.  Call `cap_opt.gather_params()` before reading
+        # fp32 parameters on other ranks (state_dict / checkpoints / leaving bf16 mode).
+        self.cap_opt.owner_only_master = bool(owner_only_master) and peer is not None
         if peer is not None:
             n_el = self.cap_opt.flat_grad.numel()
             ops16.SHADOWS.arena = peer.arena(peer.SHADOW, int(2 * n_el * 1.15) + (32 << 20))

@@ -445,7 +445,13 @@ int bmhrl_adam_peer_f32(float* const* params, const float* const* grads, float* 
                         const float* step_counts, float lr, float beta1, float beta2, float eps, float grad_scale,
                         void* const* shadow, const int* shadow_cols, const int* shadow_ld, const int* shadow_kind,
                         const long long* grad_off_bytes, const long long* param_off_bytes, const long long* shadow_off_bytes,
-                        int n_ranks, void* stream);
+                        int n_ranks, int owner_only_master, void* stream);
+/* owner_only_master != 0: the fp32 value of a weight that has a bf16 shadow is stored on the owner only (the replicas
+ * compute with the shadow; 4 of 6 bytes per element and peer saved); the replicas' fp32 copies are stale until the owners
+ * push theirs with this call (same chunk lists as the owner's bmhrl_adam_peer_f32 calls; checkpoints, mode switches). */
+int bmhrl_peer_bcast_params_f32(float* const* params, const long long* numels, const int* chunk_tensor,
+                                const int* chunk_start, int n_chunks, const long long* param_off_bytes, int n_ranks,
+                                void* stream);
 
 /* ---- input side of the step (pipeline.cu) --------------------------------------------------------------------------- */
 /* pad_sequence + rgb + flow + padding mask in one pass over a ragged batch that arrived in ONE host->device copy:

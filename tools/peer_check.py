@@ -31,8 +31,9 @@ def build(mode, dev, rank):
     ops16.SHADOWS.clear()
     ops16.SHADOWS.arena = None
     ops.RNG.salt = 0   # same dropout salts (handed out per call site on first use) in both builds
-    peer = PeerGroup(dev) if mode == "peer" else None
-    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7, grad_sync=GradSync(), peer=peer)
+    peer = PeerGroup(dev) if mode.startswith("peer") else None
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7, grad_sync=GradSync(), peer=peer,
+                      owner_only_master=(mode == "peer-owner"))
     tr.teach_warmstart()
     ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode("bf16")
@@ -51,14 +52,20 @@ def main():
     batches = [synth.synthetic_batch(V=bench.VOC, seed=77 + rank + 100 * i, **bench.SHAPE) for i in range(3)]
     batches = [{k: v.to(dev) for k, v in b.items() if torch.is_tensor(v)} for b in batches]
     out = {}
-    for mode in ("nccl", "peer"):
+    for mode in ("nccl", "peer", "peer-owner"):
         tr, model = build(mode, dev, rank)
         losses = []
         for b in batches:
             losses.append(float(tr.warmstart_step(b)))
         torch.cuda.synchronize()
+        if mode == "peer-owner":
+            stale = sum(0 if torch.equal(p.detach(), out["peer"][0][n]) else 1 for n, p in model.named_parameters())
+            tr.cap_opt.gather_params()
+            torch.cuda.synchronize()
+            if rank == 0:
+                print(f"peer-owner: {stale} tensors of rank 0 differ from the replicated run before gather_params()")
         out[mode] = ({n: p.detach().clone() for n, p in model.named_parameters()}, losses)
-        if mode == "peer":
+        if mode.startswith("peer"):
             # every rank holds the same parameters; shadows = cast of the parameters
             chk = torch.stack([p.detach().double().sum() for p in model.parameters()]).sum().reshape(1)
             allc = [torch.zeros_like(chk) for _ in range(world)]
@@ -78,7 +85,7 @@ def main():
                 if w16 is not None and not torch.equal(w16, p.detach().to(torch.bfloat16)):
                     bad += 1
             if rank == 0:
-                print(f"peer: all {world} ranks hold the same parameters: {same}; stale bf16 shadows: {bad}")
+                print(f"{mode}: all {world} ranks hold the same parameters: {same}; stale bf16 shadows: {bad}")
         if os.environ.get("PEER_CHECK_NO_TIMING"):
             continue
         # timing as a CUDA graph
@@ -99,12 +106,13 @@ def main():
         if rank == 0:
             print(f"{mode}: {float(t) * 1e3:.1f} us per step on {world} GPUs (max over ranks), losses {losses}")
         del runner, tr, model
-    pa, pb = out["nccl"][0], out["peer"][0]
-    worst = max(float((pa[n] - pb[n]).abs().max() / (pa[n].abs().max() + 1e-12)) for n in pa)
-    nd = sum(0 if torch.equal(pa[n], pb[n]) else 1 for n in pa)
-    if rank == 0:
-        print(f"nccl vs peer after 3 steps: {nd} of {len(pa)} tensors differ, worst relative difference {worst:.3e}; "
-              f"losses nccl {out['nccl'][1]} peer {out['peer'][1]}")
+    for other in ("peer", "peer-owner"):
+        pa, pb = out["nccl"][0], out[other][0]
+        worst = max(float((pa[n] - pb[n]).abs().max() / (pa[n].abs().max() + 1e-12)) for n in pa)
+        nd = sum(0 if torch.equal(pa[n], pb[n]) else 1 for n in pa)
+        if rank == 0:
+            print(f"nccl vs {other} after 3 steps: {nd} of {len(pa)} tensors differ, worst relative difference {worst:.3e}; "
+                  f"losses nccl {out['nccl'][1]} {other} {out[other][1]}")
     sys.stdout.flush()
     dist.barrier()
     os._exit(0)

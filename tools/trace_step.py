@@ -41,7 +41,8 @@ def main():
     if world > 1 and os.environ.get("BMHRL_DP", "peer") == "peer":
         from bmhrl_b200.peer import PeerGroup
         peer = PeerGroup(dev)
-    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7, grad_sync=sync, peer=peer)
+    tr = BMHRLTrainer(model, wv.to(dev), mv.to(dev), pad_idx=1, smoothing=0.7, grad_sync=sync, peer=peer,
+                      owner_only_master=os.environ.get("BMHRL_OWNER_MASTER", "1") != "0")
     {"warmstart": tr.teach_warmstart, "worker": tr.teach_worker, "manager": tr.teach_manager}[workload]()
     ops.manual_seed(1234 + rank, dev)
     ops.set_math_mode(os.environ.get("BMHRL_MATH", "bf16"))
