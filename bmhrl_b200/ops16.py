@@ -412,6 +412,52 @@ def _wgrad(dz16, x16, weights, n_each):
     return outs
 
 
+_ONES16 = {}   # device index -> (1, L) bf16 row of ones: the B operand that turns a bias gradient into a GEMM problem
+
+
+def _ones_row(device, n):
+    dev = torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    t = _ONES16.get(idx)
+    if t is None or t.shape[1] < n:
+        if torch.cuda.is_current_stream_capturing():
+            return None     # never allocate a process-wide buffer from inside a graph's private pool
+        t = torch.ones(1, pad8(max(n, 4096)), device=dev, dtype=_BF16)
+        _ONES16[idx] = t
+    return t
+
+
+FUSE_BGRAD = True   # bias gradients as one more problem of the weight-gradient launch (switch for experiments / tests)
+
+
+def _wbgrad(dz16, x16, weights, biases, n_each):
+    """Weight AND bias gradients of the (stacked) linear layers that produced dz16 from x16: (gw, gb), same convention as
+    _wgrad / _bgrad16.  When everything accumulates into FusedAdam slices the bias gradient db = dZ^T 1 rides along as a
+    second problem of the SAME tensor-core launch (A = dZ^T as for dW, B = a row of ones, N = 1): no column-sum kernel,
+    fixed summation order (one CTA per 128 outputs)."""
+    from . import ops
+    M = dz16.shape[0]
+    K = x16.shape[1]
+    ok = (FUSE_BGRAD and biases is not None and len(biases) == len(weights)
+          and all(w.requires_grad and ops._gbuf(w) is not None for w in weights)
+          and all(b is not None and b.requires_grad and ops._gbuf(b) is not None for b in biases))
+    ones = _ones_row(dz16.device, M) if ok else None
+    if ones is None:
+        return _wgrad(dz16, x16, weights, n_each), (_bgrad16(dz16, biases, n_each) if biases is not None else [None] * len(weights))
+    wd = [ops._gbuf(w) for w in weights]
+    bd = [ops._gbuf(b) for b in biases]
+    n_tot = dz16.shape[1]
+    probs = [gemm_problem(dz16, 1, x16, 1, n_tot, K, M, C32=wd[0], beta=1.0, seg=(n_each, wd[1:]) if len(weights) > 1 else None),
+             gemm_problem(dz16, 1, ones, 0, n_tot, 1, M, C32=bd[0], beta=1.0, seg=(n_each, bd[1:]) if len(biases) > 1 else None)]
+    if ops.CONCURRENT:
+        ops._WGRAD_KEEP.append((dz16, x16))
+        with torch.cuda.stream(ops.wgrad_stream(dz16.device, wd[0])):
+            gemm_group(probs)
+    else:
+        gemm_group(probs)
+    return [None] * len(weights), [None] * len(biases)
+
+
 def _bgrad16(dz16, biases, n_each):
     """bias gradients = column sums of a bf16 dZ (deterministic); same return convention as _wgrad."""
     from . import ops
@@ -541,11 +587,11 @@ class _AttnBlock(torch.autograd.Function):
         dzo = grad16_of(dy, M, Dq, cfg["p_res"], cfg["s_out"])
         if dzo is None:
             dzo = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s_out"])
-        dbo = _bgrad16(dzo, [bo], Dq)[0]
         wo16, _ = SHADOWS.get([Wo], [bo])
         do16 = empty16(M, D, dev)
         gemm_group([gemm_problem(dzo, 0, wo16, 1, M, D, Dq, b_static=True, drop_p=cfg["p_attn"], rng=cfg["rng"], salt=cfg["s_core"], C16=do16)])
-        dWo = _wgrad(dzo, o16, [Wo], Dq)[0]
+        gwo, gbo = _wbgrad(dzo, o16, [Wo], [bo], Dq)
+        dWo, dbo = gwo[0], gbo[0]
         # ---- attention core
         if self_att:
             dz = empty16(M, 3 * D, dev)
@@ -563,8 +609,7 @@ class _AttnBlock(torch.autograd.Function):
             dn = torch.empty(M, Dq, device=dev, dtype=_F32) if (need_x or ln_g is not None) else None
             if dn is not None:
                 gemm_group([gemm_problem(dz, 0, w16, 1, M, Dq, 3 * D, b_static=True, C32=dn)])
-            gw = _wgrad(dz, n16, [Wq, Wk, Wv], D)
-            gb = _bgrad16(dz, [bq, bk, bv], D)
+            gw, gb = _wbgrad(dz, n16, [Wq, Wk, Wv], [bq, bk, bv], D)
         else:
             wq16, _ = SHADOWS.get([Wq], [bq])
             wkv16, _ = SHADOWS.get([Wk, Wv], [bk, bv])
@@ -577,8 +622,9 @@ class _AttnBlock(torch.autograd.Function):
                 probs.append(gemm_problem(dzkv, 0, wkv16, 1, Mk, Dkv, 2 * D, b_static=True, C32=dkv.view(Mk, Dkv)))
             if probs:
                 gemm_group(probs)
-            gw = _wgrad(dq, n16, [Wq], D) + _wgrad(dzkv, m16, [Wk, Wv], D)
-            gb = _bgrad16(dq, [bq], D) + _bgrad16(dzkv, [bk, bv], D)
+            gw1, gb1 = _wbgrad(dq, n16, [Wq], [bq], D)
+            gw2, gb2 = _wbgrad(dzkv, m16, [Wk, Wv], [bk, bv], D)
+            gw, gb = gw1 + gw2, gb1 + gb2
         # ---- LayerNorm backward with the skip gradient folded in
         dx = dg = dbeta = None
         if ln_g is not None:
@@ -644,17 +690,17 @@ class _FfnBlock(torch.autograd.Function):
         dz2 = grad16_of(dy, M, D, cfg["p_res"], cfg["s2"])
         if dz2 is None:
             dz2 = cast16(dy2, drop_p=cfg["p_res"], rng=cfg["rng"], salt=cfg["s2"])
-        db2 = _bgrad16(dz2, [b2], D)[0]
         w1, _ = SHADOWS.get([W1], [b1])
         w2, _ = SHADOWS.get([W2], [b2])
         dz1 = empty16(M, F_, dev)   # dZ_1 = (dZ_2 W_2) o [h > 0] / (1 - p1): relu and dropout gates in the GEMM epilogue
         gs = 1.0 / (1.0 - cfg["p1"]) if cfg["p1"] > 0 else 1.0
         gemm_group([gemm_problem(dz2, 0, w2, 1, M, F_, D, b_static=True, gate=h16, gate_scale=gs, C16=dz1)])
-        dW2 = _wgrad(dz2, h16, [W2], D)[0]
+        g2w, g2b = _wbgrad(dz2, h16, [W2], [b2], D)
+        dW2, db2 = g2w[0], g2b[0]
         dn = torch.empty(M, D, device=dev, dtype=_F32)
         gemm_group([gemm_problem(dz1, 0, w1, 1, M, D, F_, b_static=True, C32=dn)])
-        dW1 = _wgrad(dz1, n16, [W1], F_)[0]
-        db1 = _bgrad16(dz1, [b1], F_)[0]
+        g1w, g1b = _wbgrad(dz1, n16, [W1], [b1], F_)
+        dW1, db1 = g1w[0], g1b[0]
         dx = dg = dbeta = None
         if ln_g is not None:
             need_aff = ln_g.requires_grad
@@ -702,13 +748,16 @@ class _Linear16(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         dz = cast16(dy2, drop_p=cfg["p"], rng=cfg["rng"], salt=cfg["salt"])
-        db = _bgrad16(dz, [b], N)[0]
         dx = None
         if ctx.needs_input_grad[0]:
             w16, _ = SHADOWS.get([W], [b])
             dx = torch.empty(xshape, device=dev, dtype=_F32)
             gemm_group([gemm_problem(dz, 0, w16, 1, M, K, N, b_static=True, C32=dx.view(M, K))])
-        dW = _wgrad(dz, x16, [W], N)[0]
+        if b is not None:
+            gw, gb = _wbgrad(dz, x16, [W], [b], N)
+            dW, db = gw[0], gb[0]
+        else:
+            dW, db = _wgrad(dz, x16, [W], N)[0], None
         return dx, dW, db, None
 
 
@@ -811,8 +860,11 @@ class _VocabStats(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty(xshape, device=dev, dtype=_F32)
             gemm_group([gemm_problem(dl, 0, w16, 1, M, K, V, b_static=True, C32=dx.view(M, K))])
-        dW = _wgrad(dl, x16, [W], V)[0]
-        db = _bgrad16(dl, [b], V)[0] if b is not None else None
+        if b is not None:
+            gw, gb = _wbgrad(dl, x16, [W], [b], V)
+            dW, db = gw[0], gb[0]
+        else:
+            dW, db = _wgrad(dl, x16, [W], V)[0], None
         return dx, dW, db, None, None, None, None, None, None
 
 
