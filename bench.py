@@ -251,25 +251,32 @@ TRAFFIC_SOURCE = ("profiles/r02_gemm_traffic.json (committed ncu capture of the 
 
 
 def gemm_roofline16(recorded, iters=20):
-    """bf16 math mode: re-issues every problem of the step's grouped GEMM launches (exact M, N, K and operand majors,
-    scratch operands, one problem per launch) and times the sequence with CUDA events on the launching stream."""
+    """bf16 math mode: re-issues the step's grouped GEMM launches as they ran (the same problems per launch: exact M, N, K
+    and operand majors, scratch operands; a weight-gradient launch carries its bias-gradient problem along) and times the
+    sequence with CUDA events on the launching stream.  Returns (FLOPs per launch, seconds per launch, launches)."""
     from bmhrl_b200 import ops16
     if not recorded:
         return 0.0, 0.0, 0
     dev = torch.device("cuda")
-    probs, flops = [], 0.0
-    for (M, N, K, a_mn, b_mn) in recorded:
-        flops += 2.0 * M * N * K
-        A = ops16.zeros16(K, M, dev) if a_mn else ops16.zeros16(M, K, dev)
-        B = ops16.zeros16(K, N, dev) if b_mn else ops16.zeros16(N, K, dev)
-        A.normal_()
-        B.normal_()
-        probs.append(ops16.gemm_problem(A, a_mn, B, b_mn, M, N, K, C16=ops16.empty16(M, N, dev)))
+    groups, flops = [], 0.0
+    for launch in recorded:
+        probs = []
+        for (M, N, K, a_mn, b_mn) in launch:
+            flops += 2.0 * M * N * K
+            A = ops16.zeros16(K, M, dev) if a_mn else ops16.zeros16(M, K, dev)
+            B = ops16.zeros16(K, N, dev) if b_mn else ops16.zeros16(N, K, dev)
+            A.normal_()
+            B.normal_()
+            if N % 8:   # bias-gradient problem (N = 1): fp32 output like in the step
+                probs.append(ops16.gemm_problem(A, a_mn, B, b_mn, M, N, K, C32=torch.zeros(M, N, device=dev)))
+            else:
+                probs.append(ops16.gemm_problem(A, a_mn, B, b_mn, M, N, K, C16=ops16.empty16(M, N, dev)))
+        groups.append(probs)
     torch.cuda.synchronize()
 
     def run():
-        for p in probs:
-            ops16.gemm_group([p])
+        for g in groups:
+            ops16.gemm_group(g)
     for _ in range(3):
         run()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -280,7 +287,7 @@ def gemm_roofline16(recorded, iters=20):
     e1.record()
     torch.cuda.synchronize()
     sec = e0.elapsed_time(e1) / 1e3 / iters
-    n = len(probs)
+    n = len(groups)
     return flops / n, sec / n, n
 
 

@@ -31,7 +31,7 @@ class GemmDesc(ctypes.Structure):
 
 
 _DESC_CHECKED = [False]
-RECORD = None  # bench.py: when a list, every problem appends (M, N, K, a_mn, b_mn)
+RECORD = None  # bench.py: when a list, every LAUNCH appends the list of its problems' (M, N, K, a_mn, b_mn)
 
 
 def _stream():
@@ -114,7 +114,7 @@ def gemm_group(problems):
         _DESC_CHECKED[0] = True
     n = len(problems)
     if RECORD is not None:
-        RECORD.extend((p.M, p.N, p.K, p.a_mn, p.b_mn) for p in problems)
+        RECORD.append([(p.M, p.N, p.K, p.a_mn, p.b_mn) for p in problems])
     arr = (GemmDesc * n)(*problems)
     LIB.call("bmhrl_gemm_bf16_group", ctypes.cast(arr, ctypes.c_void_p), n, _stream())
 
