@@ -83,8 +83,68 @@ __global__ void generate_synonyms_kernel(const long long* __restrict__ cap, long
     }
 }
 
+// The three masks of make_masks (model/masking.py:18-47, modality audio_video) and the token count of the loss
+// normaliser in ONE launch (the reference builds them with ~12 small tensor ops in front of every forward pass):
+//   V_mask[b, s]    = rgb[b, s, 0]   != 0        (rgb only, before flow is added)
+//   A_mask[b, s]    = audio[b, s, 0] != 0
+//   C_mask[b, i, j] = (cap[b, j] != pad) && j <= i
+//   *n_tokens       = #{ y != pad }                (captioning_bmrl_loops.py:1156: the normaliser of the summed loss)
+__global__ void make_masks_kernel(const float* __restrict__ rgb, long long rgb_bs, long long rgb_ss, int Sv,
+                                  const float* __restrict__ aud, long long aud_bs, long long aud_ss, int Sa,
+                                  const long long* __restrict__ cap, int L, long long pad, int B,
+                                  unsigned char* __restrict__ vm, unsigned char* __restrict__ am,
+                                  unsigned char* __restrict__ cm, const long long* __restrict__ y, long long n_y,
+                                  long long* __restrict__ n_tokens, int mask_blocks) {
+    if ((int)blockIdx.x < mask_blocks) {
+        const long long nv = (long long)B * Sv, na = (long long)B * Sa, nc = cm ? (long long)B * L * L : 0;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv + na + nc;
+             i += (long long)mask_blocks * blockDim.x) {
+            if (i < nv) {
+                vm[i] = rgb[(i / Sv) * rgb_bs + (i % Sv) * rgb_ss] != 0.f;
+            } else if (i < nv + na) {
+                const long long k = i - nv;
+                am[k] = aud[(k / Sa) * aud_bs + (k % Sa) * aud_ss] != 0.f;
+            } else {
+                const long long k = i - nv - na;
+                const int j = (int)(k % L), q = (int)((k / L) % L), b = (int)(k / ((long long)L * L));
+                cm[k] = (j <= q && cap[(long long)b * L + j] != pad) ? 1 : 0;
+            }
+        }
+        return;
+    }
+    // the last block: token count (integers: any order gives the same sum)
+    __shared__ long long red[256];
+    long long c = 0;
+    for (long long i = threadIdx.x; i < n_y; i += blockDim.x) c += y[i] != pad;
+    red[threadIdx.x] = c;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *n_tokens = red[0];
+}
+
 }  // namespace bmhrl
 using namespace bmhrl;
+
+extern "C" int bmhrl_make_masks(const float* rgb, long long rgb_batch_stride, long long rgb_frame_stride, int Sv,
+                                const float* audio, long long audio_batch_stride, long long audio_frame_stride, int Sa,
+                                const long long* captions, int L, long long pad_idx, int B, unsigned char* V_mask,
+                                unsigned char* A_mask, unsigned char* C_mask, const long long* targets, long long n_targets,
+                                long long* n_tokens, void* stream) {
+    BMHRL_CHECK_ARG(rgb && audio && V_mask && A_mask && B > 0 && Sv > 0 && Sa > 0, "bmhrl_make_masks: bad arguments");
+    BMHRL_CHECK_ARG(!C_mask || (captions && L > 0), "bmhrl_make_masks: C_mask needs the captions");
+    BMHRL_CHECK_ARG(!n_tokens || (targets && n_targets >= 0), "bmhrl_make_masks: n_tokens needs the targets");
+    const long long n = (long long)B * (Sv + Sa) + (C_mask ? (long long)B * L * L : 0);
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    make_masks_kernel<<<(int)blocks + (n_tokens ? 1 : 0), 256, 0, (cudaStream_t)stream>>>(
+        rgb, rgb_batch_stride, rgb_frame_stride, Sv, audio, audio_batch_stride, audio_frame_stride, Sa, captions, L, pad_idx, B,
+        V_mask, A_mask, C_mask, targets, n_targets, n_tokens, (int)blocks);
+    BMHRL_POST_LAUNCH("make_masks");
+    return BMHRL_OK;
+}
 
 extern "C" int bmhrl_pad_features_f32(const float* a, const float* b, const int* offsets, float* out, unsigned char* mask,
                                       int B, int S, int D, float pad_a, float pad_b, void* stream) {

@@ -1102,6 +1102,34 @@ def segment_scan(probs, expected, seg):
     return _SegmentScan.apply(probs, expected, seg)
 
 
+def make_masks_fused(rgb, audio, cap_in, pad_idx, targets=None):
+    """model/masking.py:28-53 (modality audio_video) in one launch: {'V_mask' (B,1,Sv), 'A_mask' (B,1,Sa), 'C_mask'
+    (B,L,L)} bool tensors, plus the int64 count of non-pad `targets` (the loss normaliser) when targets are given."""
+    for t, nm in ((rgb, "rgb"), (audio, "audio")):
+        if not (torch.is_tensor(t) and t.is_cuda and t.dtype == _F32 and t.dim() == 3):
+            raise RuntimeError(f"make_masks_fused: `{nm}` must be a CUDA fp32 (B, S, D) tensor (there is no CPU fallback)")
+    B, Sv, Sa = rgb.shape[0], rgb.shape[1], audio.shape[1]
+    dev = rgb.device
+    vm = torch.empty(B, 1, Sv, device=dev, dtype=torch.bool)
+    am = torch.empty(B, 1, Sa, device=dev, dtype=torch.bool)
+    cm, L = None, 0
+    if cap_in is not None:
+        cap_in = cap_in.contiguous()
+        L = cap_in.shape[-1]
+        cm = torch.empty(B, L, L, device=dev, dtype=torch.bool)
+    nt = None
+    if targets is not None:
+        targets = targets.contiguous()
+        nt = torch.empty((), device=dev, dtype=torch.int64)
+    LIB.call("bmhrl_make_masks", rgb.data_ptr(), rgb.stride(0), rgb.stride(1), Sv, audio.data_ptr(), audio.stride(0),
+             audio.stride(1), Sa, _p(cap_in), L, int(pad_idx), B, vm.data_ptr(), am.data_ptr(), _p(cm), _p(targets),
+             0 if targets is None else targets.numel(), _p(nt), _stream())
+    masks = {"V_mask": vm, "A_mask": am}
+    if cm is not None:
+        masks["C_mask"] = cm
+    return masks, nt
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # optimiser
 # ----------------------------------------------------------------------------------------------------------------

@@ -149,9 +149,15 @@ class BMHRLTrainer:
         if "V" in batch:
             masks = {"V_mask": batch["V_mask"], "A_mask": batch["A_mask"], "C_mask": c_mask(cap_in, self.pad_idx)}
             return (batch["V"], batch["audio"]), cap_in, y.contiguous(), masks
-        masks = make_masks({"rgb": batch["rgb"], "flow": batch["flow"], "audio": batch["audio"]}, cap_in,
-                           self.modality, self.pad_idx)
-        return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y.contiguous(), masks
+        y = y.contiguous()
+        if self.modality == "audio_video" and batch["rgb"].is_cuda and batch["rgb"].dtype == torch.float32:
+            # the three masks and the token count of the loss normaliser in one launch (ops.make_masks_fused)
+            masks, n_local = ops.make_masks_fused(batch["rgb"], batch["audio"], cap_in, self.pad_idx, targets=y)
+            self._n_tokens_local = (y, n_local)
+        else:
+            masks = make_masks({"rgb": batch["rgb"], "flow": batch["flow"], "audio": batch["audio"]}, cap_in,
+                               self.modality, self.pad_idx)
+        return ((batch["rgb"], batch["flow"]), batch["audio"]), cap_in, y, masks
 
     def _syn_salt(self):
         if not hasattr(self, "_synsalt"):
@@ -261,7 +267,9 @@ class BMHRLTrainer:
         communication stream BEFORE the forward pass (the ranks have just left the previous step's gradient
         all-reduce together), instead of as a rendezvous in the middle of the step.  Returns a thunk that makes the
         current stream wait for it and yields the global count."""
-        local = (y != self.pad_idx).sum()
+        pre = getattr(self, "_n_tokens_local", None)
+        self._n_tokens_local = None
+        local = pre[1] if (pre is not None and pre[0] is y) else (y != self.pad_idx).sum()
         world = getattr(self.grad_sync, "world", 1) if self.grad_sync is not None else 1
         if world <= 1 or not self.overlap_grad_sync or not local.is_cuda:
             return lambda: self._global_tokens(local)

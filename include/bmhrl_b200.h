@@ -463,6 +463,14 @@ int bmhrl_peer_bcast_params_f32(float* const* params, const long long* numels, c
  * padding rows stay VISIBLE exactly as they do there; pad_a = 0 gives the length mask. */
 int bmhrl_pad_features_f32(const float* a, const float* b, const int* offsets, float* out, unsigned char* mask, int B, int S,
                            int D, float pad_a, float pad_b, void* stream);
+/* make_masks (model/masking.py:18-47, modality audio_video) + the token count of the loss normaliser
+ * (captioning_bmrl_loops.py:1156) in one launch: V_mask (B,Sv) = rgb[b,s,0] != 0, A_mask (B,Sa) = audio[b,s,0] != 0,
+ * C_mask (B,L,L) = (captions[b,j] != pad) && j <= i (NULL: not wanted), *n_tokens = #{targets != pad} (NULL: not wanted).
+ * Masks are bytes 0 / 1 (torch.bool storage); strides in elements. */
+int bmhrl_make_masks(const float* rgb, long long rgb_batch_stride, long long rgb_frame_stride, int Sv, const float* audio,
+                     long long audio_batch_stride, long long audio_frame_stride, int Sa, const long long* captions, int L,
+                     long long pad_idx, int B, unsigned char* V_mask, unsigned char* A_mask, unsigned char* C_mask,
+                     const long long* targets, long long n_targets, long long* n_tokens, void* stream);
 /* generate_synonyms (epoch_loops/captioning_bmrl_loops.py:510-528) on the device: per row, up to and including the first
  * end token (which becomes pad_idx and ends the row's scan): with probability p a token is replaced -- by pad_idx when
  * u2 < 0.8, by a random word of [2, V-1] when u2 >= 0.9, by itself otherwise.  u1 / u2 (fp32) and rand_words (int64),

@@ -424,6 +424,37 @@ def test_errors_are_loud(gpu_lib):
         ops.layer_norm(torch.randn(4, 8, device="cuda").double(), torch.ones(8, device="cuda"), torch.zeros(8, device="cuda"))
 
 
+def test_make_masks_fused_equals_reference_masks(gpu_lib):
+    """ops.make_masks_fused (one launch) against model/masking.py:28-53 as restated in bmhrl_b200.model.masking and in the
+    oracle, including the reference's quirks (component 0 of rgb only; a zero first component masks a real frame), ragged
+    padding, non-contiguous feature views, and the non-pad target count of the loss normaliser.  Bit-exact."""
+    from bmhrl_b200 import ops
+    from bmhrl_b200.model.masking import make_masks
+    g = _g(61)
+    for B, Sv, Sa, L in ((16, 30, 80, 20), (3, 7, 5, 1), (1, 1, 1, 9)):
+        rgb = torch.randn(B, Sv, 1024, generator=g)
+        aud = torch.randn(B, Sa, 128, generator=g)
+        rgb[0, Sv // 2:, :] = 0
+        aud[B - 1, :, 0] = 0            # real frames whose first component is 0 are masked too
+        rgb[B // 2, 0, 0] = 0
+        cap = torch.randint(4, 50, (B, L + 1), generator=g)
+        cap[0, L // 2:] = 1
+        cap_in, y = cap[:, :-1].contiguous(), cap[:, 1:].contiguous()
+        want = make_masks({"rgb": rgb, "flow": rgb, "audio": aud}, cap_in, "audio_video", 1)
+        got, nt = ops.make_masks_fused(rgb.cuda(), aud.cuda(), cap_in.cuda(), 1, targets=y.cuda())
+        for k in ("V_mask", "A_mask", "C_mask"):
+            assert got[k].dtype == torch.bool and got[k].shape == want[k].shape, k
+            assert torch.equal(got[k].cpu(), want[k].bool()), (k, B)
+        assert int(nt) == int((y != 1).sum())
+        om = O.make_masks(rgb, aud, cap_in, 1)
+        assert torch.equal(got["C_mask"].cpu(), om["C_mask"]) and torch.equal(got["V_mask"].cpu(), om["V_mask"])
+        # a strided view (every second frame) and no captions / targets
+        got2, nt2 = ops.make_masks_fused(rgb.cuda()[:, ::2], aud.cuda()[:, ::2], None, 1)
+        assert nt2 is None and "C_mask" not in got2
+        assert torch.equal(got2["V_mask"].cpu(), (rgb[:, ::2, 0] != 0).unsqueeze(1))
+        assert torch.equal(got2["A_mask"].cpu(), (aud[:, ::2, 0] != 0).unsqueeze(1))
+
+
 @pytest.mark.parametrize("cell", ["lstm", "gru"])
 def test_rnn_layer_variants_bit_identical(gpu_lib, cell):
     """The three forms of one recurrent layer -- tagged-exchange persistent kernel (default), grid-barrier persistent
