@@ -464,12 +464,13 @@ def run_gpu(args):
     barrier()
     sec = e0.elapsed_time(e1) / 1e3
     # ---- end-to-end timing through the public step API with host buffers
-    def estep(r, i):
+    def estep(r, i, asynchronous=False):
         # the public step API: this batch from pinned host memory (+ the captions of the batch that follows, which a
         # prefetching loader has at hand, for the pipelined frozen critic)
+        f = r.step_async if asynchronous else r.step
         if getattr(r, "pipeline_critic", False):
-            return r.step(host[i % n_host], host[(i + 1) % n_host])
-        return r.step(host[i % n_host])
+            return f(host[i % n_host], host[(i + 1) % n_host])
+        return f(host[i % n_host])
     for i in range(args.warmup):
         float(estep(runner, i)[0])
     barrier()
@@ -477,8 +478,19 @@ def run_gpu(args):
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = 0.0
-    for i in range(args.steps):
-        last = float(estep(runner, i)[0])  # D2H read of the step's loss (synchronises)
+    if args.sync_loss or not hasattr(runner, "step_async"):
+        for i in range(args.steps):
+            last = float(estep(runner, i)[0])  # D2H read of the step's loss (synchronises every step)
+    else:
+        # every step's loss is copied to pinned host memory and READ, one step late: the host issues step i + 1 before it
+        # waits for the loss of step i (StepRunner.step_async), like any training loop that logs its loss
+        pending = None
+        for i in range(args.steps):
+            h = estep(runner, i, asynchronous=True)
+            if pending is not None:
+                last = pending.value()
+            pending = h
+        last = pending.value()
     e3.record()
     barrier()
     sec_e2e = max(e2.elapsed_time(e3) / 1e3, 0.0)
@@ -511,8 +523,17 @@ def run_gpu(args):
                 float(estep(r2, i)[0])
             barrier()
             p0.record()
+            pending = None
             for i in range(args.steps):
-                float(estep(r2, i)[0])
+                if args.sync_loss:
+                    float(estep(r2, i)[0])
+                else:
+                    h = estep(r2, i, asynchronous=True)
+                    if pending is not None:
+                        pending.value()
+                    pending = h
+            if pending is not None:
+                pending.value()
             p1.record()
             barrier()
             psec_e2e = p0.elapsed_time(p1) / 1e3
@@ -557,6 +578,8 @@ def run_gpu(args):
                                           if tr.cap_opt.owner_only_master else "") if peer is not None else
                                          "NCCL all-reduce of the flat gradient buffer overlapped with backward, replicated Adam"))),
             "e2e": {"value": clips / sec_e2e, "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "loss_read": ("float(loss) after every step" if args.sync_loss else
+                                  "every step's loss copied to pinned host memory and read one step late (step_async)"),
                     "ms_per_step": sec_e2e / args.steps * 1e3, "wall_ms_per_step": wall_e2e / args.steps * 1e3},
             "gpu_launches": graph_launches * (2 * args.steps + args.warmup) if graph_launches else launches_eager,
             "launches_per_step": graph_launches,
@@ -674,6 +697,9 @@ def main():
     ap.add_argument("--replicate-masters", action="store_true",
                     help="--dp peer: also broadcast the fp32 master of GEMM weights every step (default in bf16 mode: the "
                          "owner of a chunk keeps it, replicas compute with the broadcast bf16 shadow)")
+    ap.add_argument("--sync-loss", action="store_true",
+                    help="e2e leg: float(loss) right after every step (host stalls the GPU between steps) instead of reading "
+                         "every step's loss one step late from pinned memory (StepRunner.step_async)")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-pipeline", action="store_true",

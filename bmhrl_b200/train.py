@@ -428,6 +428,17 @@ class BMHRLTrainer:
         return cap_loss.detach(), value_loss.detach()
 
 
+class PendingLoss:
+    """A step's loss on its way to the host (StepRunner.step_async): at most four may be outstanding."""
+
+    def __init__(self, buf, event):
+        self.buf, self.event = buf, event
+
+    def value(self):
+        self.event.synchronize()
+        return float(self.buf)
+
+
 class StepRunner:
     """One training step as a CUDA graph over static input buffers.
 
@@ -570,6 +581,23 @@ class StepRunner:
             # caption_next holds -- this batch again -- for a possible repeat)
             self.prime()
         return self.replay()
+
+    def step_async(self, host_batch, next_host_batch=None):
+        """`step`, plus the device-to-host copy of the step's first result (the loss) into pinned memory, stream-ordered
+        behind the step: returns a `PendingLoss` whose `.value()` waits for exactly that copy.  A training loop reads the
+        loss of step i AFTER it has issued step i + 1, so the host never stalls the GPU between steps (with `float(loss)`
+        right after `step` the GPU idles while the host prepares and launches the next replay: ~0.1 ms per step here)."""
+        out = self.step(host_batch, next_host_batch)
+        ring = getattr(self, "_loss_ring", None)
+        if ring is None:
+            ring = self._loss_ring = [torch.empty((), dtype=out[0].dtype).pin_memory() for _ in range(4)]
+            self._loss_i = 0
+        buf = ring[self._loss_i % len(ring)]
+        self._loss_i += 1
+        buf.copy_(out[0].detach(), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(out[0].device))
+        return PendingLoss(buf, ev)
 
     def prime(self):
         """(Re)labels the batch that sits in the static buffers: needed once, before the first step of a stream of

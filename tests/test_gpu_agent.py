@@ -565,7 +565,7 @@ def test_pipelined_critic_equals_inline(gpu_lib, agent_sd, kind):
     from bmhrl_b200.train import BMHRLTrainer, StepRunner
     batches = [synth.synthetic_batch(B=4, Sv=10, Sa=14, L=7, V=VOC, seed=40 + i, ragged=True) for i in range(4)]
     res = []
-    for pipe in (False, True):
+    for pipe in (False, True, "async"):
         model, cfg = build_agent(agent_sd)
         tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD)
         (tr.teach_warmstart if kind == "warmstart" else tr.teach_worker)()
@@ -573,13 +573,24 @@ def test_pipelined_critic_equals_inline(gpu_lib, agent_sd, kind):
         from bmhrl_b200 import ops
         ops.manual_seed(3)
         ops.RNG.salt = 9000
-        run = StepRunner(tr, kind, batches[0], use_graph=True, warmup=2, pipeline_critic=pipe)
+        run = StepRunner(tr, kind, batches[0], use_graph=True, warmup=2, pipeline_critic=bool(pipe))
         losses = []
-        for i, b in enumerate(batches):
-            nxt = batches[i + 1] if i + 1 < len(batches) else None
-            losses.append(float(run.step(b, nxt)[0]) if pipe else float(run.step(b)[0]))
+        if pipe == "async":
+            # step_async: the loss of step i is read AFTER step i + 1 has been issued (pinned host copies, one step late)
+            pend = []
+            for i, b in enumerate(batches):
+                nxt = batches[i + 1] if i + 1 < len(batches) else None
+                pend.append(run.step_async(b, nxt))
+                if len(pend) > 1:
+                    losses.append(pend[-2].value())
+            losses.append(pend[-1].value())
+        else:
+            for i, b in enumerate(batches):
+                nxt = batches[i + 1] if i + 1 < len(batches) else None
+                losses.append(float(run.step(b, nxt)[0]) if pipe else float(run.step(b)[0]))
         torch.cuda.synchronize()
         res.append((losses, model.worker.core.projection.weight.detach().clone()))
-    for a, c in zip(*[r[0] for r in res]):
-        assert abs(a - c) <= 1e-6 * abs(c), res
-    assert rel(res[1][1], res[0][1]) < 1e-6
+    for other in res[1:]:
+        for a, c in zip(other[0], res[0][0]):
+            assert abs(a - c) <= 1e-6 * abs(c), res
+        assert rel(other[1], res[0][1]) < 1e-6
