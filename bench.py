@@ -439,7 +439,8 @@ def run_gpu(args):
             b["trg_caption"] = [" ".join(c.split()[:SHAPE["L"] - 2]) for c in b["trg_caption"]]
         tr.scorer = (CiderScorer(NS(itos=itos), corpus, "cpu", 0.9, 0.9) if args.scorer == "cider"
                      else BleuScorer(NS(itos=itos), "cpu", 0.9, 0.9))
-        runner = ScoredStepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3)
+        runner = ScoredStepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3,
+                                  pipeline_critic=not args.no_pipeline)
     else:
         runner = StepRunner(tr, args.workload, host[0], use_graph=not args.no_graph, warmup=3,
                             pipeline_critic=not args.no_pipeline)

@@ -486,14 +486,14 @@ class StepRunner:
             self.captured_launches = launch_count() - n0  # kernels of libbmhrl_b200 inside one graph replay
         self._need_prime = self.pipeline_critic
 
-    def _corrupt(self, caption):
+    def _corrupt(self, caption, rng=None):
         """Input tokens the model (and the critic) see: caption[:, :-1] after the reference's generate_synonyms."""
         t = self.trainer
         cap_in = caption[:, :-1].contiguous()
         if t.random_synonyms > 0:
             from . import data
             cap_in = data.generate_synonyms(cap_in, t.random_synonyms, t.cap_model.voc_size, t.end_idx, t.pad_idx,
-                                            salt=t._syn_salt())
+                                            salt=t._syn_salt(), rng=rng)
         return cap_in
 
     def _eager(self):
@@ -504,11 +504,17 @@ class StepRunner:
             return t.rl_step(self.static, self.kind == "worker", self.stabilize)
         dev = self.static["caption"].device
         cur = torch.cuda.current_stream(dev)
+        # the Philox state the next batch's token corruption draws from: a copy of the LIVE device state, taken (inside
+        # the graph, on this stream) before the step advances it.  Reading ops.RNG.current() on the side branch instead
+        # would capture the address of a snapshot made outside the graph -- the same draws in every replay.
+        if getattr(self, "rng_next", None) is None:
+            self.rng_next = ops.RNG.get_state(dev).clone()
+        self.rng_next.copy_(ops.RNG.get_state(dev))
         side = ops.side_stream(dev, 12)
         side.wait_stream(cur)
         with torch.cuda.stream(side), torch.no_grad(), ops.rnn_units_per_cta(self.critic_units_per_cta):
             # the NEXT batch's corruption + critic, beside this step, confined to a quarter of the SMs
-            nxt = self._corrupt(self.static["caption_next"])
+            nxt = self._corrupt(self.static["caption_next"], rng=self.rng_next)
             self.cap_in_next.copy_(nxt)
             self.labels_next.copy_(t.cap_model.segment_labels_of(self.cap_in_next))
         batch = {k: v for k, v in self.static.items() if k != "caption_next"}
@@ -636,7 +642,12 @@ class ScoredStepRunner:
     The autograd graph built while capturing A is consumed while capturing B; both captures share one memory pool, so
     the saved activations of A stay at fixed addresses.  Replays must alternate A, B like the captures did."""
 
-    def __init__(self, trainer, kind, example_batch, stabilize=False, use_graph=True, warmup=3):
+    def __init__(self, trainer, kind, example_batch, stabilize=False, use_graph=True, warmup=3, pipeline_critic=False):
+        """pipeline_critic (graphs only): the frozen critic -- the longest chain of graph A, which the host has to wait
+        for before it can score -- leaves graph A.  A third graph C labels the NEXT batch's (corrupted) captions on a side
+        stream while the host scores this batch and graph B runs; graph A reads the labels the previous step left behind.
+        `step(batch, next_batch)` then takes the captions of the batch that follows (None: this batch is labelled inline
+        first, correct but not pipelined)."""
         if trainer.scorer is None:
             raise RuntimeError("ScoredStepRunner needs BMHRLTrainer(scorer=...)")
         if kind not in ("worker", "manager"):
@@ -648,11 +659,24 @@ class ScoredStepRunner:
                        if k in ("rgb", "flow", "audio", "caption")}
         self.captions = list(example_batch["trg_caption"])
         self.use_graph = use_graph
-        self.graph_a = self.graph_b = None
+        self.graph_a = self.graph_b = self.graph_c = None
         self.score_buf = self.seg_buf = None
         self.scorer_seconds = 0.0
+        self.pipeline_critic = bool(pipeline_critic) and use_graph and hasattr(trainer.cap_model, "segment_labels_of")
+        self.critic_units_per_cta = int(os.environ.get("BMHRL_CRITIC_UPB", "16"))
         if not use_graph:
             return
+        if self.pipeline_critic:
+            self.static["caption_next"] = self.static["caption"].clone()
+            with torch.no_grad():
+                self.cap_in_cur = self._corrupt(self.static["caption"]).clone()
+                self.labels_cur = trainer.cap_model.segment_labels_of(self.cap_in_cur).clone()
+            self.cap_in_next = self.cap_in_cur.clone()
+            self.labels_next = self.labels_cur.clone()
+            self.critic_stream = ops.new_stream(dev.index if dev.index is not None else torch.cuda.current_device())
+            self.rng_next = ops.RNG.get_state(dev).clone()   # Philox state graph C draws from (see replay)
+            self._need_prime = True
+            torch.cuda.synchronize(dev)
         side = ops.warmup_stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
@@ -664,8 +688,15 @@ class ScoredStepRunner:
         n0 = launch_count()
         self.graph_a = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph_a):
-            trainer.rl_begin(self.static, self.train_worker)
-            self.st = trainer.rl_forward(self.static, self.train_worker)
+            batch_a = {k: v for k, v in self.static.items() if k != "caption_next"}
+            if self.pipeline_critic:
+                batch_a["caption_in"] = self.cap_in_cur
+                trainer.cap_model.precomputed_segment_labels = self.labels_cur
+            try:
+                trainer.rl_begin(batch_a, self.train_worker)
+                self.st = trainer.rl_forward(batch_a, self.train_worker)
+            finally:
+                trainer.cap_model.precomputed_segment_labels = None
             if getattr(trainer, "_zero_join", None) is not None:   # the gradient memset belongs to THIS graph
                 trainer._zero_join()
                 trainer._zero_join = None
@@ -680,8 +711,30 @@ class ScoredStepRunner:
         with torch.cuda.graph(self.graph_b, pool=self.graph_a.pool()):
             losses = trainer.rl_tail(self.st, self.score_buf, self.seg_buf, self.train_worker, self.stabilize)
             self.out = trainer.rl_finish(losses[0], losses[1], self.train_worker)
+        if self.pipeline_critic:
+            # graph C (a pool of its own: it runs BESIDE A / the host part / B): corruption + critic of the next batch
+            self.graph_c = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_c), torch.no_grad(), ops.rnn_units_per_cta(self.critic_units_per_cta):
+                self.cap_in_next.copy_(self._corrupt(self.static["caption_next"], rng=self.rng_next))
+                self.labels_next.copy_(trainer.cap_model.segment_labels_of(self.cap_in_next))
         self.captured_launches = launch_count() - n0
         del self.st  # the autograd graph has been consumed by the capture of B
+
+    def _corrupt(self, caption, rng=None):
+        """caption[:, :-1] after the reference's generate_synonyms (same as StepRunner._corrupt)."""
+        t = self.trainer
+        cap_in = caption[:, :-1].contiguous()
+        if t.random_synonyms > 0:
+            from . import data
+            cap_in = data.generate_synonyms(cap_in, t.random_synonyms, t.cap_model.voc_size, t.end_idx, t.pad_idx,
+                                            salt=t._syn_salt(), rng=rng)
+        return cap_in
+
+    def prime(self):
+        with torch.no_grad():
+            self.cap_in_cur.copy_(self._corrupt(self.static["caption"]))
+            self.labels_cur.copy_(self.trainer.cap_model.segment_labels_of(self.cap_in_cur))
+        self._need_prime = False
 
     def _host_part(self):
         import time
@@ -695,13 +748,17 @@ class ScoredStepRunner:
 
     def _eager(self):
         t = self.trainer
-        b = dict(self.static)
+        b = {k: v for k, v in self.static.items() if k != "caption_next"}
         b["trg_caption"] = self.captions
         return t.rl_step(b, self.train_worker, self.stabilize)
 
-    def load(self, host_batch, non_blocking=True):
+    def load(self, host_batch, non_blocking=True, next_host_batch=None):
         for k, buf in self.static.items():
-            buf.copy_(host_batch[k], non_blocking=non_blocking)
+            if k == "caption_next":
+                src = (next_host_batch if next_host_batch is not None else host_batch)["caption"]
+                buf.copy_(src, non_blocking=non_blocking)
+            else:
+                buf.copy_(host_batch[k], non_blocking=non_blocking)
         if "trg_caption" in host_batch:
             self.captions = list(host_batch["trg_caption"])
 
@@ -709,11 +766,27 @@ class ScoredStepRunner:
         if not self.use_graph:
             self.out = self._eager()
             return self.out
+        if not self.pipeline_critic:
+            self.graph_a.replay()
+            self._host_part()
+            self.graph_b.replay()
+            return self.out
+        dev = self.static["caption"].device
+        cur = torch.cuda.current_stream(dev)
+        self.rng_next.copy_(ops.RNG.get_state(dev))  # before graph A advances the device state: race-free, new per step
+        self.critic_stream.wait_stream(cur)          # caption_next is loaded; the previous step's hand-over is done
         self.graph_a.replay()
+        with torch.cuda.stream(self.critic_stream):  # beside A, the host part and B
+            self.graph_c.replay()
         self._host_part()
         self.graph_b.replay()
+        cur.wait_stream(self.critic_stream)
+        self.cap_in_cur.copy_(self.cap_in_next)
+        self.labels_cur.copy_(self.labels_next)
         return self.out
 
-    def step(self, host_batch):
-        self.load(host_batch)
+    def step(self, host_batch, next_host_batch=None):
+        self.load(host_batch, next_host_batch=next_host_batch)
+        if self.pipeline_critic and (self._need_prime or next_host_batch is None):
+            self.prime()    # first step of a stream, or no look-ahead: label THIS batch now
         return self.replay()

@@ -519,7 +519,7 @@ def test_scored_step_two_graphs_equals_eager(gpu_lib, golden, agent_sd, kind):
         batches.append(b)
     corpus = [c.split() for b in batches for c in b["trg_caption"]] * 2
 
-    def run(use_graph):
+    def run(use_graph, pipe=False):
         model, cfg = build_agent(agent_sd)
         wv, mv = BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda()
         vsd = synth.fill_state_dict(golden["value_fn_shapes"], seed=3)
@@ -539,10 +539,10 @@ def test_scored_step_two_graphs_equals_eager(gpu_lib, golden, agent_sd, kind):
         tr.rl_step({**_dev({k: v for k, v in batches[1].items() if k != "trg_caption"}),
                     "trg_caption": batches[1]["trg_caption"]}, kind == "worker")
         torch.cuda.synchronize()
-        runner = ScoredStepRunner(tr, kind, batches[0], use_graph=use_graph, warmup=0)
+        runner = ScoredStepRunner(tr, kind, batches[0], use_graph=use_graph, warmup=0, pipeline_critic=pipe)
         losses = []
-        for b in batches:
-            out = runner.step(b)
+        for i, b in enumerate(batches):
+            out = runner.step(b, batches[i + 1] if (pipe and i + 1 < len(batches)) else None) if pipe else runner.step(b)
             losses.append([float(o) for o in out])
         torch.cuda.synchronize()
         flat = torch.cat([p.detach().flatten() for p in model.parameters() if p.requires_grad]).clone()
@@ -550,10 +550,41 @@ def test_scored_step_two_graphs_equals_eager(gpu_lib, golden, agent_sd, kind):
 
     l_graph, p_graph = run(True)
     l_eager, p_eager = run(False)
-    assert all(np.isfinite(v) for l in l_graph + l_eager for v in l)
+    # third graph: the frozen critic of the NEXT batch beside the host scorer and graph B (pipeline_critic)
+    l_pipe, p_pipe = run(True, pipe=True)
+    assert all(np.isfinite(v) for l in l_graph + l_eager + l_pipe for v in l)
+    for a, c in zip(l_pipe, l_eager):
+        assert abs(a[0] - c[0]) <= 1e-4 * abs(c[0]) + 1e-7 and abs(a[1] - c[1]) <= 1e-4 * abs(c[1]) + 1e-7, (l_pipe, l_eager)
+    assert rel(p_pipe, p_eager) < 1e-5
     for a, c in zip(l_graph, l_eager):
         assert abs(a[0] - c[0]) <= 1e-4 * abs(c[0]) + 1e-7 and abs(a[1] - c[1]) <= 1e-4 * abs(c[1]) + 1e-7, (l_graph, l_eager)
     assert rel(p_graph, p_eager) < 1e-5
+
+
+def test_pipelined_corruption_draws_change_every_replay(gpu_lib, agent_sd):
+    """generate_synonyms of the NEXT batch runs on the side branch of the captured step: its Philox state must be the live
+    device state of the replay (a copy made inside the graph), not a snapshot whose address was captured -- the same
+    captions fed to three replays must come out corrupted three different ways."""
+    from bmhrl_b200.model.bm_hrl_agent import BMManagerValueFunction, BMWorkerValueFunction
+    from bmhrl_b200.train import BMHRLTrainer, StepRunner
+    from bmhrl_b200 import ops
+    b = synth.synthetic_batch(B=8, Sv=10, Sa=14, L=15, V=VOC, seed=5)
+    model, cfg = build_agent(agent_sd)
+    tr = BMHRLTrainer(model, BMWorkerValueFunction(cfg).cuda(), BMManagerValueFunction(cfg).cuda(), pad_idx=PAD,
+                      random_synonyms=0.5)
+    tr.teach_warmstart()
+    ops.manual_seed(9)
+    run = StepRunner(tr, "warmstart", b, use_graph=True, warmup=2, pipeline_critic=True)
+    seen = []
+    for _ in range(3):
+        run.step(b, b)
+        torch.cuda.synchronize()
+        seen.append(run.cap_in_cur.clone())      # the corrupted captions the NEXT step will read
+    assert not torch.equal(seen[0], seen[1]) and not torch.equal(seen[1], seen[2]) and not torch.equal(seen[0], seen[2])
+    clean = b["caption"][:, :-1].cuda()
+    for c in seen:      # corrupted, but still the same captions underneath
+        frac = float((c != clean).float().mean())
+        assert 0.05 < frac < 0.6, frac
 
 
 @pytest.mark.parametrize("kind", ["warmstart", "worker"])
