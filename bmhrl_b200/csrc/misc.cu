@@ -358,21 +358,16 @@ constexpr int ADAM_CHUNK = 8192;
 // second buffer -- bf16 (kind 0; the tensor-core operand copy of a weight matrix, (rows, shadow_cols) with row pitch
 // shadow_ld) or fp32 (kind 1; the N-concatenated bias of a fused Q|K|V projection).  Adam touches every updated weight
 // anyway, so the shadows cost their own bytes and no extra pass.
-__global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restrict__ params,
-                                                         const float* const* __restrict__ grads,
-                                                         float* const* __restrict__ exp_avg,
-                                                         float* const* __restrict__ exp_avg_sq,
-                                                         const long long* __restrict__ numels,
-                                                         const int* __restrict__ chunk_tensor,
-                                                         const int* __restrict__ chunk_start,
-                                                         const float* __restrict__ step_ptr, float lr, float beta1,
-                                                         float beta2, float eps, float grad_scale,
-                                                         void* const* __restrict__ shadow,
-                                                         const int* __restrict__ shadow_cols,
-                                                         const int* __restrict__ shadow_ld,
-                                                         const int* __restrict__ shadow_kind) {
-    const int t = chunk_tensor[blockIdx.x];
-    const long long s0 = chunk_start[blockIdx.x];
+__device__ __forceinline__ void adam_chunk(int chunk, float* const* __restrict__ params,
+                                           const float* const* __restrict__ grads, float* const* __restrict__ exp_avg,
+                                           float* const* __restrict__ exp_avg_sq, const long long* __restrict__ numels,
+                                           const int* __restrict__ chunk_tensor, const int* __restrict__ chunk_start,
+                                           const float* __restrict__ step_ptr, float lr, float beta1, float beta2, float eps,
+                                           float grad_scale, void* const* __restrict__ shadow,
+                                           const int* __restrict__ shadow_cols, const int* __restrict__ shadow_ld,
+                                           const int* __restrict__ shadow_kind) {
+    const int t = chunk_tensor[chunk];
+    const long long s0 = chunk_start[chunk];
     const long long n = numels[t];
     float* __restrict__ p = params[t];
     const float* __restrict__ g = grads[t];
@@ -439,6 +434,28 @@ __global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restric
             else reinterpret_cast<__nv_bfloat16*>(sh)[(i / scols) * sld + (i % scols)] = __float2bfloat16(o);
         }
     }
+}
+
+// One CTA per chunk -- or, with a grid limit (bmhrl_adam_set_grid_limit), a grid-stride loop over the chunks.  An update
+// that runs BESIDE the rest of backward must not take every thread slot of every SM: the unlimited grid (thousands of
+// CTAs, 8 x 256 threads per SM) kept every later launch of the step waiting until it had drained -- 140 us without a
+// single kernel start behind the first stage's update (profiles/r02_step_timeline.txt).
+__global__ void __launch_bounds__(256) adam_multi_kernel(float* const* __restrict__ params,
+                                                         const float* const* __restrict__ grads,
+                                                         float* const* __restrict__ exp_avg,
+                                                         float* const* __restrict__ exp_avg_sq,
+                                                         const long long* __restrict__ numels,
+                                                         const int* __restrict__ chunk_tensor,
+                                                         const int* __restrict__ chunk_start, int n_chunks,
+                                                         const float* __restrict__ step_ptr, float lr, float beta1,
+                                                         float beta2, float eps, float grad_scale,
+                                                         void* const* __restrict__ shadow,
+                                                         const int* __restrict__ shadow_cols,
+                                                         const int* __restrict__ shadow_ld,
+                                                         const int* __restrict__ shadow_kind) {
+    for (int c = blockIdx.x; c < n_chunks; c += gridDim.x)
+        adam_chunk(c, params, grads, exp_avg, exp_avg_sq, numels, chunk_tensor, chunk_start, step_ptr, lr, beta1, beta2, eps,
+                   grad_scale, shadow, shadow_cols, shadow_ld, shadow_kind);
 }
 
 // steps[active[i]] += 1 for the tensors updated this step (torch keeps one step count per parameter and skips
@@ -628,6 +645,16 @@ extern "C" int bmhrl_linear_bwd_prep_f32(const float* dY, long long lddy, const 
 
 extern "C" int bmhrl_adam_chunk_elems(void) { return ADAM_CHUNK; }
 
+static int g_adam_grid_limit = 0;
+extern "C" int bmhrl_adam_set_grid_limit(int max_ctas) {
+    g_adam_grid_limit = max_ctas > 0 ? max_ctas : 0;
+    return BMHRL_OK;
+}
+extern "C" int bmhrl_adam_get_grid_limit(void) { return g_adam_grid_limit; }
+static inline int adam_grid(int n_chunks) {
+    return (g_adam_grid_limit > 0 && n_chunks > g_adam_grid_limit) ? g_adam_grid_limit : n_chunks;
+}
+
 extern "C" int bmhrl_adam_multi_f32(float* const* params, const float* const* grads, float* const* exp_avg,
                                     float* const* exp_avg_sq, const long long* numels, const int* chunk_tensor,
                                     const int* chunk_start, int n_chunks, const float* step_counts, float lr,
@@ -635,9 +662,10 @@ extern "C" int bmhrl_adam_multi_f32(float* const* params, const float* const* gr
     BMHRL_CHECK_ARG(params && grads && exp_avg && exp_avg_sq && numels && chunk_tensor && chunk_start && step_counts,
                     "bmhrl_adam_multi_f32: null pointer");
     if (n_chunks <= 0) return BMHRL_OK;
-    adam_multi_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
-                                                                  chunk_tensor, chunk_start, step_counts, lr, beta1,
-                                                                  beta2, eps, grad_scale, nullptr, nullptr, nullptr, nullptr);
+    adam_multi_kernel<<<adam_grid(n_chunks), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
+                                                                             chunk_tensor, chunk_start, n_chunks, step_counts, lr,
+                                                                             beta1, beta2, eps, grad_scale, nullptr, nullptr,
+                                                                             nullptr, nullptr);
     BMHRL_POST_LAUNCH("adam_multi");
     return BMHRL_OK;
 }
@@ -652,10 +680,10 @@ extern "C" int bmhrl_adam_multi_shadow_f32(float* const* params, const float* co
                     "bmhrl_adam_multi_shadow_f32: null pointer");
     BMHRL_CHECK_ARG(!shadow || (shadow_cols && shadow_ld && shadow_kind), "bmhrl_adam_multi_shadow_f32: shadow tables");
     if (n_chunks <= 0) return BMHRL_OK;
-    adam_multi_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
-                                                                  chunk_tensor, chunk_start, step_counts, lr, beta1,
-                                                                  beta2, eps, grad_scale, shadow, shadow_cols, shadow_ld,
-                                                                  shadow_kind);
+    adam_multi_kernel<<<adam_grid(n_chunks), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels,
+                                                                             chunk_tensor, chunk_start, n_chunks, step_counts, lr,
+                                                                             beta1, beta2, eps, grad_scale, shadow, shadow_cols,
+                                                                             shadow_ld, shadow_kind);
     BMHRL_POST_LAUNCH("adam_multi");
     return BMHRL_OK;
 }

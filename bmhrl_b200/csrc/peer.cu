@@ -70,7 +70,7 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p, long long byte_off)
 }
 
 // Same arithmetic as adam_multi_kernel (misc.cu) on the chunks this rank owns.
-__global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict__ params,
+__device__ __forceinline__ void adam_peer_chunk(int chunk, float* const* __restrict__ params,
                                                         const float* const* __restrict__ grads,
                                                         float* const* __restrict__ exp_avg,
                                                         float* const* __restrict__ exp_avg_sq,
@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
                                                         const int* __restrict__ shadow_cols, const int* __restrict__ shadow_ld,
                                                         const int* __restrict__ shadow_kind, PeerOff og, PeerOff op, PeerOff os,
                                                         int n_ranks, int owner_only_master) {
-    const int t = chunk_tensor[blockIdx.x];
-    const long long s0 = chunk_start[blockIdx.x];
+    const int t = chunk_tensor[chunk];
+    const long long s0 = chunk_start[chunk];
     const long long n = numels[t];
     float* p = params[t];
     const float* g = grads[t];
@@ -172,6 +172,21 @@ __global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict
             }
         }
     }
+}
+
+// One CTA per owned chunk, or a grid-stride loop under bmhrl_adam_set_grid_limit (see adam_multi_kernel, misc.cu).
+__global__ void __launch_bounds__(256) adam_peer_kernel(float* const* __restrict__ params, const float* const* __restrict__ grads,
+                                                        float* const* __restrict__ exp_avg, float* const* __restrict__ exp_avg_sq,
+                                                        const long long* __restrict__ numels, const int* __restrict__ chunk_tensor,
+                                                        const int* __restrict__ chunk_start, int n_chunks,
+                                                        const float* __restrict__ step_ptr, float lr, float beta1, float beta2,
+                                                        float eps, float grad_scale, void* const* __restrict__ shadow,
+                                                        const int* __restrict__ shadow_cols, const int* __restrict__ shadow_ld,
+                                                        const int* __restrict__ shadow_kind, PeerOff og, PeerOff op, PeerOff os,
+                                                        int n_ranks, int owner_only_master) {
+    for (int c = blockIdx.x; c < n_chunks; c += gridDim.x)
+        adam_peer_chunk(c, params, grads, exp_avg, exp_avg_sq, numels, chunk_tensor, chunk_start, step_ptr, lr, beta1, beta2, eps,
+                        grad_scale, shadow, shadow_cols, shadow_ld, shadow_kind, og, op, os, n_ranks, owner_only_master);
 }
 
 // The owner's fp32 values of the listed chunks into every rank's parameter arena (after steps with owner_only_master).
@@ -293,8 +308,10 @@ extern "C" int bmhrl_adam_peer_f32(float* const* params, const float* const* gra
     fill_off(og, grad_off_bytes, n_ranks);
     fill_off(op, param_off_bytes, n_ranks);
     fill_off(os, shadow_off_bytes, n_ranks);
-    adam_peer_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels, chunk_tensor,
-                                                                 chunk_start, step_counts, lr, beta1, beta2, eps, grad_scale,
+    const int lim = bmhrl_adam_get_grid_limit();
+    const int grid = (lim > 0 && n_chunks > lim) ? lim : n_chunks;
+    adam_peer_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, numels, chunk_tensor,
+                                                                 chunk_start, n_chunks, step_counts, lr, beta1, beta2, eps, grad_scale,
                                                                  shadow, shadow_cols, shadow_ld, shadow_kind, og, op, os,
                                                                  n_ranks, owner_only_master ? 1 : 0);
     BMHRL_POST_LAUNCH("adam_peer");

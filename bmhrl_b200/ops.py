@@ -989,6 +989,25 @@ def rnn_layer(cell, x, w_ih, w_hh, b_ih, b_hh):
     return out
 
 
+class adam_grid_limit:
+    """with ops.adam_grid_limit(296): opt.step(...) -- Adam launches inside use at most that many CTAs (grid-stride loop over
+    the 8192-element chunks).  For an update that runs BESIDE other work: the unlimited grid fills every thread slot of
+    every SM and every later launch waits until it has drained (140 us without one kernel start behind the first stage's
+    update of the training step); 2 CTAs per SM keep the update near HBM speed and leave room for the step's kernels."""
+
+    def __init__(self, max_ctas):
+        self.n = int(max_ctas)
+
+    def __enter__(self):
+        self.prev = LIB.raw("bmhrl_adam_get_grid_limit")()
+        LIB.call("bmhrl_adam_set_grid_limit", self.n)
+        return self
+
+    def __exit__(self, *exc):
+        LIB.call("bmhrl_adam_set_grid_limit", self.prev)
+        return False
+
+
 class rnn_units_per_cta:
     """with ops.rnn_units_per_cta(16): ... -- recurrent layers launched inside use at least that many hidden units per
     CTA (H / 16 CTAs instead of one per SM).  For a layer that runs BESIDE other kernels (the frozen critic of the next

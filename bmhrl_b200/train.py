@@ -105,6 +105,7 @@ class BMHRLTrainer:
         self._fired = []          # stages already handed to the communication stream in this backward
         self._comm_stream = None
         self._adam_stream = None
+        self.early_adam_ctas = int(os.environ.get("BMHRL_ADAM_CTAS", "296"))   # 0 = unlimited (one CTA per chunk)
         self.overlap_grad_sync = True
         # also on ONE GPU: the Adam update of a finished stage (1.3 GB of optimiser traffic per step in total) then runs
         # under the rest of backward instead of after it
@@ -205,12 +206,14 @@ class BMHRLTrainer:
         comm = self._comm_stream
         comm.wait_stream(torch.cuda.current_stream(dev))
         ops.wait_dirty_side_streams(comm)
+        # an update that runs under the rest of backward gets a bounded grid (ops.adam_grid_limit): see there
+        lim = ops.adam_grid_limit(self.early_adam_ctas)
         if self.peer is not None:
-            with torch.cuda.stream(comm):
+            with torch.cuda.stream(comm), lim:
                 self.cap_opt.step_peer(stage, only=self._stages[stage])
             return
         if self.grad_sync is None:
-            with torch.cuda.stream(comm):
+            with torch.cuda.stream(comm), lim:
                 self.cap_opt.step(only=self._stages[stage])
             return
         # data parallel: the all-reduces of successive stages queue on the communication stream, the Adam updates on a
@@ -221,7 +224,7 @@ class BMHRLTrainer:
         with torch.cuda.stream(comm):
             self.grad_sync(self.cap_opt, only=self._stages[stage])
         self._adam_stream.wait_stream(comm)
-        with torch.cuda.stream(self._adam_stream):
+        with torch.cuda.stream(self._adam_stream), lim:
             self.cap_opt.step(only=self._stages[stage])
 
     def _sync_and_step(self, opt, mean=False):

@@ -410,6 +410,11 @@ int bmhrl_adam_multi_shadow_f32(float* const* params, const float* const* grads,
                                 const int* shadow_ld, const int* shadow_kind, void* stream);
 /* step_counts[active_tensors[i]] += 1 for i < n_active (active_tensors NULL = identity) and rng_state[1] += 1, on
  * the device; step_counts / rng_state may be NULL. */
+/* Grid limit of the Adam kernels (bmhrl_adam_multi*_f32, bmhrl_adam_peer_f32): 0 = one CTA per 8192-element chunk; n > 0 = at
+ * most n CTAs in a grid-stride loop.  For an update that runs BESIDE other work (a finished stage's update under the rest
+ * of backward): the unlimited grid takes every thread slot of every SM until it has drained. */
+int bmhrl_adam_set_grid_limit(int max_ctas);
+int bmhrl_adam_get_grid_limit(void);
 int bmhrl_tick(float* step_counts, const int* active_tensors, int n_active, unsigned long long* rng_state,
                void* stream);
 
