@@ -37,6 +37,15 @@ extern "C" int bmhrl_set_pdl(int on) {
 }
 extern "C" int bmhrl_get_pdl(void) { return bmhrl::pdl_enabled(); }
 
+static std::atomic<int> g_launch_priority{bmhrl::kNoPriority};
+namespace bmhrl {
+int launch_priority() { return g_launch_priority.load(std::memory_order_relaxed); }
+}  // namespace bmhrl
+extern "C" int bmhrl_set_launch_priority(int use, int priority) {
+    g_launch_priority.store(use ? priority : bmhrl::kNoPriority, std::memory_order_relaxed);
+    return BMHRL_OK;
+}
+
 // A new non-blocking stream on the current device with a handle no other stream shares (see the header).  Never
 // destroyed: the host layer keeps its side streams for the life of the process.
 extern "C" int bmhrl_stream_create(void** stream) {

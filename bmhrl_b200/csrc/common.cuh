@@ -77,6 +77,11 @@ __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wa
 __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 int pdl_enabled();   // api.cu: bmhrl_set_pdl(), BMHRL_PDL environment variable
+// api.cu: bmhrl_set_launch_priority().  kNoPriority: launches carry no priority attribute (they take their stream's);
+// otherwise the value becomes cudaLaunchAttributePriority of every launch_pdl / GEMM launch: inside a CUDA graph that was
+// instantiated with cudaGraphInstantiateFlagUseNodePriority the pending CTAs of a higher-priority node are placed first.
+constexpr int kNoPriority = 1 << 30;
+int launch_priority();
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
@@ -85,12 +90,22 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
+    int na = 0;
     if (pdl_enabled()) {
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    const int prio = launch_priority();
+    if (prio != kNoPriority) {
+        at[na].id = cudaLaunchAttributePriority;
+        at[na].val.priority = prio;
+        ++na;
+    }
+    if (na) {
         cfg.attrs = at;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = na;
     }
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }

@@ -707,7 +707,7 @@ static int launch_gb(const GbParams& P, int total_tiles, int split, cudaStream_t
     cfg.blockDim = dim3(192);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[2];
+    cudaLaunchAttribute at[3];
     int na = 0;
     if (P.cluster > 1) {
         at[na].id = cudaLaunchAttributeClusterDimension;
@@ -719,6 +719,11 @@ static int launch_gb(const GbParams& P, int total_tiles, int split, cudaStream_t
     if (pdl_enabled()) {
         at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (launch_priority() != kNoPriority) {
+        at[na].id = cudaLaunchAttributePriority;
+        at[na].val.priority = launch_priority();
         ++na;
     }
     if (na) {

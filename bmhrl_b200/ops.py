@@ -989,6 +989,33 @@ def rnn_layer(cell, x, w_ih, w_hh, b_ih, b_hh):
     return out
 
 
+NODE_PRIORITY = False   # train.StepRunner(node_priority=True) sets it while it captures: see launch_priority
+
+
+class launch_priority:
+    """with ops.launch_priority(p): launches of the chain kernels inside carry cudaLaunchAttributePriority p (0 = lowest,
+    negative = placed first).  No-op unless ops.NODE_PRIORITY (a graph instantiated with node priorities is being captured)."""
+
+    def __init__(self, priority):
+        self.p = int(priority)
+
+    def __enter__(self):
+        if NODE_PRIORITY:
+            self.prev = _PRIO[0]
+            _PRIO[0] = self.p
+            LIB.call("bmhrl_set_launch_priority", 1, self.p)
+        return self
+
+    def __exit__(self, *exc):
+        if NODE_PRIORITY:
+            _PRIO[0] = self.prev
+            LIB.call("bmhrl_set_launch_priority", 1, self.prev)
+        return False
+
+
+_PRIO = [0]
+
+
 class adam_grid_limit:
     """with ops.adam_grid_limit(296): opt.step(...) -- Adam launches inside use at most that many CTAs (grid-stride loop over
     the 8192-element chunks).  For an update that runs BESIDE other work: the unlimited grid fills every thread slot of

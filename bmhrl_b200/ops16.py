@@ -331,7 +331,7 @@ def ln_bwd(dy2d, x2d, gamma, mean, rstd, dres2d, need_dx, ggrad, bgrad, need_aff
             call(dx, None, None)
     if acc and ops.CONCURRENT:
         ops._WGRAD_KEEP.append((dy2d, x2d, mean, rstd))
-        with torch.cuda.stream(ops.wgrad_stream(x2d.device, dg)):
+        with torch.cuda.stream(ops.wgrad_stream(x2d.device, dg)), ops.launch_priority(0):
             call(None, dg, db)
         if need_dx:
             call_dx()
@@ -391,7 +391,7 @@ def _wgrad(dz16, x16, weights, n_each):
                             seg=(n_each, dsts[1:]) if len(weights) > 1 else None)
         if ops.CONCURRENT:
             ops._WGRAD_KEEP.append((dz16, x16))
-            with torch.cuda.stream(ops.wgrad_stream(dz16.device, dsts[0])):
+            with torch.cuda.stream(ops.wgrad_stream(dz16.device, dsts[0])), ops.launch_priority(0):
                 gemm_group([prob])
         else:
             gemm_group([prob])
@@ -451,7 +451,7 @@ def _wbgrad(dz16, x16, weights, biases, n_each):
              gemm_problem(dz16, 1, ones, 0, n_tot, 1, M, C32=bd[0], beta=1.0, seg=(n_each, bd[1:]) if len(biases) > 1 else None)]
     if ops.CONCURRENT:
         ops._WGRAD_KEEP.append((dz16, x16))
-        with torch.cuda.stream(ops.wgrad_stream(dz16.device, wd[0])):
+        with torch.cuda.stream(ops.wgrad_stream(dz16.device, wd[0])), ops.launch_priority(0):
             gemm_group(probs)
     else:
         gemm_group(probs)
@@ -471,7 +471,7 @@ def _bgrad16(dz16, biases, n_each):
         dsts = [ops._gbuf(b) for b in biases]
         if ops.CONCURRENT:   # only the optimiser reads these: off the critical path
             ops._WGRAD_KEEP.append((dz16,))
-            with torch.cuda.stream(ops.wgrad_stream(dz16.device, dsts[0])):
+            with torch.cuda.stream(ops.wgrad_stream(dz16.device, dsts[0])), ops.launch_priority(0):
                 colsum16(dz16, dsts, seg_cols=n_each if len(biases) > 1 else 0, accumulate=True)
         else:
             colsum16(dz16, dsts, seg_cols=n_each if len(biases) > 1 else 0, accumulate=True)

@@ -481,12 +481,34 @@ class StepRunner:
                     self._eager()
             torch.cuda.current_stream(dev).wait_stream(side)
             torch.cuda.synchronize(dev)
-            from ._lib import launch_count, reset_launch_count
-            self.graph = torch.cuda.CUDAGraph()
+            from ._lib import launch_count, reset_launch_count, LIB
+            # node_priority (experiment, BMHRL_NODE_PRIORITY=1): the chain kernels of the step are captured with launch
+            # priority -1, the weight / bias / affine gradient launches (nothing downstream waits for them) with 0, and the
+            # graph is instantiated with cudaGraphInstantiateFlagUseNodePriority through cuda.bindings
+            self.node_priority = os.environ.get("BMHRL_NODE_PRIORITY", "0") == "1"
+            self.graph = torch.cuda.CUDAGraph(keep_graph=True) if self.node_priority else torch.cuda.CUDAGraph()
             n0 = launch_count()
-            with torch.cuda.graph(self.graph):
-                self.out = self._eager()
+            if self.node_priority:
+                ops.NODE_PRIORITY = True
+                ops._PRIO[0] = -1
+                LIB.call("bmhrl_set_launch_priority", 1, -1)
+            try:
+                with torch.cuda.graph(self.graph):
+                    self.out = self._eager()
+            finally:
+                if self.node_priority:
+                    ops.NODE_PRIORITY = False
+                    LIB.call("bmhrl_set_launch_priority", 0, 0)
             self.captured_launches = launch_count() - n0  # kernels of libbmhrl_b200 inside one graph replay
+            self._exec = None
+            if self.node_priority:
+                from cuda.bindings import runtime as rt
+                raw = self.graph.raw_cuda_graph()
+                err, ex = rt.cudaGraphInstantiateWithFlags(rt.cudaGraph_t(int(raw)),
+                                                           int(rt.cudaGraphInstantiateFlags.cudaGraphInstantiateFlagUseNodePriority))
+                if int(err) != 0:
+                    raise RuntimeError(f"cudaGraphInstantiateWithFlags(UseNodePriority) failed: {err}")
+                self._exec, self._rt = ex, rt
         self._need_prime = self.pipeline_critic
 
     def _corrupt(self, caption, rng=None):
@@ -576,7 +598,12 @@ class StepRunner:
 
     def replay(self):
         if self.graph is not None:
-            self.graph.replay()
+            if getattr(self, "_exec", None) is not None:
+                err, = self._rt.cudaGraphLaunch(self._exec, torch.cuda.current_stream().cuda_stream)
+                if int(err) != 0:
+                    raise RuntimeError(f"cudaGraphLaunch failed: {err}")
+            else:
+                self.graph.replay()
         else:
             self.out = self._eager()
         return self.out

@@ -45,6 +45,11 @@ int bmhrl_stream_create(void** stream);
  * environment variable BMHRL_PDL=0 sets the initial value) / 0. */
 int bmhrl_set_pdl(int on);
 int bmhrl_get_pdl(void);
+/* use != 0: every following launch of the chain kernels (GEMM, attention, LayerNorm, cast) carries
+ * cudaLaunchAttributePriority = priority (CUDA stream-priority scale: lower number = placed first); use == 0: no attribute.
+ * Takes effect inside CUDA graphs instantiated with cudaGraphInstantiateFlagUseNodePriority (train.StepRunner does that
+ * when asked to: the kernels of the backward chain then overtake queued weight-gradient CTAs). */
+int bmhrl_set_launch_priority(int use, int priority);
 
 /* ---- math mode ------------------------------------------------------------------------------------------------ */
 /* 0 (default): every contraction in exact fp32 on the SIMT pipes (parity bound 1e-3, in practice ~1e-6).
