@@ -802,6 +802,14 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
         // a cluster of `split` CTAs along K when the tiles alone leave most SMs idle and every problem has K to split
         while (split < 4 && tiles * split * 2 <= n_sm + n_sm / 4 && min_kb / (split * 2) >= 2 && BN / (split * 2) >= 32) split *= 2;
     }
+    // weight-gradient launches (A and B both MN-major: dW = dZ^T X) are off the step's critical path: what counts for them
+    // is SM time, not latency (experiment switch BMHRL_GB_WGRAD_BN = 128: wider tiles, fewer operand bytes per FLOP)
+    static const int env_wbn = getenv("BMHRL_GB_WGRAD_BN") ? atoi(getenv("BMHRL_GB_WGRAD_BN")) : 0;
+    const bool is_wgrad = d[0].a_mn && d[0].b_mn;
+    if (is_wgrad && (env_wbn == 64 || env_wbn == 128) && max_n >= 128) {
+        BN = env_wbn;
+        split = 1;
+    }
     static const int env_bn = getenv("BMHRL_GB_BN") ? atoi(getenv("BMHRL_GB_BN")) : 0;
     static const int env_split = getenv("BMHRL_GB_SPLIT") ? atoi(getenv("BMHRL_GB_SPLIT")) : 0;
     if (env_bn == 64 || env_bn == 128) BN = env_bn;
@@ -810,7 +818,9 @@ extern "C" int bmhrl_gemm_bf16_group(const bmhrl_gemm_desc* d, int n, void* stre
     if (g_gb_force_split) split = g_gb_force_split;
     while (split > 1 && (BN / split < 32 || min_kb < split)) split >>= 1;
     static const int env_stages = getenv("BMHRL_GB_STAGES") ? atoi(getenv("BMHRL_GB_STAGES")) : 0;  // experiments
+    static const int env_wst = getenv("BMHRL_GB_WGRAD_STAGES") ? atoi(getenv("BMHRL_GB_WGRAD_STAGES")) : 0;
     int nstages = g_gb_force_stages ? g_gb_force_stages : (env_stages ? env_stages : (BN == 128 ? 4 : 3));
+    if (is_wgrad && env_wst >= 2 && env_wst <= 6 && !g_gb_force_stages) nstages = env_wst;
     {
         // a launch with at most one CTA per SM cannot hide the TMA round trip behind other CTAs of its own: deeper ring
         // (experiment switch BMHRL_GB_DEEP = ring depth for such launches, 0 = off)
